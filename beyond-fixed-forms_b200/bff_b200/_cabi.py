@@ -1,0 +1,99 @@
+"""ctypes binding of libbff.so (include/bff.h). No pybind, no torch extension: the library is
+a plain C ABI and is called with raw device pointers (`tensor.data_ptr()`) and the current
+CUDA stream. There is NO CPU fallback: if the library is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbff.so")
+
+BFF_DEPTH_F32, BFF_DEPTH_U16 = 0, 1
+BFF_XYZ_F32X4, BFF_XYZ_F64X3 = 0, 1
+
+
+class BffError(RuntimeError):
+    pass
+
+
+class LiftDesc(ctypes.Structure):
+    """struct bff_lift_desc (include/bff.h)."""
+    _fields_ = [
+        ("xyz", c_void_p), ("xyz_kind", c_int32), ("n_points", c_int64),
+        ("pose_inv", c_void_p), ("intrinsics", c_void_p), ("n_frames", c_int32),
+        ("depth", c_void_p), ("depth_kind", c_int32), ("depth_scale", c_float),
+        ("height", c_int32), ("width", c_int32), ("depth_thresh", c_double),
+        ("depth_min", c_double), ("depth_max", c_double),
+        ("masks2d", c_void_p), ("mask_offset", c_void_p), ("mask_query", c_void_p),
+        ("n_masks", c_int32), ("n_queries", c_int32), ("frame_viewed", c_void_p),
+        ("rows", c_void_p), ("masked_counts", c_void_p), ("viewed_counts", c_void_p),
+        ("debug_pix", c_void_p), ("debug_vis", c_void_p),
+        ("frames_per_chunk", c_int32), ("reserved", c_int32),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/bff.h declares
+SYMBOLS = {
+    "bff_version": (c_int, []),
+    "bff_last_error": (c_char_p, []),
+    "bff_lift_scene": (c_int, [POINTER(LiftDesc), c_void_p]),
+    "bff_lift_scene_launches": (c_int, [POINTER(LiftDesc)]),
+    "bff_mask_iou": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bff_rows_or_reduce": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
+    "bff_counts_max": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "bff_vote_hist": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
+    "bff_point_keep": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
+    "bff_overlap_resolve": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p]),
+    "bff_rows_and_popcount": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),
+    "bff_pack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_unpack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_rle_to_bits": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),
+    "bff_ctx_destroy": (None, [c_void_p]),
+    "bff_lift_scene_host": (c_int, [c_void_p, POINTER(LiftDesc), POINTER(c_int64), POINTER(c_int64)]),
+    "bff_mask_iou_host": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64)]),
+}
+
+_lib = None
+launch_count = 0   # kernels launched through this binding (bench.py's gpu_launches)
+
+
+def lib():
+    """Load libbff.so or raise. There is deliberately no fallback implementation."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BffError(
+                f"{LIB_PATH} not found: build it with `python beyond-fixed-forms_b200/build.py` "
+                "(nvcc, sm_100a). bff_b200 has no CPU or PyTorch fallback.")
+        h = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(h, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = lib().bff_last_error().decode(errors="replace")
+        raise BffError(f"{what} failed with status {rc}: {msg}")
+
+
+def ptr(t):
+    """Device (or host) address of a torch tensor / numpy array, or None."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        return c_void_p(t.data_ptr())
+    return c_void_p(t.ctypes.data)
+
+
+def current_stream():
+    import torch
+    return c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,259 @@
+"""Device operators: torch CUDA tensors in, torch CUDA tensors out, all work done by libbff.so.
+
+Packed masks are int32 tensors of shape (rows, ceil(N/32)) (bit b of word w = element 32*w+b).
+torch is used for device memory and streams only; every function raises if the CUDA library
+is unavailable (no fallback).
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import LiftDesc, check, current_stream, lib, ptr
+
+
+def words_for(n: int) -> int:
+    return (int(n) + 31) // 32
+
+
+def _cuda(t: torch.Tensor, dtype, what: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _cabi.BffError(f"{what} must be a CUDA tensor (bff_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{what} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _count(n: int = 1):
+    _cabi.launch_count += n
+
+
+# ----------------------------------------------------------------------------- lifting
+class LiftOutput:
+    __slots__ = ("rows", "masked_counts", "viewed_counts", "debug_pix", "debug_vis")
+
+    def __init__(self, rows, mc, vc, pix=None, vis=None):
+        self.rows, self.masked_counts, self.viewed_counts, self.debug_pix, self.debug_vis = rows, mc, vc, pix, vis
+
+
+def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: torch.Tensor, height: int, width: int,
+               masks2d: Optional[torch.Tensor] = None, mask_offset: Optional[torch.Tensor] = None,
+               mask_query: Optional[torch.Tensor] = None, n_queries: int = 1,
+               frame_viewed: Optional[torch.Tensor] = None, depth_thresh: float = 0.08,
+               depth_scale: float = 1000.0, depth_range: Optional[Sequence[float]] = None,
+               want_rows: bool = True, want_counts: bool = True, want_viewed: bool = True,
+               debug: bool = False, frames_per_chunk: int = 0) -> LiftOutput:
+    """One launch over all frames of a scene (bff_lift_scene).
+
+    xyz         (N,4) float32 [x,y,z,_] or (N,3) float64, CUDA
+    pose_inv    (F,4,4) float64 CUDA = np.linalg.inv(cam_pose) per frame (projection_2d_to_3d.py:425)
+    intrinsics  (3,3) float64 HOST (numpy / CPU tensor): passed to the kernel by value
+    depth       (F,H,W) float32 metres or uint16/int16-storage raw sensor units, CUDA
+    masks2d     (sumM, ceil(H*W/32)) int32 packed 2D masks in frame order; mask_offset (F+1,) int32
+    Returns packed rows (sumM, Wd) int32, masked_counts (Q,N) int32, viewed_counts (N,) int32."""
+    dev = xyz.device
+    if xyz.dtype == torch.float32:
+        if xyz.dim() != 2 or xyz.shape[1] != 4:
+            raise ValueError("float32 xyz must be (N,4)")
+        kind = _cabi.BFF_XYZ_F32X4
+    elif xyz.dtype == torch.float64:
+        if xyz.dim() != 2 or xyz.shape[1] != 3:
+            raise ValueError("float64 xyz must be (N,3)")
+        kind = _cabi.BFF_XYZ_F64X3
+    else:
+        raise TypeError("xyz must be float32 (N,4) or float64 (N,3)")
+    xyz = _cuda(xyz, xyz.dtype, "xyz")
+    n = xyz.shape[0]
+    pose_inv = _cuda(pose_inv, torch.float64, "pose_inv").reshape(-1, 4, 4)
+    f = pose_inv.shape[0]
+    k_host = np.ascontiguousarray(np.asarray(intrinsics, dtype=np.float64).reshape(3, 3))
+    if depth.dtype == torch.float32:
+        dkind = _cabi.BFF_DEPTH_F32
+    elif depth.dtype in (torch.int16, torch.uint16):
+        dkind = _cabi.BFF_DEPTH_U16
+    else:
+        raise TypeError("depth must be float32 or 16-bit raw")
+    depth = _cuda(depth, depth.dtype, "depth")
+    if depth.numel() != f * height * width:
+        raise ValueError(f"depth has {depth.numel()} elements, expected {f}x{height}x{width}")
+    n_masks = 0
+    if masks2d is not None and masks2d.shape[0] > 0:
+        masks2d = _cuda(masks2d, torch.int32, "masks2d")
+        n_masks = masks2d.shape[0]
+        if masks2d.shape[1] != words_for(height * width):
+            raise ValueError("masks2d has the wrong number of words per mask")
+        mask_offset = _cuda(mask_offset, torch.int32, "mask_offset")
+        if mask_offset.numel() != f + 1:
+            raise ValueError("mask_offset must have F+1 entries")
+        if mask_query is not None:
+            mask_query = _cuda(mask_query, torch.int32, "mask_query")
+    else:
+        masks2d = mask_offset = mask_query = None
+    if frame_viewed is not None:
+        frame_viewed = _cuda(frame_viewed, torch.uint8, "frame_viewed")
+    wd = words_for(n)
+    rows = torch.empty((n_masks, wd), dtype=torch.int32, device=dev) if want_rows else None
+    mc = torch.empty((n_queries, n), dtype=torch.int32, device=dev) if want_counts else None
+    vc = torch.empty((n,), dtype=torch.int32, device=dev) if want_viewed else None
+    pix = torch.empty((f, n, 2), dtype=torch.int64, device=dev) if debug else None
+    vis = torch.empty((f, wd), dtype=torch.int32, device=dev) if debug else None
+    d = LiftDesc()
+    d.xyz, d.xyz_kind, d.n_points = ptr(xyz), kind, n
+    d.pose_inv, d.intrinsics, d.n_frames = ptr(pose_inv), ptr(k_host), f
+    d.depth, d.depth_kind, d.depth_scale = ptr(depth), dkind, float(depth_scale)
+    d.height, d.width, d.depth_thresh = int(height), int(width), float(depth_thresh)
+    if depth_range is None:
+        d.depth_min, d.depth_max = 1.0, 0.0
+    else:
+        d.depth_min, d.depth_max = float(depth_range[0]), float(depth_range[1])
+    d.masks2d, d.mask_offset, d.mask_query = ptr(masks2d), ptr(mask_offset), ptr(mask_query)
+    d.n_masks, d.n_queries, d.frame_viewed = n_masks, int(n_queries), ptr(frame_viewed)
+    d.rows, d.masked_counts, d.viewed_counts = ptr(rows), ptr(mc), ptr(vc)
+    d.debug_pix, d.debug_vis = ptr(pix), ptr(vis)
+    d.frames_per_chunk = int(frames_per_chunk)
+    check(lib().bff_lift_scene(d, current_stream()), "bff_lift_scene")
+    _count(lib().bff_lift_scene_launches(d))
+    return LiftOutput(rows, mc, vc, pix, vis)
+
+
+# ----------------------------------------------------------------------------- mask algebra
+def mask_iou(a: torch.Tensor, b: Optional[torch.Tensor] = None, want_iou: bool = True):
+    """Intersections, row popcounts and (optionally) float32 IoU of packed rows.
+    b=None computes the square matrix of `a` (calculate_iou). Returns (inter, pop_a, pop_b, iou)."""
+    a = _cuda(a, torch.int32, "a")
+    same = b is None
+    b = a if same else _cuda(b, torch.int32, "b")
+    if a.shape[1] != b.shape[1]:
+        raise ValueError("row width mismatch")
+    na, nb, wd = a.shape[0], b.shape[0], a.shape[1]
+    dev = a.device
+    inter = torch.zeros((na, nb), dtype=torch.int32, device=dev)
+    pa = torch.zeros((na,), dtype=torch.int32, device=dev)
+    pb = pa if same else torch.zeros((nb,), dtype=torch.int32, device=dev)
+    iou = torch.empty((na, nb), dtype=torch.float32, device=dev) if want_iou else None
+    check(lib().bff_mask_iou(ptr(a), na, ptr(b), nb, wd, ptr(inter), ptr(pa), ptr(pb), ptr(iou), current_stream()),
+          "bff_mask_iou")
+    if na and nb:
+        _count((1 if same else 2) + 1 + (1 if want_iou else 0))
+    return inter, pa, pb, iou
+
+
+def rows_or_reduce(rows: torch.Tensor, groups: Sequence[Sequence[int]]) -> torch.Tensor:
+    """out[g] = OR of rows[k] for k in groups[g]."""
+    rows = _cuda(rows, torch.int32, "rows")
+    wd = rows.shape[1]
+    idx = np.asarray([k for g in groups for k in g], dtype=np.int32)
+    seg = np.zeros(len(groups) + 1, dtype=np.int32)
+    seg[1:] = np.cumsum([len(g) for g in groups])
+    if idx.size and (idx.min() < 0 or idx.max() >= rows.shape[0]):
+        raise IndexError("group member out of range")
+    out = torch.zeros((len(groups), wd), dtype=torch.int32, device=rows.device)
+    if len(groups) and wd:
+        d_idx = torch.from_numpy(idx).to(rows.device)
+        d_seg = torch.from_numpy(seg).to(rows.device)
+        check(lib().bff_rows_or_reduce(ptr(rows), wd, ptr(d_idx), ptr(d_seg), len(groups), ptr(out), current_stream()),
+              "bff_rows_or_reduce")
+        _count()
+    return out
+
+
+def counts_max(mc: torch.Tensor, vc: Optional[torch.Tensor]):
+    mc = _cuda(mc, torch.int32, "mc").reshape(-1)
+    if vc is not None:
+        vc = _cuda(vc, torch.int32, "vc").reshape(-1)
+    out = torch.zeros(2, dtype=torch.int32, device=mc.device)
+    check(lib().bff_counts_max(ptr(mc), ptr(vc), mc.numel(), ptr(out), current_stream()), "bff_counts_max")
+    _count()
+    m = out.cpu()
+    return int(m[0]), int(m[1])
+
+
+def vote_hist(mc: torch.Tensor, vc: Optional[torch.Tensor], mc_bins: int, vc_bins: int) -> torch.Tensor:
+    mc = _cuda(mc, torch.int32, "mc").reshape(-1)
+    if vc is not None:
+        vc = _cuda(vc, torch.int32, "vc").reshape(-1)
+    hist = torch.empty((mc_bins, vc_bins), dtype=torch.int32, device=mc.device)
+    check(lib().bff_vote_hist(ptr(mc), ptr(vc), mc.numel(), mc_bins, vc_bins, ptr(hist), current_stream()), "bff_vote_hist")
+    _count()
+    return hist
+
+
+def point_keep(mc: torch.Tensor, vc: Optional[torch.Tensor], mode: int, thr: float) -> torch.Tensor:
+    mc = _cuda(mc, torch.int32, "mc").reshape(-1)
+    if vc is not None:
+        vc = _cuda(vc, torch.int32, "vc").reshape(-1)
+    keep = torch.empty((words_for(mc.numel()),), dtype=torch.int32, device=mc.device)
+    check(lib().bff_point_keep(ptr(mc), ptr(vc), mc.numel(), int(mode), float(thr), ptr(keep), current_stream()),
+          "bff_point_keep")
+    _count()
+    return keep
+
+
+def overlap_resolve(rows: torch.Tensor, program: Sequence[Sequence[int]]) -> torch.Tensor:
+    """In place: for (dst, src) in program: rows[dst] &= ~rows[src]."""
+    rows = _cuda(rows, torch.int32, "rows")
+    prog = np.asarray(program, dtype=np.int32).reshape(-1, 2)
+    if prog.shape[0] and rows.shape[0] and rows.shape[1]:
+        if prog.min() < 0 or prog.max() >= rows.shape[0]:
+            raise IndexError("program row out of range")
+        d_prog = torch.from_numpy(prog).to(rows.device)
+        check(lib().bff_overlap_resolve(ptr(rows), rows.shape[0], rows.shape[1], ptr(d_prog), prog.shape[0], current_stream()),
+              "bff_overlap_resolve")
+        _count()
+    return rows
+
+
+def rows_and_popcount(rows: torch.Tensor, keep: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """rows &= keep (in place, if given); returns int32 popcounts per row."""
+    rows = _cuda(rows, torch.int32, "rows")
+    if keep is not None:
+        keep = _cuda(keep, torch.int32, "keep")
+        if keep.numel() != rows.shape[1]:
+            raise ValueError("keep width mismatch")
+    pop = torch.zeros((rows.shape[0],), dtype=torch.int32, device=rows.device)
+    check(lib().bff_rows_and_popcount(ptr(rows), rows.shape[0], rows.shape[1], ptr(keep), ptr(pop), current_stream()),
+          "bff_rows_and_popcount")
+    if rows.shape[0] and rows.shape[1]:
+        _count()
+    return pop
+
+
+def pack_bits(dense: torch.Tensor) -> torch.Tensor:
+    """(R,N) bool/uint8 CUDA -> (R, ceil(N/32)) int32."""
+    if dense.dtype == torch.bool:
+        dense = dense.view(torch.uint8)
+    dense = _cuda(dense, torch.uint8, "dense")
+    r, n = dense.shape
+    out = torch.zeros((r, words_for(n)), dtype=torch.int32, device=dense.device)
+    check(lib().bff_pack_bits(ptr(dense), r, n, ptr(out), current_stream()), "bff_pack_bits")
+    if r and n:
+        _count()
+    return out
+
+
+def unpack_bits(packed: torch.Tensor, n: int) -> torch.Tensor:
+    """(R, Wd) int32 -> (R,N) bool CUDA."""
+    packed = _cuda(packed, torch.int32, "packed")
+    r = packed.shape[0]
+    if packed.shape[1] != words_for(n):
+        raise ValueError("packed width does not match n")
+    out = torch.empty((r, n), dtype=torch.uint8, device=packed.device)
+    check(lib().bff_unpack_bits(ptr(packed), r, n, ptr(out), current_stream()), "bff_unpack_bits")
+    if r and n:
+        _count()
+    return out.view(torch.bool)
+
+
+def rle_to_bits(runs: np.ndarray, n_rows: int, length: int, device) -> torch.Tensor:
+    """runs (R,3) int32 [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32 on `device`."""
+    runs = np.ascontiguousarray(runs, dtype=np.int32).reshape(-1, 3)
+    wd = words_for(length)
+    out = torch.empty((n_rows, wd), dtype=torch.int32, device=device)
+    d_runs = torch.from_numpy(runs).to(device) if runs.shape[0] else None
+    check(lib().bff_rle_to_bits(ptr(d_runs), runs.shape[0], n_rows, wd, ptr(out), current_stream()), "bff_rle_to_bits")
+    if n_rows and wd and runs.shape[0]:
+        _count()
+    return out

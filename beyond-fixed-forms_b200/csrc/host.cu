@@ -1,0 +1,199 @@
+// Error reporting, context and the host-buffer entry points of libbff.so.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace bff {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+}  // namespace bff
+
+using namespace bff;
+
+extern "C" int bff_version(void) { return BFF_VERSION; }
+extern "C" const char *bff_last_error(void) { return g_err; }
+
+// A context owns one stream and a grow-only device workspace used by the *_host entry points.
+struct bff_ctx {
+    int device;
+    cudaStream_t stream;
+    unsigned char *ws;
+    size_t ws_bytes;
+};
+
+static int ctx_reserve(bff_ctx *c, size_t bytes) {
+    if (bytes <= c->ws_bytes) return BFF_OK;
+    if (c->ws) cudaFree(c->ws);
+    c->ws = nullptr;
+    c->ws_bytes = 0;
+    if (cudaMalloc(&c->ws, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("bff_ctx: cannot allocate %zu bytes of device workspace", bytes);
+        return BFF_ENOMEM;
+    }
+    c->ws_bytes = bytes;
+    return BFF_OK;
+}
+
+extern "C" int bff_ctx_create(int device, bff_ctx **out) {
+    BFF_REQUIRE(out != nullptr, "bff_ctx_create: null out");
+    BFF_CUDA(cudaSetDevice(device));
+    bff_ctx *c = new bff_ctx();
+    c->device = device;
+    c->ws = nullptr;
+    c->ws_bytes = 0;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete c;
+        set_error("bff_ctx_create: %s", cudaGetErrorString(e));
+        return BFF_ECUDA;
+    }
+    *out = c;
+    return BFF_OK;
+}
+
+extern "C" void bff_ctx_destroy(bff_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->ws) cudaFree(c->ws);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+namespace {
+struct Carver {
+    unsigned char *base;
+    size_t off = 0;
+    explicit Carver(unsigned char *b) : base(b) {}
+    template <typename T>
+    T *take(size_t count) {
+        off = (off + 255) & ~(size_t)255;
+        T *p = base ? reinterpret_cast<T *>(base + off) : nullptr;
+        off += count * sizeof(T);
+        return p;
+    }
+};
+}  // namespace
+
+extern "C" int bff_lift_scene_host(bff_ctx *c, const bff_lift_desc *h, int64_t *h2d_bytes, int64_t *d2h_bytes) {
+    BFF_REQUIRE(c && h, "bff_lift_scene_host: null argument");
+    BFF_REQUIRE(h->n_points >= 0 && h->n_frames >= 0 && h->n_masks >= 0 && h->n_queries >= 1 && h->height > 0 && h->width > 0,
+                "bff_lift_scene_host: bad sizes");
+    BFF_REQUIRE(h->debug_pix == nullptr && h->debug_vis == nullptr, "bff_lift_scene_host: debug outputs are device-API only");
+    BFF_CUDA(cudaSetDevice(c->device));
+    const size_t n = (size_t)h->n_points, f = (size_t)h->n_frames, hw = (size_t)h->height * h->width;
+    const size_t words = (n + 31) / 32, mwords = (hw + 31) / 32;
+    const size_t xyz_b = n * (h->xyz_kind == BFF_XYZ_F32X4 ? 16 : 24);
+    const size_t depth_b = f * hw * (h->depth_kind == BFF_DEPTH_U16 ? 2 : 4);
+    const size_t nm = (size_t)h->n_masks;
+    // two passes over the same carve sequence: measure, then place
+    unsigned char *base = nullptr;
+    bff_lift_desc d = *h;
+    size_t total = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        Carver cv(base);
+        d.xyz = cv.take<unsigned char>(xyz_b);
+        d.pose_inv = cv.take<double>(f * 16);
+        d.depth = cv.take<unsigned char>(depth_b);
+        d.masks2d = nm ? cv.take<uint32_t>(nm * mwords) : nullptr;
+        d.mask_offset = (nm && h->mask_offset) ? cv.take<int32_t>(f + 1) : nullptr;
+        d.mask_query = (nm && h->mask_query) ? cv.take<int32_t>(nm) : nullptr;
+        d.frame_viewed = h->frame_viewed ? cv.take<uint8_t>(f) : nullptr;
+        d.rows = (h->rows && nm) ? cv.take<uint32_t>(nm * words) : nullptr;
+        d.masked_counts = h->masked_counts ? cv.take<int32_t>((size_t)h->n_queries * n) : nullptr;
+        d.viewed_counts = h->viewed_counts ? cv.take<int32_t>(n) : nullptr;
+        total = cv.off + 256;
+        if (pass == 0) {
+            int rc = ctx_reserve(c, total);
+            if (rc != BFF_OK) return rc;
+            base = c->ws;
+        }
+    }
+    d.intrinsics = h->intrinsics;   // passed to the kernel by value from host memory
+    cudaStream_t s = c->stream;
+    int64_t up = 0, down = 0;
+    auto h2d = [&](const void *dst, const void *src, size_t bytes) -> cudaError_t {
+        if (!bytes) return cudaSuccess;
+        up += (int64_t)bytes;
+        return cudaMemcpyAsync(const_cast<void *>(dst), src, bytes, cudaMemcpyHostToDevice, s);
+    };
+    if (n && f) {
+        BFF_REQUIRE(h->xyz && h->pose_inv && h->intrinsics && h->depth, "bff_lift_scene_host: null input pointer");
+        BFF_CUDA(h2d(d.xyz, h->xyz, xyz_b));
+        BFF_CUDA(h2d(d.pose_inv, h->pose_inv, f * 128));
+        BFF_CUDA(h2d(d.depth, h->depth, depth_b));
+        if (d.masks2d) BFF_CUDA(h2d(d.masks2d, h->masks2d, nm * mwords * 4));
+        if (d.mask_offset) BFF_CUDA(h2d(d.mask_offset, h->mask_offset, (f + 1) * 4));
+        if (d.mask_query) BFF_CUDA(h2d(d.mask_query, h->mask_query, nm * 4));
+        if (d.frame_viewed) BFF_CUDA(h2d(d.frame_viewed, h->frame_viewed, f));
+    }
+    int rc = bff_lift_scene(&d, s);
+    if (rc != BFF_OK) return rc;
+    auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+        if (!bytes) return cudaSuccess;
+        down += (int64_t)bytes;
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s);
+    };
+    if (d.rows) BFF_CUDA(d2h(h->rows, d.rows, nm * words * 4));
+    if (d.masked_counts) BFF_CUDA(d2h(h->masked_counts, d.masked_counts, (size_t)h->n_queries * n * 4));
+    if (d.viewed_counts) BFF_CUDA(d2h(h->viewed_counts, d.viewed_counts, n * 4));
+    BFF_CUDA(cudaStreamSynchronize(s));
+    if (h2d_bytes) *h2d_bytes = up;
+    if (d2h_bytes) *d2h_bytes = down;
+    return BFF_OK;
+}
+
+extern "C" int bff_mask_iou_host(bff_ctx *c, const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b,
+                                 int64_t words, int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou,
+                                 int64_t *h2d_bytes, int64_t *d2h_bytes) {
+    BFF_REQUIRE(c, "bff_mask_iou_host: null context");
+    BFF_REQUIRE(n_a >= 0 && n_b >= 0 && words >= 0, "bff_mask_iou_host: negative size");
+    if (h2d_bytes) *h2d_bytes = 0;
+    if (d2h_bytes) *d2h_bytes = 0;
+    if (n_a == 0 || n_b == 0) return BFF_OK;
+    BFF_REQUIRE(a && b, "bff_mask_iou_host: null rows");
+    BFF_CUDA(cudaSetDevice(c->device));
+    const bool same = (a == b && n_a == n_b);
+    const size_t ab = (size_t)n_a * words * 4, bb = (size_t)n_b * words * 4, pairs = (size_t)n_a * n_b;
+    unsigned char *base = nullptr;
+    uint32_t *da = nullptr, *db = nullptr;
+    int32_t *di = nullptr, *dpa = nullptr, *dpb = nullptr;
+    float *dio = nullptr;
+    for (int pass = 0; pass < 2; ++pass) {
+        Carver cv(base);
+        da = cv.take<uint32_t>((size_t)n_a * words);
+        db = same ? da : cv.take<uint32_t>((size_t)n_b * words);
+        di = cv.take<int32_t>(pairs);
+        dpa = cv.take<int32_t>(n_a);
+        dpb = cv.take<int32_t>(n_b);
+        dio = iou ? cv.take<float>(pairs) : nullptr;
+        if (pass == 0) {
+            int rc = ctx_reserve(c, cv.off + 256);
+            if (rc != BFF_OK) return rc;
+            base = c->ws;
+        }
+    }
+    cudaStream_t s = c->stream;
+    int64_t up = 0, down = 0;
+    if (ab) { BFF_CUDA(cudaMemcpyAsync(da, a, ab, cudaMemcpyHostToDevice, s)); up += ab; }
+    if (!same && bb) { BFF_CUDA(cudaMemcpyAsync(db, b, bb, cudaMemcpyHostToDevice, s)); up += bb; }
+    int rc = bff_mask_iou(da, n_a, db, n_b, words, di, dpa, dpb, dio, s);
+    if (rc != BFF_OK) return rc;
+    if (inter) { BFF_CUDA(cudaMemcpyAsync(inter, di, pairs * 4, cudaMemcpyDeviceToHost, s)); down += pairs * 4; }
+    if (pop_a) { BFF_CUDA(cudaMemcpyAsync(pop_a, dpa, (size_t)n_a * 4, cudaMemcpyDeviceToHost, s)); down += (size_t)n_a * 4; }
+    if (pop_b) { BFF_CUDA(cudaMemcpyAsync(pop_b, dpb, (size_t)n_b * 4, cudaMemcpyDeviceToHost, s)); down += (size_t)n_b * 4; }
+    if (iou) { BFF_CUDA(cudaMemcpyAsync(iou, dio, pairs * 4, cudaMemcpyDeviceToHost, s)); down += pairs * 4; }
+    BFF_CUDA(cudaStreamSynchronize(s));
+    if (h2d_bytes) *h2d_bytes = up;
+    if (d2h_bytes) *d2h_bytes = down;
+    return BFF_OK;
+}

@@ -1,0 +1,331 @@
+// Packed point-mask kernels: all-pairs / rectangular intersection + IoU, segmented OR,
+// sequential overlap resolution, AND + popcount, bit pack / unpack, RLE -> bits.
+//
+// A packed row is Wd = ceil(N/32) uint32 words; every kernel here is integer work on those
+// words (AND / OR / POPC), bit-exact by construction. Reference lines replaced are cited at
+// each entry point and in include/bff.h.
+#include "common.cuh"
+
+namespace bff {
+
+// ------------------------------------------------------------------ row popcounts
+__global__ void __launch_bounds__(256) row_popcount_kernel(const uint32_t *__restrict__ rows, long long words,
+                                                          int32_t *__restrict__ pop) {
+    const uint32_t *r = rows + (long long)blockIdx.x * words;
+    int s = 0;
+    for (long long w = threadIdx.x; w < words; w += 256) s += __popc(__ldg(r + w));
+    __shared__ int red[8];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int i = 0; i < 8; ++i) t += red[i];
+        pop[blockIdx.x] = t;
+    }
+}
+
+// ------------------------------------------------------------------ intersections
+// CTA tile: 64 rows of A x 64 rows of B, one K-slice of the words; 256 threads, each owning a
+// 4 x 4 block of pairs (rows ti + 16*i of the A tile, tj + 16*j of the B tile, so that the 16
+// tj-lanes of a warp hit 16 distinct banks and the two ti values broadcast).
+constexpr int kTile = 64;
+constexpr int kKW = 32;   // words staged per step
+
+__global__ void __launch_bounds__(256)
+intersect_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *__restrict__ b, int n_b,
+                 long long words, long long words_per_slice, int symmetric, int32_t *__restrict__ inter) {
+    __shared__ uint32_t sa[kTile][kKW + 1];
+    __shared__ uint32_t sb[kTile][kKW + 1];
+    const int bi = blockIdx.y, bj = blockIdx.x;
+    if (symmetric && bj < bi) return;   // lower triangle is mirrored by the upper one
+    const int tid = threadIdx.x;
+    const int ti = tid >> 4, tj = tid & 15;
+    const long long w_begin = (long long)blockIdx.z * words_per_slice;
+    const long long w_end = min(words, w_begin + words_per_slice);
+    int acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0;
+
+    for (long long w0 = w_begin; w0 < w_end; w0 += kKW) {
+        // stage 64 x 32 words of each operand: thread -> (row = tid/32 + 8*r, word = tid%32)
+        const int lw = tid & 31;
+        const bool w_ok = (w0 + lw) < w_end;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int row = (tid >> 5) + 8 * r;
+            const int ga = bi * kTile + row, gb = bj * kTile + row;
+            sa[row][lw] = (w_ok && ga < n_a) ? __ldg(a + (long long)ga * words + w0 + lw) : 0u;
+            sb[row][lw] = (w_ok && gb < n_b) ? __ldg(b + (long long)gb * words + w0 + lw) : 0u;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < kKW; ++k) {
+            uint32_t va[4], vb[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) va[i] = sa[ti + 16 * i][k];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) vb[j] = sb[tj + 16 * j][k];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] += __popc(va[i] & vb[j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int ga = bi * kTile + ti + 16 * i;
+        if (ga >= n_a) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gb = bj * kTile + tj + 16 * j;
+            if (gb >= n_b || acc[i][j] == 0) continue;
+            atomicAdd(inter + (long long)ga * n_b + gb, acc[i][j]);
+            if (symmetric && bj != bi) atomicAdd(inter + (long long)gb * n_b + ga, acc[i][j]);
+        }
+    }
+}
+
+// IoU exactly as calculate_iou (projection_2d_to_3d.py:158-165) / calculate_iou_between_stages
+// (refinement.py:82-90): union = (f32(sA) + f32(sB)) - f32(I); iou = f32(I) / union; 0/0 = NaN.
+__global__ void iou_finalize_kernel(const int32_t *__restrict__ inter, const int32_t *__restrict__ pa,
+                                    const int32_t *__restrict__ pb, int n_a, int n_b, float *__restrict__ iou) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n_a * n_b) return;
+    const int r = (int)(i / n_b), c = (int)(i % n_b);
+    const float fi = __int2float_rn(inter[i]);
+    const float un = __fsub_rn(__fadd_rn(__int2float_rn(pa[r]), __int2float_rn(pb[c])), fi);
+    iou[i] = __fdiv_rn(fi, un);
+}
+
+// ------------------------------------------------------------------ segmented OR
+__global__ void rows_or_reduce_kernel(const uint32_t *__restrict__ rows, long long words,
+                                      const int32_t *__restrict__ idx, const int32_t *__restrict__ seg,
+                                      uint32_t *__restrict__ out) {
+    const int g = blockIdx.y;
+    const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= words) return;
+    uint32_t v = 0;
+    for (int k = seg[g]; k < seg[g + 1]; ++k) v |= __ldg(rows + (long long)idx[k] * words + w);
+    out[(long long)g * words + w] = v;
+}
+
+// ------------------------------------------------------------------ overlap resolution
+// Every thread owns one word column and replays the host-built program rows[dst] &= ~rows[src]
+// in order (projection_2d_to_3d.py:295-299). Columns are independent because the update is
+// element-wise. Rows are cached in shared memory when they fit.
+__global__ void __launch_bounds__(128)
+overlap_resolve_kernel(uint32_t *__restrict__ rows, int n_rows, long long words,
+                       const int32_t *__restrict__ prog, int n_steps, int use_smem) {
+    extern __shared__ uint32_t s_col[];   // n_rows x 128
+    const long long w = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (w >= words) return;
+    if (use_smem) {
+        for (int r = 0; r < n_rows; ++r) s_col[r * 128 + threadIdx.x] = rows[(long long)r * words + w];
+        for (int k = 0; k < n_steps; ++k) {
+            const int dst = __ldg(prog + 2 * k), src = __ldg(prog + 2 * k + 1);
+            s_col[dst * 128 + threadIdx.x] &= ~s_col[src * 128 + threadIdx.x];
+        }
+        for (int r = 0; r < n_rows; ++r) rows[(long long)r * words + w] = s_col[r * 128 + threadIdx.x];
+    } else {
+        for (int k = 0; k < n_steps; ++k) {
+            const int dst = __ldg(prog + 2 * k), src = __ldg(prog + 2 * k + 1);
+            rows[(long long)dst * words + w] &= ~rows[(long long)src * words + w];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ AND keep + popcount
+__global__ void __launch_bounds__(256)
+rows_and_popcount_kernel(uint32_t *__restrict__ rows, long long words, const uint32_t *__restrict__ keep,
+                         int32_t *__restrict__ pop) {
+    uint32_t *r = rows + (long long)blockIdx.x * words;
+    int s = 0;
+    for (long long w = threadIdx.x; w < words; w += 256) {
+        uint32_t v = r[w];
+        if (keep != nullptr) {
+            v &= __ldg(keep + w);
+            r[w] = v;
+        }
+        s += __popc(v);
+    }
+    __shared__ int red[8];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0 && pop != nullptr) {
+        int t = 0;
+        for (int i = 0; i < 8; ++i) t += red[i];
+        pop[blockIdx.x] = t;
+    }
+}
+
+// ------------------------------------------------------------------ pack / unpack
+__global__ void __launch_bounds__(256)
+pack_bits_kernel(const uint8_t *__restrict__ dense, long long n, long long words, uint32_t *__restrict__ packed) {
+    const int row = blockIdx.y;
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;   // element index (warp = one word)
+    const bool bit = (i < n) && (__ldg(dense + (long long)row * n + i) != 0);
+    const unsigned w = __ballot_sync(0xffffffffu, bit);
+    if ((threadIdx.x & 31) == 0 && (i >> 5) < words) packed[(long long)row * words + (i >> 5)] = w;
+}
+
+__global__ void __launch_bounds__(256)
+unpack_bits_kernel(const uint32_t *__restrict__ packed, long long n, long long words, uint8_t *__restrict__ dense) {
+    const int row = blockIdx.y;
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    dense[(long long)row * n + i] = (uint8_t)((__ldg(packed + (long long)row * words + (i >> 5)) >> (i & 31)) & 1u);
+}
+
+// ------------------------------------------------------------------ RLE -> bits
+// One warp per run [lo, hi) of row r: lanes stride over the touched words and OR their part in.
+__global__ void __launch_bounds__(256)
+rle_to_bits_kernel(const int32_t *__restrict__ runs, long long n_runs, long long words, uint32_t *__restrict__ packed) {
+    const long long run = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (run >= n_runs) return;
+    const int lane = threadIdx.x & 31;
+    const int r = __ldg(runs + 3 * run);
+    const long long lo = __ldg(runs + 3 * run + 1), hi = __ldg(runs + 3 * run + 2);
+    if (hi <= lo) return;
+    const long long w_first = lo >> 5, w_last = (hi - 1) >> 5;
+    uint32_t *row = packed + (long long)r * words;
+    for (long long w = w_first + lane; w <= w_last; w += 32) {
+        uint32_t m = 0xffffffffu;
+        if (w == w_first) m &= 0xffffffffu << (lo & 31);
+        if (w == w_last) m &= 0xffffffffu >> (31 - ((hi - 1) & 31));
+        atomicOr(row + w, m);
+    }
+}
+
+}  // namespace bff
+
+using namespace bff;
+
+extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
+                            int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_a >= 0 && n_b >= 0 && words >= 0, "bff_mask_iou: negative size");
+    if (n_a == 0 || n_b == 0) return BFF_OK;
+    BFF_REQUIRE(a && b, "bff_mask_iou: null rows");
+    BFF_REQUIRE(!iou || (inter && pop_a && pop_b), "bff_mask_iou: iou needs inter, pop_a and pop_b buffers");
+    if (pop_a) {
+        if (words > 0) row_popcount_kernel<<<n_a, 256, 0, stream>>>(a, words, pop_a);
+        else BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));
+    }
+    if (pop_b) {
+        if (words > 0) row_popcount_kernel<<<n_b, 256, 0, stream>>>(b, words, pop_b);
+        else BFF_CUDA(cudaMemsetAsync(pop_b, 0, (size_t)n_b * 4, stream));
+    }
+    if (inter) {
+        BFF_CUDA(cudaMemsetAsync(inter, 0, (size_t)n_a * n_b * 4, stream));
+        if (words > 0) {
+            const int symmetric = (a == b && n_a == n_b) ? 1 : 0;
+            const int ta = (n_a + kTile - 1) / kTile, tb = (n_b + kTile - 1) / kTile;
+            // K-slices: enough CTAs to fill the machine a few times, slices a multiple of kKW words
+            long long tiles = (long long)ta * tb;
+            if (symmetric) tiles = (long long)ta * (ta + 1) / 2;
+            long long slices = ceil_div64((long long)kNumSMs * 8, tiles);
+            const long long max_slices = ceil_div64(words, kKW);
+            if (slices > max_slices) slices = max_slices;
+            if (slices < 1) slices = 1;
+            if (slices > 65535) slices = 65535;
+            long long wps = ceil_div64(ceil_div64(words, slices), kKW) * kKW;
+            slices = ceil_div64(words, wps);
+            dim3 grid((unsigned)tb, (unsigned)ta, (unsigned)slices);
+            intersect_kernel<<<grid, 256, 0, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter);
+        }
+    }
+    if (iou) {
+        const long long tot = (long long)n_a * n_b;
+        iou_finalize_kernel<<<(unsigned)ceil_div64(tot, 256), 256, 0, stream>>>(inter, pop_a, pop_b, n_a, n_b, iou);
+    }
+    BFF_LAUNCH_CHECK("bff_mask_iou kernels");
+    return BFF_OK;
+}
+
+extern "C" int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int32_t *idx, const int32_t *seg,
+                                  int32_t n_groups, uint32_t *out, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_groups >= 0 && words >= 0, "bff_rows_or_reduce: negative size");
+    if (n_groups == 0 || words == 0) return BFF_OK;
+    BFF_REQUIRE(rows && idx && seg && out, "bff_rows_or_reduce: null pointer");
+    BFF_REQUIRE(n_groups <= 65535, "bff_rows_or_reduce: too many groups");
+    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_groups);
+    rows_or_reduce_kernel<<<grid, 256, 0, stream>>>(rows, words, idx, seg, out);
+    BFF_LAUNCH_CHECK("rows_or_reduce_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_overlap_resolve(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+                                   int32_t n_steps, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_rows >= 0 && words >= 0 && n_steps >= 0, "bff_overlap_resolve: negative size");
+    if (n_rows == 0 || words == 0 || n_steps == 0) return BFF_OK;
+    BFF_REQUIRE(rows && prog, "bff_overlap_resolve: null pointer");
+    const size_t smem = (size_t)n_rows * 128 * 4;
+    const int use_smem = smem <= 160 * 1024;
+    if (use_smem)
+        BFF_CUDA(cudaFuncSetAttribute((const void *)overlap_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    overlap_resolve_kernel<<<(unsigned)ceil_div64(words, 128), 128, use_smem ? smem : 0, stream>>>(rows, n_rows, words, prog, n_steps, use_smem);
+    BFF_LAUNCH_CHECK("overlap_resolve_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t words, const uint32_t *keep,
+                                     int32_t *pop, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_rows >= 0 && words >= 0, "bff_rows_and_popcount: negative size");
+    if (n_rows == 0) return BFF_OK;
+    if (words == 0) {
+        if (pop) BFF_CUDA(cudaMemsetAsync(pop, 0, (size_t)n_rows * 4, stream));
+        return BFF_OK;
+    }
+    BFF_REQUIRE(rows, "bff_rows_and_popcount: null rows");
+    rows_and_popcount_kernel<<<n_rows, 256, 0, stream>>>(rows, words, keep, pop);
+    BFF_LAUNCH_CHECK("rows_and_popcount_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_pack_bits(const uint8_t *dense, int32_t n_rows, int64_t n, uint32_t *packed, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_rows >= 0 && n >= 0, "bff_pack_bits: negative size");
+    if (n_rows == 0 || n == 0) return BFF_OK;
+    BFF_REQUIRE(dense && packed, "bff_pack_bits: null pointer");
+    BFF_REQUIRE(n_rows <= 65535, "bff_pack_bits: too many rows");
+    const long long words = ceil_div64(n, 32);
+    dim3 grid((unsigned)ceil_div64(words * 32, 256), (unsigned)n_rows);
+    pack_bits_kernel<<<grid, 256, 0, stream>>>(dense, n, words, packed);
+    BFF_LAUNCH_CHECK("pack_bits_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n, uint8_t *dense, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_rows >= 0 && n >= 0, "bff_unpack_bits: negative size");
+    if (n_rows == 0 || n == 0) return BFF_OK;
+    BFF_REQUIRE(dense && packed, "bff_unpack_bits: null pointer");
+    BFF_REQUIRE(n_rows <= 65535, "bff_unpack_bits: too many rows");
+    const long long words = ceil_div64(n, 32);
+    dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_rows);
+    unpack_bits_kernel<<<grid, 256, 0, stream>>>(packed, n, words, dense);
+    BFF_LAUNCH_CHECK("unpack_bits_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_rows, int64_t words,
+                               uint32_t *packed, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_runs >= 0 && n_rows >= 0 && words >= 0, "bff_rle_to_bits: negative size");
+    if (n_rows == 0 || words == 0) return BFF_OK;
+    BFF_REQUIRE(packed, "bff_rle_to_bits: null output");
+    BFF_CUDA(cudaMemsetAsync(packed, 0, (size_t)n_rows * words * 4, stream));
+    if (n_runs == 0) return BFF_OK;
+    BFF_REQUIRE(runs, "bff_rle_to_bits: null runs");
+    rle_to_bits_kernel<<<(unsigned)ceil_div64(n_runs * 32, 256), 256, 0, stream>>>(runs, n_runs, words, packed);
+    BFF_LAUNCH_CHECK("rle_to_bits_kernel");
+    return BFF_OK;
+}

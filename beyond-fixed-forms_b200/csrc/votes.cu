@@ -1,0 +1,134 @@
+// Vote statistics for the point filter of tools/projection_2d_to_3d.py:512-583:
+// max of the count vectors, the 2-D (masked_count, viewed_count) histogram from which the host
+// derives detected_ratio.unique() / masked_counts.unique(), and the per-point keep predicate.
+#include "common.cuh"
+
+namespace bff {
+
+__global__ void __launch_bounds__(256)
+counts_max_kernel(const int32_t *__restrict__ mc, const int32_t *__restrict__ vc, long long n, int32_t *__restrict__ out2) {
+    int m0 = 0, m1 = 0;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        m0 = max(m0, __ldg(mc + i));
+        if (vc != nullptr) m1 = max(m1, __ldg(vc + i));
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        m0 = max(m0, __shfl_down_sync(0xffffffffu, m0, o));
+        m1 = max(m1, __shfl_down_sync(0xffffffffu, m1, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (m0 > 0) atomicMax(out2, m0);
+        if (m1 > 0) atomicMax(out2 + 1, m1);
+    }
+}
+
+// Warp-aggregated histogram: lanes that hit the same bin elect one leader which adds the group
+// size once (__match_any_sync), first into a CTA-private shared-memory histogram when the bins
+// fit, then the non-empty shared bins are flushed with one global atomic each.
+constexpr int kHistSmemBins = 8192;
+
+__global__ void __launch_bounds__(256)
+vote_hist_kernel(const int32_t *__restrict__ mc, const int32_t *__restrict__ vc, long long n, int mc_bins, int vc_bins,
+                 uint32_t *__restrict__ hist, int use_smem) {
+    __shared__ uint32_t s_hist[kHistSmemBins];
+    const int bins = mc_bins * vc_bins;
+    if (use_smem) {
+        for (int i = threadIdx.x; i < bins; i += 256) s_hist[i] = 0;
+        __syncthreads();
+    }
+    const long long stride = (long long)gridDim.x * 256;
+    const long long n_round = (n + 31) / 32 * 32;   // keep warps converged for __match_any_sync
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n_round; i += stride) {
+        int bin = -1;
+        if (i < n) {
+            int a = __ldg(mc + i), b = vc ? __ldg(vc + i) : 0;
+            a = min(max(a, 0), mc_bins - 1);
+            b = min(max(b, 0), vc_bins - 1);
+            bin = a * vc_bins + b;
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, bin);
+        const int leader = __ffs(peers) - 1;
+        if (bin >= 0 && (int)(threadIdx.x & 31) == leader) {
+            if (use_smem) atomicAdd(&s_hist[bin], (uint32_t)__popc(peers));
+            else atomicAdd(hist + bin, (uint32_t)__popc(peers));
+        }
+    }
+    if (use_smem) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < bins; i += 256) {
+            const uint32_t v = s_hist[i];
+            if (v) atomicAdd(hist + i, v);
+        }
+    }
+}
+
+// keep bit per point; float32 arithmetic identical to torch's masked_counts / (viewed_counts + 1)
+// on float32 tensors (projection_2d_to_3d.py:571) followed by the strict < compare (:578).
+__global__ void __launch_bounds__(256)
+point_keep_kernel(const int32_t *__restrict__ mc, const int32_t *__restrict__ vc, long long n, long long words, int mode,
+                  float thr, uint32_t *__restrict__ keep) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    bool k = false;
+    if (i < n) {
+        const int m = __ldg(mc + i);
+        if (m > 0) {
+            const float fm = __int2float_rn(m);
+            if (mode == 0) {
+                const float r = __fdiv_rn(fm, __fadd_rn(__int2float_rn(__ldg(vc + i)), 1.0f));
+                k = !(r < thr);
+            } else if (mode == 1) {
+                k = !(fm < thr);
+            } else {
+                k = true;
+            }
+        }
+    }
+    const unsigned w = __ballot_sync(0xffffffffu, k);
+    if ((threadIdx.x & 31) == 0 && (i >> 5) < words) keep[i >> 5] = w;
+}
+
+}  // namespace bff
+
+using namespace bff;
+
+extern "C" int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, int32_t *out2, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n >= 0 && out2, "bff_counts_max: bad arguments");
+    BFF_CUDA(cudaMemsetAsync(out2, 0, 8, stream));
+    if (n == 0) return BFF_OK;
+    BFF_REQUIRE(mc, "bff_counts_max: null counts");
+    long long blocks = ceil_div64(n, 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    counts_max_kernel<<<(unsigned)blocks, 256, 0, stream>>>(mc, vc, n, out2);
+    BFF_LAUNCH_CHECK("counts_max_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mc_bins, int32_t vc_bins,
+                             uint32_t *hist, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n >= 0 && mc_bins >= 1 && vc_bins >= 1 && hist, "bff_vote_hist: bad arguments");
+    BFF_REQUIRE((long long)mc_bins * vc_bins < (1LL << 31), "bff_vote_hist: too many bins");
+    BFF_REQUIRE(vc != nullptr || vc_bins == 1, "bff_vote_hist: vc_bins must be 1 without viewed counts");
+    BFF_CUDA(cudaMemsetAsync(hist, 0, (size_t)mc_bins * vc_bins * 4, stream));
+    if (n == 0) return BFF_OK;
+    BFF_REQUIRE(mc, "bff_vote_hist: null counts");
+    long long blocks = ceil_div64(n, 256);
+    if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+    const int use_smem = (long long)mc_bins * vc_bins <= kHistSmemBins;
+    vote_hist_kernel<<<(unsigned)blocks, 256, 0, stream>>>(mc, vc, n, mc_bins, vc_bins, hist, use_smem);
+    BFF_LAUNCH_CHECK("vote_hist_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
+                              uint32_t *keep, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n >= 0 && mode >= 0 && mode <= 2, "bff_point_keep: bad arguments");
+    if (n == 0) return BFF_OK;
+    BFF_REQUIRE(mc && keep && (mode != 0 || vc), "bff_point_keep: null pointer");
+    const long long words = ceil_div64(n, 32);
+    point_keep_kernel<<<(unsigned)ceil_div64(words * 32, 256), 256, 0, stream>>>(mc, vc, n, words, mode, thr, keep);
+    BFF_LAUNCH_CHECK("point_keep_kernel");
+    return BFF_OK;
+}

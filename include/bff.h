@@ -1,0 +1,171 @@
+/*
+ * bff.h -- C ABI of libbff.so: the sm_100a kernels behind BeyondFF's 2D->3D lifting,
+ * aggregation/filtering and refinement hot path.
+ *
+ * The reference (zhenghao2519/Beyond-Fixed-Forms) has no FFI of its own: the path is plain
+ * numpy/torch inside tools/projection_2d_to_3d.py and tools/refinement.py. Each entry point
+ * below names the reference lines it replaces; INTEGRATION.md shows the ctypes stub a
+ * maintainer of the reference would add at those lines.
+ *
+ * Conventions
+ *  - every function returns 0 (BFF_OK) or a negative bff_status; bff_last_error() gives a
+ *    thread-local message for the last failure on the calling thread;
+ *  - *_dev / unsuffixed functions take DEVICE pointers owned by the caller and enqueue work
+ *    on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream); they never
+ *    allocate and never synchronise the device;
+ *  - bff_*_host functions take HOST pointers, stage through a bff_ctx-owned device
+ *    workspace, and return after the results are back in host memory;
+ *  - packed masks: row-major uint32 words, bit b of word w = element 32*w + b; a packed
+ *    point row has Wd = ceil(N/32) words, a packed H x W image mask has ceil(H*W/32) words
+ *    with element index y*W + x (the reference's flattening, rle_encode_decode.py:63-99);
+ *  - bits beyond N in the last word of a row are always written as 0 and must be 0 on input.
+ */
+#ifndef BFF_H_
+#define BFF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFF_VERSION 100
+
+typedef enum bff_status {
+    BFF_OK = 0,
+    BFF_EINVAL = -1,     /* bad argument (null pointer, negative size, unsupported combination) */
+    BFF_ECUDA = -2,      /* a CUDA runtime call or launch failed */
+    BFF_ENOMEM = -3      /* workspace allocation failed (host-buffer entry points only) */
+} bff_status;
+
+typedef enum bff_depth_kind {
+    BFF_DEPTH_F32 = 0,   /* float32 metres, as the reference holds it after /depth_scale and resize */
+    BFF_DEPTH_U16 = 1    /* raw uint16 sensor units; the kernel computes (float)u16 / depth_scale in fp32,
+                            bit-identical to projection_2d_to_3d.py:431-435 when no resize is needed */
+} bff_depth_kind;
+
+typedef enum bff_xyz_kind {
+    BFF_XYZ_F32X4 = 0,   /* float4 per point (x,y,z,unused); exact iff the float64 cloud is float32-representable */
+    BFF_XYZ_F64X3 = 1    /* three doubles per point */
+} bff_xyz_kind;
+
+/* Description of one scene's lifting job. All pointers are device pointers for
+ * bff_lift_scene and host pointers for bff_lift_scene_host. */
+typedef struct bff_lift_desc {
+    /* cloud: tools/projection_2d_to_3d.py:385-390 */
+    const void *xyz;            /* n_points elements of xyz_kind */
+    int32_t xyz_kind;           /* bff_xyz_kind */
+    int64_t n_points;           /* N */
+    /* cameras: :370-376 (intrinsics), :422-425 (np.linalg.inv(cam_pose), computed by the caller) */
+    const double *pose_inv;     /* (n_frames, 4, 4) row-major float64 inverse poses */
+    const double *intrinsics;   /* (3, 3) row-major float64 */
+    int32_t n_frames;           /* F */
+    /* depth: :431-436 */
+    const void *depth;          /* (n_frames, height, width) of depth_kind */
+    int32_t depth_kind;         /* bff_depth_kind */
+    float depth_scale;          /* divisor for BFF_DEPTH_U16 (reference: 1000) */
+    int32_t height, width;      /* H, W = cfg.height_2d, cfg.width_2d */
+    double depth_thresh;        /* reference: 0.08 (:438,:565) */
+    /* Optional conservative depth range of NON-ZERO depth values (metres). Points whose camera z
+     * lies outside [depth_min - 2*thresh, depth_max + 2*thresh] cannot pass |z - d| < thresh and
+     * skip the divides. Set depth_min > depth_max (e.g. 1, 0) to disable. */
+    double depth_min, depth_max;
+    /* 2D masks: :395-421, packed bits, all frames concatenated in frame order */
+    const uint32_t *masks2d;    /* (n_masks, ceil(H*W/32)) */
+    const int32_t *mask_offset; /* (n_frames + 1) exclusive prefix of masks per frame; NULL = no masks */
+    const int32_t *mask_query;  /* (n_masks) query id in [0, n_queries); NULL = all 0 */
+    int32_t n_masks;            /* sum of M_f */
+    int32_t n_queries;          /* Q >= 1 */
+    const uint8_t *frame_viewed;/* (n_frames) 1 = frame counts into viewed_counts (:538-567); NULL = all */
+    /* outputs */
+    uint32_t *rows;             /* (n_masks, Wd) packed lifted 3D rows (:441-457); may be NULL */
+    int32_t *masked_counts;     /* (n_queries, N) votes, one per mask hit (:459-461); may be NULL */
+    int32_t *viewed_counts;     /* (N) frames in which the point is visible (:567); may be NULL */
+    int64_t *debug_pix;         /* optional (n_frames, N, 2) int64 [x, y] exactly as :37-48 returns */
+    uint32_t *debug_vis;        /* optional (n_frames, Wd) packed visibility (:51-70) */
+    /* launch shape: frames per CTA chunk (0 = automatic) */
+    int32_t frames_per_chunk;
+    int32_t reserved;
+} bff_lift_desc;
+
+int bff_version(void);
+const char *bff_last_error(void);
+
+/* Replaces the per-frame loops of tools/projection_2d_to_3d.py:413-461 and :538-567
+ * (compute_projected_pts_tensor :37, compute_visibility_mask_tensor :51,
+ * compute_visible_masked_pts_tensor :73, masked_counts/viewed_counts updates) with one launch
+ * over all frames. Outputs are fully overwritten. */
+int bff_lift_scene(const bff_lift_desc *desc, void *stream);
+
+/* Number of kernels bff_lift_scene launches for this description (for launch accounting). */
+int bff_lift_scene_launches(const bff_lift_desc *desc);
+
+/* Replaces calculate_iou (projection_2d_to_3d.py:149-166) and calculate_iou_between_stages
+ * (refinement.py:69-90, before its transpose): a (nA, Wd), b (nB, Wd) packed rows ->
+ * inter (nA, nB) int32, pop_a (nA), pop_b (nB) int32, and optionally iou (nA, nB) float32 =
+ * f32(I) / ((f32(sA) + f32(sB)) - f32(I)), 0/0 = NaN. b == a computes the square matrix.
+ * inter / pop_a / pop_b / iou may each be NULL. */
+int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
+                 int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou, void *stream);
+
+/* Replaces the OR-merges of merge_masks (projection_2d_to_3d.py:214-223) and refinement.py:248,269:
+ * out[g] = OR over k in [seg[g], seg[g+1]) of rows[idx[k]].  rows (n_rows, words), out (n_groups, words). */
+int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int32_t *idx, const int32_t *seg,
+                       int32_t n_groups, uint32_t *out, void *stream);
+
+/* Max of masked_counts (per query) and viewed_counts, so the histogram below can be sized:
+ * out[0] = max(mc), out[1] = max(vc). vc may be NULL (out[1] = 0). */
+int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, int32_t *out2, void *stream);
+
+/* 2-D histogram of (masked_count, viewed_count) pairs: hist[(mc * (vc_bins)) + vc] += 1.
+ * The host derives the reference's detected_ratio.unique() / masked_counts.unique()
+ * (projection_2d_to_3d.py:512-578) from the non-empty bins. vc may be NULL (vc_bins = 1). hist is overwritten. */
+int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mc_bins, int32_t vc_bins,
+                  uint32_t *hist, void *stream);
+
+/* Per-point keep predicate -> packed bits keep (Wd):
+ *  mode 0 (detected ratio, :571-583): keep = mc > 0 && !(f32(mc) / (f32(vc) + 1) < thr)
+ *  mode 1 (occurrence, :512-522,583):  keep = mc > 0 && !(f32(mc) < thr)
+ *  mode 2 (no filter):                 keep = mc > 0 */
+int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
+                   uint32_t *keep, void *stream);
+
+/* solve_overlapping's sequential pass (projection_2d_to_3d.py:295-299) on packed rows, in place.
+ * prog (n_steps, 2) int32: step k clears from row prog[k][0] the bits of row prog[k][1]
+ * (rows[dst] &= ~rows[src]) in list order; every word column runs the program independently. */
+int bff_overlap_resolve(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+                        int32_t n_steps, void *stream);
+
+/* rows[r] &= keep (if keep != NULL, in place) and pop[r] = popcount(rows[r]) afterwards
+ * (projection_2d_to_3d.py:592-596). */
+int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t words, const uint32_t *keep,
+                          int32_t *pop, void *stream);
+
+/* bool/uint8 (n_rows, n) <-> packed (n_rows, ceil(n/32)). Non-zero bytes are set bits. */
+int bff_pack_bits(const uint8_t *dense, int32_t n_rows, int64_t n, uint32_t *packed, void *stream);
+int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n, uint8_t *dense, void *stream);
+
+/* RLE -> packed bits without a dense intermediate (rle_decode_batch, rle_encode_decode.py:35-61;
+ * rle_decode, refinement.py:26-39). runs (n_runs, 3) int32 = [row, lo, hi) already clipped to
+ * [0, length] by the host with Python-slice semantics. packed (n_rows, words) is overwritten. */
+int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_rows, int64_t words,
+                    uint32_t *packed, void *stream);
+
+/* ---- host-buffer entry points (what a ctypes/numpy binding in the reference would call) ---- */
+typedef struct bff_ctx bff_ctx;
+int bff_ctx_create(int device, bff_ctx **out);
+void bff_ctx_destroy(bff_ctx *ctx);
+/* Same contract as bff_lift_scene with every pointer in HOST memory (pinned or pageable).
+ * Copies inputs to the device, runs the kernels, copies rows / counts back, and returns
+ * after the outputs are valid. h2d_bytes / d2h_bytes (may be NULL) receive the bytes moved. */
+int bff_lift_scene_host(bff_ctx *ctx, const bff_lift_desc *host_desc, int64_t *h2d_bytes, int64_t *d2h_bytes);
+/* Host-buffer form of bff_mask_iou. */
+int bff_mask_iou_host(bff_ctx *ctx, const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b,
+                      int64_t words, int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou,
+                      int64_t *h2d_bytes, int64_t *d2h_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BFF_H_ */
