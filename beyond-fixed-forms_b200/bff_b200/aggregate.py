@@ -1,0 +1,130 @@
+"""Aggregation, point filtering and overlap resolution of lifted 3D masks on PACKED rows.
+
+Host-side mirror of aggregate / calculate_iou / calculate_feature_similarity / merge_masks /
+find_unconnected_subgraphs_tensor / solve_overlapping and the filtering block of
+tools/projection_2d_to_3d.py (:100-301, :512-623). The O(Ins^2 N) and O(Ins N) work runs in
+libbff.so on bit-packed rows; what stays on the host are decisions over tiny matrices, made
+with the same torch CPU ops as the reference so comparison/promotion semantics are identical.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+
+
+def label_equality(labels: Sequence[str]) -> torch.Tensor:
+    """calculate_feature_similarity (projection_2d_to_3d.py:169-187): exact string equality.
+    (The reference's similarity threshold argument is unused)"""
+    ids: dict = {}
+    v = torch.tensor([ids.setdefault(l, len(ids)) for l in labels], dtype=torch.int64)
+    return v.unsqueeze(0) == v.unsqueeze(1)
+
+
+def connected_groups(adj: torch.Tensor) -> List[List[int]]:
+    """find_unconnected_subgraphs_tensor (projection_2d_to_3d.py:250-274) without the O(Ins^4)
+    closure: for every not-yet-visited node in index order, the ascending list of nodes reachable
+    from it by a path of length >= 1. A node without self edge and without neighbours (an empty
+    lifted row: its IoU diagonal is NaN) yields [] and marks nothing visited, like the reference."""
+    a = adj.to(torch.bool).cpu().numpy()
+    n = a.shape[0]
+    nbrs = [np.flatnonzero(a[i]) for i in range(n)]
+    visited = np.zeros(n, dtype=bool)
+    out: List[List[int]] = []
+    for i in range(n):
+        if visited[i]:
+            continue
+        reach = np.zeros(n, dtype=bool)
+        stack = list(nbrs[i])
+        reach[stack] = True
+        while stack:
+            u = stack.pop()
+            for v in nbrs[u]:
+                if not reach[v]:
+                    reach[v] = True
+                    stack.append(v)
+        comp = [int(k) for k in np.flatnonzero(reach)]
+        out.append(comp)
+        visited[reach] = True
+    return out
+
+
+def aggregate_rows(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], iou_thres: float,
+                   min_members: int):
+    """aggregate + merge_masks (projection_2d_to_3d.py:100-146,190-247) on packed rows.
+    rows (Ins,Wd) int32 CUDA; conf (Ins,) CPU tensor as torch.tensor(list of 0-d) builds it.
+    Returns (agg_rows CUDA or None, conf_agg CPU tensor, labels_agg, groups)."""
+    _, _, _, iou = ops.mask_iou(rows)                           # K7: popcount intersections, exact fp32 IoU
+    merge = label_equality(labels) & (iou.cpu() > iou_thres)    # python float vs f32 tensor: torch semantics
+    groups = [g for g in connected_groups(merge) if len(g) >= min_members]
+    print("masks_to_be_merged", groups)
+    used = [g for g in groups if g != []]
+    if not used:
+        return None, None, [], []
+    agg = ops.rows_or_reduce(rows, used)                        # K10
+    confs = []
+    for g in used:
+        c = [conf[k] for k in g]
+        confs.append(sum(c) / len(c))                           # sequential, index order (:220-224)
+    return agg, torch.tensor(confs), [labels[g[0]] for g in used], groups
+
+
+def keep_points(mc: torch.Tensor, vc: Optional[torch.Tensor], cfg) -> torch.Tensor:
+    """Point filter (projection_2d_to_3d.py:512-583) -> packed keep bits (Wd,) int32 CUDA.
+    The reference's `tensor.unique()` over N points is replaced by the (masked, viewed) histogram:
+    every distinct value of the ratio comes from a non-empty bin, so the unique list is the same."""
+    mc = mc.reshape(-1)
+    if cfg["if_occurance_threshold"]:
+        mmax, _ = ops.counts_max(mc, None)
+        hist = ops.vote_hist(mc, None, mmax + 1, 1).cpu().reshape(-1)
+        u = torch.nonzero(hist > 0).reshape(-1).to(torch.float32)       # ascending == unique() order
+        t = u[math.floor(cfg["occurance_threshold"] * u.shape[0])]
+        return ops.point_keep(mc, None, 1, float(t))
+    if cfg["if_detected_ratio_threshold"]:
+        mmax, vmax = ops.counts_max(mc, vc)
+        hist = ops.vote_hist(mc, vc, mmax + 1, vmax + 1).cpu()
+        nz = torch.nonzero(hist > 0)
+        ratio = nz[:, 0].to(torch.float32) / (nz[:, 1].to(torch.float32) + 1)   # :571 in float32
+        u = ratio.unique()
+        t = u[math.floor(cfg["detected_ratio_threshold"] * u.shape[0])]
+        print("detected_ratio_thres_value", t)
+        return ops.point_keep(mc, vc, 0, float(t))
+    return ops.point_keep(mc, None, 2, 0.0)
+
+
+def overlap_program(inter: torch.Tensor, group_sizes: Sequence[int]) -> List[Tuple[int, int]]:
+    """solve_overlapping's schedule (projection_2d_to_3d.py:285-299): pairs i<j that overlap in the
+    incoming rows, in (i, j) order; the mask merged from more members keeps the shared points."""
+    ov = (inter.cpu() > 0).numpy()
+    prog = []
+    n = ov.shape[0]
+    for i in range(n):
+        for j in np.flatnonzero(ov[i, i + 1:]) + i + 1:
+            j = int(j)
+            if group_sizes[i] > group_sizes[j]:
+                prog.append((j, i))          # rows[j] &= ~rows[i]
+            else:
+                prog.append((i, j))          # rows[i] &= ~rows[j]
+    return prog
+
+
+def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[str], groups: List[List[int]],
+                      keep_bits: torch.Tensor, n_points: int, cfg):
+    """projection_2d_to_3d.py:583-634: overlap resolution, AND with the kept points, row filter,
+    and (the dict that is saved, the packed rows of its masks)."""
+    inter, before, _, _ = ops.mask_iou(agg, want_iou=False)
+    sizes = [len(g) for g in groups]          # as the reference: indexed by position in the merge list
+    ops.overlap_resolve(agg, overlap_program(inter, sizes))
+    after = ops.rows_and_popcount(agg, keep_bits)
+    before64, after64 = before.cpu().to(torch.int64), after.cpu().to(torch.int64)
+    sel = (after64 > cfg["remove_small_masks"]) & (after64 > cfg["remove_filtered_masks"] * before64)
+    idx = torch.nonzero(sel).reshape(-1)
+    out_rows = agg[idx.to(agg.device)]
+    ins = ops.unpack_bits(out_rows, n_points)
+    print("after filtering", ins.shape)
+    result = {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
+    return result, out_rows

@@ -192,18 +192,29 @@ def point_keep(mc: torch.Tensor, vc: Optional[torch.Tensor], mode: int, thr: flo
     return keep
 
 
-def overlap_resolve(rows: torch.Tensor, program: Sequence[Sequence[int]]) -> torch.Tensor:
-    """In place: for (dst, src) in program: rows[dst] &= ~rows[src]."""
+def _row_program(fn_name: str, rows: torch.Tensor, program: Sequence[Sequence[int]]) -> torch.Tensor:
+    if not rows.is_contiguous():
+        raise ValueError("in-place row programs need a contiguous rows tensor")
     rows = _cuda(rows, torch.int32, "rows")
     prog = np.asarray(program, dtype=np.int32).reshape(-1, 2)
     if prog.shape[0] and rows.shape[0] and rows.shape[1]:
         if prog.min() < 0 or prog.max() >= rows.shape[0]:
             raise IndexError("program row out of range")
         d_prog = torch.from_numpy(prog).to(rows.device)
-        check(lib().bff_overlap_resolve(ptr(rows), rows.shape[0], rows.shape[1], ptr(d_prog), prog.shape[0], current_stream()),
-              "bff_overlap_resolve")
+        check(getattr(lib(), fn_name)(ptr(rows), rows.shape[0], rows.shape[1], ptr(d_prog), prog.shape[0], current_stream()),
+              fn_name)
         _count()
     return rows
+
+
+def overlap_resolve(rows: torch.Tensor, program: Sequence[Sequence[int]]) -> torch.Tensor:
+    """In place, sequentially: for (dst, src) in program: rows[dst] &= ~rows[src]."""
+    return _row_program("bff_overlap_resolve", rows, program)
+
+
+def rows_or_into(rows: torch.Tensor, program: Sequence[Sequence[int]]) -> torch.Tensor:
+    """In place, sequentially: for (dst, src) in program: rows[dst] |= rows[src]."""
+    return _row_program("bff_rows_or_into", rows, program)
 
 
 def rows_and_popcount(rows: torch.Tensor, keep: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -1,0 +1,197 @@
+"""Stage-1 / stage-2 refinement on packed point masks: the body of tools/refinement.py
+(:135-428). Mask algebra (RLE ingest, IoU, OR-merges) runs in libbff.so; matching decisions are
+taken on the small IoU matrices with the same torch CPU ops as the reference."""
+from __future__ import annotations
+
+import os
+from typing import Callable, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import ops, scene_io
+from .rle import runs_for_device
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+with open(os.path.join(_HERE, "stage1_classes.txt")) as _fh:
+    # index -> label table of the stage-1 (Open3DIS) results, refinement.py:58-62
+    STAGE1_CLASS_NAMES: List[str] = [l.strip() for l in _fh if l.strip()]
+
+
+def idx_to_label(idx) -> str:
+    return STAGE1_CLASS_NAMES[idx]
+
+
+def iou_between_stages(rows1: torch.Tensor, rows2: torch.Tensor) -> torch.Tensor:
+    """calculate_iou_between_stages (refinement.py:69-90): (m, n) float32 CPU matrix."""
+    _, _, _, iou = ops.mask_iou(rows1, rows2)
+    return iou.cpu().T
+
+
+def stage1_rows(stage1: dict, device) -> torch.Tensor:
+    """RLE stage-1 masks -> packed rows on the device (refinement.py:26-39,186-189 without the
+    dense uint8 intermediate)."""
+    rles = list(stage1["ins"])
+    if not rles:
+        return torch.zeros((0, 0), dtype=torch.int32, device=device)
+    runs, length = runs_for_device(rles)
+    return ops.rle_to_bits(runs, len(rles), length, device)
+
+
+def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
+                sim_fn: Callable[[str, str], float], device) -> dict:
+    """Pass 1 for one scene (refinement.py:182-312). Returns packed rows + the small vectors pass 2 needs."""
+    q_ = query.replace(" ", "_")
+    s1 = stage1_rows(stage1, device)
+    n_points = int(stage1["ins"][0]["length"]) if len(stage1["ins"]) else 0
+    labels = [idx_to_label(i) for i in stage1["final_class"]]
+    if len(stage2["conf"]) == 0:
+        print("Empty stage 2 mask")
+        other = [i for i, l in enumerate(labels) if l == q_]
+        return {"ious": [], "sims": [], "m1": None, "m2": None, "conf2": [], "n_points": n_points,
+                "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+    s2 = ops.pack_bits(stage2["ins"].to(device))
+    s2_conf = stage2["conf"]
+    mm = torch.argmax(iou_between_stages(s1, s2), dim=1)                       # :208-213
+    sel = s1[mm.to(device)]
+    g = iou_between_stages(sel, sel)                                           # :217-219
+    g[range(len(mm)), range(len(mm))] = 0
+    g = (g > stage1_iou_thres).to(int)
+    best: list = []
+    redirect = torch.ones(len(g), dtype=torch.int) * -1
+    or_prog = []                                                               # sequential in-place ORs (:248)
+    for i in range(len(g)):
+        if redirect[i] != -1:
+            best.append(mm[redirect[i]])
+            continue
+        best.append(mm[i])
+        if g[i].sum() > 0:
+            for j in torch.nonzero(g[i] == 1).reshape(-1).tolist():
+                redirect[j] = i
+                or_prog.append((int(mm[i]), int(mm[j])))
+    ops.rows_or_into(s1, or_prog)
+    print("DEBUG best_match_after_iou_check", best)
+    best = torch.tensor(best)
+    uniq, cnt = torch.unique(best, return_counts=True)                        # :258
+    for u, c in zip(uniq, cnt):
+        if c > 1:
+            hit = best == u
+            members = torch.nonzero(hit).reshape(-1).tolist()
+            merged = ops.rows_or_reduce(s2, [members])
+            mconf = s2_conf[hit].mean()
+            keep = torch.nonzero(~hit).reshape(-1).to(device)
+            s2 = torch.cat([s2[keep], merged])
+            s2_conf = torch.cat([s2_conf[~hit], mconf.unsqueeze(0)])
+            best = torch.cat([best[~hit], u.unsqueeze(0)])
+    iou = iou_between_stages(s1, s2)                                           # :285-290
+    mm = torch.argmax(iou, dim=1)
+    other = [i for i, l in enumerate(labels) if l == q_ and i not in mm]      # :293
+    matched_labels = [labels[k] for k in mm]
+    sims = [float(sim_fn(query, l)) for l in matched_labels]                   # :297-302
+    ious = iou[range(len(mm)), mm]
+    print("iou for matched labels", ious)
+    print("Matched labels:", matched_labels)
+    print("Clip similarities:", sims)
+    return {"ious": ious, "sims": sims, "m1": s1[mm.to(device)], "m2": s2, "conf2": s2_conf, "n_points": n_points,
+            "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+
+
+def similarity_threshold(all_sims: Sequence[Sequence[float]], percentile: float) -> float:
+    """Global over the scenes of the class (refinement.py:317-324). Raises IndexError like the
+    reference when no scene produced a match."""
+    u = sorted(set(s for sims in all_sims for s in sims))
+    print("Unique similarities:", u)
+    return u[int(len(u) * percentile)]
+
+
+def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float) -> dict:
+    """Selection (refinement.py:330-426) -> the dict that is saved."""
+    out = {"ins": [], "conf": [], "final_class": []}
+    picked = []                                  # (source rows tensor, row index)
+    for k in range(p1["other"].shape[0]):
+        picked.append((p1["other"], k))
+        out["conf"].append(torch.tensor(0.5))
+        out["final_class"].append(query)
+    for k, iou in enumerate(p1["ious"]):
+        if iou > iou_thres:
+            if p1["sims"][k] < sim_thres:
+                continue
+            picked.append((p1["m1"], k))
+        else:
+            picked.append((p1["m2"], k))
+        out["conf"].append(p1["conf2"][k])
+        out["final_class"].append(query)
+    if picked:
+        rows = torch.stack([src[k] for src, k in picked])
+        out["ins"] = ops.unpack_bits(rows, p1["n_points"]).cpu()
+        out["conf"] = torch.stack(out["conf"])
+    return out
+
+
+class ClipTextSimilarity:
+    """Cosine similarity of CLIP text embeddings (refinement.py:93-117), with a per-pair cache.
+    CLIP is the reference's model and an INPUT to this path; it is used when importable."""
+
+    def __init__(self, device):
+        import clip  # the reference's dependency (OpenAI CLIP); out of scope to re-implement
+        self._clip = clip
+        self.device = device
+        self.model, _ = clip.load("ViT-L/14", device=device)
+        self._cache: Dict[tuple, float] = {}
+
+    def __call__(self, query: str, label: str) -> float:
+        key = (query, label)
+        if key not in self._cache:
+            a = self._clip.tokenize([query]).to(self.device)
+            b = self._clip.tokenize([label]).to(self.device)
+            with torch.no_grad():
+                fa, fb = self.model.encode_text(a), self.model.encode_text(b)
+            sim = fa @ fb.T
+            sim = sim / (fa.norm(dim=-1, keepdim=True) * fb.norm(dim=-1, keepdim=True).T)
+            self._cache[key] = sim.item()
+        return self._cache[key]
+
+
+def refine_class(cfg, cls: str, device, sim_fn: Callable[[str, str], float]):
+    """Both passes over every scene of one class; writes <final_output_dir>/<cls>/<scene>.pth."""
+    g = (lambda k: cfg[k]) if isinstance(cfg, dict) else (lambda k: getattr(cfg, k))
+    stage1_dir, mask_3d_dir = g("stage_1_results_dir"), g("mask_3d_dir")
+    ckpt_path = f"./checkpoints/refinement_checkpoint_{cls}.yaml"             # :41-43
+    ckpt = scene_io.read_checkpoint(ckpt_path)
+    stage2_files = sorted(s for s in os.listdir(os.path.join(mask_3d_dir, cls)) if s.endswith("_00.pth"))
+    per_scene = []
+    for fn in stage2_files:
+        scene_id = fn.replace(".pth", "")
+        p1_path = os.path.join(stage1_dir, f"{scene_id}.pth")
+        p2_path = os.path.join(mask_3d_dir, cls, f"{scene_id}.pth")
+        if not (os.path.exists(p1_path) and os.path.exists(p2_path)):
+            continue                                                           # :175-178 (B10: misaligns pass 2)
+        per_scene.append(pass1_scene(scene_io.torch_load(p1_path), scene_io.torch_load(p2_path), cls,
+                                     g("stage1_iou_thres"), sim_fn, device))
+    sim_thres = similarity_threshold([p["sims"] for p in per_scene], g("refinment_sim_percentile"))
+    for s, fn in enumerate(stage2_files):
+        scene_id = fn.replace(".pth", "")
+        p1 = per_scene[s]                                                      # positional, like the reference
+        print("DEBUG all ious", p1["ious"])
+        out = pass2_scene(p1, cls, g("refiment_iou_thres"), sim_thres)
+        scene_io.save_result(out, g("final_output_dir"), cls, scene_id)
+        if len(p1["ious"]) != 0 and len(out["final_class"]) != 0:
+            ckpt[scene_id] = True                                              # :427-428
+            scene_io.write_checkpoint(ckpt_path, ckpt)
+
+
+def main(argv=None):
+    """CLI body of tools/refinement.py: same arguments, config keys and outputs."""
+    import argparse
+    import yaml
+    parser = argparse.ArgumentParser(description="Configuration Beyond Fixed Forms")
+    parser.add_argument("--config", type=str, required=True, help="Config")
+    parser.add_argument("--cls", type=str, required=True, help="Class")
+    args = parser.parse_args(argv)
+    cfg = yaml.safe_load(open(args.config, "r").read())
+    if not torch.cuda.is_available():
+        raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    device = torch.device("cuda", 0)
+    print("Processing class:", args.cls.replace(" ", "_"))
+    refine_class(cfg, args.cls, device, ClipTextSimilarity(device))
+    return 0

@@ -1,0 +1,125 @@
+"""Readers/writers of the reference's on-disk tree. Same files, same
+parsing calls as the reference so that the bytes handed to the kernels are the bytes the
+reference computes on; everything after parsing goes to the GPU."""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+DEPTH_SCALE = 1000.0      # tools/projection_2d_to_3d.py:346 (hard-coded there, not a config key)
+DEPTH_THRESH = 0.08       # tools/projection_2d_to_3d.py:438,565
+
+
+def torch_load(path: str):
+    """torch.load as the reference calls it (projection_2d_to_3d.py:396, refinement.py:182-183);
+    the files hold numpy RLE arrays, so weights_only must be off on torch >= 2.6."""
+    return torch.load(path, map_location="cpu", weights_only=False)
+
+
+def load_cloud(scene_npy_dir: str, scene_id: str) -> np.ndarray:
+    """(N,3) float64 xyz (projection_2d_to_3d.py:385-387; file written by tools/utils/ply2npy.py)."""
+    return np.ascontiguousarray(np.load(os.path.join(scene_npy_dir, f"{scene_id}.npy"))[:, :3], dtype=np.float64)
+
+
+def load_intrinsics(scene_2d_dir: str, scene_id: str) -> np.ndarray:
+    """projection_2d_to_3d.py:370-376."""
+    return np.loadtxt(os.path.join(scene_2d_dir, scene_id, "intrinsic", "intrinsic_color.txt"))[:3, :3]
+
+
+def load_pose_inverse(scene_2d_dir: str, scene_id: str, frame_id: str) -> np.ndarray:
+    """np.linalg.inv(np.loadtxt(pose)) exactly as projection_2d_to_3d.py:422,425 (LAPACK on the
+    host; a rigid-transform shortcut would give different bits). Non-finite poses give NaNs."""
+    pose = np.loadtxt(os.path.join(scene_2d_dir, scene_id, "pose", f"{frame_id}.txt"))
+    return np.linalg.inv(pose)
+
+
+def list_view_frames(scene_2d_dir: str, scene_id: str, downsample_ratio: int) -> List[str]:
+    """Frame ids of color/*.jpg sorted numerically, every `downsample_ratio`-th
+    (projection_2d_to_3d.py:526-535)."""
+    image_dir = os.path.join(scene_2d_dir, scene_id, "color")
+    names = [f for f in os.listdir(image_dir) if f.endswith(".jpg")]
+    names.sort(key=lambda x: int(x.split(".")[0]))
+    return [f[:-4] for f in names[::downsample_ratio]]
+
+
+def load_depth_raw(scene_2d_dir: str, scene_id: str, frame_id: str) -> np.ndarray:
+    import cv2
+    path = os.path.join(scene_2d_dir, scene_id, "depth", f"{frame_id}.png")
+    img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+    if img is None:
+        raise FileNotFoundError(path)      # the reference dies on None.astype (AttributeError)
+    return img
+
+
+def depth_to_metres(raw: np.ndarray, width: int, height: int) -> np.ndarray:
+    """float32 depth at mask resolution as projection_2d_to_3d.py:431-436 builds it (host path,
+    used when a resize is needed; OpenCV bilinear kept on the host -- SURVEY.md 8f N2)."""
+    import cv2
+    d = raw.astype(np.float32) / int(DEPTH_SCALE)
+    return cv2.resize(d, (int(width), int(height)))
+
+
+class FrameSet:
+    """Frames of one scene ready for the device: inverse poses, depth stack, viewed flags."""
+
+    def __init__(self, frame_ids: List[str], pose_inv: np.ndarray, depth: np.ndarray, depth_is_raw: bool,
+                 viewed: np.ndarray, depth_range: Optional[Tuple[float, float]]):
+        self.frame_ids, self.pose_inv, self.depth = frame_ids, pose_inv, depth
+        self.depth_is_raw, self.viewed, self.depth_range = depth_is_raw, viewed, depth_range
+
+
+def load_frames(scene_2d_dir: str, scene_id: str, frame_ids: Sequence[str], viewed: Sequence[bool],
+                width: int, height: int) -> FrameSet:
+    f = len(frame_ids)
+    pose_inv = np.empty((f, 4, 4), np.float64)
+    raws = []
+    for i, fid in enumerate(frame_ids):
+        pose_inv[i] = load_pose_inverse(scene_2d_dir, scene_id, fid)
+        raws.append(load_depth_raw(scene_2d_dir, scene_id, fid))
+    same = all(r.dtype == np.uint16 and r.shape == (height, width) for r in raws)
+    if same:
+        depth = np.stack(raws) if raws else np.zeros((0, height, width), np.uint16)
+        rng = (0.0, 65535.0 / DEPTH_SCALE)
+        return FrameSet(list(frame_ids), pose_inv, depth, True, np.asarray(viewed, np.uint8), rng)
+    depth = np.stack([depth_to_metres(r, width, height) for r in raws]) if raws else np.zeros((0, height, width), np.float32)
+    rng = None
+    if depth.size and np.isfinite(depth).all():
+        rng = (float(min(depth.min(), 0.0)), float(depth.max()))
+    return FrameSet(list(frame_ids), pose_inv, depth, False, np.asarray(viewed, np.uint8), rng)
+
+
+def cloud_for_device(xyz: np.ndarray, device) -> torch.Tensor:
+    """float4 fp32 when the float64 cloud is float32-representable (ScanNet PLYs are), else (N,3) f64."""
+    x32 = xyz.astype(np.float32)
+    if np.array_equal(x32.astype(np.float64), xyz):
+        x4 = np.zeros((xyz.shape[0], 4), np.float32)
+        x4[:, :3] = x32
+        return torch.from_numpy(x4).to(device)
+    return torch.from_numpy(np.ascontiguousarray(xyz, np.float64)).to(device)
+
+
+def empty_stage2() -> dict:
+    """What the reference saves when nothing is lifted/aggregated (projection_2d_to_3d.py:465-478,496-509)."""
+    return {"ins": torch.tensor([[]]), "conf": torch.tensor([]), "final_class": []}
+
+
+def save_result(result: dict, out_dir: str, cls: str, scene_id: str):
+    os.makedirs(os.path.join(out_dir, cls), exist_ok=True)
+    torch.save(result, os.path.join(out_dir, cls, f"{scene_id}.pth"))
+
+
+def read_checkpoint(path: str) -> dict:
+    import yaml
+    if os.path.exists(path):
+        with open(path, "r") as fh:
+            return yaml.safe_load(fh) or {}
+    return {}
+
+
+def write_checkpoint(path: str, ckpt: dict):
+    import yaml
+    with open(path, "w") as fh:
+        yaml.safe_dump(ckpt, fh)

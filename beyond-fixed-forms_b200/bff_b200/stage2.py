@@ -1,0 +1,102 @@
+"""Stage 2 driver: lifting + aggregation + filtering of one scene / one class, the body of
+tools/projection_2d_to_3d.py __main__ (:336-634) on the GPU path."""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from . import aggregate, lift as lift_mod, scene_io
+
+
+def cfg_get(cfg, key):
+    return cfg[key] if isinstance(cfg, dict) else getattr(cfg, key)
+
+
+def needs_viewed_counts(cfg) -> bool:
+    """viewed_counts are only computed on the detected-ratio branch (projection_2d_to_3d.py:512,524)."""
+    return (not cfg_get(cfg, "if_occurance_threshold")) and bool(cfg_get(cfg, "if_detected_ratio_threshold"))
+
+
+def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor, vc: Optional[torch.Tensor],
+                         n_points: int, cfg):
+    """Everything after the frame loop (projection_2d_to_3d.py:463-634) for one query.
+    Returns (dict to save, reached_filter) -- the reference only writes its scene checkpoint when
+    the filter stage is reached (:580-581)."""
+    c = {k: cfg_get(cfg, k) for k in ("iou_thres", "min_aggragated_masks", "if_occurance_threshold", "occurance_threshold",
+                                      "if_detected_ratio_threshold", "detected_ratio_threshold", "remove_filtered_masks",
+                                      "remove_small_masks")}
+    if len(conf_list) == 0:
+        print("No 3d masks detected in backprojection!")
+        return scene_io.empty_stage2(), False
+    conf = torch.tensor(conf_list)                                  # :484-486
+    agg, conf_agg, labels_agg, groups = aggregate.aggregate_rows(rows, conf, labels, c["iou_thres"], c["min_aggragated_masks"])
+    if agg is None:
+        print("No 3d masks detected after aggregation")
+        return scene_io.empty_stage2(), False
+    keep = aggregate.keep_points(mc, vc, c)
+    print("before filtering", torch.Size([agg.shape[0], n_points]))
+    result, _ = aggregate.filter_and_select(agg, conf_agg, labels_agg, groups, keep, n_points, c)
+    return result, True
+
+
+def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
+    """One iteration of the scene loop (projection_2d_to_3d.py:365-634).
+    Returns (dict to save, reached_filter)."""
+    from . import dist as dist_mod
+    width, height = int(cfg_get(cfg, "width_2d")), int(cfg_get(cfg, "height_2d"))
+    scene_2d_dir = cfg_get(cfg, "scene_2d_dir")
+    print("Working on", scene_id, "class", cls)
+    intr = scene_io.load_intrinsics(scene_2d_dir, scene_id)
+    xyz = scene_io.load_cloud(cfg_get(cfg, "scene_npy_dir"), scene_id)
+    records = scene_io.torch_load(os.path.join(cfg_get(cfg, "mask_2d_dir"), cls, f"{scene_id}.pth"))
+    q = lift_mod.QueryMasks.from_file_records(cls, records)
+    want_viewed = needs_viewed_counts(cfg)
+    conf_list, labels = q.flat_conf_and_labels()
+    # the reference skips the viewed-count pass when nothing was lifted or nothing aggregates; its
+    # result is unused in those cases, so computing it in the same launch changes nothing on disk
+    view_ids = scene_io.list_view_frames(scene_2d_dir, scene_id, int(cfg_get(cfg, "downsample_ratio"))) if (want_viewed and conf_list) else None
+    frame_ids, viewed, per_frame = lift_mod.plan_frames([q], view_ids)
+    if dist_ctx is not None and dist_ctx.world_size > 1:
+        lifted = dist_mod.lift_sharded(dist_ctx, xyz, intr, scene_2d_dir, scene_id, frame_ids, viewed, per_frame, [q],
+                                       height, width, want_viewed and bool(conf_list), device)
+    else:
+        frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height)
+        lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, [q], height, width,
+                               want_viewed and bool(conf_list))
+    return aggregate_and_filter(lifted.rows[0], conf_list, labels, lifted.masked_counts[0], lifted.viewed_counts,
+                                xyz.shape[0], cfg)
+
+
+def main(argv=None):
+    """CLI body of tools/projection_2d_to_3d.py: same arguments, config keys, outputs, checkpoints."""
+    import argparse
+    import yaml
+    parser = argparse.ArgumentParser(description="Configuration Open3DIS")
+    parser.add_argument("--config", type=str, required=True, help="Config")
+    parser.add_argument("--cls", type=str, required=True, help="Class")
+    args = parser.parse_args(argv)
+    cfg = yaml.safe_load(open(args.config, "r").read())
+    if not torch.cuda.is_available():
+        raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    from . import dist as dist_mod
+    dist_ctx = dist_mod.init_from_env()
+    device = torch.device("cuda", dist_ctx.local_rank if dist_ctx else 0)
+    torch.cuda.set_device(device)
+    cls = args.cls
+    ckpt_path = f"checkpoints/projection_2d_to_3d_checkpoint_{cls}.yaml"     # :320-322
+    ckpt = scene_io.read_checkpoint(ckpt_path)
+    seg_dir = os.path.join(cfg["mask_2d_dir"], cls)
+    scenes = sorted(s for s in os.listdir(seg_dir) if s.endswith("_00.pth"))  # :361-363
+    for s in scenes:
+        scene_id = s[:-4]
+        result, reached_filter = process_scene(cfg, cls, scene_id, device, dist_ctx)
+        if dist_ctx is None or dist_ctx.rank == 0:
+            scene_io.save_result(result, cfg["mask_3d_dir"], cls, scene_id)
+            if reached_filter:
+                ckpt[scene_id] = True
+                scene_io.write_checkpoint(ckpt_path, ckpt)
+    if dist_ctx is not None:
+        dist_ctx.finalize()
+    return 0

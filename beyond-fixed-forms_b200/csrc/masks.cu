@@ -117,9 +117,13 @@ __global__ void rows_or_reduce_kernel(const uint32_t *__restrict__ rows, long lo
 // Every thread owns one word column and replays the host-built program rows[dst] &= ~rows[src]
 // in order (projection_2d_to_3d.py:295-299). Columns are independent because the update is
 // element-wise. Rows are cached in shared memory when they fit.
+template <bool OR_INTO>
+__device__ __forceinline__ uint32_t row_step(uint32_t dst, uint32_t src) { return OR_INTO ? (dst | src) : (dst & ~src); }
+
+template <bool OR_INTO>
 __global__ void __launch_bounds__(128)
-overlap_resolve_kernel(uint32_t *__restrict__ rows, int n_rows, long long words,
-                       const int32_t *__restrict__ prog, int n_steps, int use_smem) {
+row_program_kernel(uint32_t *__restrict__ rows, int n_rows, long long words,
+                   const int32_t *__restrict__ prog, int n_steps, int use_smem) {
     extern __shared__ uint32_t s_col[];   // n_rows x 128
     const long long w = (long long)blockIdx.x * 128 + threadIdx.x;
     if (w >= words) return;
@@ -127,13 +131,13 @@ overlap_resolve_kernel(uint32_t *__restrict__ rows, int n_rows, long long words,
         for (int r = 0; r < n_rows; ++r) s_col[r * 128 + threadIdx.x] = rows[(long long)r * words + w];
         for (int k = 0; k < n_steps; ++k) {
             const int dst = __ldg(prog + 2 * k), src = __ldg(prog + 2 * k + 1);
-            s_col[dst * 128 + threadIdx.x] &= ~s_col[src * 128 + threadIdx.x];
+            s_col[dst * 128 + threadIdx.x] = row_step<OR_INTO>(s_col[dst * 128 + threadIdx.x], s_col[src * 128 + threadIdx.x]);
         }
         for (int r = 0; r < n_rows; ++r) rows[(long long)r * words + w] = s_col[r * 128 + threadIdx.x];
     } else {
         for (int k = 0; k < n_steps; ++k) {
             const int dst = __ldg(prog + 2 * k), src = __ldg(prog + 2 * k + 1);
-            rows[(long long)dst * words + w] &= ~rows[(long long)src * words + w];
+            rows[(long long)dst * words + w] = row_step<OR_INTO>(rows[(long long)dst * words + w], rows[(long long)src * words + w]);
         }
     }
 }
@@ -260,19 +264,30 @@ extern "C" int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int
     return BFF_OK;
 }
 
+template <bool OR_INTO>
+static int run_row_program(const char *name, uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+                           int32_t n_steps, cudaStream_t stream) {
+    BFF_REQUIRE(n_rows >= 0 && words >= 0 && n_steps >= 0, "%s: negative size", name);
+    if (n_rows == 0 || words == 0 || n_steps == 0) return BFF_OK;
+    BFF_REQUIRE(rows && prog, "%s: null pointer", name);
+    const size_t smem = (size_t)n_rows * 128 * 4;
+    // the shared-memory column cache pays off when the program revisits rows; it must also fit
+    const int use_smem = smem <= 160 * 1024 && n_steps >= n_rows;
+    if (use_smem)
+        BFF_CUDA(cudaFuncSetAttribute((const void *)row_program_kernel<OR_INTO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    row_program_kernel<OR_INTO><<<(unsigned)ceil_div64(words, 128), 128, use_smem ? smem : 0, stream>>>(rows, n_rows, words, prog, n_steps, use_smem);
+    BFF_LAUNCH_CHECK(name);
+    return BFF_OK;
+}
+
 extern "C" int bff_overlap_resolve(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
                                    int32_t n_steps, void *stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    BFF_REQUIRE(n_rows >= 0 && words >= 0 && n_steps >= 0, "bff_overlap_resolve: negative size");
-    if (n_rows == 0 || words == 0 || n_steps == 0) return BFF_OK;
-    BFF_REQUIRE(rows && prog, "bff_overlap_resolve: null pointer");
-    const size_t smem = (size_t)n_rows * 128 * 4;
-    const int use_smem = smem <= 160 * 1024;
-    if (use_smem)
-        BFF_CUDA(cudaFuncSetAttribute((const void *)overlap_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    overlap_resolve_kernel<<<(unsigned)ceil_div64(words, 128), 128, use_smem ? smem : 0, stream>>>(rows, n_rows, words, prog, n_steps, use_smem);
-    BFF_LAUNCH_CHECK("overlap_resolve_kernel");
-    return BFF_OK;
+    return run_row_program<false>("bff_overlap_resolve", rows, n_rows, words, prog, n_steps, (cudaStream_t)stream_);
+}
+
+extern "C" int bff_rows_or_into(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+                                int32_t n_steps, void *stream_) {
+    return run_row_program<true>("bff_rows_or_into", rows, n_rows, words, prog, n_steps, (cudaStream_t)stream_);
 }
 
 extern "C" int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t words, const uint32_t *keep,

@@ -32,6 +32,12 @@ extern "C" {
 
 #define BFF_VERSION 100
 
+#if defined(__GNUC__)
+#define BFF_API __attribute__((visibility("default")))
+#else
+#define BFF_API
+#endif
+
 typedef enum bff_status {
     BFF_OK = 0,
     BFF_EINVAL = -1,     /* bad argument (null pointer, negative size, unsupported combination) */
@@ -59,7 +65,7 @@ typedef struct bff_lift_desc {
     int64_t n_points;           /* N */
     /* cameras: :370-376 (intrinsics), :422-425 (np.linalg.inv(cam_pose), computed by the caller) */
     const double *pose_inv;     /* (n_frames, 4, 4) row-major float64 inverse poses */
-    const double *intrinsics;   /* (3, 3) row-major float64 */
+    const double *intrinsics;   /* (3, 3) row-major float64; ALWAYS a HOST pointer (passed to the kernel by value) */
     int32_t n_frames;           /* F */
     /* depth: :431-436 */
     const void *depth;          /* (n_frames, height, width) of depth_kind */
@@ -89,79 +95,84 @@ typedef struct bff_lift_desc {
     int32_t reserved;
 } bff_lift_desc;
 
-int bff_version(void);
-const char *bff_last_error(void);
+BFF_API int bff_version(void);
+BFF_API const char *bff_last_error(void);
 
 /* Replaces the per-frame loops of tools/projection_2d_to_3d.py:413-461 and :538-567
  * (compute_projected_pts_tensor :37, compute_visibility_mask_tensor :51,
  * compute_visible_masked_pts_tensor :73, masked_counts/viewed_counts updates) with one launch
  * over all frames. Outputs are fully overwritten. */
-int bff_lift_scene(const bff_lift_desc *desc, void *stream);
+BFF_API int bff_lift_scene(const bff_lift_desc *desc, void *stream);
 
 /* Number of kernels bff_lift_scene launches for this description (for launch accounting). */
-int bff_lift_scene_launches(const bff_lift_desc *desc);
+BFF_API int bff_lift_scene_launches(const bff_lift_desc *desc);
 
 /* Replaces calculate_iou (projection_2d_to_3d.py:149-166) and calculate_iou_between_stages
  * (refinement.py:69-90, before its transpose): a (nA, Wd), b (nB, Wd) packed rows ->
  * inter (nA, nB) int32, pop_a (nA), pop_b (nB) int32, and optionally iou (nA, nB) float32 =
  * f32(I) / ((f32(sA) + f32(sB)) - f32(I)), 0/0 = NaN. b == a computes the square matrix.
  * inter / pop_a / pop_b / iou may each be NULL. */
-int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
+BFF_API int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
                  int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou, void *stream);
 
 /* Replaces the OR-merges of merge_masks (projection_2d_to_3d.py:214-223) and refinement.py:248,269:
  * out[g] = OR over k in [seg[g], seg[g+1]) of rows[idx[k]].  rows (n_rows, words), out (n_groups, words). */
-int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int32_t *idx, const int32_t *seg,
+BFF_API int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int32_t *idx, const int32_t *seg,
                        int32_t n_groups, uint32_t *out, void *stream);
 
 /* Max of masked_counts (per query) and viewed_counts, so the histogram below can be sized:
  * out[0] = max(mc), out[1] = max(vc). vc may be NULL (out[1] = 0). */
-int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, int32_t *out2, void *stream);
+BFF_API int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, int32_t *out2, void *stream);
 
 /* 2-D histogram of (masked_count, viewed_count) pairs: hist[(mc * (vc_bins)) + vc] += 1.
  * The host derives the reference's detected_ratio.unique() / masked_counts.unique()
  * (projection_2d_to_3d.py:512-578) from the non-empty bins. vc may be NULL (vc_bins = 1). hist is overwritten. */
-int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mc_bins, int32_t vc_bins,
+BFF_API int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mc_bins, int32_t vc_bins,
                   uint32_t *hist, void *stream);
 
 /* Per-point keep predicate -> packed bits keep (Wd):
  *  mode 0 (detected ratio, :571-583): keep = mc > 0 && !(f32(mc) / (f32(vc) + 1) < thr)
  *  mode 1 (occurrence, :512-522,583):  keep = mc > 0 && !(f32(mc) < thr)
  *  mode 2 (no filter):                 keep = mc > 0 */
-int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
+BFF_API int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
                    uint32_t *keep, void *stream);
 
 /* solve_overlapping's sequential pass (projection_2d_to_3d.py:295-299) on packed rows, in place.
  * prog (n_steps, 2) int32: step k clears from row prog[k][0] the bits of row prog[k][1]
  * (rows[dst] &= ~rows[src]) in list order; every word column runs the program independently. */
-int bff_overlap_resolve(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+BFF_API int bff_overlap_resolve(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
                         int32_t n_steps, void *stream);
+
+/* The in-place stage-1 merge of refinement.py:230-249 on packed rows: step k does
+ * rows[prog[k][0]] |= rows[prog[k][1]] in list order (later steps see earlier results). */
+BFF_API int bff_rows_or_into(uint32_t *rows, int32_t n_rows, int64_t words, const int32_t *prog,
+                             int32_t n_steps, void *stream);
 
 /* rows[r] &= keep (if keep != NULL, in place) and pop[r] = popcount(rows[r]) afterwards
  * (projection_2d_to_3d.py:592-596). */
-int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t words, const uint32_t *keep,
+BFF_API int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t words, const uint32_t *keep,
                           int32_t *pop, void *stream);
 
 /* bool/uint8 (n_rows, n) <-> packed (n_rows, ceil(n/32)). Non-zero bytes are set bits. */
-int bff_pack_bits(const uint8_t *dense, int32_t n_rows, int64_t n, uint32_t *packed, void *stream);
-int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n, uint8_t *dense, void *stream);
+BFF_API int bff_pack_bits(const uint8_t *dense, int32_t n_rows, int64_t n, uint32_t *packed, void *stream);
+BFF_API int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n, uint8_t *dense, void *stream);
 
 /* RLE -> packed bits without a dense intermediate (rle_decode_batch, rle_encode_decode.py:35-61;
  * rle_decode, refinement.py:26-39). runs (n_runs, 3) int32 = [row, lo, hi) already clipped to
  * [0, length] by the host with Python-slice semantics. packed (n_rows, words) is overwritten. */
-int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_rows, int64_t words,
+BFF_API int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_rows, int64_t words,
                     uint32_t *packed, void *stream);
 
 /* ---- host-buffer entry points (what a ctypes/numpy binding in the reference would call) ---- */
 typedef struct bff_ctx bff_ctx;
-int bff_ctx_create(int device, bff_ctx **out);
-void bff_ctx_destroy(bff_ctx *ctx);
+BFF_API int bff_ctx_create(int device, bff_ctx **out);
+BFF_API void bff_ctx_destroy(bff_ctx *ctx);
 /* Same contract as bff_lift_scene with every pointer in HOST memory (pinned or pageable).
  * Copies inputs to the device, runs the kernels, copies rows / counts back, and returns
  * after the outputs are valid. h2d_bytes / d2h_bytes (may be NULL) receive the bytes moved. */
-int bff_lift_scene_host(bff_ctx *ctx, const bff_lift_desc *host_desc, int64_t *h2d_bytes, int64_t *d2h_bytes);
+BFF_API int bff_lift_scene_host(bff_ctx *ctx, const bff_lift_desc *host_desc, int64_t *h2d_bytes, int64_t *d2h_bytes);
 /* Host-buffer form of bff_mask_iou. */
-int bff_mask_iou_host(bff_ctx *ctx, const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b,
+BFF_API int bff_mask_iou_host(bff_ctx *ctx, const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b,
                       int64_t words, int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou,
                       int64_t *h2d_bytes, int64_t *d2h_bytes);
 
