@@ -1,0 +1,483 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the BeyondFF lifting + refinement hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (our arm; torchrun launches N>1)
+    python bench.py --impl reference --gpus N --steps K ...   (the reference's CPU path, host cores)
+
+A "step" is one pass of the whole hot path over one synthetic ScanNet200-shaped scene
+(BASELINE.json configs[1]: 250k points, 300 frames 640x480, 1 query, 200 stage-1 masks):
+RLE 2D masks -> packed bits, projection + visibility + mask gather + votes for every frame
+(bff_lift_scene), all-pairs IoU + aggregation, point filter, overlap resolution, then the
+stage-1/stage-2 refinement of that scene. `value` = point-view projections (N x F, each
+(frame, point) counted once) per second of the WHOLE step with inputs resident in HBM; `e2e`
+is the same through the host API with pinned host buffers in and the final masks out.
+With N > 1 every rank lifts its own block of 300 frames of one (300 x N)-frame scene
+(weak scaling) and one exchange step follows (NCCL allreduce of votes + allgather of rows).
+
+Only the cpu_baseline / --impl reference legs touch oracle/ (the reference's numpy path
+restated, oracle/reference_port.py); the GPU arm raises if libbff.so is missing.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "beyond-fixed-forms_b200"))
+
+import numpy as np
+import torch
+
+WORKLOADS = {
+    # name: (N points, frames per rank, W, H, stage-1 masks, boxes)   -- BASELINE.json configs
+    "c1": dict(n_points=150_000, n_frames=100, width=640, height=480, n_stage1=50, n_boxes=14),
+    "c2": dict(n_points=250_000, n_frames=300, width=640, height=480, n_stage1=200, n_boxes=14),
+    "tiny": dict(n_points=20_000, n_frames=12, width=320, height=240, n_stage1=20, n_boxes=9),
+}
+QUERY = "office chair"
+
+
+# ----------------------------------------------------------------------------- synthetic inputs
+def build_inputs(workload: str, rank: int, world: int, device, max_frames=None):
+    """In-memory inputs of one scene in the reference's wire formats (RLE 2D masks per frame,
+    uint16 depth, float64 poses/intrinsics, RLE stage-1 masks). Frames [rank*F, (rank+1)*F) of a
+    (F*world)-frame trajectory are rendered on `device` (input fabrication, untimed)."""
+    from bff_b200 import synth
+    from bff_b200.refine import STAGE1_CLASS_NAMES
+    from bff_b200.rle import rle_encode_rows
+    w = WORKLOADS[workload]
+    f_rank = w["n_frames"]
+    n_render = f_rank if max_frames is None else min(max_frames, f_rank)   # the CPU arms only need their sample
+    spec = synth.SceneSpec(n_points=w["n_points"], n_frames=f_rank * world, width=w["width"], height=w["height"],
+                           n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=2000, n_queries=1)
+    sc = synth.make_scene(spec)
+    lo, hi = rank * f_rank, (rank + 1) * f_rank
+    hgt, wid = spec.height, spec.width
+    depth = np.zeros((f_rank, hgt, wid), np.uint16)
+    records = []
+    for f in range(lo, lo + n_render):
+        mm, obj = synth.render_frame(sc, f, device)
+        depth[f - lo] = mm.cpu().numpy().astype(np.uint16)
+        rng = np.random.default_rng(spec.seed * 7919 + f)
+        ms = synth.frame_masks(sc, f, obj.cpu(), 0, rng)
+        if ms:
+            records.append({"frame_id": f"{sc.frame_ids[f]}.jpg",
+                            "segmented_frame_masks": rle_encode_rows(torch.stack(ms).reshape(len(ms), -1)),
+                            "confidences": torch.as_tensor(rng.uniform(0.2, 0.45, len(ms)).astype(np.float32)),
+                            "labels": [QUERY] * len(ms)})
+    rng = np.random.default_rng(spec.seed + 7)
+    m1, c1, conf1 = synth.stage1_masks(sc, [QUERY], STAGE1_CLASS_NAMES, rng)
+    stage1 = {"ins": rle_encode_rows(torch.from_numpy(m1)), "conf": torch.from_numpy(conf1),
+              "final_class": torch.from_numpy(c1)}
+    pinv = np.stack([np.linalg.inv(p) for p in sc.poses[lo:hi]])
+    return dict(spec=spec, xyz=sc.xyz, K=sc.K, poses=sc.poses[lo:hi], pinv=pinv, depth=depth, records=records,
+                frame_ids=[str(i) for i in sc.frame_ids[lo:hi]], stage1=stage1, cfg=dict(synth.DEFAULT_CFG))
+
+
+def fake_similarity(query: str, label: str) -> float:
+    """CLIP text similarity is an INPUT of the path (refinement.py:93-117); a deterministic table stands in."""
+    import hashlib
+    h = int.from_bytes(hashlib.sha1((query + "|" + label).encode()).digest()[:4], "little")
+    return 0.5 + (h % 1000) / 2000.0
+
+
+# ----------------------------------------------------------------------------- our arm
+class GpuScene:
+    """Host-staged (pinned) and device-resident forms of one rank's inputs + the step itself."""
+
+    def __init__(self, inp, device, dist_ctx=None):
+        from bff_b200 import lift as lift_mod, scene_io
+        from bff_b200.rle import runs_for_device
+        self.inp, self.dev, self.dist = inp, device, dist_ctx
+        spec = inp["spec"]
+        self.n, self.h, self.w = spec.n_points, spec.height, spec.width
+        self.f = inp["depth"].shape[0]
+        q = lift_mod.QueryMasks.from_file_records(QUERY, inp["records"])
+        self.q = q
+        self.frame_ids, self.viewed, self.per_frame = lift_mod.plan_frames([q], inp["frame_ids"])
+        order = {fid: i for i, fid in enumerate(inp["frame_ids"])}
+        perm = [order[fid] for fid in self.frame_ids]           # mask frames first, then view-only frames
+        rles, _, offsets = lift_mod.mask_layout(self.per_frame, [q], 0, len(self.frame_ids))
+        runs, length = runs_for_device(rles)
+        assert length == self.h * self.w
+        self.n_masks = len(rles)
+        self.conf_list, self.labels = q.flat_conf_and_labels()
+        s1_runs, s1_len = runs_for_device(list(inp["stage1"]["ins"]))
+        assert s1_len == self.n
+
+        def pin(a):
+            t = torch.from_numpy(np.ascontiguousarray(a))
+            return t.pin_memory() if torch.cuda.is_available() else t
+        x32 = inp["xyz"].astype(np.float32)
+        assert np.array_equal(x32.astype(np.float64), inp["xyz"])
+        x4 = np.zeros((self.n, 4), np.float32)
+        x4[:, :3] = x32
+        # host side (pinned): exactly what bff's loaders hand to the device
+        self.host = dict(xyz=pin(x4), pinv=pin(inp["pinv"][perm]), depth=pin(inp["depth"][perm].view(np.int16)),
+                         runs=pin(runs), offsets=pin(np.asarray(offsets, np.int32)),
+                         viewed=pin(np.asarray(self.viewed, np.uint8)), s1_runs=pin(s1_runs))
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
+        self.devin = None
+        self.stage_ms = {}
+
+    def upload(self):
+        return {k: v.to(self.dev, non_blocking=True) for k, v in self.host.items()}
+
+    def step(self, d, timers=None):
+        """One pass of the hot path on device-resident inputs `d`. Returns the final dict (host)."""
+        from bff_b200 import ops, refine, stage2
+        inp, cfg = self.inp, self.inp["cfg"]
+        ev = (lambda: None) if timers is None else (lambda: timers.append(_event()))
+        ev()
+        masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+        ev()
+        out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
+                             mask_offset=d["offsets"] if self.n_masks else None, frame_viewed=d["viewed"],
+                             depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535))
+        ev()
+        rows, mc, vc = out.rows, out.masked_counts, out.viewed_counts
+        conf_list, labels = self.conf_list, self.labels
+        if self.dist is not None and self.dist.world_size > 1:
+            from bff_b200 import dist as dist_mod
+            rows, mc, vc = dist_mod.exchange(self.dist, rows, self.rows_per_rank, mc, vc)
+            conf_list, labels = self.all_conf, self.all_labels
+        ev()
+        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg)
+        ev()
+        s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
+        p1 = refine.pass1_scene(inp["stage1"], res2, QUERY, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)
+        thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+        final = refine.pass2_scene(p1, QUERY, cfg["refiment_iou_thres"], thr)
+        ev()
+        self.last_stage2 = res2
+        return final
+
+
+def _event():
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def lift_algorithmic_bytes(g: GpuScene) -> int:
+    """per frame 16*N (xyz) + depth bytes*H*W + M_f*H*W/8 + M_f*4*Wd, + 4*N*(1+Q) per scene.
+    Depth is consumed as uint16 here (2 bytes per pixel), which is what the product path feeds."""
+    n, hw = g.n, g.h * g.w
+    wd = (n + 31) // 32
+    return g.f * (16 * n + 2 * hw) + g.n_masks * ((hw + 31) // 32 * 4 + 4 * wd) + 4 * n * 2
+
+
+class ClockSampler:
+    QUERY_FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                    "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY_FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                p = [x.strip() for x in line.split(",")]
+                if len(p) < 6:
+                    continue
+                try:
+                    sm.append(float(p[0]))
+                    mx.append(float(p[1]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, p[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(max(mx))
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def measured_peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload: str):
+    """dram bytes per lift_kernel launch from the committed ncu --set full capture, if one exists."""
+    p = os.path.join(ROOT, "profiles", "lift_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:
+            return None
+    return None
+
+
+def run_gpu(args):
+    from bff_b200 import _cabi, dist as dist_mod
+    _cabi.lib()          # fail loudly when the CUDA library is missing
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (GPU arm) needs a CUDA device; there is no CPU fallback")
+    ctx = dist_mod.init_from_env("nccl")
+    rank, world = (ctx.rank, ctx.world_size) if ctx else (0, 1)
+    local = ctx.local_rank if ctx else 0
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    import torch.distributed as dist
+    inp = build_inputs(args.workload, rank, world, dev)
+    g = GpuScene(inp, dev, ctx)
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (g.n_masks, [float(c) for c in g.conf_list], g.labels))
+        g.rows_per_rank = [x[0] for x in gathered]
+        g.all_conf = [torch.tensor(c) for x in gathered for c in x[1]]
+        g.all_labels = [l for x in gathered for l in x[2]]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    d = g.upload()
+    torch.cuda.synchronize()
+    final = None
+    for _ in range(args.warmup):
+        final = g.step(d)
+        _ = g.step(g.upload())
+    if args.profile:
+        # for `ncu --profile-from-start off`: only these steps are captured; no number is reported
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        for _ in range(args.steps):
+            g.step(d)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        if ctx:
+            ctx.finalize()
+        return
+    # ---- device-resident timing: K steps, each bracketed by events, L2 flushed in between (untimed)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = _cabi.launch_count
+    tot_ms, lift_ms, iou_ms_acc, stage_acc = 0.0, 0.0, 0.0, np.zeros(5)
+    wall0 = time.time()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        tm = []
+        final = g.step(d, tm)
+        torch.cuda.synchronize()
+        ms = [tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)]
+        stage_acc += np.asarray(ms)
+        tot_ms += tm[0].elapsed_time(tm[-1])
+        lift_ms += ms[1]
+    launches = _cabi.launch_count - launches0
+    barrier()
+    wall_dev = time.time() - wall0
+    clocks = sampler.stop() if rank == 0 else None
+    # ---- end to end: pinned host buffers -> device -> step -> final masks on the host
+    e2e_ms = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        barrier()
+        t0 = time.perf_counter()
+        final = g.step(g.upload())
+        torch.cuda.synchronize()
+        e2e_ms += (time.perf_counter() - t0) * 1e3
+    d2h = 0
+    if isinstance(final["ins"], torch.Tensor):
+        d2h = final["ins"].numel() * final["ins"].element_size()
+    # ---- IoU kernel alone (mask-IoU pairs/s of the aggregation-sized square call)
+    from bff_b200 import ops
+    rows = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], g.h, g.w,
+                          masks2d=ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w), mask_offset=d["offsets"]).rows
+    for _ in range(3):
+        ops.mask_iou(rows)
+    torch.cuda.synchronize()
+    e0 = _event()
+    for _ in range(10):
+        ops.mask_iou(rows)
+    e1 = _event()
+    torch.cuda.synchronize()
+    iou_ms = e0.elapsed_time(e1) / 10
+    # ---- reduce over ranks (max time)
+    t = torch.tensor([tot_ms, lift_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tot_ms, lift_ms, e2e_ms = (float(x) for x in t.cpu())
+    if rank != 0:
+        if ctx:
+            ctx.finalize()
+        return
+    k = args.steps
+    pv = g.n * g.f * world
+    ms_step, ms_lift, ms_e2e = tot_ms / k, lift_ms / k, e2e_ms / k
+    peak, peak_src = measured_peak_hbm()
+    alg = lift_algorithmic_bytes(g)
+    achieved = alg / (ms_lift * 1e-3) / 1e9
+    line = {
+        "metric": "point-view projections/sec (whole lifting+aggregation+refinement step)",
+        "value": pv / (ms_step * 1e-3), "unit": "point-views/s", "n_gpus": world, "steps": k, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"{args.workload}: ScanNet200-shaped scene, {g.n} points, {g.f} frames/GPU {g.w}x{g.h}, "
+                               f"1 query, {g.n_masks} lifted 2D masks/GPU, {len(inp['stage1']['ins'])} stage-1 masks",
+                   "n_points": g.n, "frames_per_gpu": g.f, "lifted_masks_per_gpu": g.n_masks,
+                   "parallelism": f"frame-sharded x{world}" if world > 1 else "single GPU",
+                   "l2": "256 MB flush written between timed steps; per-step inputs are 211 MB (> 126 MB L2)"},
+        "stages_ms": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
+                              (stage_acc / k).round(4).tolist())),
+        "lift_point_views_per_s": pv / (ms_lift * 1e-3),
+        "iou_pairs_per_s": (rows.shape[0] ** 2) / (iou_ms * 1e-3), "iou_call": f"{rows.shape[0]}x{rows.shape[0]} rows x {g.n} points, {iou_ms:.4f} ms",
+        "e2e": {"value": pv / (ms_e2e * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": int(g.h2d_bytes),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "bff::lift_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms_lift},
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(inp, args.cpu_frames)
+    print(json.dumps(line), flush=True)
+    if ctx:
+        ctx.finalize()
+
+
+# ----------------------------------------------------------------------------- CPU baseline (oracle port)
+def cpu_frames_of(inp, n_frames):
+    """First n_frames of the rank's block as the reference's per-frame inputs (dense float32 masks/depth)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import reference_port as RP
+    by_frame = {r["frame_id"][:-4]: r for r in inp["records"]}
+    hgt, wid = inp["spec"].height, inp["spec"].width
+    mask_frames, view_frames = [], []
+    for i, fid in enumerate(inp["frame_ids"][:n_frames]):
+        depth = inp["depth"][i].astype(np.float32) / 1000
+        fr = {"pose": inp["poses"][i], "depth": depth}
+        view_frames.append(fr)
+        if fid in by_frame:
+            r = by_frame[fid]
+            masks = np.stack([RP.rle_to_mask(m).reshape(hgt, wid) for m in r["segmented_frame_masks"]]).astype(np.float32)
+            mask_frames.append(dict(fr, masks=masks, conf=r["confidences"], labels=r["labels"]))
+    return mask_frames, view_frames
+
+
+def cpu_step(inp, mask_frames, view_frames):
+    """The reference's path for one scene on the CPU (numpy/OpenBLAS + torch CPU, oracle/reference_port.py)."""
+    import reference_port as RP
+    from bff_b200.refine import STAGE1_CLASS_NAMES
+    cfg = inp["cfg"]
+    res2 = RP.stage2_scene(inp["xyz"], inp["K"], mask_frames, view_frames, cfg)
+    s1 = torch.from_numpy(np.stack([RP.rle_to_mask(r) for r in inp["stage1"]["ins"]]))
+    labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
+    p1 = RP.refine_pass1(s1, labels, res2, QUERY, cfg["stage1_iou_thres"], fake_similarity)
+    thr = RP.sim_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+    return RP.refine_pass2(p1, QUERY, cfg["refiment_iou_thres"], thr)
+
+
+def cpu_baseline(inp, n_frames):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n_frames = min(n_frames, inp["depth"].shape[0])
+    mask_frames, view_frames = cpu_frames_of(inp, n_frames)
+    t0 = time.perf_counter()
+    cpu_step(inp, mask_frames, view_frames)
+    dt = time.perf_counter() - t0
+    n = inp["spec"].n_points
+    return {"value": n * n_frames / dt, "unit": "point-views/s", "cores": cores, "kind": "port",
+            "sample": f"first {n_frames} of {inp['depth'].shape[0]} frames of the same scene ({n} points), whole path "
+                      f"(lift + viewed pass + aggregate + filter + refine), {dt:.2f} s, oracle/reference_port.py "
+                      "(numpy/OpenBLAS + torch CPU like the reference)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port) on the host cores, same metric and config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # input fabrication only
+    inp = build_inputs(args.workload, 0, 1, dev, max_frames=args.cpu_frames)
+    n_frames = min(args.cpu_frames, inp["depth"].shape[0])
+    mask_frames, view_frames = cpu_frames_of(inp, n_frames)
+    for _ in range(min(args.warmup, 1)):
+        cpu_step(inp, mask_frames[:2], view_frames[:2])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_step(inp, mask_frames, view_frames)
+    dt = (time.perf_counter() - t0) / args.steps
+    n = inp["spec"].n_points
+    v = n * n_frames / dt
+    sample = (f"each step = first {n_frames} of {inp['depth'].shape[0]} frames of the scene ({n} points), whole path; "
+              "oracle/reference_port.py (numpy/OpenBLAS + torch CPU)")
+    print(json.dumps({
+        "impl": "reference", "metric": "point-view projections/sec (whole lifting+aggregation+refinement step)",
+        "value": v, "unit": "point-views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": f"{args.workload} (bounded sample: {n_frames} frames per step)"},
+        "cpu_baseline": {"value": v, "unit": "point-views/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "point-views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-frames", type=int, default=40, help="frames in the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

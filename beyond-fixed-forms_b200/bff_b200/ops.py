@@ -258,13 +258,19 @@ def unpack_bits(packed: torch.Tensor, n: int) -> torch.Tensor:
     return out.view(torch.bool)
 
 
-def rle_to_bits(runs: np.ndarray, n_rows: int, length: int, device) -> torch.Tensor:
-    """runs (R,3) int32 [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32 on `device`."""
-    runs = np.ascontiguousarray(runs, dtype=np.int32).reshape(-1, 3)
+def rle_to_bits_dev(runs: torch.Tensor, n_rows: int, length: int) -> torch.Tensor:
+    """runs (R,3) int32 CUDA [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32."""
+    runs = _cuda(runs, torch.int32, "runs").reshape(-1, 3)
     wd = words_for(length)
-    out = torch.empty((n_rows, wd), dtype=torch.int32, device=device)
-    d_runs = torch.from_numpy(runs).to(device) if runs.shape[0] else None
-    check(lib().bff_rle_to_bits(ptr(d_runs), runs.shape[0], n_rows, wd, ptr(out), current_stream()), "bff_rle_to_bits")
+    out = torch.empty((n_rows, wd), dtype=torch.int32, device=runs.device)
+    check(lib().bff_rle_to_bits(ptr(runs) if runs.shape[0] else None, runs.shape[0], n_rows, wd, ptr(out),
+                                current_stream()), "bff_rle_to_bits")
     if n_rows and wd and runs.shape[0]:
         _count()
     return out
+
+
+def rle_to_bits(runs: np.ndarray, n_rows: int, length: int, device) -> torch.Tensor:
+    """runs (R,3) int32 host [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32 on `device`."""
+    runs = np.ascontiguousarray(runs, dtype=np.int32).reshape(-1, 3)
+    return rle_to_bits_dev(torch.from_numpy(runs).to(device), n_rows, length)

@@ -39,10 +39,11 @@ def stage1_rows(stage1: dict, device) -> torch.Tensor:
 
 
 def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
-                sim_fn: Callable[[str, str], float], device) -> dict:
-    """Pass 1 for one scene (refinement.py:182-312). Returns packed rows + the small vectors pass 2 needs."""
+                sim_fn: Callable[[str, str], float], device, s1_rows: Optional[torch.Tensor] = None) -> dict:
+    """Pass 1 for one scene (refinement.py:182-312). Returns packed rows + the small vectors pass 2 needs.
+    `s1_rows`: the stage-1 masks already decoded to packed rows on the device (modified in place)."""
     q_ = query.replace(" ", "_")
-    s1 = stage1_rows(stage1, device)
+    s1 = stage1_rows(stage1, device) if s1_rows is None else s1_rows
     n_points = int(stage1["ins"][0]["length"]) if len(stage1["ins"]) else 0
     labels = [idx_to_label(i) for i in stage1["final_class"]]
     if len(stage2["conf"]) == 0:
