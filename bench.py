@@ -185,8 +185,11 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY_FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+            t0 = time.time()                       # nvidia-smi needs a moment before its first sample
+            while time.time() - t0 < 5.0 and os.path.getsize(self.path) == 0:
+                time.sleep(0.02)
         except Exception:
             self.proc = None
 
@@ -292,9 +295,9 @@ def run_gpu(args):
         return
     # ---- device-resident timing: K steps, each bracketed by events, L2 flushed in between (untimed)
     sampler = ClockSampler(local)
-    barrier()
     if rank == 0:
         sampler.start()
+    barrier()
     launches0 = _cabi.launch_count
     tot_ms, lift_ms, iou_ms_acc, stage_acc = 0.0, 0.0, 0.0, np.zeros(5)
     wall0 = time.time()
@@ -463,7 +466,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))

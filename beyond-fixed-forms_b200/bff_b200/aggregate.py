@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from . import ops
+from ._log import log
 
 
 def label_equality(labels: Sequence[str]) -> torch.Tensor:
@@ -61,7 +62,7 @@ def aggregate_rows(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str]
     _, _, _, iou = ops.mask_iou(rows)                           # K7: popcount intersections, exact fp32 IoU
     merge = label_equality(labels) & (iou.cpu() > iou_thres)    # python float vs f32 tensor: torch semantics
     groups = [g for g in connected_groups(merge) if len(g) >= min_members]
-    print("masks_to_be_merged", groups)
+    log("masks_to_be_merged", groups)
     used = [g for g in groups if g != []]
     if not used:
         return None, None, [], []
@@ -91,7 +92,7 @@ def keep_points(mc: torch.Tensor, vc: Optional[torch.Tensor], cfg) -> torch.Tens
         ratio = nz[:, 0].to(torch.float32) / (nz[:, 1].to(torch.float32) + 1)   # :571 in float32
         u = ratio.unique()
         t = u[math.floor(cfg["detected_ratio_threshold"] * u.shape[0])]
-        print("detected_ratio_thres_value", t)
+        log("detected_ratio_thres_value", t)
         return ops.point_keep(mc, vc, 0, float(t))
     return ops.point_keep(mc, None, 2, 0.0)
 
@@ -125,6 +126,6 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
     idx = torch.nonzero(sel).reshape(-1)
     out_rows = agg[idx.to(agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
-    print("after filtering", ins.shape)
+    log("after filtering", ins.shape)
     result = {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
     return result, out_rows

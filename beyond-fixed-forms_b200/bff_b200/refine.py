@@ -9,7 +9,8 @@ from typing import Callable, Dict, List, Optional, Sequence
 import numpy as np
 import torch
 
-from . import ops, scene_io
+from . import _log, ops, scene_io
+from ._log import log
 from .rle import runs_for_device
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -47,7 +48,7 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
     n_points = int(stage1["ins"][0]["length"]) if len(stage1["ins"]) else 0
     labels = [idx_to_label(i) for i in stage1["final_class"]]
     if len(stage2["conf"]) == 0:
-        print("Empty stage 2 mask")
+        log("Empty stage 2 mask")
         other = [i for i, l in enumerate(labels) if l == q_]
         return {"ious": [], "sims": [], "m1": None, "m2": None, "conf2": [], "n_points": n_points,
                 "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
@@ -71,7 +72,7 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
                 redirect[j] = i
                 or_prog.append((int(mm[i]), int(mm[j])))
     ops.rows_or_into(s1, or_prog)
-    print("DEBUG best_match_after_iou_check", best)
+    log("DEBUG best_match_after_iou_check", best)
     best = torch.tensor(best)
     uniq, cnt = torch.unique(best, return_counts=True)                        # :258
     for u, c in zip(uniq, cnt):
@@ -90,9 +91,9 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
     matched_labels = [labels[k] for k in mm]
     sims = [float(sim_fn(query, l)) for l in matched_labels]                   # :297-302
     ious = iou[range(len(mm)), mm]
-    print("iou for matched labels", ious)
-    print("Matched labels:", matched_labels)
-    print("Clip similarities:", sims)
+    log("iou for matched labels", ious)
+    log("Matched labels:", matched_labels)
+    log("Clip similarities:", sims)
     return {"ious": ious, "sims": sims, "m1": s1[mm.to(device)], "m2": s2, "conf2": s2_conf, "n_points": n_points,
             "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
 
@@ -101,7 +102,7 @@ def similarity_threshold(all_sims: Sequence[Sequence[float]], percentile: float)
     """Global over the scenes of the class (refinement.py:317-324). Raises IndexError like the
     reference when no scene produced a match."""
     u = sorted(set(s for sims in all_sims for s in sims))
-    print("Unique similarities:", u)
+    log("Unique similarities:", u)
     return u[int(len(u) * percentile)]
 
 
@@ -173,7 +174,7 @@ def refine_class(cfg, cls: str, device, sim_fn: Callable[[str, str], float]):
     for s, fn in enumerate(stage2_files):
         scene_id = fn.replace(".pth", "")
         p1 = per_scene[s]                                                      # positional, like the reference
-        print("DEBUG all ious", p1["ious"])
+        log("DEBUG all ious", p1["ious"])
         out = pass2_scene(p1, cls, g("refiment_iou_thres"), sim_thres)
         scene_io.save_result(out, g("final_output_dir"), cls, scene_id)
         if len(p1["ious"]) != 0 and len(out["final_class"]) != 0:
@@ -189,10 +190,11 @@ def main(argv=None):
     parser.add_argument("--config", type=str, required=True, help="Config")
     parser.add_argument("--cls", type=str, required=True, help="Class")
     args = parser.parse_args(argv)
+    _log.VERBOSE = True
     cfg = yaml.safe_load(open(args.config, "r").read())
     if not torch.cuda.is_available():
         raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
     device = torch.device("cuda", 0)
-    print("Processing class:", args.cls.replace(" ", "_"))
+    log("Processing class:", args.cls.replace(" ", "_"))
     refine_class(cfg, args.cls, device, ClipTextSimilarity(device))
     return 0

@@ -7,7 +7,8 @@ from typing import Optional
 
 import torch
 
-from . import aggregate, lift as lift_mod, scene_io
+from . import _log, aggregate, lift as lift_mod, scene_io
+from ._log import log
 
 
 def cfg_get(cfg, key):
@@ -28,15 +29,15 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
                                       "if_detected_ratio_threshold", "detected_ratio_threshold", "remove_filtered_masks",
                                       "remove_small_masks")}
     if len(conf_list) == 0:
-        print("No 3d masks detected in backprojection!")
+        log("No 3d masks detected in backprojection!")
         return scene_io.empty_stage2(), False
     conf = torch.tensor(conf_list)                                  # :484-486
     agg, conf_agg, labels_agg, groups = aggregate.aggregate_rows(rows, conf, labels, c["iou_thres"], c["min_aggragated_masks"])
     if agg is None:
-        print("No 3d masks detected after aggregation")
+        log("No 3d masks detected after aggregation")
         return scene_io.empty_stage2(), False
     keep = aggregate.keep_points(mc, vc, c)
-    print("before filtering", torch.Size([agg.shape[0], n_points]))
+    log("before filtering", torch.Size([agg.shape[0], n_points]))
     result, _ = aggregate.filter_and_select(agg, conf_agg, labels_agg, groups, keep, n_points, c)
     return result, True
 
@@ -47,7 +48,7 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
     from . import dist as dist_mod
     width, height = int(cfg_get(cfg, "width_2d")), int(cfg_get(cfg, "height_2d"))
     scene_2d_dir = cfg_get(cfg, "scene_2d_dir")
-    print("Working on", scene_id, "class", cls)
+    log("Working on", scene_id, "class", cls)
     intr = scene_io.load_intrinsics(scene_2d_dir, scene_id)
     xyz = scene_io.load_cloud(cfg_get(cfg, "scene_npy_dir"), scene_id)
     records = scene_io.torch_load(os.path.join(cfg_get(cfg, "mask_2d_dir"), cls, f"{scene_id}.pth"))
@@ -77,6 +78,7 @@ def main(argv=None):
     parser.add_argument("--config", type=str, required=True, help="Config")
     parser.add_argument("--cls", type=str, required=True, help="Class")
     args = parser.parse_args(argv)
+    _log.VERBOSE = True
     cfg = yaml.safe_load(open(args.config, "r").read())
     if not torch.cuda.is_available():
         raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
