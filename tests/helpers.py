@@ -74,3 +74,89 @@ def random_scene(seed, n=5000, f=7, h=60, w=80, m_per_frame=(0, 1, 2, 3), n_quer
     return dict(xyz=xyz, K=K, poses=poses, pinv=np.stack([np.linalg.inv(p) for p in poses]), depth=depth,
                 masks=masks, mask_off=np.asarray(off, np.int32), mask_query=np.asarray(query, np.int32),
                 h=h, w=w, n=n, f=f, n_queries=n_queries)
+
+
+# ----------------------------------------------------------------------------- golden tree helpers
+def load_expected():
+    import os
+    import torch
+    from conftest import GOLDEN
+    return torch.load(os.path.join(GOLDEN, "e2e.pth"), weights_only=False)
+
+
+def copy_tree(tmp_path):
+    """A writable copy of tests/golden/tree (the CLIs write outputs and checkpoints under cwd)."""
+    import os
+    import shutil
+    from conftest import GOLDEN
+    dst = os.path.join(str(tmp_path), "tree")
+    shutil.copytree(os.path.join(GOLDEN, "tree"), dst)
+    os.makedirs(os.path.join(dst, "checkpoints"), exist_ok=True)
+    return dst
+
+
+def fake_clip_sim(query, label):
+    """What refinement.py:93-117 computes with the fake `clip` of oracle/run_reference.py."""
+    import run_reference as RR
+    a, b = RR.fake_clip_similarity_vector(query), RR.fake_clip_similarity_vector(label)
+    sim = a @ b.T
+    sim = sim / (a.norm(dim=-1, keepdim=True) * b.norm(dim=-1, keepdim=True).T)
+    return sim.item()
+
+
+def check_against_expected(result, rec, what):
+    """result: dict as saved; rec: record of oracle/make_golden.py:_pack_result."""
+    import torch
+    assert list(result["final_class"]) == rec["final_class"], what
+    if rec["ins_dtype"] == "list":
+        assert isinstance(result["ins"], list) and len(result["ins"]) == 0, what
+        assert isinstance(result["conf"], list) and len(result["conf"]) == 0, what
+        return
+    ins = result["ins"]
+    assert isinstance(ins, torch.Tensor) and tuple(ins.shape) == rec["ins_shape"], (what, ins.shape, rec["ins_shape"])
+    assert str(ins.dtype) == rec["ins_dtype"], (what, ins.dtype)
+    if ins.numel():
+        exp = np.unpackbits(rec["ins_bits"], axis=1)[:, :ins.shape[1]].astype(bool)
+        np.testing.assert_array_equal(ins.cpu().numpy().astype(bool), exp, err_msg=what)       # bit-exact masks
+    conf = result["conf"]
+    assert isinstance(conf, torch.Tensor) == rec["conf_is_tensor"], what
+    np.testing.assert_allclose(np.asarray(conf, dtype=np.float32), np.asarray(rec["conf"], dtype=np.float32),
+                               rtol=1e-5, err_msg=what)                                      # north_star tolerance
+
+
+def port_run_class(cfg, cls):
+    """oracle/reference_port.py driven over an on-disk tree like the reference's two CLIs.
+    Returns ({scene: stage-2 dict}, {scene: final dict}). cwd must be the tree root."""
+    import os
+    import torch
+    import reference_port as RP
+    from bff_b200 import scene_io
+    from bff_b200.refine import STAGE1_CLASS_NAMES
+    h, w = cfg["height_2d"], cfg["width_2d"]
+    seg_dir = os.path.join(cfg["mask_2d_dir"], cls)
+    stage2, finals, p1s = {}, {}, []
+    scenes = sorted(s[:-4] for s in os.listdir(seg_dir) if s.endswith("_00.pth"))
+    for sid in scenes:
+        K = scene_io.load_intrinsics(cfg["scene_2d_dir"], sid)
+        xyz = scene_io.load_cloud(cfg["scene_npy_dir"], sid)
+
+        def frame(fid):
+            pose = np.loadtxt(os.path.join(cfg["scene_2d_dir"], sid, "pose", f"{fid}.txt"))
+            depth = scene_io.depth_to_metres(scene_io.load_depth_raw(cfg["scene_2d_dir"], sid, fid), w, h)
+            return {"pose": pose, "depth": depth}
+        mask_frames = []
+        for r in scene_io.torch_load(os.path.join(seg_dir, f"{sid}.pth")):
+            fr = frame(r["frame_id"][:-4])
+            fr["masks"] = np.stack([RP.rle_to_mask(m).reshape(h, w) for m in r["segmented_frame_masks"]]).astype(np.float32)
+            fr["conf"], fr["labels"] = r["confidences"], r["labels"]
+            mask_frames.append(fr)
+        view = [frame(f) for f in scene_io.list_view_frames(cfg["scene_2d_dir"], sid, cfg["downsample_ratio"])]
+        stage2[sid] = RP.stage2_scene(xyz, K, mask_frames, view, cfg)
+        s1 = scene_io.torch_load(os.path.join(cfg["stage_1_results_dir"], f"{sid}.pth"))
+        s1_ins = torch.from_numpy(np.stack([RP.rle_to_mask(r) for r in s1["ins"]]))
+        labels = [STAGE1_CLASS_NAMES[int(i)] for i in s1["final_class"]]
+        p1s.append(RP.refine_pass1(s1_ins, labels, stage2[sid], cls, cfg["stage1_iou_thres"], fake_clip_sim))
+    thr = RP.sim_threshold([p["sims"] for p in p1s], cfg["refinment_sim_percentile"])
+    for sid, p1 in zip(scenes, p1s):
+        finals[sid] = RP.refine_pass2(p1, cls, cfg["refiment_iou_thres"], thr)
+    return stage2, finals

@@ -1,0 +1,37 @@
+"""GPU: the drop-in CLIs (tools/projection_2d_to_3d.py, tools/refinement.py -> bff_b200.stage2/refine.main)
+run on the committed input tree must write the same .pth files as the UNMODIFIED reference CLIs did
+(tests/golden/e2e.pth, made by oracle/make_golden.py): instance masks bit-exact, final_class equal,
+confidences within 1e-5 relative, empty forms identical."""
+import os
+
+import pytest
+import torch
+
+from helpers import check_against_expected, copy_tree, load_expected
+
+pytestmark = pytest.mark.gpu
+
+
+def _install_fake_clip():
+    # CLIP is an input of the path; the same deterministic fake the goldens were made with
+    import run_reference as RR
+    RR._install_stubs()
+
+
+@pytest.mark.parametrize("cfg_name,out2,outf", [("config.yaml", "output/mask_3d", "output/final_output"),
+                                                 ("config_occ.yaml", "output_occ/mask_3d", "output_occ/final_output")])
+@pytest.mark.parametrize("cls", ["office chair", "table"])
+def test_cli_outputs_match_reference(cuda_dev, tmp_path, monkeypatch, cfg_name, out2, outf, cls):
+    from bff_b200 import refine, stage2
+    tree = copy_tree(tmp_path)
+    monkeypatch.chdir(tree)
+    _install_fake_clip()
+    expected = load_expected()
+    assert stage2.main(["--config", cfg_name, "--cls", cls]) == 0
+    assert refine.main(["--config", cfg_name, "--cls", cls]) == 0
+    for sid in ("scene0001_00", "scene0002_00", "scene0003_00"):
+        got2 = torch.load(os.path.join(tree, out2, cls, f"{sid}.pth"), weights_only=False)
+        gotf = torch.load(os.path.join(tree, outf, cls, f"{sid}.pth"), weights_only=False)
+        check_against_expected(got2, expected[(cfg_name, cls, "mask_3d", sid)], f"stage2 {cls} {sid}")
+        check_against_expected(gotf, expected[(cfg_name, cls, "final", sid)], f"final {cls} {sid}")
+    assert os.path.exists(os.path.join(tree, "checkpoints", f"projection_2d_to_3d_checkpoint_{cls}.yaml"))
