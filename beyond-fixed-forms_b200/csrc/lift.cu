@@ -24,7 +24,13 @@
 namespace bff {
 
 constexpr int kLiftThreads = 256;
-constexpr int kMaxFramesPerChunk = 256;
+constexpr int kMaxFramesPerChunk = 256;   // <= kLiftThreads: one thread prepares one frame's culling planes
+// Per-frame culling data in shared memory (structure of arrays, index [k * fc + frame]):
+//   0..5   camera-z as a function of the world point: n(3), d, |n|(1+eps), eps|d|
+//   6..25  four image-border planes (left, right, top, bottom), each n(3), d(+slack), |n|(1+eps)
+constexpr int kPlaneDoubles = 26;
+constexpr int kFrameSmemBytes = 128 + kPlaneDoubles * 8 + 8;   // + mask offset and viewed flag (2 ints)
+constexpr int kChunkSmemExtra = 8;                              // the (fc+1)-th mask offset, padded
 
 struct LiftParams {
     const void *xyz;
@@ -61,12 +67,114 @@ __device__ __forceinline__ long long f64_to_i64_numpy(double v) {
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// ---------------------------------------------------------------------------------------------
+// Conservative warp-level culling. It only ever SKIPS work whose result is known: a (point, frame)
+// pair can be visible only if (a) its camera z lies in (z_lo, z_hi) -- the window around the non-zero
+// depths of the frame set -- and (b) its pixel rounds into the image, i.e. for z > 0:
+//   -0.5 <= q0/z <= W-0.5  and  -0.5 <= q1/z <= H-0.5   (q = K @ p_cam, projection_2d_to_3d.py:43-47).
+// Both are linear in the world point, so a sphere (c, r) around the warp's 32 points is entirely
+// outside when  n.c + d + |n| r < 0  for one of the planes. The planes are padded by half a pixel
+// ([-1, W] instead of [-0.5, W-0.5]) and every bound carries a 1e-9 relative slack, 7 orders of
+// magnitude above fp64 rounding; NaN/inf make every comparison false, i.e. "do not cull".
+constexpr double kCullEps = 1e-9;
+
+__device__ __forceinline__ void store_plane(double *dst, int fc, int k, double ax, double ay, double az, const double *P) {
+    // camera-space functional a.p_cam  ->  world-space n.p + d with p_cam = R p + t (rows 0..2 of inv(pose))
+    const double n0 = ax * P[0] + ay * P[4] + az * P[8];
+    const double n1 = ax * P[1] + ay * P[5] + az * P[9];
+    const double n2 = ax * P[2] + ay * P[6] + az * P[10];
+    const double d = ax * P[3] + ay * P[7] + az * P[11];
+    dst[(k + 0) * fc] = n0;
+    dst[(k + 1) * fc] = n1;
+    dst[(k + 2) * fc] = n2;
+    dst[(k + 3) * fc] = d + kCullEps * fabs(d);
+    dst[(k + 4) * fc] = sqrt(n0 * n0 + n1 * n1 + n2 * n2) * (1.0 + kCullEps);
+}
+
+__device__ __forceinline__ void build_frame_planes(const double *P, const LiftParams &p, double *dst, int fc) {
+    const double nz = sqrt(P[8] * P[8] + P[9] * P[9] + P[10] * P[10]) * (1.0 + kCullEps);
+    dst[0 * fc] = P[8];
+    dst[1 * fc] = P[9];
+    dst[2 * fc] = P[10];
+    dst[3 * fc] = P[11];
+    dst[4 * fc] = nz;
+    dst[5 * fc] = kCullEps * fabs(P[11]);
+    const double W = (double)p.width, H = (double)p.height;
+    store_plane(dst, fc, 6, p.k[0], p.k[1], p.k[2] + 1.0, P);          // q0 + z >= 0      (u >= -1)
+    store_plane(dst, fc, 11, -p.k[0], -p.k[1], W - p.k[2], P);         // W z - q0 >= 0    (u <= W)
+    store_plane(dst, fc, 16, p.k[3], p.k[4], p.k[5] + 1.0, P);         // q1 + z >= 0      (v >= -1)
+    store_plane(dst, fc, 21, -p.k[3], -p.k[4], H - p.k[5], P);         // H z - q1 >= 0    (v <= H)
+}
+
+__device__ __forceinline__ double warp_min(double v) {
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Sphere (centre of the bounding box, radius to the farthest point) of the valid lanes' points.
+// The radius is inflated so that n.c evaluated in floating point stays an upper bound (|n.c| error
+// <= eps |n| (|cx|+|cy|+|cz|)). Returns false when the warp holds no point at all.
+__device__ __forceinline__ bool warp_sphere(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr) {
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    const double lx = warp_min(valid ? x : inf), hx = warp_max(valid ? x : -inf);
+    const double ly = warp_min(valid ? y : inf), hy = warp_max(valid ? y : -inf);
+    const double lz = warp_min(valid ? z : inf), hz = warp_max(valid ? z : -inf);
+    cx = 0.5 * lx + 0.5 * hx;
+    cy = 0.5 * ly + 0.5 * hy;
+    cz = 0.5 * lz + 0.5 * hz;
+    const double dx = x - cx, dy = y - cy, dz = z - cz;
+    const double d2 = warp_max(valid ? (dx * dx + dy * dy + dz * dz) : 0.0);
+    cr = sqrt(d2) * (1.0 + kCullEps) + kCullEps * (fabs(cx) + fabs(cy) + fabs(cz));
+    return __any_sync(0xffffffffu, valid);
+}
+
+__device__ __forceinline__ bool warp_may_see(const double *pl, int fc, double cx, double cy, double cz, double cr,
+                                             double z_lo, double z_hi) {
+    const double zc = pl[0 * fc] * cx + pl[1 * fc] * cy + pl[2 * fc] * cz + pl[3 * fc];
+    const double zr = pl[4 * fc] * cr + pl[5 * fc];
+    if (zc + zr < z_lo || zc - zr > z_hi) return false;      // no depth value can match anywhere in the sphere
+    if (zc - zr > 0.0) {                                      // whole sphere in front of the camera: border planes apply
+#pragma unroll
+        for (int k = 6; k < kPlaneDoubles; k += 5) {
+            const double v = pl[k * fc] * cx + pl[(k + 1) * fc] * cy + pl[(k + 2) * fc] * cz + pl[(k + 3) * fc];
+            if (v + pl[(k + 4) * fc] * cr < 0.0) return false;
+        }
+    }
+    return true;
+}
+
+// rint(q0/z), rint(q1/z) without the two IEEE divisions whenever that is provably the same integer:
+// one approximate reciprocal refined by two Newton steps (relative error ~2^-50), then u = q0 * r. The
+// correctly rounded quotient and u differ by < 1e-10 for |u| < 65536, so both round to the same integer
+// unless u lies within 1e-8 of a half-integer -- then (and for NaN/inf/huge values) the caller divides
+// exactly. Pixel indices stay bit-exact; the divisions disappear from > 99.9999 % of the lanes.
+__device__ __forceinline__ bool fast_rounded_quotients(double q0, double q1, double z, double &xr, double &yr) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(z));
+    double e = fma(-z, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-z, r, 1.0);
+    r = fma(r, e, r);
+    const double u = q0 * r, v = q1 * r;
+    xr = rint(u);
+    yr = rint(v);
+    const double lim = 0.5 - 1e-8;
+    return (fabs(u) < 65536.0) && (fabs(v) < 65536.0) && (fabs(u - xr) < lim) && (fabs(v - yr) < lim);
+}
+
 template <int XYZ_KIND, int DEPTH_KIND, bool MULTI_Q, bool DEBUG>
-__global__ void __launch_bounds__(kLiftThreads)
+__global__ void __launch_bounds__(kLiftThreads, 5)
 lift_kernel(const __grid_constant__ LiftParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *s_pose = reinterpret_cast<double *>(smem_raw);                       // fc x 16 doubles
-    int32_t *s_acc = reinterpret_cast<int32_t *>(smem_raw + (size_t)p.frames_per_chunk * 128);  // Q x blockDim (MULTI_Q)
+    double *s_plane = s_pose + (size_t)p.frames_per_chunk * 16;                   // kPlaneDoubles x fc (SoA)
+    int32_t *s_moff = reinterpret_cast<int32_t *>(s_plane + (size_t)p.frames_per_chunk * kPlaneDoubles);  // fc + 2 mask offsets
+    int32_t *s_view = s_moff + p.frames_per_chunk + 2;                                                   // fc viewed flags
+    int32_t *s_acc = s_view + p.frames_per_chunk;                                                        // Q x blockDim (MULTI_Q)
     __shared__ __align__(8) unsigned long long s_bar;
 
     const int tid = threadIdx.x;
@@ -122,7 +230,37 @@ lift_kernel(const __grid_constant__ LiftParams p) {
         }
     }
 
-    for (int fl = 0; fl < nf; ++fl) {
+    // ---- per-frame culling planes (one thread per frame of the chunk), see warp_may_see()
+    const int fc = p.frames_per_chunk;
+    if (!DEBUG && tid < nf) build_frame_planes(s_pose + tid * 16, p, s_plane + tid, fc);
+    // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible)
+    double cx, cy, cz, cr;
+    const bool warp_has_points = warp_sphere(valid, x, y, z, cx, cy, cz, cr);
+    for (int i = tid; i <= nf; i += kLiftThreads) {
+        s_moff[i] = p.mask_offset != nullptr ? __ldg(p.mask_offset + f0 + i) : 0;
+        if (i < nf) s_view[i] = (p.frame_viewed == nullptr || __ldg(p.frame_viewed + f0 + i)) ? 1 : 0;
+    }
+    __syncthreads();
+
+    for (int fb = 0; fb < nf; fb += 32) {
+      // lane l decides for frame fb + l whether ANY point of this warp can be visible in it
+      unsigned todo;
+      {
+          const int fl = fb + lane;
+          bool see = fl < nf && warp_has_points;
+          if (!DEBUG && see) see = warp_may_see(s_plane + fl, fc, cx, cy, cz, cr, p.z_lo, p.z_hi);
+          todo = __ballot_sync(0xffffffffu, see);
+      }
+      if (p.dbg_vis != nullptr && lane == 0 && pt < p.n_points) {
+          // frames skipped below still owe their (all-zero) visibility word
+          for (unsigned m = ~todo; m != 0u; m &= m - 1u) {
+              const int fl = fb + __ffs(m) - 1;
+              if (fl < nf) p.dbg_vis[(long long)(f0 + fl) * p.words + word_idx] = 0u;
+          }
+      }
+      while (todo != 0u) {
+        const int fl = fb + __ffs(todo) - 1;
+        todo &= todo - 1u;
         const int f = f0 + fl;
         const double *P = s_pose + fl * 16;
         // camera z first: projection_2d_to_3d.py:424-425, row 2 of inv(pose) @ [x y z 1]
@@ -150,16 +288,18 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             q1 = fma(p.k[4], Y, q1);
             q1 = fma(p.k[5], Z, q1);
             bool inside = true;
-            if (!DEBUG) {
-                // conservative frustum pre-test: outside => rint(q/Z) is certainly not in [0, W)
-                const double nz = -Z;
-                const double bw = p.w_hi * Z, bh = p.h_hi * Z;
-                inside = (q0 >= fmin(nz, bw)) && (q0 <= fmax(nz, bw)) && (q1 >= fmin(nz, bh)) && (q1 <= fmax(nz, bh));
+            if (!DEBUG && Z > 0.0) {
+                // conservative frustum pre-test: outside => rint(q/Z) is certainly not in [0, W) x [0, H).
+                // (Z <= 0 or NaN skips the pre-test and takes the exact path below.)
+                inside = (q0 >= -Z) && (q0 <= p.w_hi * Z) && (q1 >= -Z) && (q1 <= p.h_hi * Z);
             }
             if (inside) {
-                const double u = __ddiv_rn(q0, Z);   // divisor is camera z (:43)
-                const double v = __ddiv_rn(q1, Z);
-                const double xr = rint(u), yr = rint(v);   // np.round: half to even (:47)
+                double xr, yr;
+                if (DEBUG || !fast_rounded_quotients(q0, q1, Z, xr, yr)) {
+                    const double u = __ddiv_rn(q0, Z);   // divisor is camera z (:43)
+                    const double v = __ddiv_rn(q1, Z);
+                    xr = rint(u); yr = rint(v);          // np.round: half to even (:47)
+                }
                 if (DEBUG) {
                     long long *o = p.dbg_pix + ((long long)f * p.n_points + pt) * 2;
                     o[0] = f64_to_i64_numpy(xr);
@@ -182,9 +322,9 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             const unsigned vw = __ballot_sync(0xffffffffu, vis);
             if (lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
         }
-        if (p.frame_viewed == nullptr || p.frame_viewed[f]) cnt_view += vis ? 1 : 0;
-        if (p.mask_offset != nullptr) {
-            const int m0 = p.mask_offset[f], m1 = p.mask_offset[f + 1];
+        cnt_view += (vis ? 1 : 0) & s_view[fl];
+        {
+            const int m0 = s_moff[fl], m1 = s_moff[fl + 1];
             for (int m = m0; m < m1; ++m) {
                 bool bit = false;
                 if (vis) bit = (__ldg(p.masks2d + (long long)m * p.mask_words + (pidx >> 5)) >> (pidx & 31)) & 1u;
@@ -197,6 +337,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
                 }
             }
         }
+      }
     }
 
     // ---- flush votes once per (point, chunk)
@@ -243,7 +384,7 @@ int auto_frames_per_chunk(long long n_points, int n_frames) {
     if (chunks < 1) chunks = 1;
     long long fc = ceil_div64(n_frames, chunks);
     if (fc < 8) fc = 8;
-    if (fc > kMaxFramesPerChunk) fc = kMaxFramesPerChunk;
+    if (fc > 128) fc = 128;   // 128 frames x 336 B of shared memory keeps >= 4 CTAs per SM resident
     if (fc > n_frames) fc = n_frames;
     return (int)fc;
 }
@@ -324,7 +465,7 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     const bool multi_q = d->n_queries > 1;
     const bool debug = d->debug_pix != nullptr;
     LiftKernel k = pick(d->xyz_kind, d->depth_kind, multi_q, debug);
-    const size_t smem = (size_t)fc * 128 + (multi_q ? (size_t)d->n_queries * kLiftThreads * 4 : 0);
+    const size_t smem = (size_t)fc * kFrameSmemBytes + kChunkSmemExtra + (multi_q ? (size_t)d->n_queries * kLiftThreads * 4 : 0);
     BFF_REQUIRE(smem <= 200 * 1024, "bff_lift_scene: %d queries need %zu bytes of shared memory", d->n_queries, smem);
     BFF_CUDA(cudaFuncSetAttribute((const void *)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ceil_div64(n, kLiftThreads), (unsigned)chunks);

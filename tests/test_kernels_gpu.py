@@ -209,3 +209,35 @@ def test_vote_statistics(cuda_dev):
     np.testing.assert_array_equal(unpack_rows(keep.cpu().numpy()[None], n)[0], exp.numpy())
     keep1 = ops.point_keep(dmc, None, 1, 3.0)
     np.testing.assert_array_equal(unpack_rows(keep1.cpu().numpy()[None], n)[0], mc >= 3)
+
+
+def test_lift_half_integer_pixels_round_like_numpy(cuda_dev):
+    """Quotients that sit exactly on, and one ulp either side of, k + 0.5 must round half-to-even exactly
+    as np.round does (projection_2d_to_3d.py:47): this is where the kernel's reciprocal fast path has to
+    fall back to the IEEE division."""
+    import oracle as O
+    from bff_b200 import ops
+    h, w, zc = 48, 64, 2.0
+    K = np.array([[128.0, 0.0, 16.0], [0.0, 128.0, 8.0], [0.0, 0.0, 1.0]])
+    ks = np.arange(-2, w + 2)
+    xs = (ks + 0.5 - 16.0) * zc / 128.0                     # u = 128 x / z + 16 = k + 0.5 exactly
+    pts = []
+    for dx in (xs, np.nextafter(xs, np.inf), np.nextafter(xs, -np.inf)):
+        for yv in ((10 + 0.5 - 8.0) * zc / 128.0, (11 - 8.0) * zc / 128.0):
+            pts.append(np.stack([dx, np.full_like(dx, yv), np.full_like(dx, zc)], 1))
+    xyz = np.concatenate(pts)
+    n = xyz.shape[0]
+    pinv = np.eye(4)[None].copy()
+    depth = np.full((1, h, w), zc, np.float32)
+    yy, xx = np.mgrid[0:h, 0:w]
+    masks = np.stack([(xx % 2 == 0), (yy % 2 == 0), (xx + yy) % 3 == 0])
+    off = np.array([0, 3], np.int32)
+    rows_o, mc_o, vc_o = O.lift_scene(xyz, pinv, K, depth, 0.08, masks.astype(np.uint8), off)
+    assert vc_o.sum() > 300
+    packed2d = pack_rows(masks.reshape(3, -1)).view(np.int32)
+    out = ops.lift_scene(torch.from_numpy(xyz).to(cuda_dev), torch.from_numpy(pinv).to(cuda_dev), K,
+                         torch.from_numpy(depth).to(cuda_dev), h, w, masks2d=torch.from_numpy(packed2d).to(cuda_dev),
+                         mask_offset=torch.from_numpy(off).to(cuda_dev), depth_range=(0.5, 10.0))
+    np.testing.assert_array_equal(unpack_rows(out.rows.cpu().numpy(), n), rows_o)
+    np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)
+    np.testing.assert_array_equal(out.masked_counts.cpu().numpy(), mc_o)
