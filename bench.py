@@ -123,8 +123,10 @@ class GpuScene:
                          runs=pin(runs), offsets=pin(np.asarray(offsets, np.int32)),
                          viewed=pin(np.asarray(self.viewed, np.uint8)), s1_runs=pin(s1_runs))
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
-        self.devin = None
-        self.stage_ms = {}
+        self.lift_events = None
+        if torch.cuda.is_available():
+            # recorded inside bff_lift_scene around its memsets + kernel: the launch itself, without host gaps
+            self.lift_events = (_event(), _event())
 
     def upload(self):
         return {k: v.to(self.dev, non_blocking=True) for k, v in self.host.items()}
@@ -139,7 +141,8 @@ class GpuScene:
         ev()
         out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
                              mask_offset=d["offsets"] if self.n_masks else None, frame_viewed=d["viewed"],
-                             depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535))
+                             depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535),
+                             timing_events=self.lift_events if timers is not None else None)
         ev()
         rows, mc, vc = out.rows, out.masked_counts, out.viewed_counts
         conf_list, labels = self.conf_list, self.labels
@@ -282,6 +285,19 @@ def run_gpu(args):
     for _ in range(args.warmup):
         final = g.step(d)
         _ = g.step(g.upload())
+    if args.pyprofile:
+        import cProfile, pstats
+        pr = cProfile.Profile()
+        pr.enable()
+        for _ in range(args.steps):
+            g.step(d)
+        torch.cuda.synchronize()
+        pr.disable()
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("cumulative").print_stats(45)
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(25)
+        if ctx:
+            ctx.finalize()
+        return
     if args.profile:
         # for `ncu --profile-from-start off`: only these steps are captured; no number is reported
         torch.cuda.synchronize()
@@ -310,7 +326,7 @@ def run_gpu(args):
         ms = [tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)]
         stage_acc += np.asarray(ms)
         tot_ms += tm[0].elapsed_time(tm[-1])
-        lift_ms += ms[1]
+        lift_ms += g.lift_events[0].elapsed_time(g.lift_events[1])
     launches = _cabi.launch_count - launches0
     barrier()
     wall_dev = time.time() - wall0
@@ -472,6 +488,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-frames", type=int, default=40, help="frames in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -32,6 +32,7 @@ class LiftDesc(ctypes.Structure):
         ("rows", c_void_p), ("masked_counts", c_void_p), ("viewed_counts", c_void_p),
         ("debug_pix", c_void_p), ("debug_vis", c_void_p),
         ("frames_per_chunk", c_int32), ("reserved", c_int32),
+        ("ev_start", c_void_p), ("ev_stop", c_void_p),
     ]
 
 

@@ -21,17 +21,12 @@ from ._log import log
 def label_equality(labels: Sequence[str]) -> torch.Tensor:
     """calculate_feature_similarity (projection_2d_to_3d.py:169-187): exact string equality.
     (The reference's similarity threshold argument is unused)"""
-    ids: dict = {}
-    v = torch.tensor([ids.setdefault(l, len(ids)) for l in labels], dtype=torch.int64)
+    _, inv = np.unique(np.asarray(list(labels), dtype=object).astype(str), return_inverse=True) if len(labels) else ((), np.zeros(0, np.int64))
+    v = torch.from_numpy(np.asarray(inv, dtype=np.int64))
     return v.unsqueeze(0) == v.unsqueeze(1)
 
 
-def connected_groups(adj: torch.Tensor) -> List[List[int]]:
-    """find_unconnected_subgraphs_tensor (projection_2d_to_3d.py:250-274) without the O(Ins^4)
-    closure: for every not-yet-visited node in index order, the ascending list of nodes reachable
-    from it by a path of length >= 1. A node without self edge and without neighbours (an empty
-    lifted row: its IoU diagonal is NaN) yields [] and marks nothing visited, like the reference."""
-    a = adj.to(torch.bool).cpu().numpy()
+def _connected_groups_general(a: np.ndarray) -> List[List[int]]:
     n = a.shape[0]
     nbrs = [np.flatnonzero(a[i]) for i in range(n)]
     visited = np.zeros(n, dtype=bool)
@@ -48,10 +43,35 @@ def connected_groups(adj: torch.Tensor) -> List[List[int]]:
                 if not reach[v]:
                     reach[v] = True
                     stack.append(v)
-        comp = [int(k) for k in np.flatnonzero(reach)]
-        out.append(comp)
+        out.append([int(k) for k in np.flatnonzero(reach)])
         visited[reach] = True
     return out
+
+
+def connected_groups(adj: torch.Tensor) -> List[List[int]]:
+    """find_unconnected_subgraphs_tensor (projection_2d_to_3d.py:250-274) without the O(Ins^4)
+    closure: for every not-yet-visited node in index order, the ascending list of nodes reachable
+    from it by a path of length >= 1. A node without self edge and without neighbours (an empty
+    lifted row: its IoU diagonal is NaN) yields [] and marks nothing visited, like the reference.
+    The merge matrix is symmetric (IoU and label equality both are), in which case the lists are the
+    connected components (scipy csgraph, C speed) ordered by smallest member."""
+    a = np.ascontiguousarray(adj.to(torch.bool).cpu().numpy())
+    n = a.shape[0]
+    if n == 0:
+        return []
+    if not np.array_equal(a, a.T):
+        return _connected_groups_general(a)
+    from scipy.sparse import csr_matrix
+    from scipy.sparse.csgraph import connected_components
+    r, c = np.nonzero(a)
+    _, lab = connected_components(csr_matrix((np.ones(r.size, np.int8), (r, c)), shape=(n, n)), directed=False)
+    has_edge = np.zeros(n, bool)
+    has_edge[r] = True
+    order = np.argsort(lab, kind="stable")                    # members ascending inside each component
+    bounds = np.flatnonzero(np.diff(lab[order])) + 1
+    comps = np.split(order, bounds)
+    comps.sort(key=lambda c: c[0])                            # emitted when their smallest node is reached
+    return [[int(k) for k in c] if has_edge[c[0]] else [] for c in comps]
 
 
 def aggregate_rows(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], iou_thres: float,
@@ -67,11 +87,12 @@ def aggregate_rows(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str]
     if not used:
         return None, None, [], []
     agg = ops.rows_or_reduce(rows, used)                        # K10
-    confs = []
-    for g in used:
-        c = [conf[k] for k in g]
-        confs.append(sum(c) / len(c))                           # sequential, index order (:220-224)
-    return agg, torch.tensor(confs), [labels[g[0]] for g in used], groups
+    # conf = sum(conf_k) / len, the sum taken sequentially in float32 in index order (:220-224)
+    c32 = conf.to(torch.float32).numpy()
+    confs = np.empty(len(used), np.float32)
+    for i, g in enumerate(used):
+        confs[i] = np.cumsum(c32[g], dtype=np.float32)[-1] / np.float32(len(g))
+    return agg, torch.from_numpy(confs), [labels[g[0]] for g in used], groups
 
 
 def keep_points(mc: torch.Tensor, vc: Optional[torch.Tensor], cfg) -> torch.Tensor:

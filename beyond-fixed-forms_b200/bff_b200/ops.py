@@ -6,6 +6,7 @@ is unavailable (no fallback).
 """
 from __future__ import annotations
 
+from ctypes import c_void_p
 from typing import Optional, Sequence
 
 import numpy as np
@@ -45,7 +46,7 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
                frame_viewed: Optional[torch.Tensor] = None, depth_thresh: float = 0.08,
                depth_scale: float = 1000.0, depth_range: Optional[Sequence[float]] = None,
                want_rows: bool = True, want_counts: bool = True, want_viewed: bool = True,
-               debug: bool = False, frames_per_chunk: int = 0) -> LiftOutput:
+               debug: bool = False, frames_per_chunk: int = 0, timing_events=None) -> LiftOutput:
     """One launch over all frames of a scene (bff_lift_scene).
 
     xyz         (N,4) float32 [x,y,z,_] or (N,3) float64, CUDA
@@ -114,6 +115,8 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     d.rows, d.masked_counts, d.viewed_counts = ptr(rows), ptr(mc), ptr(vc)
     d.debug_pix, d.debug_vis = ptr(pix), ptr(vis)
     d.frames_per_chunk = int(frames_per_chunk)
+    if timing_events is not None:      # two recorded torch.cuda.Event(enable_timing=True): re-recorded around the launch
+        d.ev_start, d.ev_stop = c_void_p(timing_events[0].cuda_event), c_void_p(timing_events[1].cuda_event)
     check(lib().bff_lift_scene(d, current_stream()), "bff_lift_scene")
     _count(lib().bff_lift_scene_launches(d))
     return LiftOutput(rows, mc, vc, pix, vis)

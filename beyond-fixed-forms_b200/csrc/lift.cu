@@ -425,12 +425,16 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     if (rc != BFF_OK) return rc;
     const long long words = ceil_div64(d->n_points, 32);
     const long long n = d->n_points;
+    if (d->ev_start) BFF_CUDA(cudaEventRecord((cudaEvent_t)d->ev_start, stream));
     // outputs are fully overwritten: zero them first (rows get only their non-zero words stored)
     if (d->rows && d->n_masks > 0 && words > 0)
         BFF_CUDA(cudaMemsetAsync(d->rows, 0, (size_t)d->n_masks * words * 4, stream));
     if (d->masked_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->masked_counts, 0, (size_t)d->n_queries * n * 4, stream));
     if (d->viewed_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->viewed_counts, 0, (size_t)n * 4, stream));
-    if (n == 0 || d->n_frames == 0) return BFF_OK;
+    if (n == 0 || d->n_frames == 0) {
+        if (d->ev_stop) BFF_CUDA(cudaEventRecord((cudaEvent_t)d->ev_stop, stream));
+        return BFF_OK;
+    }
 
     LiftParams p;
     p.xyz = d->xyz; p.pose_inv = d->pose_inv; p.depth = d->depth; p.masks2d = d->masks2d;
@@ -471,5 +475,6 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     dim3 grid((unsigned)ceil_div64(n, kLiftThreads), (unsigned)chunks);
     k<<<grid, kLiftThreads, smem, stream>>>(p);
     BFF_LAUNCH_CHECK("lift_kernel");
+    if (d->ev_stop) BFF_CUDA(cudaEventRecord((cudaEvent_t)d->ev_stop, stream));
     return BFF_OK;
 }

@@ -93,6 +93,9 @@ typedef struct bff_lift_desc {
     /* launch shape: frames per CTA chunk (0 = automatic) */
     int32_t frames_per_chunk;
     int32_t reserved;
+    /* optional cudaEvent_t handles recorded on `stream` right before the first and right after the last
+     * device operation of the call (for callers that time the launch itself); NULL = none */
+    void *ev_start, *ev_stop;
 } bff_lift_desc;
 
 BFF_API int bff_version(void);
