@@ -9,7 +9,7 @@ import os
 from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbff.so")
+LIB_PATH = os.environ.get("BFF_LIB_PATH") or os.path.join(_HERE, "libbff.so")   # override: experiment builds only
 
 BFF_DEPTH_F32, BFF_DEPTH_U16 = 0, 1
 BFF_XYZ_F32X4, BFF_XYZ_F64X3 = 0, 1

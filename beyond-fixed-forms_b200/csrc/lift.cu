@@ -24,6 +24,12 @@
 namespace bff {
 
 constexpr int kLiftThreads = 256;
+#ifndef BFF_LIFT_MIN_BLOCKS
+#define BFF_LIFT_MIN_BLOCKS 6      // resident CTAs per SM the register allocation is tuned for (measured best of 4..8)
+#endif
+#ifndef BFF_LIFT_PIPE
+#define BFF_LIFT_PIPE 1            // surviving frames processed per loop iteration (1 or 2; 2 measured slower)
+#endif
 constexpr int kMaxFramesPerChunk = 256;   // <= kLiftThreads: one thread prepares one frame's culling planes
 // Per-frame culling data in shared memory (structure of arrays, index [k * fc + frame]):
 //   0..5   camera-z as a function of the world point: n(3), d, |n|(1+eps), eps|d|
@@ -166,8 +172,70 @@ __device__ __forceinline__ bool fast_rounded_quotients(double q0, double q1, dou
     return (fabs(u) < 65536.0) && (fabs(v) < 65536.0) && (fabs(u - xr) < lim) && (fabs(v - yr) < lim);
 }
 
+// Projection of one point into one frame (projection_2d_to_3d.py:424-425, :37-48) up to the integer pixel.
+// Returns true when the pixel is inside the image; Z = camera z, pix = y * W + x.
+template <bool DEBUG>
+__device__ __forceinline__ bool locate_pixel(const LiftParams &p, const double *P, int f, double x, double y, double z,
+                                             bool valid, long long pt, double &Z, int &pix) {
+    // camera z first: row 2 of inv(pose) @ [x y z 1]
+    Z = fma(P[8], x, 0.0);
+    Z = fma(P[9], y, Z);
+    Z = fma(P[10], z, Z);
+    Z = fma(P[11], 1.0, Z);
+    pix = 0;
+    if (!(valid && (DEBUG || (Z >= p.z_lo && Z <= p.z_hi)))) return false;
+    double X = fma(P[0], x, 0.0);
+    X = fma(P[1], y, X);
+    X = fma(P[2], z, X);
+    X = fma(P[3], 1.0, X);
+    double Y = fma(P[4], x, 0.0);
+    Y = fma(P[5], y, Y);
+    Y = fma(P[6], z, Y);
+    Y = fma(P[7], 1.0, Y);
+    // K @ p, rows 0 and 1 (:43)
+    double q0 = fma(p.k[0], X, 0.0);
+    q0 = fma(p.k[1], Y, q0);
+    q0 = fma(p.k[2], Z, q0);
+    double q1 = fma(p.k[3], X, 0.0);
+    q1 = fma(p.k[4], Y, q1);
+    q1 = fma(p.k[5], Z, q1);
+    if (!DEBUG && Z > 0.0) {
+        // conservative frustum pre-test: outside => rint(q/Z) is certainly not in [0, W) x [0, H).
+        // (Z <= 0 or NaN skips the pre-test and takes the exact path below.)
+        if (!((q0 >= -Z) && (q0 <= p.w_hi * Z) && (q1 >= -Z) && (q1 <= p.h_hi * Z))) return false;
+    }
+    double xr, yr;
+    if (DEBUG || !fast_rounded_quotients(q0, q1, Z, xr, yr)) {
+        const double u = __ddiv_rn(q0, Z);   // divisor is camera z (:43)
+        const double v = __ddiv_rn(q1, Z);
+        xr = rint(u); yr = rint(v);          // np.round: half to even (:47)
+    }
+    if (DEBUG) {
+        long long *o = p.dbg_pix + ((long long)f * p.n_points + pt) * 2;
+        o[0] = f64_to_i64_numpy(xr);
+        o[1] = f64_to_i64_numpy(yr);
+    }
+    if (!(xr >= 0.0 && xr < (double)p.width && yr >= 0.0 && yr < (double)p.height)) return false;
+    pix = (int)yr * p.width + (int)xr;
+    return true;
+}
+
+template <int DEPTH_KIND>
+__device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, int pix) {
+    const long long off = (long long)f * p.height * p.width + pix;
+    if (DEPTH_KIND == BFF_DEPTH_U16) return (unsigned)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + off);
+    return __ldg(reinterpret_cast<const unsigned *>(p.depth) + off);
+}
+
+template <int DEPTH_KIND>
+__device__ __forceinline__ float depth_value(unsigned raw, float depth_scale) {
+    // uint16 sensor units -> float32 metres exactly as projection_2d_to_3d.py:431-435 (fp32 divide)
+    if (DEPTH_KIND == BFF_DEPTH_U16) return __fdiv_rn((float)raw, depth_scale);
+    return __uint_as_float(raw);
+}
+
 template <int XYZ_KIND, int DEPTH_KIND, bool MULTI_Q, bool DEBUG>
-__global__ void __launch_bounds__(kLiftThreads, 5)
+__global__ void __launch_bounds__(kLiftThreads, BFF_LIFT_MIN_BLOCKS)
 lift_kernel(const __grid_constant__ LiftParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *s_pose = reinterpret_cast<double *>(smem_raw);                       // fc x 16 doubles
@@ -258,72 +326,39 @@ lift_kernel(const __grid_constant__ LiftParams p) {
               if (fl < nf) p.dbg_vis[(long long)(f0 + fl) * p.words + word_idx] = 0u;
           }
       }
+      // Two surviving frames per iteration: both depth gathers are in flight before either is consumed
+      // (the gather -> compare -> mask gather chain is latency bound, the frames are independent).
       while (todo != 0u) {
-        const int fl = fb + __ffs(todo) - 1;
+        const int flA = fb + __ffs(todo) - 1;
         todo &= todo - 1u;
-        const int f = f0 + fl;
-        const double *P = s_pose + fl * 16;
-        // camera z first: projection_2d_to_3d.py:424-425, row 2 of inv(pose) @ [x y z 1]
-        double Z = fma(P[8], x, 0.0);
-        Z = fma(P[9], y, Z);
-        Z = fma(P[10], z, Z);
-        Z = fma(P[11], 1.0, Z);
-        bool vis = false;
-        long long pidx = 0;
-        bool cand = valid && (DEBUG || (Z >= p.z_lo && Z <= p.z_hi));
-        if (cand) {
-            double X = fma(P[0], x, 0.0);
-            X = fma(P[1], y, X);
-            X = fma(P[2], z, X);
-            X = fma(P[3], 1.0, X);
-            double Y = fma(P[4], x, 0.0);
-            Y = fma(P[5], y, Y);
-            Y = fma(P[6], z, Y);
-            Y = fma(P[7], 1.0, Y);
-            // K @ p, rows 0 and 1 (:43)
-            double q0 = fma(p.k[0], X, 0.0);
-            q0 = fma(p.k[1], Y, q0);
-            q0 = fma(p.k[2], Z, q0);
-            double q1 = fma(p.k[3], X, 0.0);
-            q1 = fma(p.k[4], Y, q1);
-            q1 = fma(p.k[5], Z, q1);
-            bool inside = true;
-            if (!DEBUG && Z > 0.0) {
-                // conservative frustum pre-test: outside => rint(q/Z) is certainly not in [0, W) x [0, H).
-                // (Z <= 0 or NaN skips the pre-test and takes the exact path below.)
-                inside = (q0 >= -Z) && (q0 <= p.w_hi * Z) && (q1 >= -Z) && (q1 <= p.h_hi * Z);
-            }
-            if (inside) {
-                double xr, yr;
-                if (DEBUG || !fast_rounded_quotients(q0, q1, Z, xr, yr)) {
-                    const double u = __ddiv_rn(q0, Z);   // divisor is camera z (:43)
-                    const double v = __ddiv_rn(q1, Z);
-                    xr = rint(u); yr = rint(v);          // np.round: half to even (:47)
-                }
-                if (DEBUG) {
-                    long long *o = p.dbg_pix + ((long long)f * p.n_points + pt) * 2;
-                    o[0] = f64_to_i64_numpy(xr);
-                    o[1] = f64_to_i64_numpy(yr);
-                }
-                if (xr >= 0.0 && xr < (double)p.width && yr >= 0.0 && yr < (double)p.height) {
-                    pidx = (long long)yr * p.width + (long long)xr;
-                    float d;
-                    const long long off = (long long)f * p.height * p.width + pidx;
-                    if (DEPTH_KIND == BFF_DEPTH_U16)
-                        d = __fdiv_rn((float)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + off), p.depth_scale);
-                    else
-                        d = __ldg(reinterpret_cast<const float *>(p.depth) + off);
-                    // :62-66: depth != 0 and |z - depth| < thresh in float64
-                    vis = (d != 0.0f) && (fabs(Z - (double)d) < p.thresh);
-                }
-            }
+        const bool hasB = BFF_LIFT_PIPE > 1 && todo != 0u;
+        const int flB = hasB ? fb + __ffs(todo) - 1 : flA;
+        if (hasB) todo &= todo - 1u;
+        double ZA, ZB = 0.0;
+        int pixA, pixB = 0;
+        const bool inA = locate_pixel<DEBUG>(p, s_pose + flA * 16, f0 + flA, x, y, z, valid, pt, ZA, pixA);
+        const unsigned rawA = inA ? load_depth_raw<DEPTH_KIND>(p, f0 + flA, pixA) : 0u;
+        bool inB = false;
+        unsigned rawB = 0u;
+        if (hasB) {
+            inB = locate_pixel<DEBUG>(p, s_pose + flB * 16, f0 + flB, x, y, z, valid, pt, ZB, pixB);
+            rawB = inB ? load_depth_raw<DEPTH_KIND>(p, f0 + flB, pixB) : 0u;
         }
-        if (p.dbg_vis != nullptr) {
-            const unsigned vw = __ballot_sync(0xffffffffu, vis);
-            if (lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
-        }
-        cnt_view += (vis ? 1 : 0) & s_view[fl];
-        {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            if (half == 1 && !hasB) break;
+            const int fl = half ? flB : flA;
+            const int f = f0 + fl;
+            const int pidx = half ? pixB : pixA;
+            const double Z = half ? ZB : ZA;
+            const float d = depth_value<DEPTH_KIND>(half ? rawB : rawA, p.depth_scale);
+            // :62-66: in bounds, depth != 0 and |z - depth| < thresh in float64
+            const bool vis = (half ? inB : inA) && (d != 0.0f) && (fabs(Z - (double)d) < p.thresh);
+            if (p.dbg_vis != nullptr) {
+                const unsigned vw = __ballot_sync(0xffffffffu, vis);
+                if (lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
+            }
+            cnt_view += (vis ? 1 : 0) & s_view[fl];
             const int m0 = s_moff[fl], m1 = s_moff[fl + 1];
             for (int m = m0; m < m1; ++m) {
                 bool bit = false;
@@ -378,13 +413,13 @@ static LiftKernel pick(int xyz_kind, int depth_kind, bool multi_q, bool debug) {
 }
 
 int auto_frames_per_chunk(long long n_points, int n_frames) {
+    // One 32-frame ballot batch per CTA measured best on B200 (scripts/lift_variants.py: 0.33 ms at 30-38
+    // frames per chunk vs 0.40 ms at 100 on the 250k-point / 300-frame scene): short CTAs balance the
+    // uneven work that culling leaves and keep shared memory per CTA small. Larger chunks only when the
+    // grid would become unreasonably big.
     const long long tiles = ceil_div64(n_points, kLiftThreads);
-    // aim for >= ~16 CTAs per SM in total so the tail is short, keep chunks >= 8 frames
-    long long chunks = ceil_div64((long long)kNumSMs * 16, tiles > 0 ? tiles : 1);
-    if (chunks < 1) chunks = 1;
-    long long fc = ceil_div64(n_frames, chunks);
-    if (fc < 8) fc = 8;
-    if (fc > 128) fc = 128;   // 128 frames x 336 B of shared memory keeps >= 4 CTAs per SM resident
+    long long fc = 32;
+    while (fc < kMaxFramesPerChunk && tiles * ceil_div64(n_frames, fc) > (1LL << 21)) fc *= 2;
     if (fc > n_frames) fc = n_frames;
     return (int)fc;
 }
