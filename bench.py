@@ -151,7 +151,7 @@ class GpuScene:
             rows, mc, vc = dist_mod.exchange(self.dist, rows, self.rows_per_rank, mc, vc)
             conf_list, labels = self.all_conf, self.all_labels
         ev()
-        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg)
+        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg, keep_rows=True)
         ev()
         s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
         p1 = refine.pass1_scene(inp["stage1"], res2, QUERY, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)

@@ -36,6 +36,28 @@ class LiftDesc(ctypes.Structure):
     ]
 
 
+class Stage2Desc(ctypes.Structure):
+    """struct bff_stage2_desc (include/bff.h)."""
+    _fields_ = [
+        ("rows", c_void_p), ("n_rows", c_int32), ("n_points", c_int64),
+        ("conf", c_void_p), ("label_id", c_void_p), ("mc", c_void_p), ("vc", c_void_p),
+        ("iou_thres", c_float), ("min_aggregated", c_int32), ("filter_mode", c_int32), ("filter_fraction", c_double),
+        ("agg_rows", c_void_p), ("cap_groups", c_int32), ("n_groups", c_void_p), ("group_first", c_void_p),
+        ("group_size", c_void_p), ("group_conf", c_void_p), ("before", c_void_p), ("after", c_void_p),
+        ("members", c_void_p), ("filter_value", c_void_p),
+    ]
+
+
+class RefineDesc(ctypes.Structure):
+    """struct bff_refine_desc (include/bff.h)."""
+    _fields_ = [
+        ("s1_rows", c_void_p), ("n1", c_int32), ("s2_rows", c_void_p), ("n2", c_int32), ("n_points", c_int64),
+        ("s2_conf", c_void_p), ("stage1_iou_thres", c_float),
+        ("s2_out", c_void_p), ("n2_out", c_void_p), ("s2_conf_out", c_void_p), ("match", c_void_p),
+        ("match_iou", c_void_p), ("best_match_log", c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/bff.h declares
 SYMBOLS = {
     "bff_version": (c_int, []),
@@ -53,6 +75,9 @@ SYMBOLS = {
     "bff_pack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_unpack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_rle_to_bits": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_stage2_aggregate": (c_int, [c_void_p, POINTER(Stage2Desc), c_void_p]),
+    "bff_refine_match": (c_int, [c_void_p, POINTER(RefineDesc), c_void_p]),
+    "bff_rows_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),
     "bff_ctx_destroy": (None, [c_void_p]),
     "bff_lift_scene_host": (c_int, [c_void_p, POINTER(LiftDesc), POINTER(c_int64), POINTER(c_int64)]),
@@ -99,3 +124,15 @@ def ptr(t):
 def current_stream():
     import torch
     return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_ctxs = {}
+
+
+def ctx(device_index: int):
+    """One bff_ctx (stream + scratch arenas) per device, created on first use."""
+    if device_index not in _ctxs:
+        h = c_void_p()
+        check(lib().bff_ctx_create(int(device_index), ctypes.byref(h)), "bff_ctx_create")
+        _ctxs[device_index] = h
+    return _ctxs[device_index]

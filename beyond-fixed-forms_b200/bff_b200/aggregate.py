@@ -150,3 +150,64 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
     log("after filtering", ins.shape)
     result = {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
     return result, out_rows
+
+
+# ----------------------------------------------------------------------------- fused C++ pipeline
+def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], mc: torch.Tensor,
+                           vc: Optional[torch.Tensor], n_points: int, cfg):
+    """aggregate_rows + keep_points + the overlap/AND/popcount half of filter_and_select in ONE call
+    (bff_stage2_aggregate): the component search, threshold pick and overlap schedule run in C++ next to the
+    kernel launches. Returns None when nothing aggregates, else
+    (agg_rows CUDA (G,Wd), conf_agg CPU (G,), labels_agg, groups, before (G,) int64, after (G,) int64)."""
+    from . import _cabi
+    n = rows.shape[0]
+    ids: dict = {}
+    label_id = np.asarray([ids.setdefault(l, len(ids)) for l in labels], dtype=np.int32)
+    conf32 = np.ascontiguousarray(conf.numpy(), dtype=np.float32)
+    if cfg["if_occurance_threshold"]:
+        mode, frac = 1, float(cfg["occurance_threshold"])
+    elif cfg["if_detected_ratio_threshold"]:
+        mode, frac = 0, float(cfg["detected_ratio_threshold"])
+    else:
+        mode, frac = 2, 0.0
+    cap = n // max(int(cfg["min_aggragated_masks"]), 1) + 1
+    agg = torch.empty((cap, rows.shape[1]), dtype=torch.int32, device=rows.device)
+    n_groups = np.zeros(1, np.int32)
+    first, size = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    gconf = np.zeros(cap, np.float32)
+    before, after = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    members = np.zeros(n, np.int32)
+    fval = np.zeros(1, np.float32)
+    mc = mc.reshape(-1)
+    d = _cabi.Stage2Desc()
+    d.rows, d.n_rows, d.n_points = _cabi.ptr(rows), n, int(n_points)
+    d.conf, d.label_id, d.mc, d.vc = _cabi.ptr(conf32), _cabi.ptr(label_id), _cabi.ptr(mc), _cabi.ptr(vc if mode == 0 else None)
+    d.iou_thres = float(np.float32(cfg["iou_thres"]))
+    d.min_aggregated, d.filter_mode, d.filter_fraction = int(cfg["min_aggragated_masks"]), mode, frac
+    d.agg_rows, d.cap_groups = _cabi.ptr(agg), cap
+    d.n_groups, d.group_first, d.group_size, d.group_conf = _cabi.ptr(n_groups), _cabi.ptr(first), _cabi.ptr(size), _cabi.ptr(gconf)
+    d.before, d.after, d.members, d.filter_value = _cabi.ptr(before), _cabi.ptr(after), _cabi.ptr(members), _cabi.ptr(fval)
+    _cabi.check(_cabi.lib().bff_stage2_aggregate(_cabi.ctx(rows.device.index or 0), d, _cabi.current_stream()), "bff_stage2_aggregate")
+    g = int(n_groups[0])
+    _cabi.launch_count += 5 + (12 if g else 0)      # kernels inside the call (popcount x2, intersect, adjacency, ...)
+    if g == 0:
+        log("masks_to_be_merged", [])
+        return None
+    off = np.concatenate([[0], np.cumsum(size[:g])])
+    groups = [members[off[k]:off[k + 1]].tolist() for k in range(g)]
+    log("masks_to_be_merged", groups)
+    if mode != 2:
+        log("detected_ratio_thres_value" if mode == 0 else "occurance_thres_value", torch.tensor(fval[0]))
+    return (agg[:g], torch.from_numpy(gconf[:g].copy()), [labels[int(i)] for i in first[:g]], groups,
+            torch.from_numpy(before[:g].astype(np.int64)), torch.from_numpy(after[:g].astype(np.int64)))
+
+
+def select_rows(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[str], before64: torch.Tensor,
+                after64: torch.Tensor, n_points: int, cfg):
+    """Row filter + the saved dict (projection_2d_to_3d.py:601-634), torch semantics for the comparisons."""
+    sel = (after64 > cfg["remove_small_masks"]) & (after64 > cfg["remove_filtered_masks"] * before64)
+    idx = torch.nonzero(sel).reshape(-1)
+    out_rows = agg[idx.to(agg.device)]
+    ins = ops.unpack_bits(out_rows, n_points)
+    log("after filtering", ins.shape)
+    return {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows

@@ -19,6 +19,9 @@ with open(os.path.join(_HERE, "stage1_classes.txt")) as _fh:
     STAGE1_CLASS_NAMES: List[str] = [l.strip() for l in _fh if l.strip()]
 
 
+FUSED = True     # bff_refine_match (C++ decisions next to the launches); False = one Python/torch call per step
+
+
 def idx_to_label(idx) -> str:
     return STAGE1_CLASS_NAMES[idx]
 
@@ -52,8 +55,10 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
         other = [i for i, l in enumerate(labels) if l == q_]
         return {"ious": [], "sims": [], "m1": None, "m2": None, "conf2": [], "n_points": n_points,
                 "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
-    s2 = ops.pack_bits(stage2["ins"].to(device))
+    s2 = stage2["rows"] if "rows" in stage2 else ops.pack_bits(stage2["ins"].to(device))
     s2_conf = stage2["conf"]
+    if FUSED and s2_conf.dtype == torch.float32:
+        return _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device)
     mm = torch.argmax(iou_between_stages(s1, s2), dim=1)                       # :208-213
     sel = s1[mm.to(device)]
     g = iou_between_stages(sel, sel)                                           # :217-219
@@ -96,6 +101,38 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
     log("Clip similarities:", sims)
     return {"ious": ious, "sims": sims, "m1": s1[mm.to(device)], "m2": s2, "conf2": s2_conf, "n_points": n_points,
             "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+
+
+def _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:
+    """The matching part of pass 1 (refinement.py:208-290) in one call: bff_refine_match."""
+    from . import _cabi
+    n1, n2 = s1.shape[0], s2.shape[0]
+    conf32 = np.ascontiguousarray(s2_conf.numpy(), dtype=np.float32)
+    s2_out = torch.empty_like(s2)
+    n2_out = np.zeros(1, np.int32)
+    conf_out, match_iou = np.zeros(n2, np.float32), np.zeros(n2, np.float32)
+    match, best_log = np.zeros(n2, np.int32), np.zeros(n2, np.int32)
+    d = _cabi.RefineDesc()
+    d.s1_rows, d.n1, d.s2_rows, d.n2, d.n_points = _cabi.ptr(s1), n1, _cabi.ptr(s2), n2, int(n_points)
+    d.s2_conf, d.stage1_iou_thres = _cabi.ptr(conf32), float(np.float32(stage1_iou_thres))
+    d.s2_out, d.n2_out, d.s2_conf_out = _cabi.ptr(s2_out), _cabi.ptr(n2_out), _cabi.ptr(conf_out)
+    d.match, d.match_iou, d.best_match_log = _cabi.ptr(match), _cabi.ptr(match_iou), _cabi.ptr(best_log)
+    _cabi.check(_cabi.lib().bff_refine_match(_cabi.ctx(s1.device.index or 0), d, _cabi.current_stream()), "bff_refine_match")
+    _cabi.launch_count += 14
+    m = int(n2_out[0])
+    mm = match[:m]
+    log("DEBUG best_match_after_iou_check", [torch.tensor(int(b)) for b in best_log])
+    matched = set(int(k) for k in mm)
+    other = [i for i, l in enumerate(labels) if l == q_ and i not in matched]      # :293
+    matched_labels = [labels[int(k)] for k in mm]
+    sims = [float(sim_fn(query, l)) for l in matched_labels]                       # :297-302
+    ious = torch.from_numpy(match_iou[:m].copy())
+    log("iou for matched labels", ious)
+    log("Matched labels:", matched_labels)
+    log("Clip similarities:", sims)
+    mm_dev = torch.from_numpy(mm.astype(np.int64)).to(device)
+    return {"ious": ious, "sims": sims, "m1": s1[mm_dev], "m2": s2_out[:m], "conf2": torch.from_numpy(conf_out[:m].copy()),
+            "n_points": n_points, "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
 
 
 def similarity_threshold(all_sims: Sequence[Sequence[float]], percentile: float) -> float:

@@ -40,4 +40,28 @@ static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b;
 
 constexpr int kNumSMs = 148;  // B200
 
+// Grow-only bump arena (device or pinned host). reset() at the start of a call recycles all blocks;
+// pointers stay valid until the next reset because blocks are never moved, only added.
+struct Arena {
+    struct Block { unsigned char *p; size_t cap; };
+    Block blocks[32];
+    int n_blocks = 0, cur = 0;
+    size_t off = 0;
+    bool pinned_host = false;
+    void reset() { cur = 0; off = 0; }
+    void *take(size_t bytes);          // nullptr on allocation failure (error text set)
+    void release();
+    template <typename T> T *get(size_t count) { return reinterpret_cast<T *>(take(count * sizeof(T))); }
+};
+
 }  // namespace bff
+
+// A context owns one stream and grow-only workspaces used by the host-buffer and pipeline entry points.
+struct bff_ctx {
+    int device;
+    cudaStream_t stream;
+    unsigned char *ws;      // bff_*_host staging (single block)
+    size_t ws_bytes;
+    bff::Arena dev;         // pipeline scratch on the device
+    bff::Arena pin;         // pipeline scratch in pinned host memory
+};

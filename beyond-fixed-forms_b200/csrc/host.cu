@@ -22,13 +22,45 @@ using namespace bff;
 extern "C" int bff_version(void) { return BFF_VERSION; }
 extern "C" const char *bff_last_error(void) { return g_err; }
 
-// A context owns one stream and a grow-only device workspace used by the *_host entry points.
-struct bff_ctx {
-    int device;
-    cudaStream_t stream;
-    unsigned char *ws;
-    size_t ws_bytes;
-};
+namespace bff {
+void *Arena::take(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    if (bytes == 0) bytes = 256;
+    while (cur < n_blocks) {
+        if (off + bytes <= blocks[cur].cap) {
+            void *r = blocks[cur].p + off;
+            off += bytes;
+            return r;
+        }
+        ++cur;
+        off = 0;
+    }
+    if (n_blocks == 32) {
+        set_error("bff arena: too many blocks");
+        return nullptr;
+    }
+    size_t cap = bytes > ((size_t)32 << 20) ? bytes : ((size_t)32 << 20);
+    unsigned char *p = nullptr;
+    cudaError_t e = pinned_host ? cudaMallocHost(&p, cap) : cudaMalloc(&p, cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("bff arena: cannot allocate %zu bytes of %s memory", cap, pinned_host ? "pinned host" : "device");
+        return nullptr;
+    }
+    blocks[n_blocks] = {p, cap};
+    cur = n_blocks++;
+    off = bytes;
+    return p;
+}
+void Arena::release() {
+    for (int i = 0; i < n_blocks; ++i) {
+        if (pinned_host) cudaFreeHost(blocks[i].p);
+        else cudaFree(blocks[i].p);
+    }
+    n_blocks = cur = 0;
+    off = 0;
+}
+}  // namespace bff
 
 static int ctx_reserve(bff_ctx *c, size_t bytes) {
     if (bytes <= c->ws_bytes) return BFF_OK;
@@ -51,6 +83,7 @@ extern "C" int bff_ctx_create(int device, bff_ctx **out) {
     c->device = device;
     c->ws = nullptr;
     c->ws_bytes = 0;
+    c->pin.pinned_host = true;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         delete c;
@@ -65,6 +98,8 @@ extern "C" void bff_ctx_destroy(bff_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->ws) cudaFree(c->ws);
+    c->dev.release();
+    c->pin.release();
     cudaStreamDestroy(c->stream);
     delete c;
 }

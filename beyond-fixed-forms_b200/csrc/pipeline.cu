@@ -1,0 +1,359 @@
+// Fused host+device pipelines (include/bff.h: bff_stage2_aggregate, bff_refine_match, bff_rows_gather).
+//
+// The reference takes its small decisions (which masks merge, which threshold, which pairs overlap, which
+// stage-1 mask matches) with torch ops on tiny tensors between heavy tensor ops. Here the heavy ops are the
+// kernels of masks.cu / votes.cu and the decisions are plain C++ on pinned host copies of the tiny matrices,
+// so one call replaces dozens of Python-level launches. Every decision cites the reference lines it mirrors;
+// float32 comparisons / divisions are done in float32 exactly like torch does them.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace bff {
+
+// adjacency of the merge graph: same label AND iou > thr, IoU in float32 as calculate_iou computes it
+// (projection_2d_to_3d.py:120-122,158-165). NaN (0/0) compares false.
+__global__ void merge_adjacency_kernel(const int32_t *__restrict__ inter, const int32_t *__restrict__ pop,
+                                       const int32_t *__restrict__ label, int n, float thr, uint8_t *__restrict__ adj) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n * n) return;
+    const int r = (int)(i / n), c = (int)(i % n);
+    const float fi = __int2float_rn(inter[i]);
+    const float un = __fsub_rn(__fadd_rn(__int2float_rn(pop[r]), __int2float_rn(pop[c])), fi);
+    adj[i] = (label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
+}
+
+__global__ void rows_gather_kernel(const uint32_t *__restrict__ rows, long long words, const int32_t *__restrict__ idx,
+                                   uint32_t *__restrict__ out) {
+    const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= words) return;
+    out[(long long)blockIdx.y * words + w] = __ldg(rows + (long long)idx[blockIdx.y] * words + w);
+}
+
+struct UnionFind {
+    std::vector<int> parent;
+    explicit UnionFind(int n) : parent(n) { for (int i = 0; i < n; ++i) parent[i] = i; }
+    int find(int x) { while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; } return x; }
+    void unite(int a, int b) { a = find(a); b = find(b); if (a != b) { if (a < b) parent[b] = a; else parent[a] = b; } }  // root = smallest member
+};
+
+}  // namespace bff
+
+using namespace bff;
+
+#define PIPE_TAKE(var, arena, type, count)                         \
+    type *var = (arena).get<type>(count);                          \
+    if (!var) return BFF_ENOMEM
+
+static int upload_i32(bff_ctx *c, const std::vector<int32_t> &v, int32_t **dev_out, cudaStream_t s) {
+    const size_t n = v.empty() ? 1 : v.size();
+    int32_t *h = c->pin.get<int32_t>(n);
+    int32_t *d = c->dev.get<int32_t>(n);
+    if (!h || !d) return BFF_ENOMEM;
+    if (!v.empty()) {
+        memcpy(h, v.data(), v.size() * 4);
+        BFF_CUDA(cudaMemcpyAsync(d, h, v.size() * 4, cudaMemcpyHostToDevice, s));
+    }
+    *dev_out = d;
+    return BFF_OK;
+}
+
+extern "C" int bff_rows_gather(bff_ctx *c, const uint32_t *rows, int64_t words, const int32_t *idx_host, int32_t n_idx,
+                               uint32_t *out, void *stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    BFF_REQUIRE(c && n_idx >= 0 && words >= 0, "bff_rows_gather: bad arguments");
+    if (n_idx == 0 || words == 0) return BFF_OK;
+    BFF_REQUIRE(rows && idx_host && out, "bff_rows_gather: null pointer");
+    BFF_REQUIRE(n_idx <= 65535, "bff_rows_gather: too many rows");
+    c->dev.reset();
+    c->pin.reset();
+    int32_t *d_idx = nullptr;
+    int rc = upload_i32(c, std::vector<int32_t>(idx_host, idx_host + n_idx), &d_idx, s);
+    if (rc != BFF_OK) return rc;
+    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_idx);
+    rows_gather_kernel<<<grid, 256, 0, s>>>(rows, words, d_idx, out);
+    BFF_LAUNCH_CHECK("rows_gather_kernel");
+    // the pinned staging buffer is reused by the next call: make sure the copy has been consumed
+    BFF_CUDA(cudaStreamSynchronize(s));
+    return BFF_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// bff_stage2_aggregate
+extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    BFF_REQUIRE(c && d, "bff_stage2_aggregate: null argument");
+    BFF_REQUIRE(d->n_rows > 0 && d->n_points > 0, "bff_stage2_aggregate: empty input (the caller handles 'nothing lifted')");
+    BFF_REQUIRE(d->rows && d->conf && d->label_id && d->mc && d->agg_rows && d->n_groups && d->group_first && d->group_size &&
+                    d->group_conf && d->before && d->after,
+                "bff_stage2_aggregate: null pointer");
+    BFF_REQUIRE(d->min_aggregated >= 1, "bff_stage2_aggregate: min_aggregated must be >= 1");
+    BFF_REQUIRE(d->filter_mode >= 0 && d->filter_mode <= 2 && (d->filter_mode != 0 || d->vc), "bff_stage2_aggregate: bad filter mode");
+    BFF_REQUIRE(d->n_rows <= 46340, "bff_stage2_aggregate: too many rows");
+    BFF_CUDA(cudaSetDevice(c->device));
+    c->dev.reset();
+    c->pin.reset();
+    const int n = d->n_rows;
+    const int64_t words = ceil_div64(d->n_points, 32);
+    const size_t nn = (size_t)n * n;
+
+    // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
+    PIPE_TAKE(d_inter, c->dev, int32_t, nn);
+    PIPE_TAKE(d_pop, c->dev, int32_t, n);
+    PIPE_TAKE(d_adj, c->dev, uint8_t, nn);
+    PIPE_TAKE(h_adj, c->pin, uint8_t, nn);
+    int32_t *d_label = nullptr;
+    int rc = upload_i32(c, std::vector<int32_t>(d->label_id, d->label_id + n), &d_label, s);
+    if (rc != BFF_OK) return rc;
+    rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
+    if (rc != BFF_OK) return rc;
+    merge_adjacency_kernel<<<(unsigned)ceil_div64((int64_t)nn, 256), 256, 0, s>>>(d_inter, d_pop, d_label, n, d->iou_thres, d_adj);
+    BFF_LAUNCH_CHECK("merge_adjacency_kernel");
+    BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, nn, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaStreamSynchronize(s));
+
+    // ---- connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric, so the
+    // reference's reachability lists are the components, emitted by smallest member, members ascending).
+    // A node without any edge (an empty row: IoU diagonal NaN) forms no group.
+    UnionFind uf(n);
+    std::vector<char> has_edge(n, 0);
+    for (int i = 0; i < n; ++i) {
+        const uint8_t *row = h_adj + (size_t)i * n;
+        for (int j = 0; j < n; ++j)
+            if (row[j]) { has_edge[i] = 1; if (j > i) uf.unite(i, j); }
+    }
+    std::vector<int> root(n), count(n, 0);
+    for (int i = 0; i < n; ++i) { root[i] = uf.find(i); count[root[i]]++; }
+    // kept groups (:203): len >= min_aggregated; roots ascending == order of smallest member
+    std::vector<int> group_of_root(n, -1);
+    int g = 0;
+    for (int r = 0; r < n; ++r)
+        if (root[r] == r && has_edge[r] && count[r] >= d->min_aggregated) group_of_root[r] = g++;
+    *d->n_groups = g;
+    if (d->filter_value) *d->filter_value = 0.0f;
+    if (g == 0) return BFF_OK;
+    BFF_REQUIRE(g <= d->cap_groups, "bff_stage2_aggregate: %d groups exceed cap_groups %d", g, d->cap_groups);
+    std::vector<int32_t> seg(g + 1, 0), idx;
+    idx.reserve(n);
+    {
+        std::vector<std::vector<int32_t>> mem(g);
+        for (int i = 0; i < n; ++i) { const int gi = group_of_root[root[i]]; if (gi >= 0) mem[gi].push_back(i); }
+        for (int k = 0; k < g; ++k) {
+            // conf = sum(conf_k) / len, summed sequentially in float32 in index order (:220-224)
+            float acc = 0.0f;
+            for (int32_t m : mem[k]) { acc = acc + d->conf[m]; idx.push_back(m); }
+            d->group_conf[k] = acc / (float)mem[k].size();
+            d->group_first[k] = mem[k][0];
+            d->group_size[k] = (int32_t)mem[k].size();
+            seg[k + 1] = (int32_t)idx.size();
+        }
+    }
+    if (d->members) memcpy(d->members, idx.data(), idx.size() * 4);
+
+    // ---- OR-merge the members (:214-223)
+    int32_t *d_idx = nullptr, *d_seg = nullptr;
+    if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
+    if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
+    if ((rc = bff_rows_or_reduce(d->rows, words, d_idx, d_seg, g, d->agg_rows, s)) != BFF_OK) return rc;
+
+    // ---- pair overlaps of the merged rows + row sums 'before' (:285-291, :592), issued now, read later
+    PIPE_TAKE(d_ginter, c->dev, int32_t, (size_t)g * g);
+    PIPE_TAKE(d_before, c->dev, int32_t, g);
+    PIPE_TAKE(h_ginter, c->pin, int32_t, (size_t)g * g);
+    if ((rc = bff_mask_iou(d->agg_rows, g, d->agg_rows, g, words, d_ginter, d_before, d_before, nullptr, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(h_ginter, d_ginter, (size_t)g * g * 4, cudaMemcpyDeviceToHost, s));
+    PIPE_TAKE(h_before, c->pin, int32_t, g);
+    BFF_CUDA(cudaMemcpyAsync(h_before, d_before, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+
+    // ---- point filter (:512-583): the unique() over N values comes from the (masked, viewed) histogram
+    PIPE_TAKE(d_keep, c->dev, uint32_t, words);
+    float thr = 0.0f;
+    if (d->filter_mode == 2) {
+        if ((rc = bff_point_keep(d->mc, nullptr, d->n_points, 2, 0.0f, d_keep, s)) != BFF_OK) return rc;
+    } else {
+        PIPE_TAKE(d_max, c->dev, int32_t, 2);
+        PIPE_TAKE(h_max, c->pin, int32_t, 2);
+        const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
+        if ((rc = bff_counts_max(d->mc, vc, d->n_points, d_max, s)) != BFF_OK) return rc;
+        BFF_CUDA(cudaMemcpyAsync(h_max, d_max, 8, cudaMemcpyDeviceToHost, s));
+        BFF_CUDA(cudaStreamSynchronize(s));
+        const int mb = h_max[0] + 1, vb = vc ? h_max[1] + 1 : 1;
+        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
+        PIPE_TAKE(h_hist, c->pin, uint32_t, (size_t)mb * vb);
+        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
+        BFF_CUDA(cudaMemcpyAsync(h_hist, d_hist, (size_t)mb * vb * 4, cudaMemcpyDeviceToHost, s));
+        BFF_CUDA(cudaStreamSynchronize(s));
+        std::vector<float> u;
+        for (int a = 0; a < mb; ++a)
+            for (int b = 0; b < vb; ++b)
+                if (h_hist[(size_t)a * vb + b]) u.push_back(d->filter_mode == 0 ? (float)a / ((float)b + 1.0f) : (float)a);   // :571 in float32
+        std::sort(u.begin(), u.end());
+        u.erase(std::unique(u.begin(), u.end()), u.end());
+        // u[floor(p * len(u))] with p a Python float (:516-517, :575-576); out of range raises in the reference
+        const double pos = floor(d->filter_fraction * (double)u.size());
+        BFF_REQUIRE(pos >= 0.0 && pos < (double)u.size(), "bff_stage2_aggregate: filter fraction %g selects index %g of %zu unique values",
+                    d->filter_fraction, pos, u.size());
+        thr = u[(size_t)pos];
+        if ((rc = bff_point_keep(d->mc, vc, d->n_points, d->filter_mode, thr, d_keep, s)) != BFF_OK) return rc;
+    }
+    if (d->filter_value) *d->filter_value = thr;
+    BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps + 'before' are on the host now
+
+    // ---- solve_overlapping's sequential schedule (:285-299): pairs i<j that overlap in the incoming rows;
+    // the mask merged from MORE members keeps the shared points, ties: i loses
+    std::vector<int32_t> prog;
+    for (int i = 0; i < g; ++i)
+        for (int j = i + 1; j < g; ++j)
+            if (h_ginter[(size_t)i * g + j] > 0) {
+                if (d->group_size[i] > d->group_size[j]) { prog.push_back(j); prog.push_back(i); }
+                else { prog.push_back(i); prog.push_back(j); }
+            }
+    if (!prog.empty()) {
+        int32_t *d_prog = nullptr;
+        if ((rc = upload_i32(c, prog, &d_prog, s)) != BFF_OK) return rc;
+        if ((rc = bff_overlap_resolve(d->agg_rows, g, words, d_prog, (int32_t)(prog.size() / 2), s)) != BFF_OK) return rc;
+    }
+    // ---- ins &= masked_points, row sums 'after' (:594-596)
+    PIPE_TAKE(d_after, c->dev, int32_t, g);
+    if ((rc = bff_rows_and_popcount(d->agg_rows, g, words, d_keep, d_after, s)) != BFF_OK) return rc;
+    PIPE_TAKE(h_after, c->pin, int32_t, g);
+    BFF_CUDA(cudaMemcpyAsync(h_after, d_after, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaStreamSynchronize(s));
+    memcpy(d->before, h_before, (size_t)g * 4);
+    memcpy(d->after, h_after, (size_t)g * 4);
+    return BFF_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// bff_refine_match
+// torch.argmax semantics (refinement.py:211,288): first maximum; NaN counts as the maximum (first NaN wins).
+static int argmax_torch(const float *v, int n, int stride) {
+    int best = 0;
+    float cur = v[0];
+    for (int i = 1; i < n; ++i) {
+        const float x = v[(size_t)i * stride];
+        if ((x > cur) || (isnan(x) && !isnan(cur))) { best = i; cur = x; }
+    }
+    return best;
+}
+
+extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    BFF_REQUIRE(c && d, "bff_refine_match: null argument");
+    BFF_REQUIRE(d->n1 > 0 && d->n2 > 0 && d->n_points > 0, "bff_refine_match: empty input (the caller handles empty stages)");
+    BFF_REQUIRE(d->s1_rows && d->s2_rows && d->s2_conf && d->s2_out && d->n2_out && d->s2_conf_out && d->match && d->match_iou,
+                "bff_refine_match: null pointer");
+    BFF_REQUIRE(d->n2 <= 65535, "bff_refine_match: too many stage-2 masks");
+    BFF_CUDA(cudaSetDevice(c->device));
+    c->dev.reset();
+    c->pin.reset();
+    const int n1 = d->n1, n2 = d->n2;
+    const int64_t words = ceil_div64(d->n_points, 32);
+    int rc;
+    // scratch for an (n1 x k) IoU, k <= n2
+    PIPE_TAKE(d_inter, c->dev, int32_t, (size_t)n1 * n2);
+    PIPE_TAKE(d_p1, c->dev, int32_t, n1);
+    PIPE_TAKE(d_p2, c->dev, int32_t, n2);
+    PIPE_TAKE(d_iou, c->dev, float, (size_t)n1 * n2);
+    PIPE_TAKE(h_iou, c->pin, float, (size_t)n1 * n2);
+
+    // ---- iou(stage1, stage2), max_match = argmax over stage-1 (:208-213)
+    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_rows, n2, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaStreamSynchronize(s));
+    std::vector<int32_t> mm(n2);
+    for (int k = 0; k < n2; ++k) mm[k] = argmax_torch(h_iou + k, n1, n2);
+
+    // ---- IoU among the matched stage-1 masks, diagonal zeroed, thresholded (:217-224)
+    PIPE_TAKE(d_sel, c->dev, uint32_t, (size_t)n2 * words);
+    PIPE_TAKE(d_ginter, c->dev, int32_t, (size_t)n2 * n2);
+    PIPE_TAKE(d_gpop, c->dev, int32_t, n2);
+    PIPE_TAKE(d_giou, c->dev, float, (size_t)n2 * n2);
+    PIPE_TAKE(h_giou, c->pin, float, (size_t)n2 * n2);
+    int32_t *d_mm = nullptr;
+    if ((rc = upload_i32(c, mm, &d_mm, s)) != BFF_OK) return rc;
+    {
+        dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n2);
+        rows_gather_kernel<<<grid, 256, 0, s>>>(d->s1_rows, words, d_mm, d_sel);
+        BFF_LAUNCH_CHECK("rows_gather_kernel");
+    }
+    if ((rc = bff_mask_iou(d_sel, n2, d_sel, n2, words, d_ginter, d_gpop, d_gpop, d_giou, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(h_giou, d_giou, (size_t)n2 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaStreamSynchronize(s));
+
+    // ---- sequential merge loop (:230-249): redirects + in-place ORs of stage-1 rows, in list order
+    std::vector<int32_t> best(n2), redirect(n2, -1), or_prog;
+    for (int i = 0; i < n2; ++i) {
+        if (redirect[i] != -1) { best[i] = mm[redirect[i]]; continue; }
+        best[i] = mm[i];
+        for (int j = 0; j < n2; ++j) {
+            if (j == i) continue;                                            // diagonal set to 0 (:219)
+            if (h_giou[(size_t)i * n2 + j] > d->stage1_iou_thres) {
+                redirect[j] = i;
+                or_prog.push_back(mm[i]);
+                or_prog.push_back(mm[j]);
+            }
+        }
+    }
+    if (d->best_match_log) memcpy(d->best_match_log, best.data(), (size_t)n2 * 4);
+    if (!or_prog.empty()) {
+        int32_t *d_prog = nullptr;
+        if ((rc = upload_i32(c, or_prog, &d_prog, s)) != BFF_OK) return rc;
+        if ((rc = bff_rows_or_into(d->s1_rows, n1, words, d_prog, (int32_t)(or_prog.size() / 2), s)) != BFF_OK) return rc;
+    }
+
+    // ---- stage-2 masks that share a stage-1 match are merged (:258-281): any() of the rows, mean of the
+    // confidences, the merged mask moves to the END; matches are visited in ascending order (torch.unique)
+    std::vector<std::vector<int32_t>> cur(n2);
+    std::vector<float> cur_conf(d->s2_conf, d->s2_conf + n2);
+    std::vector<int32_t> cur_best(best);
+    for (int k = 0; k < n2; ++k) cur[k] = {k};
+    std::vector<int32_t> uniq(best);
+    std::sort(uniq.begin(), uniq.end());
+    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+    for (int32_t u : uniq) {
+        if (std::count(best.begin(), best.end(), u) <= 1) continue;
+        std::vector<std::vector<int32_t>> keep;
+        std::vector<float> keep_conf;
+        std::vector<int32_t> keep_best, merged;
+        float sum = 0.0f;
+        int cnt = 0;
+        for (size_t k = 0; k < cur.size(); ++k) {
+            if (cur_best[k] == u) {
+                merged.insert(merged.end(), cur[k].begin(), cur[k].end());
+                sum += cur_conf[k];
+                ++cnt;
+            } else {
+                keep.push_back(cur[k]); keep_conf.push_back(cur_conf[k]); keep_best.push_back(cur_best[k]);
+            }
+        }
+        keep.push_back(merged); keep_conf.push_back(sum / (float)cnt); keep_best.push_back(u);
+        cur.swap(keep); cur_conf.swap(keep_conf); cur_best.swap(keep_best);
+    }
+    const int m = (int)cur.size();
+    *d->n2_out = m;
+    std::vector<int32_t> idx, seg(m + 1, 0);
+    for (int k = 0; k < m; ++k) {
+        idx.insert(idx.end(), cur[k].begin(), cur[k].end());
+        seg[k + 1] = (int32_t)idx.size();
+        d->s2_conf_out[k] = cur_conf[k];
+    }
+    int32_t *d_idx = nullptr, *d_seg = nullptr;
+    if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
+    if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
+    if ((rc = bff_rows_or_reduce(d->s2_rows, words, d_idx, d_seg, m, d->s2_out, s)) != BFF_OK) return rc;
+
+    // ---- IoU of the merged stage-1 masks with the merged stage-2 masks, final argmax (:285-290)
+    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_out, m, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * m * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaStreamSynchronize(s));
+    for (int k = 0; k < m; ++k) {
+        d->match[k] = argmax_torch(h_iou + k, n1, m);
+        d->match_iou[k] = h_iou[(size_t)d->match[k] * m + k];
+    }
+    return BFF_OK;
+}

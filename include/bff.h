@@ -179,6 +179,63 @@ BFF_API int bff_mask_iou_host(bff_ctx *ctx, const uint32_t *a, int32_t n_a, cons
                       int64_t words, int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou,
                       int64_t *h2d_bytes, int64_t *d2h_bytes);
 
+/* ---- fused host+device pipelines: the small decisions between kernels (component search, thresholds,
+ * overlap schedule, argmax matching) run in C++ next to the launches instead of one Python/torch call each.
+ * Device pointers are the caller's (torch) tensors; work is enqueued on `stream`, which the function
+ * synchronises whenever a decision needs device results; scratch comes from the bff_ctx arenas. ---- */
+
+/* aggregate + point filter + solve_overlapping of ONE query's lifted rows
+ * (tools/projection_2d_to_3d.py:100-146,190-301,512-596). */
+typedef struct bff_stage2_desc {
+    const uint32_t *rows;       /* device (n_rows, Wd) lifted rows in file order (:481) */
+    int32_t n_rows;
+    int64_t n_points;
+    const float *conf;          /* host (n_rows) float32 confidences (:484-486) */
+    const int32_t *label_id;    /* host (n_rows); equal ids <=> equal label strings (:169-187) */
+    const int32_t *mc;          /* device (N) masked_counts of this query */
+    const int32_t *vc;          /* device (N) viewed_counts; required for filter_mode 0 */
+    float iou_thres;            /* cfg.iou_thres as float32 (torch compares `f32 tensor > python float` in float32) */
+    int32_t min_aggregated;     /* cfg.min_aggragated_masks, must be >= 1 here */
+    int32_t filter_mode;        /* 0 detected ratio (:524-578), 1 occurrence (:512-522), 2 none */
+    double filter_fraction;     /* cfg.detected_ratio_threshold / cfg.occurance_threshold */
+    /* outputs */
+    uint32_t *agg_rows;         /* device (cap_groups, Wd): merged rows after overlap resolution AND the point filter */
+    int32_t cap_groups;
+    int32_t *n_groups;          /* host: aggregated masks that passed min_aggregated (0 = 'nothing after aggregation') */
+    int32_t *group_first;       /* host (cap_groups): smallest member = source of the group's label (:226) */
+    int32_t *group_size;        /* host (cap_groups) */
+    float *group_conf;          /* host (cap_groups): sequential float32 mean of the members' confidences (:220-224) */
+    int32_t *before;            /* host (cap_groups): row sums before solve_overlapping (:592) */
+    int32_t *after;             /* host (cap_groups): row sums after overlap resolution and `&= masked_points` (:596) */
+    int32_t *members;           /* host (n_rows), optional: members of the kept groups, concatenated (for the log line) */
+    float *filter_value;        /* host, optional: the threshold that was picked (:576) */
+} bff_stage2_desc;
+BFF_API int bff_stage2_aggregate(bff_ctx *ctx, const bff_stage2_desc *desc, void *stream);
+
+/* pass 1 of tools/refinement.py for one scene (:208-290): stage-1 / stage-2 matching, the in-place stage-1
+ * OR-merges, merging of stage-2 masks that share a stage-1 match, and the final IoU + argmax. */
+typedef struct bff_refine_desc {
+    uint32_t *s1_rows;          /* device (n1, Wd) stage-1 masks, MODIFIED in place like the reference (:248) */
+    int32_t n1;
+    const uint32_t *s2_rows;    /* device (n2, Wd) stage-2 masks */
+    int32_t n2;
+    int64_t n_points;
+    const float *s2_conf;       /* host (n2) */
+    float stage1_iou_thres;     /* cfg.stage1_iou_thres as float32 */
+    /* outputs */
+    uint32_t *s2_out;           /* device (n2, Wd): stage-2 rows after merging (:258-281), n2_out rows used */
+    int32_t *n2_out;            /* host */
+    float *s2_conf_out;         /* host (n2) */
+    int32_t *match;             /* host (n2): argmax stage-1 index per remaining stage-2 mask (:288) */
+    float *match_iou;           /* host (n2): iou[k, match[k]] (:308) */
+    int32_t *best_match_log;    /* host (n2), optional: best_match_after_iou_check before merging (:252) */
+} bff_refine_desc;
+BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *stream);
+
+/* out[k] = rows[idx[k]] (device gather of packed rows; idx on the HOST). */
+BFF_API int bff_rows_gather(bff_ctx *ctx, const uint32_t *rows, int64_t words, const int32_t *idx_host, int32_t n_idx,
+                            uint32_t *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

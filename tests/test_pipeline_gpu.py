@@ -1,0 +1,65 @@
+"""GPU: the fused C++ pipelines (bff_stage2_aggregate, bff_refine_match) give exactly the results of the
+step-by-step Python/torch path (which the golden end-to-end tests pin to the reference), on scenes with
+hundreds of lifted masks, both point-filter modes, and against the CPU oracle port."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(inp, g, d, fused, cfg):
+    from bff_b200 import ops, refine, stage2
+    import bench
+    stage2.FUSED = refine.FUSED = fused
+    try:
+        masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+        out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], g.h, g.w, masks2d=masks2d, mask_offset=d["offsets"],
+                             frame_viewed=d["viewed"], depth_range=(0.0, 65.535))
+        res2, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, cfg,
+                                              keep_rows=fused)
+        s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), g.n)
+        p1 = refine.pass1_scene(inp["stage1"], res2, bench.QUERY, cfg["stage1_iou_thres"], bench.fake_similarity, g.dev, s1_rows=s1)
+        thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+        return res2, p1, refine.pass2_scene(p1, bench.QUERY, cfg["refiment_iou_thres"], thr)
+    finally:
+        stage2.FUSED = refine.FUSED = True
+
+
+def _same(a, b, what):
+    assert list(a["final_class"]) == list(b["final_class"]), what
+    if isinstance(a["ins"], list):
+        assert isinstance(b["ins"], list) and len(a["ins"]) == len(b["ins"]) == 0, what
+        return
+    assert torch.equal(a["ins"], b["ins"]), what
+    assert torch.equal(torch.as_tensor(a["conf"]), torch.as_tensor(b["conf"])), what
+
+
+@pytest.mark.parametrize("occurrence", [False, True])
+def test_fused_pipeline_equals_stepwise_and_port(cuda_dev, occurrence):
+    sys.path.insert(0, ROOT)
+    import bench
+    inp = bench.build_inputs("tiny", 0, 1, cuda_dev)
+    cfg = dict(inp["cfg"])
+    if occurrence:
+        cfg.update(if_occurance_threshold=True, if_detected_ratio_threshold=False)
+    inp["cfg"] = cfg
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    assert g.n_masks > 15
+    a2, ap1, afin = _run(inp, g, d, True, cfg)
+    b2, bp1, bfin = _run(inp, g, d, False, cfg)
+    assert a2["ins"].shape[0] >= 2 and afin["ins"].shape[0] >= 2
+    _same(a2, b2, "stage 2")
+    _same(afin, bfin, "final")
+    assert torch.equal(torch.as_tensor(ap1["ious"]), torch.as_tensor(bp1["ious"])) and ap1["sims"] == bp1["sims"]
+    # and the dense CPU port of the reference (oracle) on the same inputs
+    mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
+    pfin = bench.cpu_step(inp, mask_frames, view_frames)
+    assert torch.equal(afin["ins"], pfin["ins"]) and list(afin["final_class"]) == list(pfin["final_class"])
+    np.testing.assert_allclose(afin["conf"].numpy(), pfin["conf"].numpy(), rtol=1e-5)
