@@ -148,7 +148,7 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
     out_rows = agg[idx.to(agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
-    result = {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
+    result = {"ins": ops.to_host(ins), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
     return result, out_rows
 
 
@@ -210,4 +210,4 @@ def select_rows(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[
     out_rows = agg[idx.to(agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
-    return {"ins": ins.cpu(), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows
+    return {"ins": ops.to_host(ins), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows

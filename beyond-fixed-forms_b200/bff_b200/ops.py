@@ -277,3 +277,14 @@ def rle_to_bits(runs: np.ndarray, n_rows: int, length: int, device) -> torch.Ten
     """runs (R,3) int32 host [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32 on `device`."""
     runs = np.ascontiguousarray(runs, dtype=np.int32).reshape(-1, 3)
     return rle_to_bits_dev(torch.from_numpy(runs).to(device), n_rows, length)
+
+
+def to_host(t: torch.Tensor) -> torch.Tensor:
+    """Device -> host through pinned memory (torch's caching host allocator recycles the blocks), about 3x
+    the bandwidth of `.cpu()` into pageable memory for the multi-megabyte (Ins, N) bool outputs."""
+    if not t.is_cuda or t.numel() == 0:
+        return t.cpu()
+    out = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    out.copy_(t, non_blocking=True)
+    torch.cuda.current_stream(t.device).synchronize()
+    return out

@@ -162,7 +162,7 @@ def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float) -> dic
         out["final_class"].append(query)
     if picked:
         rows = torch.stack([src[k] for src, k in picked])
-        out["ins"] = ops.unpack_bits(rows, p1["n_points"]).cpu()
+        out["ins"] = ops.to_host(ops.unpack_bits(rows, p1["n_points"]))
         out["conf"] = torch.stack(out["conf"])
     return out
 
