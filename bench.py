@@ -11,8 +11,9 @@ RLE 2D masks -> packed bits, projection + visibility + mask gather + votes for e
 stage-1/stage-2 refinement of that scene. `value` = point-view projections (N x F, each
 (frame, point) counted once) per second of the WHOLE step with inputs resident in HBM; `e2e`
 is the same through the host API with pinned host buffers in and the final masks out.
-With N > 1 every rank lifts its own block of 300 frames of one (300 x N)-frame scene
-(weak scaling) and one exchange step follows (NCCL allreduce of votes + allgather of rows).
+With N > 1 every rank processes its OWN scene of that shape (scenes are the path's independent units:
+weak scaling, no data-path collective); the frame-sharded variant of one (300 x N)-frame scene with its
+NCCL exchange (allreduce of votes + allgather of rows) is measured in the same run as `frame_sharded`.
 
 Only the cpu_baseline / --impl reference legs touch oracle/ (the reference's numpy path
 restated, oracle/reference_port.py); the GPU arm raises if libbff.so is missing.
@@ -44,7 +45,7 @@ QUERY = "office chair"
 
 
 # ----------------------------------------------------------------------------- synthetic inputs
-def build_inputs(workload: str, rank: int, world: int, device, max_frames=None):
+def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, seed: int = 2000):
     """In-memory inputs of one scene in the reference's wire formats (RLE 2D masks per frame,
     uint16 depth, float64 poses/intrinsics, RLE stage-1 masks). Frames [rank*F, (rank+1)*F) of a
     (F*world)-frame trajectory are rendered on `device` (input fabrication, untimed)."""
@@ -55,7 +56,7 @@ def build_inputs(workload: str, rank: int, world: int, device, max_frames=None):
     f_rank = w["n_frames"]
     n_render = f_rank if max_frames is None else min(max_frames, f_rank)   # the CPU arms only need their sample
     spec = synth.SceneSpec(n_points=w["n_points"], n_frames=f_rank * world, width=w["width"], height=w["height"],
-                           n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=2000, n_queries=1)
+                           n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=seed, n_queries=1)
     sc = synth.make_scene(spec)
     lo, hi = rank * f_rank, (rank + 1) * f_rank
     hgt, wid = spec.height, spec.width
@@ -263,14 +264,12 @@ def run_gpu(args):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     import torch.distributed as dist
-    inp = build_inputs(args.workload, rank, world, dev)
-    g = GpuScene(inp, dev, ctx)
-    if world > 1:
-        gathered = [None] * world
-        dist.all_gather_object(gathered, (g.n_masks, [float(c) for c in g.conf_list], g.labels))
-        g.rows_per_rank = [x[0] for x in gathered]
-        g.all_conf = [torch.tensor(c) for x in gathered for c in x[1]]
-        g.all_labels = [l for x in gathered for l in x[2]]
+    # N > 1: scenes are the independent units of the path (the reference's outermost loop, :365), so the headline
+    # run gives every rank its OWN c2-shaped scene and needs no data-path collective (weak scaling); the
+    # frame-sharded variant of ONE scene (NCCL all-reduce + all-gather) is measured afterwards as `frame_sharded`.
+    # (every rank fabricates the same seeded scene, so per-GPU work is identical by construction)
+    inp = build_inputs(args.workload, 0, 1, dev)
+    g = GpuScene(inp, dev, None)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
     def barrier():
@@ -356,6 +355,9 @@ def run_gpu(args):
     e1 = _event()
     torch.cuda.synchronize()
     iou_ms = e0.elapsed_time(e1) / 10
+    fs = None
+    if world > 1 and not args.no_frame_sharded:
+        fs = frame_sharded_run(args, ctx, dev, flush, barrier)
     # ---- reduce over ranks (max time)
     t = torch.tensor([tot_ms, lift_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -379,7 +381,7 @@ def run_gpu(args):
         "config": {"workload": f"{args.workload}: ScanNet200-shaped scene, {g.n} points, {g.f} frames/GPU {g.w}x{g.h}, "
                                f"1 query, {g.n_masks} lifted 2D masks/GPU, {len(inp['stage1']['ins'])} stage-1 masks",
                    "n_points": g.n, "frames_per_gpu": g.f, "lifted_masks_per_gpu": g.n_masks,
-                   "parallelism": f"frame-sharded x{world}" if world > 1 else "single GPU",
+                   "parallelism": f"scene-parallel x{world}: one scene per GPU, no data-path collective" if world > 1 else "single GPU",
                    "l2": "256 MB flush written between timed steps; per-step inputs are 211 MB (> 126 MB L2)"},
         "stages_ms": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
                               (stage_acc / k).round(4).tolist())),
@@ -393,11 +395,50 @@ def run_gpu(args):
                      "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms_lift},
         "clocks": clocks,
     }
+    if fs is not None:
+        line["frame_sharded"] = fs
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(inp, args.cpu_frames)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if ctx:
         ctx.finalize()
+
+
+def frame_sharded_run(args, ctx, dev, flush, barrier):
+    """ONE scene of F x world frames, rank r lifting frames [r F, (r+1) F) (weak scaling in frames), then the one
+    exchange step (int32 vote all-reduce + rank-ordered row all-gather over NCCL) and aggregation/refinement on
+    every rank. Returns the secondary result object; max over ranks."""
+    import torch.distributed as dist
+    rank, world = ctx.rank, ctx.world_size
+    inp = build_inputs(args.workload, rank, world, dev)
+    g = GpuScene(inp, dev, ctx)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (g.n_masks, [float(c) for c in g.conf_list], g.labels))
+    g.rows_per_rank = [x[0] for x in gathered]
+    g.all_conf = [torch.tensor(c) for x in gathered for c in x[1]]
+    g.all_labels = [l for x in gathered for l in x[2]]
+    d = g.upload()
+    for _ in range(2):
+        g.step(d)
+    steps = max(1, min(args.steps, 5))
+    tot, stage = 0.0, np.zeros(5)
+    barrier()
+    for _ in range(steps):
+        flush.fill_(1)
+        barrier()
+        tm = []
+        g.step(d, tm)
+        torch.cuda.synchronize()
+        stage += np.asarray([tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)])
+        tot += tm[0].elapsed_time(tm[-1])
+    t = torch.tensor([tot], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.cpu()) / steps
+    return {"value": g.n * g.f * world / (ms * 1e-3), "unit": "point-views/s", "ms_per_step": ms, "steps": steps,
+            "frames_total": g.f * world, "lifted_masks_total": int(sum(g.rows_per_rank)),
+            "stages_ms_rank0": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
+                                        (stage / steps).round(4).tolist())),
+            "collectives": "all_reduce(SUM,int32)[votes] + all_gather[packed rows], NCCL"}
 
 
 # ----------------------------------------------------------------------------- CPU baseline (oracle port)
@@ -469,17 +510,35 @@ def run_reference(args):
     v = n * n_frames / dt
     sample = (f"each step = first {n_frames} of {inp['depth'].shape[0]} frames of the scene ({n} points), whole path; "
               "oracle/reference_port.py (numpy/OpenBLAS + torch CPU)")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "point-view projections/sec (whole lifting+aggregation+refinement step)",
         "value": v, "unit": "point-views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic", "config": {"workload": f"{args.workload} (bounded sample: {n_frames} frames per step)"},
         "cpu_baseline": {"value": v, "unit": "point-views/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "point-views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }), flush=True)
+    })
+
+
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line goes to the process's original stdout; everything else that libraries print to
+    fd 1 (NCCL's version banner, for instance) was diverted to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -488,6 +547,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-frames", type=int, default=40, help="frames in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the secondary frame-sharded measurement")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
