@@ -339,6 +339,30 @@ def run_gpu(args):
         final = g.step(g.upload())
         torch.cuda.synchronize()
         e2e_ms += (time.perf_counter() - t0) * 1e3
+    # ---- the same, as a scene loop is actually served: while scene i is processed, scene i+1's inputs are
+    # already moving host -> device on a copy stream (every step still uploads all of its own inputs and
+    # reads its result back inside the timed region; only the two are allowed to overlap)
+    copy_stream = torch.cuda.Stream(device=dev)
+
+    def upload_async():
+        with torch.cuda.stream(copy_stream):
+            dd = g.upload()
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return dd, ev
+    barrier()
+    t0 = time.perf_counter()
+    nxt = upload_async()
+    for i in range(args.steps):
+        dd, ev = nxt
+        if i + 1 < args.steps:
+            nxt = upload_async()
+        torch.cuda.current_stream().wait_event(ev)
+        for t_ in dd.values():
+            t_.record_stream(torch.cuda.current_stream())
+        final = g.step(dd)
+    torch.cuda.synchronize()
+    e2e_pipe_ms = (time.perf_counter() - t0) * 1e3
     d2h = 0
     if isinstance(final["ins"], torch.Tensor):
         d2h = final["ins"].numel() * final["ins"].element_size()
@@ -359,17 +383,17 @@ def run_gpu(args):
     if world > 1 and not args.no_frame_sharded:
         fs = frame_sharded_run(args, ctx, dev, flush, barrier)
     # ---- reduce over ranks (max time)
-    t = torch.tensor([tot_ms, lift_ms, e2e_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([tot_ms, lift_ms, e2e_ms, e2e_pipe_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    tot_ms, lift_ms, e2e_ms = (float(x) for x in t.cpu())
+    tot_ms, lift_ms, e2e_ms, e2e_pipe_ms = (float(x) for x in t.cpu())
     if rank != 0:
         if ctx:
             ctx.finalize()
         return
     k = args.steps
     pv = g.n * g.f * world
-    ms_step, ms_lift, ms_e2e = tot_ms / k, lift_ms / k, e2e_ms / k
+    ms_step, ms_lift, ms_e2e, ms_e2e_pipe = tot_ms / k, lift_ms / k, e2e_ms / k, e2e_pipe_ms / k
     peak, peak_src = measured_peak_hbm()
     alg = lift_algorithmic_bytes(g)
     achieved = alg / (ms_lift * 1e-3) / 1e9
@@ -387,8 +411,11 @@ def run_gpu(args):
                               (stage_acc / k).round(4).tolist())),
         "lift_point_views_per_s": pv / (ms_lift * 1e-3),
         "iou_pairs_per_s": (rows.shape[0] ** 2) / (iou_ms * 1e-3), "iou_call": f"{rows.shape[0]}x{rows.shape[0]} rows x {g.n} points, {iou_ms:.4f} ms",
-        "e2e": {"value": pv / (ms_e2e * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": int(g.h2d_bytes),
-                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e},
+        "e2e": {"value": pv / (ms_e2e_pipe * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": int(g.h2d_bytes),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e_pipe,
+                "how": "K consecutive scenes through the host API: pinned host inputs -> device -> step -> final masks on the "
+                       "host; scene i+1's upload overlaps scene i's compute (copy stream); wall clock over the K steps",
+                "serial_ms_per_step": ms_e2e, "serial_value": pv / (ms_e2e * 1e-3)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "bff::lift_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(args.workload), "peak_source": peak_src,

@@ -1,0 +1,63 @@
+"""CPU: host-side decision logic of the product (no GPU): component search fast path == general BFS,
+sequential float32 means, label equality, frame planning, RLE run clipping (Python-slice semantics)."""
+import numpy as np
+import torch
+
+from bff_b200 import aggregate, lift, rle
+
+
+def test_connected_groups_fast_path_equals_general_bfs():
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        n = int(rng.integers(1, 70))
+        a = rng.random((n, n)) < 0.05
+        a = a | a.T
+        for i in range(n):
+            if rng.random() < 0.3:
+                a[i, :] = False
+                a[:, i] = False
+        assert aggregate.connected_groups(torch.from_numpy(a)) == aggregate._connected_groups_general(a)
+    # asymmetric input takes the general path: reachability, not components
+    a = np.zeros((4, 4), bool)
+    a[0, 1] = a[1, 2] = True
+    assert aggregate.connected_groups(torch.from_numpy(a)) == [[1, 2], []]
+
+
+def test_sequential_float32_mean_matches_python_sum_of_tensors():
+    rng = np.random.default_rng(1)
+    for _ in range(100):
+        n = int(rng.integers(1, 60))
+        c = torch.from_numpy(rng.uniform(0.2, 0.45, n).astype(np.float32))
+        ref = sum([c[k] for k in range(n)]) / n                       # what merge_masks does (:220-224)
+        got = np.cumsum(c.numpy(), dtype=np.float32)[-1] / np.float32(n)
+        assert ref.item() == float(got)
+
+
+def test_label_equality():
+    m = aggregate.label_equality(["a", "b", "a", "c c", "b"])
+    exp = torch.tensor([[1, 0, 1, 0, 0], [0, 1, 0, 0, 1], [1, 0, 1, 0, 0], [0, 0, 0, 1, 0], [0, 1, 0, 0, 1]], dtype=torch.bool)
+    assert torch.equal(m, exp) and aggregate.label_equality([]).shape == (0, 0)
+
+
+def test_plan_frames_visits_each_frame_once_and_keeps_file_order():
+    q = lift.QueryMasks("q", ["30", "10", "50"], [[{}], [{}, {}], [{}]], [None] * 3, [["q"], ["q", "q"], ["q"]])
+    order, viewed, per_frame = lift.plan_frames([q], ["0", "10", "20", "30", "40"])
+    assert order == ["30", "10", "50", "0", "20", "40"]                # mask frames in FILE order, then view-only frames
+    assert viewed == [True, True, False, True, True, True]             # frame 50 has masks but is not a listed view
+    assert lift.query_row_index(per_frame, [q]) == [[0, 1, 2, 3]]
+    rles, mq, off = lift.mask_layout(per_frame, [q], 0, len(order))
+    assert off == [0, 1, 3, 4, 4, 4, 4] and mq == [0, 0, 0, 0]
+
+
+def test_rle_runs_follow_python_slice_semantics():
+    r = {"length": 50, "counts": np.array([0, 5, 48, 10, 60, 3, 10, 0, 20, 5], np.int64)}
+    lo, hi, L = rle.runs_of(r)
+    m = np.zeros(50, np.uint8)
+    for s, n in zip(r["counts"][0::2], r["counts"][1::2]):            # the reference's loop (refinement.py:33-38)
+        m[int(s) - 1:int(s) - 1 + int(n)] = 1
+    d = np.zeros(50, np.uint8)
+    for a, b in zip(lo, hi):
+        d[a:b] = 1
+    assert np.array_equal(d, m) and L == 50
+    runs, length = rle.runs_for_device([r, {"length": 50, "counts": np.zeros(0, np.int64)}])
+    assert length == 50 and set(runs[:, 0].tolist()) == {0}
