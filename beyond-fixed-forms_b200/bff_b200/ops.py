@@ -288,3 +288,20 @@ def to_host(t: torch.Tensor) -> torch.Tensor:
     out.copy_(t, non_blocking=True)
     torch.cuda.current_stream(t.device).synchronize()
     return out
+
+
+def upload(dst: torch.Tensor, src_pinned: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+    """dst (CUDA) <- src (pinned host) through bff_upload: an SM-driven copy that leaves the copy engines free.
+    Enqueued on `stream` (default: current)."""
+    if not (dst.is_cuda and dst.is_contiguous() and src_pinned.is_contiguous()):
+        raise ValueError("upload needs a contiguous CUDA destination and a contiguous host source")
+    if not src_pinned.is_pinned():
+        raise ValueError("upload needs pinned host memory")
+    nbytes = src_pinned.numel() * src_pinned.element_size()
+    if nbytes != dst.numel() * dst.element_size():
+        raise ValueError("size mismatch")
+    st = stream if stream is not None else torch.cuda.current_stream(dst.device)
+    check(lib().bff_upload(ptr(dst), c_void_p(src_pinned.data_ptr()), nbytes, c_void_p(st.cuda_stream)), "bff_upload")
+    if nbytes >= 16:
+        _count()
+    return dst

@@ -232,3 +232,43 @@ extern "C" int bff_mask_iou_host(bff_ctx *c, const uint32_t *a, int32_t n_a, con
     if (d2h_bytes) *d2h_bytes = down;
     return BFF_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// bff_upload: SM-driven host -> device copy (see include/bff.h). 32 CTAs x 512 threads x 4 x 16-byte loads keep
+// ~1 MB of reads in flight, enough to cover PCIe latency at full link bandwidth, while leaving the copy
+// engines free for the small staging copies of a pipeline that runs concurrently.
+namespace bff {
+__global__ void __launch_bounds__(512) upload_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, long long n16) {
+    const long long stride = (long long)gridDim.x * 512;
+    long long i = (long long)blockIdx.x * 512 + threadIdx.x;
+    for (; i + 3 * stride < n16; i += 4 * stride) {
+        const uint4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+        dst[i] = a; dst[i + stride] = b; dst[i + 2 * stride] = c; dst[i + 3 * stride] = d;
+    }
+    for (; i < n16; i += stride) dst[i] = src[i];
+}
+}  // namespace bff
+
+extern "C" int bff_upload(void *dst, const void *src_host, int64_t bytes, void *stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    BFF_REQUIRE(bytes >= 0, "bff_upload: negative size");
+    if (bytes == 0) return BFF_OK;
+    BFF_REQUIRE(dst && src_host, "bff_upload: null pointer");
+    BFF_REQUIRE((((uintptr_t)dst | (uintptr_t)src_host) & 15) == 0, "bff_upload: pointers must be 16-byte aligned");
+    void *src_dev = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer(&src_dev, const_cast<void *>(src_host), 0);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("bff_upload: source is not page-locked host memory (%s)", cudaGetErrorString(e));
+        return BFF_EINVAL;
+    }
+    const long long n16 = bytes / 16;
+    if (n16 > 0) {
+        upload_kernel<<<32, 512, 0, s>>>(reinterpret_cast<const uint4 *>(src_dev), reinterpret_cast<uint4 *>(dst), n16);
+        BFF_LAUNCH_CHECK("upload_kernel");
+    }
+    if (bytes & 15)
+        BFF_CUDA(cudaMemcpyAsync((char *)dst + n16 * 16, (const char *)src_host + n16 * 16, (size_t)(bytes & 15), cudaMemcpyHostToDevice, s));
+    return BFF_OK;
+}

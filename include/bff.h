@@ -232,6 +232,13 @@ typedef struct bff_refine_desc {
 } bff_refine_desc;
 BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *stream);
 
+/* Host -> device copy done by a small kernel that reads PINNED host memory directly (zero-copy loads over
+ * PCIe) instead of a copy engine. Used to prefetch the next scene's depth stack while the current scene is
+ * processed: a 180 MB cudaMemcpyAsync would occupy the H2D copy engine and every small staging copy of the
+ * running pipeline would queue behind it. `src_host` must be page-locked (cudaHostAlloc / cudaHostRegister /
+ * torch pin_memory); dst and src 16-byte aligned. */
+BFF_API int bff_upload(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
+
 /* out[k] = rows[idx[k]] (device gather of packed rows; idx on the HOST). */
 BFF_API int bff_rows_gather(bff_ctx *ctx, const uint32_t *rows, int64_t words, const int32_t *idx_host, int32_t n_idx,
                             uint32_t *out, void *stream);
