@@ -64,6 +64,8 @@ SYMBOLS = {
     "bff_last_error": (c_char_p, []),
     "bff_lift_scene": (c_int, [POINTER(LiftDesc), c_void_p]),
     "bff_lift_scene_launches": (c_int, [POINTER(LiftDesc)]),
+    "bff_visibility": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_double, c_void_p, c_void_p]),
+    "bff_mask_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "bff_mask_iou": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bff_rows_or_reduce": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_counts_max": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),

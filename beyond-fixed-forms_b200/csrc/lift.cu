@@ -513,3 +513,63 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     if (d->ev_stop) BFF_CUDA(cudaEventRecord((cudaEvent_t)d->ev_stop, stream));
     return BFF_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// Stand-alone forms of the reference's two per-frame helpers for callers that already hold pixel indices
+// (bff_b200/reference_api.py): compute_visibility_mask_tensor (:51-70) and
+// compute_visible_masked_pts_tensor (:73-92). The scene path uses the fused lift_kernel instead.
+namespace bff {
+__global__ void __launch_bounds__(256)
+visibility_kernel(const long long *__restrict__ pix, const double *__restrict__ z, long long n, const float *__restrict__ depth,
+                  int height, int width, double thresh, uint32_t *__restrict__ vis) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    bool v = false;
+    if (i < n) {
+        const long long px = pix[2 * i], py = pix[2 * i + 1];
+        if (px >= 0 && px < width && py >= 0 && py < height) {
+            const float d = __ldg(depth + py * width + px);
+            v = (d != 0.0f) && (fabs(z[i] - (double)d) < thresh);
+        }
+    }
+    const unsigned w = __ballot_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0 && i < n) vis[i >> 5] = w;
+}
+
+__global__ void __launch_bounds__(256)
+mask_gather_kernel(const long long *__restrict__ pix, const uint32_t *__restrict__ vis, long long n, const uint32_t *__restrict__ masks2d,
+                   long long mask_words, int width, long long words, uint32_t *__restrict__ rows) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    const int m = blockIdx.y;
+    bool bit = false;
+    if (i < n && ((vis[i >> 5] >> (i & 31)) & 1u)) {
+        const long long p = pix[2 * i + 1] * width + pix[2 * i];
+        bit = (__ldg(masks2d + (long long)m * mask_words + (p >> 5)) >> (p & 31)) & 1u;
+    }
+    const unsigned w = __ballot_sync(0xffffffffu, bit);
+    if ((threadIdx.x & 31) == 0 && i < n) rows[(long long)m * words + (i >> 5)] = w;
+}
+}  // namespace bff
+
+extern "C" int bff_visibility(const int64_t *pix, const double *z, int64_t n, const float *depth, int32_t height, int32_t width,
+                              double thresh, uint32_t *vis, void *stream_) {
+    BFF_REQUIRE(n >= 0 && height > 0 && width > 0, "bff_visibility: bad sizes");
+    if (n == 0) return BFF_OK;
+    BFF_REQUIRE(pix && z && depth && vis, "bff_visibility: null pointer");
+    visibility_kernel<<<(unsigned)ceil_div64(n, 256), 256, 0, (cudaStream_t)stream_>>>((const long long *)pix, z, n, depth, height, width, thresh, vis);
+    BFF_LAUNCH_CHECK("visibility_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_mask_gather(const int64_t *pix, const uint32_t *vis, int64_t n, const uint32_t *masks2d, int32_t n_masks,
+                               int32_t height, int32_t width, uint32_t *rows, void *stream_) {
+    BFF_REQUIRE(n >= 0 && n_masks >= 0 && height > 0 && width > 0, "bff_mask_gather: bad sizes");
+    if (n == 0 || n_masks == 0) return BFF_OK;
+    BFF_REQUIRE(pix && vis && masks2d && rows, "bff_mask_gather: null pointer");
+    BFF_REQUIRE(n_masks <= 65535, "bff_mask_gather: too many masks");
+    dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_masks);
+    mask_gather_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>((const long long *)pix, vis, n, masks2d,
+                                                                ceil_div64((long long)height * width, 32), width, ceil_div64(n, 32), rows);
+    BFF_LAUNCH_CHECK("mask_gather_kernel");
+    return BFF_OK;
+}

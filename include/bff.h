@@ -110,6 +110,15 @@ BFF_API int bff_lift_scene(const bff_lift_desc *desc, void *stream);
 /* Number of kernels bff_lift_scene launches for this description (for launch accounting). */
 BFF_API int bff_lift_scene_launches(const bff_lift_desc *desc);
 
+/* Stand-alone per-frame helpers for callers that already hold pixel indices (the scene path is bff_lift_scene):
+ * compute_visibility_mask_tensor (projection_2d_to_3d.py:51-70): pix (n,2) int64 [x,y], z (n) float64 camera z,
+ * depth (H,W) float32 -> packed visibility bits (ceil(n/32)); and compute_visible_masked_pts_tensor (:73-92):
+ * packed 2D masks (n_masks, ceil(H*W/32)) sampled at the visible points -> packed rows (n_masks, ceil(n/32)). */
+BFF_API int bff_visibility(const int64_t *pix, const double *z, int64_t n, const float *depth, int32_t height, int32_t width,
+                           double thresh, uint32_t *vis, void *stream);
+BFF_API int bff_mask_gather(const int64_t *pix, const uint32_t *vis, int64_t n, const uint32_t *masks2d, int32_t n_masks,
+                            int32_t height, int32_t width, uint32_t *rows, void *stream);
+
 /* Replaces calculate_iou (projection_2d_to_3d.py:149-166) and calculate_iou_between_stages
  * (refinement.py:69-90, before its transpose): a (nA, Wd), b (nB, Wd) packed rows ->
  * inter (nA, nB) int32, pop_a (nA), pop_b (nB) int32, and optionally iou (nA, nB) float32 =

@@ -9,6 +9,9 @@ import sys
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "beyond-fixed-forms_b200"))
 
 from bff_b200.refine import main  # noqa: E402
+# the reference's importable functions, same names and signatures, served by the GPU library
+from bff_b200.reference_api import (  # noqa: E402,F401
+    rle_decode, calculate_iou_between_stages)
 
 if __name__ == "__main__":
     sys.exit(main())
