@@ -86,6 +86,67 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
                                 xyz.shape[0], cfg)
 
 
+def process_scene_queries(cfg, classes, scene_id: str, device):
+    """Several text queries of ONE scene in one pass (BASELINE config 3): projection,
+    visibility and viewed_counts are computed once and shared, the 2D masks of all queries are gathered in
+    the same launch (per-query vote buffers), then each query is aggregated and filtered on its own rows.
+    Returns {cls: (dict to save, reached_filter)}; every dict equals what process_scene gives for that class."""
+    width, height = int(cfg_get(cfg, "width_2d")), int(cfg_get(cfg, "height_2d"))
+    scene_2d_dir = cfg_get(cfg, "scene_2d_dir")
+    intr = scene_io.load_intrinsics(scene_2d_dir, scene_id)
+    xyz = scene_io.load_cloud(cfg_get(cfg, "scene_npy_dir"), scene_id)
+    queries = []
+    for cls in classes:
+        records = scene_io.torch_load(os.path.join(cfg_get(cfg, "mask_2d_dir"), cls, f"{scene_id}.pth"))
+        queries.append(lift_mod.QueryMasks.from_file_records(cls, records))
+    want_viewed = needs_viewed_counts(cfg)
+    any_masks = any(len(r) for q in queries for r in q.rles)
+    view_ids = scene_io.list_view_frames(scene_2d_dir, scene_id, int(cfg_get(cfg, "downsample_ratio"))) if (want_viewed and any_masks) else None
+    frame_ids, viewed, per_frame = lift_mod.plan_frames(queries, view_ids)
+    out = {}
+    if not frame_ids:
+        return {q.query: aggregate_and_filter(None, [], [], None, None, xyz.shape[0], cfg) for q in queries}
+    frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height)
+    lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, queries, height, width,
+                           want_viewed and any_masks)
+    for qi, q in enumerate(queries):
+        conf_list, labels = q.flat_conf_and_labels()
+        out[q.query] = aggregate_and_filter(lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts,
+                                            xyz.shape[0], cfg)
+    return out
+
+
+def main_multi(argv=None):
+    """tools/projection_2d_to_3d_multi.py: `--config C --cls q1 q2 ...` -- the same outputs and checkpoints as one
+    reference run per class, with the per-scene projection shared by all classes."""
+    import argparse
+    import yaml
+    parser = argparse.ArgumentParser(description="BeyondFF lifting for several classes at once")
+    parser.add_argument("--config", type=str, required=True)
+    parser.add_argument("--cls", type=str, nargs="+", required=True)
+    args = parser.parse_args(argv)
+    _log.VERBOSE = True
+    cfg = yaml.safe_load(open(args.config, "r").read())
+    if not torch.cuda.is_available():
+        raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    device = torch.device("cuda", 0)
+    scenes = None
+    for cls in args.cls:                                   # the classes must list the same scenes
+        names = sorted(s for s in os.listdir(os.path.join(cfg["mask_2d_dir"], cls)) if s.endswith("_00.pth"))
+        if scenes is not None and names != scenes:
+            raise ValueError(f"class {cls!r} lists other scenes than {args.cls[0]!r}")
+        scenes = names
+    ckpts = {cls: scene_io.read_checkpoint(f"checkpoints/projection_2d_to_3d_checkpoint_{cls}.yaml") for cls in args.cls}
+    for s in scenes:
+        scene_id = s[:-4]
+        for cls, (result, reached_filter) in process_scene_queries(cfg, args.cls, scene_id, device).items():
+            scene_io.save_result(result, cfg["mask_3d_dir"], cls, scene_id)
+            if reached_filter:
+                ckpts[cls][scene_id] = True
+                scene_io.write_checkpoint(f"checkpoints/projection_2d_to_3d_checkpoint_{cls}.yaml", ckpts[cls])
+    return 0
+
+
 def main(argv=None):
     """CLI body of tools/projection_2d_to_3d.py: same arguments, config keys, outputs, checkpoints."""
     import argparse

@@ -35,3 +35,19 @@ def test_cli_outputs_match_reference(cuda_dev, tmp_path, monkeypatch, cfg_name, 
         check_against_expected(got2, expected[(cfg_name, cls, "mask_3d", sid)], f"stage2 {cls} {sid}")
         check_against_expected(gotf, expected[(cfg_name, cls, "final", sid)], f"final {cls} {sid}")
     assert os.path.exists(os.path.join(tree, "checkpoints", f"projection_2d_to_3d_checkpoint_{cls}.yaml"))
+
+
+@pytest.mark.parametrize("cfg_name,out2", [("config.yaml", "output/mask_3d"), ("config_occ.yaml", "output_occ/mask_3d")])
+def test_multi_query_run_equals_one_reference_run_per_class(cuda_dev, tmp_path, monkeypatch, cfg_name, out2):
+    """Two text queries lifted in ONE pass per scene (shared projection / visibility / viewed counts, per-query
+    votes) must write what the reference wrote when it was run once per class."""
+    from bff_b200 import stage2
+    tree = copy_tree(tmp_path)
+    monkeypatch.chdir(tree)
+    expected = load_expected()
+    classes = ["office chair", "table"]
+    assert stage2.main_multi(["--config", cfg_name, "--cls"] + classes) == 0
+    for cls in classes:
+        for sid in ("scene0001_00", "scene0002_00", "scene0003_00"):
+            got = torch.load(os.path.join(tree, out2, cls, f"{sid}.pth"), weights_only=False)
+            check_against_expected(got, expected[(cfg_name, cls, "mask_3d", sid)], f"multi stage2 {cls} {sid}")
