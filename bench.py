@@ -109,6 +109,7 @@ class GpuScene:
         assert length == self.h * self.w
         self.n_masks = len(rles)
         self.conf_list, self.labels = q.flat_conf_and_labels()
+        self.conf_list = torch.tensor(self.conf_list) if self.conf_list else []   # :484-486, parsed once with the file
         s1_runs, s1_len = runs_for_device(list(inp["stage1"]["ins"]))
         assert s1_len == self.n
 
@@ -132,8 +133,9 @@ class GpuScene:
     def upload(self):
         return {k: v.to(self.dev, non_blocking=True) for k, v in self.host.items()}
 
-    def step(self, d, timers=None):
-        """One pass of the hot path on device-resident inputs `d`. Returns the final dict (host)."""
+    def step(self, d, timers=None, to_host=True):
+        """One pass of the hot path on device-resident inputs `d`. Returns the final dict; its (k,N) bool masks
+        are copied to the host (pinned) when `to_host`, else they stay in HBM like the inputs."""
         from bff_b200 import ops, refine, stage2
         inp, cfg = self.inp, self.inp["cfg"]
         ev = (lambda: None) if timers is None else (lambda: timers.append(_event()))
@@ -152,12 +154,12 @@ class GpuScene:
             rows, mc, vc = dist_mod.exchange(self.dist, rows, self.rows_per_rank, mc, vc)
             conf_list, labels = self.all_conf, self.all_labels
         ev()
-        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg, keep_rows=True)
+        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg, keep_rows=True, to_host=to_host)
         ev()
         s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
         p1 = refine.pass1_scene(inp["stage1"], res2, QUERY, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)
         thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
-        final = refine.pass2_scene(p1, QUERY, cfg["refiment_iou_thres"], thr)
+        final = refine.pass2_scene(p1, QUERY, cfg["refiment_iou_thres"], thr, to_host=to_host)
         ev()
         self.last_stage2 = res2
         return final
@@ -320,7 +322,7 @@ def run_gpu(args):
         flush.fill_(1)
         torch.cuda.synchronize()
         tm = []
-        final = g.step(d, tm)
+        final = g.step(d, tm, to_host=False)
         torch.cuda.synchronize()
         ms = [tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)]
         stage_acc += np.asarray(ms)
@@ -451,7 +453,7 @@ def frame_sharded_run(args, ctx, dev, flush, barrier):
     gathered = [None] * world
     dist.all_gather_object(gathered, (g.n_masks, [float(c) for c in g.conf_list], g.labels))
     g.rows_per_rank = [x[0] for x in gathered]
-    g.all_conf = [torch.tensor(c) for x in gathered for c in x[1]]
+    g.all_conf = torch.tensor([c for x in gathered for c in x[1]], dtype=torch.float32)
     g.all_labels = [l for x in gathered for l in x[2]]
     d = g.upload()
     for _ in range(2):

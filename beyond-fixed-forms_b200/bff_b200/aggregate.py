@@ -135,7 +135,7 @@ def overlap_program(inter: torch.Tensor, group_sizes: Sequence[int]) -> List[Tup
 
 
 def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[str], groups: List[List[int]],
-                      keep_bits: torch.Tensor, n_points: int, cfg):
+                      keep_bits: torch.Tensor, n_points: int, cfg, to_host: bool = True):
     """projection_2d_to_3d.py:583-634: overlap resolution, AND with the kept points, row filter,
     and (the dict that is saved, the packed rows of its masks)."""
     inter, before, _, _ = ops.mask_iou(agg, want_iou=False)
@@ -148,7 +148,7 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
     out_rows = agg[idx.to(agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
-    result = {"ins": ops.to_host(ins), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
+    result = {"ins": ops.to_host(ins) if to_host else ins, "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
     return result, out_rows
 
 
@@ -203,11 +203,11 @@ def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Seque
 
 
 def select_rows(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[str], before64: torch.Tensor,
-                after64: torch.Tensor, n_points: int, cfg):
+                after64: torch.Tensor, n_points: int, cfg, to_host: bool = True):
     """Row filter + the saved dict (projection_2d_to_3d.py:601-634), torch semantics for the comparisons."""
     sel = (after64 > cfg["remove_small_masks"]) & (after64 > cfg["remove_filtered_masks"] * before64)
     idx = torch.nonzero(sel).reshape(-1)
     out_rows = agg[idx.to(agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
-    return {"ins": ops.to_host(ins), "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows
+    return {"ins": ops.to_host(ins) if to_host else ins, "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows

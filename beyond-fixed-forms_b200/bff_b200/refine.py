@@ -49,7 +49,7 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
     q_ = query.replace(" ", "_")
     s1 = stage1_rows(stage1, device) if s1_rows is None else s1_rows
     n_points = int(stage1["ins"][0]["length"]) if len(stage1["ins"]) else 0
-    labels = [idx_to_label(i) for i in stage1["final_class"]]
+    labels = [STAGE1_CLASS_NAMES[i] for i in torch.as_tensor(stage1["final_class"]).tolist()]
     if len(stage2["conf"]) == 0:
         log("Empty stage 2 mask")
         other = [i for i, l in enumerate(labels) if l == q_]
@@ -143,27 +143,40 @@ def similarity_threshold(all_sims: Sequence[Sequence[float]], percentile: float)
     return u[int(len(u) * percentile)]
 
 
-def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float) -> dict:
-    """Selection (refinement.py:330-426) -> the dict that is saved."""
+def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float, to_host: bool = True) -> dict:
+    """Selection (refinement.py:330-426) -> the dict that is saved: the other stage-1 masks of the class first
+    (conf 0.5), then per matched pair the stage-1 mask (IoU above the threshold and CLIP-similar enough), nothing
+    (IoU above, not similar) or the stage-2 mask (IoU not above); confidences are the stage-2 ones."""
     out = {"ins": [], "conf": [], "final_class": []}
-    picked = []                                  # (source rows tensor, row index)
-    for k in range(p1["other"].shape[0]):
-        picked.append((p1["other"], k))
-        out["conf"].append(torch.tensor(0.5))
-        out["final_class"].append(query)
+    n_other = p1["other"].shape[0]
+    kept, from_s1 = [], []
     for k, iou in enumerate(p1["ious"]):
-        if iou > iou_thres:
+        if iou > iou_thres:                      # float32 tensor element vs python float, like the reference (:360)
             if p1["sims"][k] < sim_thres:
                 continue
-            picked.append((p1["m1"], k))
+            kept.append(k)
+            from_s1.append(True)
         else:
-            picked.append((p1["m2"], k))
-        out["conf"].append(p1["conf2"][k])
-        out["final_class"].append(query)
-    if picked:
-        rows = torch.stack([src[k] for src, k in picked])
-        out["ins"] = ops.to_host(ops.unpack_bits(rows, p1["n_points"]))
-        out["conf"] = torch.stack(out["conf"])
+            kept.append(k)
+            from_s1.append(False)
+    total = n_other + len(kept)
+    if total == 0:
+        return out
+    out["final_class"] = [query] * total
+    parts = [p1["other"]] if n_other else []
+    if kept:
+        dev = p1["m2"].device
+        k_dev = torch.tensor(kept, dtype=torch.long, device=dev)
+        s1_flag = torch.tensor(from_s1, dtype=torch.bool, device=dev).unsqueeze(1)
+        parts.append(torch.where(s1_flag, p1["m1"][k_dev], p1["m2"][k_dev]))
+    rows = torch.cat(parts) if len(parts) > 1 else parts[0]
+    ins = ops.unpack_bits(rows, p1["n_points"])
+    out["ins"] = ops.to_host(ins) if to_host else ins
+    conf2 = p1["conf2"]
+    if isinstance(conf2, torch.Tensor) and conf2.dtype == torch.float32:
+        out["conf"] = torch.cat([torch.full((n_other,), 0.5), conf2[torch.tensor(kept, dtype=torch.long)]])
+    else:                                        # mixed dtypes: let torch.stack promote exactly like the reference (:412)
+        out["conf"] = torch.stack([torch.tensor(0.5)] * n_other + [conf2[k] for k in kept])
     return out
 
 

@@ -24,7 +24,7 @@ def needs_viewed_counts(cfg) -> bool:
 
 
 def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor, vc: Optional[torch.Tensor],
-                         n_points: int, cfg, keep_rows: bool = False):
+                         n_points: int, cfg, keep_rows: bool = False, to_host: bool = True):
     """Everything after the frame loop (projection_2d_to_3d.py:463-634) for one query.
     Returns (dict to save, reached_filter) -- the reference only writes its scene checkpoint when
     the filter stage is reached (:580-581)."""
@@ -34,7 +34,7 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
     if len(conf_list) == 0:
         log("No 3d masks detected in backprojection!")
         return scene_io.empty_stage2(), False
-    conf = torch.tensor(conf_list)                                  # :484-486
+    conf = conf_list if isinstance(conf_list, torch.Tensor) else torch.tensor(conf_list)    # :484-486
     if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
         fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c)
         if fused is None:
@@ -42,7 +42,7 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
             return scene_io.empty_stage2(), False
         agg, conf_agg, labels_agg, groups, before64, after64 = fused
         log("before filtering", torch.Size([agg.shape[0], n_points]))
-        result, out_rows = aggregate.select_rows(agg, conf_agg, labels_agg, before64, after64, n_points, c)
+        result, out_rows = aggregate.select_rows(agg, conf_agg, labels_agg, before64, after64, n_points, c, to_host)
         if keep_rows:
             result["rows"] = out_rows        # packed CUDA rows for an in-process refinement (never saved)
         return result, True
@@ -52,7 +52,7 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
         return scene_io.empty_stage2(), False
     keep = aggregate.keep_points(mc, vc, c)
     log("before filtering", torch.Size([agg.shape[0], n_points]))
-    result, out_rows = aggregate.filter_and_select(agg, conf_agg, labels_agg, groups, keep, n_points, c)
+    result, out_rows = aggregate.filter_and_select(agg, conf_agg, labels_agg, groups, keep, n_points, c, to_host)
     if keep_rows:
         result["rows"] = out_rows
     return result, True

@@ -17,12 +17,14 @@ namespace bff {
 
 // adjacency of the merge graph: same label AND iou > thr, IoU in float32 as calculate_iou computes it
 // (projection_2d_to_3d.py:120-122,158-165). NaN (0/0) compares false.
+// Rows of `adj` are padded to `stride` (a multiple of 8) bytes so the host can scan them 8 bytes at a time.
 __global__ void merge_adjacency_kernel(const int32_t *__restrict__ inter, const int32_t *__restrict__ pop,
-                                       const int32_t *__restrict__ label, int n, float thr, uint8_t *__restrict__ adj) {
+                                       const int32_t *__restrict__ label, int n, int stride, float thr, uint8_t *__restrict__ adj) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (long long)n * n) return;
-    const int r = (int)(i / n), c = (int)(i % n);
-    const float fi = __int2float_rn(inter[i]);
+    if (i >= (long long)n * stride) return;
+    const int r = (int)(i / stride), c = (int)(i % stride);
+    if (c >= n) { adj[i] = 0; return; }
+    const float fi = __int2float_rn(inter[(long long)r * n + c]);
     const float un = __fsub_rn(__fadd_rn(__int2float_rn(pop[r]), __int2float_rn(pop[c])), fi);
     adj[i] = (label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
 }
@@ -104,16 +106,18 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
     PIPE_TAKE(d_inter, c->dev, int32_t, nn);
     PIPE_TAKE(d_pop, c->dev, int32_t, n);
-    PIPE_TAKE(d_adj, c->dev, uint8_t, nn);
-    PIPE_TAKE(h_adj, c->pin, uint8_t, nn);
+    const int stride = (n + 7) & ~7;
+    const size_t adj_bytes = (size_t)n * stride;
+    PIPE_TAKE(d_adj, c->dev, uint8_t, adj_bytes);
+    PIPE_TAKE(h_adj, c->pin, uint8_t, adj_bytes);
     int32_t *d_label = nullptr;
     int rc = upload_i32(c, std::vector<int32_t>(d->label_id, d->label_id + n), &d_label, s);
     if (rc != BFF_OK) return rc;
     rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
     if (rc != BFF_OK) return rc;
-    merge_adjacency_kernel<<<(unsigned)ceil_div64((int64_t)nn, 256), 256, 0, s>>>(d_inter, d_pop, d_label, n, d->iou_thres, d_adj);
+    merge_adjacency_kernel<<<(unsigned)ceil_div64((int64_t)adj_bytes, 256), 256, 0, s>>>(d_inter, d_pop, d_label, n, stride, d->iou_thres, d_adj);
     BFF_LAUNCH_CHECK("merge_adjacency_kernel");
-    BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, nn, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));
     BFF_CUDA(cudaStreamSynchronize(s));
 
     // ---- connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric, so the
@@ -122,9 +126,14 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     UnionFind uf(n);
     std::vector<char> has_edge(n, 0);
     for (int i = 0; i < n; ++i) {
-        const uint8_t *row = h_adj + (size_t)i * n;
-        for (int j = 0; j < n; ++j)
-            if (row[j]) { has_edge[i] = 1; if (j > i) uf.unite(i, j); }
+        const uint8_t *row = h_adj + (size_t)i * stride;
+        for (int j0 = 0; j0 < stride; j0 += 8) {
+            uint64_t w;
+            memcpy(&w, row + j0, 8);
+            if (!w) continue;                                   // the merge graph is sparse: skip 8 zero entries at once
+            for (int j = j0; j < j0 + 8; ++j)
+                if (row[j]) { has_edge[i] = 1; if (j > i) uf.unite(i, j); }
+        }
     }
     std::vector<int> root(n), count(n, 0);
     for (int i = 0; i < n; ++i) { root[i] = uf.find(i); count[root[i]]++; }
