@@ -4,9 +4,22 @@
 // A packed row is Wd = ceil(N/32) uint32 words; every kernel here is integer work on those
 // words (AND / OR / POPC), bit-exact by construction. Reference lines replaced are cited at
 // each entry point and in include/bff.h.
+#include <stdlib.h>
+
 #include "common.cuh"
+#include "iou_umma.cuh"
 
 namespace bff {
+
+// Row counts from which the tcgen05 (int8 tensor core) intersection beats the POPC kernel: the tensor path
+// works on 128 x 128 row tiles, so small operands (the 200 x 7 refinement calls) stay on the CUDA cores.
+// BFF_IOU_PATH=popc|umma forces one path (used by the tests to cross-check them).
+static int iou_use_umma(int n_a, int n_b, long long words) {
+    const char *e = getenv("BFF_IOU_PATH");
+    if (e && e[0] == 'p') return 0;
+    if (e && e[0] == 'u') return 1;
+    return n_a >= 96 && n_b >= 96 && words >= 64;
+}
 
 // ------------------------------------------------------------------ row popcounts
 __global__ void __launch_bounds__(256) row_popcount_kernel(const uint32_t *__restrict__ rows, long long words,
@@ -239,8 +252,12 @@ extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, i
             if (slices > 65535) slices = 65535;
             long long wps = ceil_div64(ceil_div64(words, slices), kKW) * kKW;
             slices = ceil_div64(words, wps);
-            dim3 grid((unsigned)tb, (unsigned)ta, (unsigned)slices);
-            intersect_kernel<<<grid, 256, 0, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter);
+            if (iou_use_umma(n_a, n_b, words)) {
+                BFF_CUDA(umma::launch_intersect(a, n_a, b, n_b, words, symmetric, inter, kNumSMs, stream));
+            } else {
+                dim3 grid((unsigned)tb, (unsigned)ta, (unsigned)slices);
+                intersect_kernel<<<grid, 256, 0, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter);
+            }
         }
     }
     if (iou) {

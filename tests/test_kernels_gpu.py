@@ -241,3 +241,30 @@ def test_lift_half_integer_pixels_round_like_numpy(cuda_dev):
     np.testing.assert_array_equal(unpack_rows(out.rows.cpu().numpy(), n), rows_o)
     np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)
     np.testing.assert_array_equal(out.masked_counts.cpu().numpy(), mc_o)
+
+
+@pytest.mark.parametrize("na,nb,n", [(130, 97, 4099), (257, 129, 12345), (300, 300, 100001), (96, 513, 2049)])
+def test_tensor_core_intersections_equal_popc_path_and_oracle(cuda_dev, monkeypatch, na, nb, n):
+    """The tcgen05 (int8, TMEM) intersection kernel against the POPC kernel and the C oracle on ragged shapes:
+    rows not multiples of 128, word counts not multiples of the 4-word stage, square (symmetric) and rectangular."""
+    import oracle as O
+    from bff_b200 import ops
+    rng = np.random.default_rng(na * 7 + nb)
+    a = rng.random((na, n)) < rng.uniform(0, 0.4, size=(na, 1))
+    b = rng.random((nb, n)) < 0.15
+    a[5] = False
+    da = torch.from_numpy(pack_rows(a).view(np.int32)).to(cuda_dev)
+    db = torch.from_numpy(pack_rows(b).view(np.int32)).to(cuda_dev)
+    res = {}
+    for path in ("umma", "popc"):
+        monkeypatch.setenv("BFF_IOU_PATH", path)
+        res[path] = (ops.mask_iou(da, db), ops.mask_iou(da))
+    for k in range(2):
+        for t_u, t_p in zip(res["umma"][k], res["popc"][k]):
+            assert torch.equal(torch.nan_to_num(t_u.float(), nan=-1.0), torch.nan_to_num(t_p.float(), nan=-1.0))
+    inter_o, iou_o = O.mask_iou(a[:40], b)
+    np.testing.assert_array_equal(res["umma"][0][0].cpu().numpy()[:40], inter_o)
+    nan = np.isnan(iou_o)
+    got = res["umma"][0][3].cpu().numpy()[:40]
+    assert np.array_equal(np.isnan(got), nan)
+    np.testing.assert_array_equal(got[~nan].view(np.int32), iou_o[~nan].view(np.int32))
