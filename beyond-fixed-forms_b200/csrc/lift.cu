@@ -18,6 +18,10 @@
 // so only the explicit fma() calls fuse.
 #include <cuda.h>
 #include <math.h>
+#include <string.h>
+
+#include <atomic>
+#include <cmath>
 
 #include "common.cuh"
 
@@ -55,6 +59,8 @@ struct LiftParams {
     double thresh;
     double z_lo, z_hi;     // camera-z window outside which no depth can match
     double w_hi, h_hi;     // (W + 1), (H + 1) for the conservative frustum pre-test
+    double wd, hd;         // (double)W, (double)H
+    long long hw;          // H * W
     long long n_points;
     long long words;       // Wd
     long long mask_words;  // ceil(H*W/32)
@@ -63,6 +69,8 @@ struct LiftParams {
     int height, width;
     int n_queries;
     float depth_scale;
+    float depth_rcp;       // 1 / depth_scale in float32
+    int fast_div;          // x / depth_scale == the 3-operation sequence of depth_value() for every uint16 x (checked on the host)
     int atomic_flush;      // >1 frame chunk: counts are combined with atomics
 };
 
@@ -135,6 +143,36 @@ __device__ __forceinline__ bool warp_sphere(bool valid, double x, double y, doub
     const double dx = x - cx, dy = y - cy, dz = z - cz;
     const double d2 = warp_max(valid ? (dx * dx + dy * dy + dz * dz) : 0.0);
     cr = sqrt(d2) * (1.0 + kCullEps) + kCullEps * (fabs(cx) + fabs(cy) + fabs(cz));
+    return __any_sync(0xffffffffu, valid);
+}
+
+// The same sphere for float32 clouds with one redux.sync per extreme instead of five shuffle rounds each:
+// floats map monotonically to unsigned integers, the squared radius is rounded UP to float32 first, so
+// the sphere only ever grows. Lanes with a NaN coordinate do not contribute (such points are never visible).
+__device__ __forceinline__ unsigned f32_ordered(float v) {
+    const unsigned u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ double f32_unordered(unsigned u) {
+    return (double)__uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+__device__ __forceinline__ bool warp_sphere_f32(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr) {
+    const float fx = (float)x, fy = (float)y, fz = (float)z;      // exact: the cloud is float32
+    const bool use = valid && fx == fx && fy == fy && fz == fz;
+    const unsigned lo = 0xff800000u /* ordered(+inf) */, hi = 0x007fffffu /* ordered(-inf) */;
+    const double lx = f32_unordered(__reduce_min_sync(0xffffffffu, use ? f32_ordered(fx) : lo));
+    const double hx = f32_unordered(__reduce_max_sync(0xffffffffu, use ? f32_ordered(fx) : hi));
+    const double ly = f32_unordered(__reduce_min_sync(0xffffffffu, use ? f32_ordered(fy) : lo));
+    const double hy = f32_unordered(__reduce_max_sync(0xffffffffu, use ? f32_ordered(fy) : hi));
+    const double lz = f32_unordered(__reduce_min_sync(0xffffffffu, use ? f32_ordered(fz) : lo));
+    const double hz = f32_unordered(__reduce_max_sync(0xffffffffu, use ? f32_ordered(fz) : hi));
+    cx = 0.5 * lx + 0.5 * hx;
+    cy = 0.5 * ly + 0.5 * hy;
+    cz = 0.5 * lz + 0.5 * hz;
+    const double dx = x - cx, dy = y - cy, dz = z - cz;
+    const float d2 = use ? __double2float_ru(dx * dx + dy * dy + dz * dz) : 0.0f;   // >= 0: bit pattern order == value order
+    const double r2 = (double)__uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(d2)));
+    cr = sqrt(r2) * (1.0 + kCullEps) + kCullEps * (fabs(cx) + fabs(cy) + fabs(cz));
     return __any_sync(0xffffffffu, valid);
 }
 
@@ -215,22 +253,31 @@ __device__ __forceinline__ bool locate_pixel(const LiftParams &p, const double *
         o[0] = f64_to_i64_numpy(xr);
         o[1] = f64_to_i64_numpy(yr);
     }
-    if (!(xr >= 0.0 && xr < (double)p.width && yr >= 0.0 && yr < (double)p.height)) return false;
+    if (!(xr >= 0.0 && xr < p.wd && yr >= 0.0 && yr < p.hd)) return false;
     pix = (int)yr * p.width + (int)xr;
     return true;
 }
 
 template <int DEPTH_KIND>
 __device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, int pix) {
-    const long long off = (long long)f * p.height * p.width + pix;
+    const long long off = (long long)f * p.hw + pix;
     if (DEPTH_KIND == BFF_DEPTH_U16) return (unsigned)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + off);
     return __ldg(reinterpret_cast<const unsigned *>(p.depth) + off);
 }
 
 template <int DEPTH_KIND>
-__device__ __forceinline__ float depth_value(unsigned raw, float depth_scale) {
-    // uint16 sensor units -> float32 metres exactly as projection_2d_to_3d.py:431-435 (fp32 divide)
-    if (DEPTH_KIND == BFF_DEPTH_U16) return __fdiv_rn((float)raw, depth_scale);
+__device__ __forceinline__ float depth_value(unsigned raw, const LiftParams &p) {
+    // uint16 sensor units -> float32 metres exactly as projection_2d_to_3d.py:431-435 (fp32 divide).
+    // fast_div: q = x * rcp, one residual correction -- the correctly rounded quotient for every uint16 x
+    // (bff_lift_scene checks all 65536 values on the host before it sets the flag); else the IEEE divide.
+    if (DEPTH_KIND == BFF_DEPTH_U16) {
+        const float x = (float)raw;
+        if (p.fast_div) {
+            const float q = __fmul_rn(x, p.depth_rcp);
+            return __fmaf_rn(__fmaf_rn(-q, p.depth_scale, x), p.depth_rcp, q);
+        }
+        return __fdiv_rn(x, p.depth_scale);
+    }
     return __uint_as_float(raw);
 }
 
@@ -303,7 +350,8 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     if (!DEBUG && tid < nf) build_frame_planes(s_pose + tid * 16, p, s_plane + tid, fc);
     // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible)
     double cx, cy, cz, cr;
-    const bool warp_has_points = warp_sphere(valid, x, y, z, cx, cy, cz, cr);
+    const bool warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr)
+                                                             : warp_sphere(valid, x, y, z, cx, cy, cz, cr);
     for (int i = tid; i <= nf; i += kLiftThreads) {
         s_moff[i] = p.mask_offset != nullptr ? __ldg(p.mask_offset + f0 + i) : 0;
         if (i < nf) s_view[i] = (p.frame_viewed == nullptr || __ldg(p.frame_viewed + f0 + i)) ? 1 : 0;
@@ -351,20 +399,29 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             const int f = f0 + fl;
             const int pidx = half ? pixB : pixA;
             const double Z = half ? ZB : ZA;
-            const float d = depth_value<DEPTH_KIND>(half ? rawB : rawA, p.depth_scale);
+            const float d = depth_value<DEPTH_KIND>(half ? rawB : rawA, p);
             // :62-66: in bounds, depth != 0 and |z - depth| < thresh in float64
             const bool vis = (half ? inB : inA) && (d != 0.0f) && (fabs(Z - (double)d) < p.thresh);
-            if (p.dbg_vis != nullptr) {
-                const unsigned vw = __ballot_sync(0xffffffffu, vis);
-                if (lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
-            }
+            // the warp's visibility word; a warp without any visible point owes this frame nothing more
+            const unsigned vw = __ballot_sync(0xffffffffu, vis);
+            if (p.dbg_vis != nullptr && lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
+            if (vw == 0u) continue;
             cnt_view += (vis ? 1 : 0) & s_view[fl];
             const int m0 = s_moff[fl], m1 = s_moff[fl + 1];
+            if (m0 >= m1) continue;
+            // masks of a frame are consecutive rows of both the packed 2D masks and the packed output rows
+            const uint32_t *mp = p.masks2d + ((long long)m0 * p.mask_words + (pidx >> 5));
+            uint32_t *rp = p.rows != nullptr ? p.rows + ((long long)m0 * p.words + word_idx) : nullptr;
+            const int sh = pidx & 31;
             for (int m = m0; m < m1; ++m) {
                 bool bit = false;
-                if (vis) bit = (__ldg(p.masks2d + (long long)m * p.mask_words + (pidx >> 5)) >> (pidx & 31)) & 1u;
+                if (vis) bit = (__ldg(mp) >> sh) & 1u;
+                mp += p.mask_words;
                 const unsigned w = __ballot_sync(0xffffffffu, bit);
-                if (w != 0u && lane == 0 && p.rows != nullptr) p.rows[(long long)m * p.words + word_idx] = w;
+                if (rp != nullptr) {
+                    if (w != 0u && lane == 0) *rp = w;
+                    rp += p.words;
+                }
                 if (MULTI_Q) {
                     if (bit) s_acc[(p.mask_query ? p.mask_query[m] : 0) * kLiftThreads + tid] += 1;
                 } else {
@@ -428,6 +485,24 @@ int auto_frames_per_chunk(long long n_points, int n_frames) {
 
 using namespace bff;
 
+// x / scale == fma(fma(-q, scale, x), rcp, q) with q = x * rcp for EVERY uint16 x? (exhaustive; the result for the
+// last scale asked about is remembered -- scenes use one scale, 1000)
+static bool fast_div_is_exact(float scale) {
+    static std::atomic<unsigned long long> memo{0};   // scale bits << 2 | known << 1 | exact
+    unsigned bits;
+    memcpy(&bits, &scale, 4);
+    const unsigned long long m = memo.load(std::memory_order_acquire);
+    if ((m >> 2) == bits && (m & 2)) return m & 1;
+    bool ok = scale > 0.0f && std::isfinite(scale);
+    const float rc = 1.0f / scale;
+    for (unsigned x = 0; ok && x < 65536u; ++x) {
+        const float fx = (float)x, q = fx * rc;
+        ok = fmaf(fmaf(-q, scale, fx), rc, q) == fx / scale;
+    }
+    memo.store(((unsigned long long)bits << 2) | 2ull | (ok ? 1ull : 0ull), std::memory_order_release);
+    return ok;
+}
+
 static int validate(const bff_lift_desc *d) {
     BFF_REQUIRE(d != nullptr, "bff_lift_scene: null descriptor");
     BFF_REQUIRE(d->n_points >= 0 && d->n_frames >= 0, "bff_lift_scene: negative sizes");
@@ -488,6 +563,8 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
         p.z_lo = -INFINITY; p.z_hi = INFINITY;
     }
     p.w_hi = (double)d->width + 1.0; p.h_hi = (double)d->height + 1.0;
+    p.wd = (double)d->width; p.hd = (double)d->height;
+    p.hw = (long long)d->height * d->width;
     p.n_points = n; p.words = words;
     p.mask_words = ceil_div64((long long)d->height * d->width, 32);
     p.n_frames = d->n_frames;
@@ -498,6 +575,8 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     p.height = d->height; p.width = d->width;
     p.n_queries = d->n_queries;
     p.depth_scale = d->depth_scale;
+    p.depth_rcp = 1.0f / d->depth_scale;
+    p.fast_div = d->depth_kind == BFF_DEPTH_U16 && fast_div_is_exact(d->depth_scale);
     const int chunks = (d->n_frames + fc - 1) / fc;
     p.atomic_flush = chunks > 1;
 
