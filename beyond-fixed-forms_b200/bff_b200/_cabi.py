@@ -11,7 +11,7 @@ from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BFF_LIB_PATH") or os.path.join(_HERE, "libbff.so")   # override: experiment builds only
 
-BFF_DEPTH_F32, BFF_DEPTH_U16 = 0, 1
+BFF_DEPTH_F32, BFF_DEPTH_U16, BFF_DEPTH_U16_BILINEAR = 0, 1, 2
 BFF_XYZ_F32X4, BFF_XYZ_F64X3 = 0, 1
 
 
@@ -32,6 +32,7 @@ class LiftDesc(ctypes.Structure):
         ("rows", c_void_p), ("masked_counts", c_void_p), ("viewed_counts", c_void_p),
         ("debug_pix", c_void_p), ("debug_vis", c_void_p),
         ("frames_per_chunk", c_int32), ("reserved", c_int32),
+        ("src_height", c_int32), ("src_width", c_int32), ("resize_x", c_void_p), ("resize_y", c_void_p),
         ("ev_start", c_void_p), ("ev_stop", c_void_p),
     ]
 
@@ -64,6 +65,9 @@ SYMBOLS = {
     "bff_last_error": (c_char_p, []),
     "bff_lift_scene": (c_int, [POINTER(LiftDesc), c_void_p]),
     "bff_lift_scene_launches": (c_int, [POINTER(LiftDesc)]),
+    "bff_resize_table": (c_int, [c_int32, c_int32, c_void_p]),
+    "bff_depth_resize": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_float, c_void_p, c_void_p, c_int32, c_int32,
+                                 c_void_p, c_void_p]),
     "bff_visibility": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_double, c_void_p, c_void_p]),
     "bff_mask_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "bff_mask_iou": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

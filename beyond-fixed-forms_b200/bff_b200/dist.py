@@ -89,7 +89,7 @@ def lift_sharded(ctx: DistCtx, xyz: np.ndarray, intrinsics: np.ndarray, scene_2d
     inject the oracle there to check the sharding and exchange logic without a GPU."""
     f = len(frame_ids)
     lo, hi = shard_bounds(f, ctx.world_size, ctx.rank)
-    load_fn = load_fn or (lambda ids, vw: scene_io.load_frames(scene_2d_dir, scene_id, ids, vw, width, height))
+    load_fn = load_fn or (lambda ids, vw: scene_io.load_frames(scene_2d_dir, scene_id, ids, vw, width, height, device))
     lift_fn = lift_fn or lift_mod.lift_frames
     frames = load_fn(frame_ids[lo:hi], viewed[lo:hi])
     rles, mask_query, offsets = lift_mod.mask_layout(per_frame, queries, lo, hi)

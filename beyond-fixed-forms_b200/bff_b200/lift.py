@@ -134,7 +134,7 @@ def lift_frames(xyz_dev: torch.Tensor, intrinsics: np.ndarray, frames: scene_io.
         n_queries=max(n_queries, 1),
         frame_viewed=torch.from_numpy(frames.viewed).to(dev) if want_viewed else None,
         depth_thresh=depth_thresh, depth_scale=scene_io.DEPTH_SCALE, depth_range=frames.depth_range,
-        want_viewed=want_viewed, frames_per_chunk=frames_per_chunk)
+        want_viewed=want_viewed, frames_per_chunk=frames_per_chunk, native_size=getattr(frames, "native_size", None))
 
 
 def split_rows(all_rows: torch.Tensor, per_frame: List[list], queries: Sequence[QueryMasks]) -> List[torch.Tensor]:

@@ -46,13 +46,16 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
                frame_viewed: Optional[torch.Tensor] = None, depth_thresh: float = 0.08,
                depth_scale: float = 1000.0, depth_range: Optional[Sequence[float]] = None,
                want_rows: bool = True, want_counts: bool = True, want_viewed: bool = True,
-               debug: bool = False, frames_per_chunk: int = 0, timing_events=None) -> LiftOutput:
+               debug: bool = False, frames_per_chunk: int = 0, timing_events=None,
+               native_size: Optional[Sequence[int]] = None) -> LiftOutput:
     """One launch over all frames of a scene (bff_lift_scene).
 
     xyz         (N,4) float32 [x,y,z,_] or (N,3) float64, CUDA
     pose_inv    (F,4,4) float64 CUDA = np.linalg.inv(cam_pose) per frame (projection_2d_to_3d.py:425)
     intrinsics  (3,3) float64 HOST (numpy / CPU tensor): passed to the kernel by value
-    depth       (F,H,W) float32 metres or uint16/int16-storage raw sensor units, CUDA
+    depth       (F,H,W) float32 metres or uint16/int16-storage raw sensor units, CUDA; with
+                native_size=(Hs,Ws) != (H,W): (F,Hs,Ws) raw sensor units sampled in the kernel exactly like
+                cv2.resize(depth, (W,H)) (projection_2d_to_3d.py:436) -- BFF_DEPTH_U16_BILINEAR
     masks2d     (sumM, ceil(H*W/32)) int32 packed 2D masks in frame order; mask_offset (F+1,) int32
     Returns packed rows (sumM, Wd) int32, masked_counts (Q,N) int32, viewed_counts (N,) int32."""
     dev = xyz.device
@@ -78,7 +81,16 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     else:
         raise TypeError("depth must be float32 or 16-bit raw")
     depth = _cuda(depth, depth.dtype, "depth")
-    if depth.numel() != f * height * width:
+    taps = None
+    if native_size is not None and (int(native_size[0]), int(native_size[1])) != (int(height), int(width)):
+        if dkind != _cabi.BFF_DEPTH_U16:
+            raise TypeError("in-kernel resize needs raw 16-bit depth")
+        dkind = _cabi.BFF_DEPTH_U16_BILINEAR
+        hs, ws = int(native_size[0]), int(native_size[1])
+        if depth.numel() != f * hs * ws:
+            raise ValueError(f"depth has {depth.numel()} elements, expected {f}x{hs}x{ws}")
+        taps = (resize_table(width, ws, dev), resize_table(height, hs, dev))
+    elif depth.numel() != f * height * width:
         raise ValueError(f"depth has {depth.numel()} elements, expected {f}x{height}x{width}")
     n_masks = 0
     if masks2d is not None and masks2d.shape[0] > 0:
@@ -115,11 +127,49 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     d.rows, d.masked_counts, d.viewed_counts = ptr(rows), ptr(mc), ptr(vc)
     d.debug_pix, d.debug_vis = ptr(pix), ptr(vis)
     d.frames_per_chunk = int(frames_per_chunk)
+    if taps is not None:
+        d.src_height, d.src_width, d.resize_x, d.resize_y = hs, ws, ptr(taps[0]), ptr(taps[1])
     if timing_events is not None:      # two recorded torch.cuda.Event(enable_timing=True): re-recorded around the launch
         d.ev_start, d.ev_stop = c_void_p(timing_events[0].cuda_event), c_void_p(timing_events[1].cuda_event)
     check(lib().bff_lift_scene(d, current_stream()), "bff_lift_scene")
     _count(lib().bff_lift_scene_launches(d))
     return LiftOutput(rows, mc, vc, pix, vis)
+
+
+_tap_cache = {}
+
+
+def resize_table(n_dst: int, n_src: int, device=None):
+    """bff_resize_table: (n_dst, 2) int32 rows [source index, float32 weight bits] of one axis of
+    cv2.resize(..., INTER_LINEAR). Host numpy array, or a cached CUDA copy when `device` is given."""
+    key = (int(n_dst), int(n_src))
+    if key not in _tap_cache:
+        t = np.empty((key[0], 2), np.int32)
+        check(lib().bff_resize_table(key[0], key[1], ptr(t)), "bff_resize_table")
+        _tap_cache[key] = {"host": t}
+    ent = _tap_cache[key]
+    if device is None:
+        return ent["host"]
+    dk = str(device)
+    if dk not in ent:
+        ent[dk] = torch.from_numpy(ent["host"]).to(device)
+    return ent[dk]
+
+
+def depth_resize(raw: torch.Tensor, height: int, width: int, depth_scale: float = 1000.0) -> torch.Tensor:
+    """(F,Hs,Ws) raw 16-bit depth on the GPU -> (F,H,W) float32 metres = cv2.resize(raw.astype(f32)/scale, (W,H))
+    (projection_2d_to_3d.py:431-436), bff_depth_resize."""
+    if raw.dtype not in (torch.int16, torch.uint16) or raw.dim() != 3:
+        raise TypeError("raw depth must be a (F,Hs,Ws) 16-bit tensor")
+    raw = _cuda(raw, raw.dtype, "raw")
+    f, hs, ws = raw.shape
+    out = torch.empty((f, int(height), int(width)), dtype=torch.float32, device=raw.device)
+    tx, ty = resize_table(width, ws, raw.device), resize_table(height, hs, raw.device)
+    check(lib().bff_depth_resize(ptr(raw), f, hs, ws, float(depth_scale), ptr(tx), ptr(ty), int(height), int(width), ptr(out),
+                                 current_stream()), "bff_depth_resize")
+    if f:
+        _count(1)
+    return out
 
 
 # ----------------------------------------------------------------------------- mask algebra

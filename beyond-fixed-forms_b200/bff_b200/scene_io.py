@@ -63,16 +63,41 @@ def depth_to_metres(raw: np.ndarray, width: int, height: int) -> np.ndarray:
 
 
 class FrameSet:
-    """Frames of one scene ready for the device: inverse poses, depth stack, viewed flags."""
+    """Frames of one scene ready for the device: inverse poses, depth stack, viewed flags.
+    native_size = (Hs, Ws) when `depth` is raw uint16 at the sensor's size and the lift kernel resamples it
+    to mask resolution itself (BFF_DEPTH_U16_BILINEAR); None when depth already has mask resolution."""
 
     def __init__(self, frame_ids: List[str], pose_inv: np.ndarray, depth: np.ndarray, depth_is_raw: bool,
-                 viewed: np.ndarray, depth_range: Optional[Tuple[float, float]]):
+                 viewed: np.ndarray, depth_range: Optional[Tuple[float, float]], native_size=None):
         self.frame_ids, self.pose_inv, self.depth = frame_ids, pose_inv, depth
         self.depth_is_raw, self.viewed, self.depth_range = depth_is_raw, viewed, depth_range
+        self.native_size = native_size
+
+
+IN_KERNEL_RESIZE = True      # False: always resize on the host with cv2.resize like the reference (:436)
+_resize_checked = {}
+
+
+def device_resize_matches_cv2(src_hw, dst_hw, device) -> bool:
+    """Run-time gate of the in-kernel depth resize: bff_depth_resize (the arithmetic the lift kernel uses for
+    BFF_DEPTH_U16_BILINEAR) against THIS machine's cv2.resize on a seeded probe image of the same size pair,
+    bit for bit. cv2's result depends on its build (IPP or not); on a mismatch the frames are resized on the
+    host by cv2 itself, as the reference does, and handed over as float32. Checked once per size pair."""
+    key = (tuple(src_hw), tuple(dst_hw), str(device))
+    if key not in _resize_checked:
+        import cv2
+        from . import ops
+        rng = np.random.default_rng(12345)
+        raw = rng.integers(300, 9000, tuple(src_hw)).astype(np.uint16)
+        raw[rng.random(tuple(src_hw)) < 0.03] = 0
+        want = depth_to_metres(raw, dst_hw[1], dst_hw[0])
+        got = ops.depth_resize(torch.from_numpy(raw.view(np.int16)[None]).to(device), dst_hw[0], dst_hw[1], DEPTH_SCALE)[0].cpu().numpy()
+        _resize_checked[key] = bool(np.array_equal(got.view(np.int32), want.view(np.int32)))
+    return _resize_checked[key]
 
 
 def load_frames(scene_2d_dir: str, scene_id: str, frame_ids: Sequence[str], viewed: Sequence[bool],
-                width: int, height: int) -> FrameSet:
+                width: int, height: int, device=None) -> FrameSet:
     f = len(frame_ids)
     pose_inv = np.empty((f, 4, 4), np.float64)
     raws = []
@@ -84,6 +109,12 @@ def load_frames(scene_2d_dir: str, scene_id: str, frame_ids: Sequence[str], view
         depth = np.stack(raws) if raws else np.zeros((0, height, width), np.uint16)
         rng = (0.0, 65535.0 / DEPTH_SCALE)
         return FrameSet(list(frame_ids), pose_inv, depth, True, np.asarray(viewed, np.uint8), rng)
+    native = raws[0].shape if raws else None
+    if (IN_KERNEL_RESIZE and device is not None and raws and all(r.dtype == np.uint16 and r.ndim == 2 and r.shape == native for r in raws)
+            and device_resize_matches_cv2(native, (height, width), device)):
+        # blended values lie between 0 and the largest sample: the culling window starts at 0
+        return FrameSet(list(frame_ids), pose_inv, np.stack(raws), True, np.asarray(viewed, np.uint8),
+                        (0.0, 65535.0 / DEPTH_SCALE), native_size=(int(native[0]), int(native[1])))
     depth = np.stack([depth_to_metres(r, width, height) for r in raws]) if raws else np.zeros((0, height, width), np.float32)
     rng = None
     if depth.size and np.isfinite(depth).all():

@@ -79,7 +79,7 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
         lifted = dist_mod.lift_sharded(dist_ctx, xyz, intr, scene_2d_dir, scene_id, frame_ids, viewed, per_frame, [q],
                                        height, width, want_viewed and bool(conf_list), device)
     else:
-        frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height)
+        frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
         lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, [q], height, width,
                                want_viewed and bool(conf_list))
     return aggregate_and_filter(lifted.rows[0], conf_list, labels, lifted.masked_counts[0], lifted.viewed_counts,
@@ -106,7 +106,7 @@ def process_scene_queries(cfg, classes, scene_id: str, device):
     out = {}
     if not frame_ids:
         return {q.query: aggregate_and_filter(None, [], [], None, None, xyz.shape[0], cfg) for q in queries}
-    frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height)
+    frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
     lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, queries, height, width,
                            want_viewed and any_masks)
     for qi, q in enumerate(queries):

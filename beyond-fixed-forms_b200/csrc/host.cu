@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <vector>
+
 #include "common.cuh"
 
 namespace bff {
@@ -128,7 +130,10 @@ extern "C" int bff_lift_scene_host(bff_ctx *c, const bff_lift_desc *h, int64_t *
     const size_t n = (size_t)h->n_points, f = (size_t)h->n_frames, hw = (size_t)h->height * h->width;
     const size_t words = (n + 31) / 32, mwords = (hw + 31) / 32;
     const size_t xyz_b = n * (h->xyz_kind == BFF_XYZ_F32X4 ? 16 : 24);
-    const size_t depth_b = f * hw * (h->depth_kind == BFF_DEPTH_U16 ? 2 : 4);
+    const bool bilinear = h->depth_kind == BFF_DEPTH_U16_BILINEAR;
+    BFF_REQUIRE(!bilinear || (h->src_height > 0 && h->src_width > 0), "bff_lift_scene_host: bad native depth size");
+    const size_t depth_b = bilinear ? f * (size_t)h->src_height * h->src_width * 2
+                                    : f * hw * (h->depth_kind == BFF_DEPTH_U16 ? 2 : 4);
     const size_t nm = (size_t)h->n_masks;
     // two passes over the same carve sequence: measure, then place
     unsigned char *base = nullptr;
@@ -139,6 +144,8 @@ extern "C" int bff_lift_scene_host(bff_ctx *c, const bff_lift_desc *h, int64_t *
         d.xyz = cv.take<unsigned char>(xyz_b);
         d.pose_inv = cv.take<double>(f * 16);
         d.depth = cv.take<unsigned char>(depth_b);
+        d.resize_x = bilinear ? cv.take<bff_resize_tap>((size_t)h->width) : nullptr;
+        d.resize_y = bilinear ? cv.take<bff_resize_tap>((size_t)h->height) : nullptr;
         d.masks2d = nm ? cv.take<uint32_t>(nm * mwords) : nullptr;
         d.mask_offset = (nm && h->mask_offset) ? cv.take<int32_t>(f + 1) : nullptr;
         d.mask_query = (nm && h->mask_query) ? cv.take<int32_t>(nm) : nullptr;
@@ -166,6 +173,17 @@ extern "C" int bff_lift_scene_host(bff_ctx *c, const bff_lift_desc *h, int64_t *
         BFF_CUDA(h2d(d.xyz, h->xyz, xyz_b));
         BFF_CUDA(h2d(d.pose_inv, h->pose_inv, f * 128));
         BFF_CUDA(h2d(d.depth, h->depth, depth_b));
+        if (bilinear) {
+            // host tables: the caller's, or built here (bff_resize_table) when it passes none
+            std::vector<bff_resize_tap> tx, ty;
+            const bff_resize_tap *hx = h->resize_x, *hy = h->resize_y;
+            if (!hx) { tx.resize(h->width); bff_resize_table(h->width, h->src_width, tx.data()); hx = tx.data(); }
+            if (!hy) { ty.resize(h->height); bff_resize_table(h->height, h->src_height, ty.data()); hy = ty.data(); }
+            BFF_CUDA(cudaMemcpyAsync(const_cast<bff_resize_tap *>(d.resize_x), hx, (size_t)h->width * 8, cudaMemcpyHostToDevice, s));
+            BFF_CUDA(cudaMemcpyAsync(const_cast<bff_resize_tap *>(d.resize_y), hy, (size_t)h->height * 8, cudaMemcpyHostToDevice, s));
+            BFF_CUDA(cudaStreamSynchronize(s));      // the (pageable) table vectors die with this scope
+            up += ((int64_t)h->width + h->height) * 8;
+        }
         if (d.masks2d) BFF_CUDA(h2d(d.masks2d, h->masks2d, nm * mwords * 4));
         if (d.mask_offset) BFF_CUDA(h2d(d.mask_offset, h->mask_offset, (f + 1) * 4));
         if (d.mask_query) BFF_CUDA(h2d(d.mask_query, h->mask_query, nm * 4));

@@ -60,7 +60,9 @@ struct LiftParams {
     double z_lo, z_hi;     // camera-z window outside which no depth can match
     double w_hi, h_hi;     // (W + 1), (H + 1) for the conservative frustum pre-test
     double wd, hd;         // (double)W, (double)H
-    long long hw;          // H * W
+    long long hw;          // H * W (BFF_DEPTH_U16_BILINEAR: src_height * src_width, the stride of one depth frame)
+    const bff_resize_tap *tap_x, *tap_y;   // BFF_DEPTH_U16_BILINEAR: per-column / per-row source taps
+    int src_w, src_h;
     long long n_points;
     long long words;       // Wd
     long long mask_words;  // ceil(H*W/32)
@@ -214,13 +216,13 @@ __device__ __forceinline__ bool fast_rounded_quotients(double q0, double q1, dou
 // Returns true when the pixel is inside the image; Z = camera z, pix = y * W + x.
 template <bool DEBUG>
 __device__ __forceinline__ bool locate_pixel(const LiftParams &p, const double *P, int f, double x, double y, double z,
-                                             bool valid, long long pt, double &Z, int &pix) {
+                                             bool valid, long long pt, double &Z, int &pix, int &px, int &py) {
     // camera z first: row 2 of inv(pose) @ [x y z 1]
     Z = fma(P[8], x, 0.0);
     Z = fma(P[9], y, Z);
     Z = fma(P[10], z, Z);
     Z = fma(P[11], 1.0, Z);
-    pix = 0;
+    pix = 0; px = 0; py = 0;
     if (!(valid && (DEBUG || (Z >= p.z_lo && Z <= p.z_hi)))) return false;
     double X = fma(P[0], x, 0.0);
     X = fma(P[1], y, X);
@@ -254,12 +256,53 @@ __device__ __forceinline__ bool locate_pixel(const LiftParams &p, const double *
         o[1] = f64_to_i64_numpy(yr);
     }
     if (!(xr >= 0.0 && xr < p.wd && yr >= 0.0 && yr < p.hd)) return false;
-    pix = (int)yr * p.width + (int)xr;
+    px = (int)xr; py = (int)yr;
+    pix = py * p.width + px;
     return true;
 }
 
+// uint16 sensor units -> float32 metres exactly as projection_2d_to_3d.py:431-435 (fp32 divide).
+// fast_div: q = x * rcp, one residual correction -- the correctly rounded quotient for every uint16 x
+// (bff_lift_scene checks all 65536 values on the host before it sets the flag); else the IEEE divide.
+__device__ __forceinline__ float u16_to_metres(unsigned raw, float scale, float rcp, int fast_div) {
+    const float x = (float)raw;
+    if (fast_div) {
+        const float q = __fmul_rn(x, rcp);
+        return __fmaf_rn(__fmaf_rn(-q, scale, x), rcp, q);
+    }
+    return __fdiv_rn(x, scale);
+}
+
+// cv2.resize(depth, (W, H)) at ONE output pixel (projection_2d_to_3d.py:436): horizontal blends of the two source
+// rows, then the vertical blend, each fmaf(s1 - s0, w, s0) in float32 (bff.h: bff_resize_table).
+__device__ __forceinline__ float bilinear_sample(const unsigned short *__restrict__ img, int src_w, int src_h,
+                                                 bff_resize_tap tx, bff_resize_tap ty, float scale, float rcp, int fast_div) {
+    const int x0 = tx.index, x1 = min(x0 + 1, src_w - 1);
+    const int y0 = ty.index, y1 = min(y0 + 1, src_h - 1);
+    const unsigned short *r0 = img + (long long)y0 * src_w, *r1 = img + (long long)y1 * src_w;
+    const float s00 = u16_to_metres(__ldg(r0 + x0), scale, rcp, fast_div), s01 = u16_to_metres(__ldg(r0 + x1), scale, rcp, fast_div);
+    const float s10 = u16_to_metres(__ldg(r1 + x0), scale, rcp, fast_div), s11 = u16_to_metres(__ldg(r1 + x1), scale, rcp, fast_div);
+    const float h0 = __fmaf_rn(__fsub_rn(s01, s00), tx.weight, s00);
+    const float h1 = __fmaf_rn(__fsub_rn(s11, s10), tx.weight, s10);
+    return __fmaf_rn(__fsub_rn(h1, h0), ty.weight, h0);
+}
+
+__device__ __forceinline__ bff_resize_tap load_tap(const bff_resize_tap *t) {
+    const int2 v = __ldg(reinterpret_cast<const int2 *>(t));
+    bff_resize_tap r;
+    r.index = v.x;
+    r.weight = __int_as_float(v.y);
+    return r;
+}
+
+// raw depth word of an in-image pixel: the uint16 / float32 bits, or the float32 bits of the sampled value
 template <int DEPTH_KIND>
-__device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, int pix) {
+__device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, int pix, int px, int py) {
+    if (DEPTH_KIND == BFF_DEPTH_U16_BILINEAR) {
+        const unsigned short *img = reinterpret_cast<const unsigned short *>(p.depth) + (long long)f * p.hw;
+        return __float_as_uint(bilinear_sample(img, p.src_w, p.src_h, load_tap(p.tap_x + px), load_tap(p.tap_y + py),
+                                               p.depth_scale, p.depth_rcp, p.fast_div));
+    }
     const long long off = (long long)f * p.hw + pix;
     if (DEPTH_KIND == BFF_DEPTH_U16) return (unsigned)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + off);
     return __ldg(reinterpret_cast<const unsigned *>(p.depth) + off);
@@ -267,17 +310,7 @@ __device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, i
 
 template <int DEPTH_KIND>
 __device__ __forceinline__ float depth_value(unsigned raw, const LiftParams &p) {
-    // uint16 sensor units -> float32 metres exactly as projection_2d_to_3d.py:431-435 (fp32 divide).
-    // fast_div: q = x * rcp, one residual correction -- the correctly rounded quotient for every uint16 x
-    // (bff_lift_scene checks all 65536 values on the host before it sets the flag); else the IEEE divide.
-    if (DEPTH_KIND == BFF_DEPTH_U16) {
-        const float x = (float)raw;
-        if (p.fast_div) {
-            const float q = __fmul_rn(x, p.depth_rcp);
-            return __fmaf_rn(__fmaf_rn(-q, p.depth_scale, x), p.depth_rcp, q);
-        }
-        return __fdiv_rn(x, p.depth_scale);
-    }
+    if (DEPTH_KIND == BFF_DEPTH_U16) return u16_to_metres(raw, p.depth_scale, p.depth_rcp, p.fast_div);
     return __uint_as_float(raw);
 }
 
@@ -383,14 +416,14 @@ lift_kernel(const __grid_constant__ LiftParams p) {
         const int flB = hasB ? fb + __ffs(todo) - 1 : flA;
         if (hasB) todo &= todo - 1u;
         double ZA, ZB = 0.0;
-        int pixA, pixB = 0;
-        const bool inA = locate_pixel<DEBUG>(p, s_pose + flA * 16, f0 + flA, x, y, z, valid, pt, ZA, pixA);
-        const unsigned rawA = inA ? load_depth_raw<DEPTH_KIND>(p, f0 + flA, pixA) : 0u;
+        int pixA, pixB = 0, pxA, pyA, pxB = 0, pyB = 0;
+        const bool inA = locate_pixel<DEBUG>(p, s_pose + flA * 16, f0 + flA, x, y, z, valid, pt, ZA, pixA, pxA, pyA);
+        const unsigned rawA = inA ? load_depth_raw<DEPTH_KIND>(p, f0 + flA, pixA, pxA, pyA) : 0u;
         bool inB = false;
         unsigned rawB = 0u;
         if (hasB) {
-            inB = locate_pixel<DEBUG>(p, s_pose + flB * 16, f0 + flB, x, y, z, valid, pt, ZB, pixB);
-            rawB = inB ? load_depth_raw<DEPTH_KIND>(p, f0 + flB, pixB) : 0u;
+            inB = locate_pixel<DEBUG>(p, s_pose + flB * 16, f0 + flB, x, y, z, valid, pt, ZB, pixB, pxB, pyB);
+            rawB = inB ? load_depth_raw<DEPTH_KIND>(p, f0 + flB, pixB, pxB, pyB) : 0u;
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -461,12 +494,16 @@ static LiftKernel pick2(bool multi_q, bool debug) {
     return multi_q ? lift_kernel<X, D, true, false> : lift_kernel<X, D, false, false>;
 }
 
+template <int X>
+static LiftKernel pick1(int depth_kind, bool multi_q, bool debug) {
+    if (depth_kind == BFF_DEPTH_U16) return pick2<X, BFF_DEPTH_U16>(multi_q, debug);
+    if (depth_kind == BFF_DEPTH_U16_BILINEAR) return pick2<X, BFF_DEPTH_U16_BILINEAR>(multi_q, debug);
+    return pick2<X, BFF_DEPTH_F32>(multi_q, debug);
+}
+
 static LiftKernel pick(int xyz_kind, int depth_kind, bool multi_q, bool debug) {
-    if (xyz_kind == BFF_XYZ_F32X4)
-        return depth_kind == BFF_DEPTH_U16 ? pick2<BFF_XYZ_F32X4, BFF_DEPTH_U16>(multi_q, debug)
-                                           : pick2<BFF_XYZ_F32X4, BFF_DEPTH_F32>(multi_q, debug);
-    return depth_kind == BFF_DEPTH_U16 ? pick2<BFF_XYZ_F64X3, BFF_DEPTH_U16>(multi_q, debug)
-                                       : pick2<BFF_XYZ_F64X3, BFF_DEPTH_F32>(multi_q, debug);
+    return xyz_kind == BFF_XYZ_F32X4 ? pick1<BFF_XYZ_F32X4>(depth_kind, multi_q, debug)
+                                     : pick1<BFF_XYZ_F64X3>(depth_kind, multi_q, debug);
 }
 
 int auto_frames_per_chunk(long long n_points, int n_frames) {
@@ -508,7 +545,13 @@ static int validate(const bff_lift_desc *d) {
     BFF_REQUIRE(d->n_points >= 0 && d->n_frames >= 0, "bff_lift_scene: negative sizes");
     BFF_REQUIRE(d->n_points < (1LL << 31) * 32, "bff_lift_scene: too many points");
     BFF_REQUIRE(d->xyz_kind == BFF_XYZ_F32X4 || d->xyz_kind == BFF_XYZ_F64X3, "bff_lift_scene: bad xyz_kind %d", d->xyz_kind);
-    BFF_REQUIRE(d->depth_kind == BFF_DEPTH_F32 || d->depth_kind == BFF_DEPTH_U16, "bff_lift_scene: bad depth_kind %d", d->depth_kind);
+    BFF_REQUIRE(d->depth_kind == BFF_DEPTH_F32 || d->depth_kind == BFF_DEPTH_U16 || d->depth_kind == BFF_DEPTH_U16_BILINEAR,
+                "bff_lift_scene: bad depth_kind %d", d->depth_kind);
+    if (d->depth_kind == BFF_DEPTH_U16_BILINEAR) {
+        BFF_REQUIRE(d->src_height > 0 && d->src_width > 0, "bff_lift_scene: bad native depth size %dx%d", d->src_height, d->src_width);
+        BFF_REQUIRE(d->n_points == 0 || d->n_frames == 0 || (d->resize_x && d->resize_y), "bff_lift_scene: bilinear depth without resize tables");
+        BFF_REQUIRE((((uintptr_t)d->resize_x | (uintptr_t)d->resize_y) & 7) == 0, "bff_lift_scene: resize tables must be 8-byte aligned");
+    }
     BFF_REQUIRE(d->height > 0 && d->width > 0, "bff_lift_scene: bad image size %dx%d", d->height, d->width);
     BFF_REQUIRE((long long)d->height * d->width < (1LL << 31), "bff_lift_scene: image too large");
     BFF_REQUIRE(d->n_queries >= 1, "bff_lift_scene: n_queries must be >= 1");
@@ -519,7 +562,7 @@ static int validate(const bff_lift_desc *d) {
         BFF_REQUIRE(((uintptr_t)d->pose_inv & 15) == 0, "bff_lift_scene: pose_inv must be 16-byte aligned");
         BFF_REQUIRE(d->xyz_kind != BFF_XYZ_F32X4 || ((uintptr_t)d->xyz & 15) == 0, "bff_lift_scene: float4 xyz must be 16-byte aligned");
     }
-    BFF_REQUIRE(d->depth_kind != BFF_DEPTH_U16 || d->depth_scale != 0.0f, "bff_lift_scene: depth_scale is 0");
+    BFF_REQUIRE(d->depth_kind == BFF_DEPTH_F32 || d->depth_scale != 0.0f, "bff_lift_scene: depth_scale is 0");
     BFF_REQUIRE(d->frames_per_chunk >= 0, "bff_lift_scene: negative frames_per_chunk");
     return BFF_OK;
 }
@@ -565,6 +608,12 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     p.w_hi = (double)d->width + 1.0; p.h_hi = (double)d->height + 1.0;
     p.wd = (double)d->width; p.hd = (double)d->height;
     p.hw = (long long)d->height * d->width;
+    p.tap_x = p.tap_y = nullptr; p.src_w = p.src_h = 0;
+    if (d->depth_kind == BFF_DEPTH_U16_BILINEAR) {
+        p.hw = (long long)d->src_height * d->src_width;
+        p.tap_x = d->resize_x; p.tap_y = d->resize_y;
+        p.src_w = d->src_width; p.src_h = d->src_height;
+    }
     p.n_points = n; p.words = words;
     p.mask_words = ceil_div64((long long)d->height * d->width, 32);
     p.n_frames = d->n_frames;
@@ -575,8 +624,8 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     p.height = d->height; p.width = d->width;
     p.n_queries = d->n_queries;
     p.depth_scale = d->depth_scale;
-    p.depth_rcp = 1.0f / d->depth_scale;
-    p.fast_div = d->depth_kind == BFF_DEPTH_U16 && fast_div_is_exact(d->depth_scale);
+    p.depth_rcp = d->depth_scale != 0.0f ? 1.0f / d->depth_scale : 0.0f;
+    p.fast_div = d->depth_kind != BFF_DEPTH_F32 && fast_div_is_exact(d->depth_scale);
     const int chunks = (d->n_frames + fc - 1) / fc;
     p.atomic_flush = chunks > 1;
 
@@ -650,5 +699,51 @@ extern "C" int bff_mask_gather(const int64_t *pix, const uint32_t *vis, int64_t 
     mask_gather_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>((const long long *)pix, vis, n, masks2d,
                                                                 ceil_div64((long long)height * width, 32), width, ceil_div64(n, 32), rows);
     BFF_LAUNCH_CHECK("mask_gather_kernel");
+    return BFF_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Depth ingest of projection_2d_to_3d.py:431-436 as a stand-alone device op (bff.h: bff_depth_resize).
+namespace bff {
+__global__ void __launch_bounds__(256)
+depth_resize_kernel(const unsigned short *__restrict__ src, int src_h, int src_w, float scale, float rcp, int fast_div,
+                    const bff_resize_tap *__restrict__ tap_x, const bff_resize_tap *__restrict__ tap_y, int dst_h, int dst_w,
+                    float *__restrict__ dst) {
+    const int x = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y, f = blockIdx.z;
+    if (x >= dst_w) return;
+    const unsigned short *img = src + (long long)f * src_h * src_w;
+    dst[((long long)f * dst_h + y) * dst_w + x] = bilinear_sample(img, src_w, src_h, load_tap(tap_x + x), load_tap(tap_y + y), scale, rcp, fast_div);
+}
+}  // namespace bff
+
+extern "C" int bff_resize_table(int32_t n_dst, int32_t n_src, bff_resize_tap *taps) {
+    BFF_REQUIRE(n_dst > 0 && n_src > 0 && taps, "bff_resize_table: bad arguments");
+    const double scale = (double)n_src / (double)n_dst;
+    for (int i = 0; i < n_dst; ++i) {
+        const double f = ((double)i + 0.5) * scale - 0.5;
+        double fl = floor(f);
+        int idx = (int)fl;
+        float w = (float)(f - fl);
+        if (idx < 0) { idx = 0; w = 0.0f; }
+        if (idx >= n_src - 1) { idx = n_src - 1; w = 0.0f; }
+        taps[i].index = idx;
+        taps[i].weight = w;
+    }
+    return BFF_OK;
+}
+
+extern "C" int bff_depth_resize(const uint16_t *src, int32_t n_frames, int32_t src_h, int32_t src_w, float depth_scale,
+                                const bff_resize_tap *tap_x, const bff_resize_tap *tap_y, int32_t dst_h, int32_t dst_w,
+                                float *dst, void *stream_) {
+    BFF_REQUIRE(n_frames >= 0 && src_h > 0 && src_w > 0 && dst_h > 0 && dst_w > 0, "bff_depth_resize: bad sizes");
+    BFF_REQUIRE(depth_scale != 0.0f, "bff_depth_resize: depth_scale is 0");
+    if (n_frames == 0) return BFF_OK;
+    BFF_REQUIRE(src && tap_x && tap_y && dst, "bff_depth_resize: null pointer");
+    BFF_REQUIRE(n_frames <= 65535 && dst_h <= 65535, "bff_depth_resize: too many frames / rows for one launch");
+    dim3 grid((unsigned)ceil_div64(dst_w, 256), (unsigned)dst_h, (unsigned)n_frames);
+    depth_resize_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(src, src_h, src_w, depth_scale, 1.0f / depth_scale,
+                                                                  fast_div_is_exact(depth_scale) ? 1 : 0, tap_x, tap_y, dst_h, dst_w, dst);
+    BFF_LAUNCH_CHECK("depth_resize_kernel");
     return BFF_OK;
 }

@@ -47,14 +47,26 @@ typedef enum bff_status {
 
 typedef enum bff_depth_kind {
     BFF_DEPTH_F32 = 0,   /* float32 metres, as the reference holds it after /depth_scale and resize */
-    BFF_DEPTH_U16 = 1    /* raw uint16 sensor units; the kernel computes (float)u16 / depth_scale in fp32,
+    BFF_DEPTH_U16 = 1,   /* raw uint16 sensor units; the kernel computes (float)u16 / depth_scale in fp32,
                             bit-identical to projection_2d_to_3d.py:431-435 when no resize is needed */
+    BFF_DEPTH_U16_BILINEAR = 2
+                         /* raw uint16 at the sensor's NATIVE size (src_height, src_width); the kernel samples it at
+                            mask resolution with the arithmetic of cv2.resize(depth, (W, H)) (projection_2d_to_3d.py:436,
+                            :563; default configs upsample 640x480 -> 1296x968), so the resized float32 image never
+                            exists: see bff_resize_table / bff_depth_resize for the exact formula */
 } bff_depth_kind;
 
 typedef enum bff_xyz_kind {
     BFF_XYZ_F32X4 = 0,   /* float4 per point (x,y,z,unused); exact iff the float64 cloud is float32-representable */
     BFF_XYZ_F64X3 = 1    /* three doubles per point */
 } bff_xyz_kind;
+
+/* One output coordinate of a bilinear resize: the two source taps are index and min(index + 1, n_src - 1),
+ * blended as fmaf(s1 - s0, weight, s0) in float32. */
+typedef struct bff_resize_tap {
+    int32_t index;
+    float weight;
+} bff_resize_tap;
 
 /* Description of one scene's lifting job. All pointers are device pointers for
  * bff_lift_scene and host pointers for bff_lift_scene_host. */
@@ -93,6 +105,11 @@ typedef struct bff_lift_desc {
     /* launch shape: frames per CTA chunk (0 = automatic) */
     int32_t frames_per_chunk;
     int32_t reserved;
+    /* BFF_DEPTH_U16_BILINEAR only: native depth size and the per-axis sampling tables of bff_resize_table
+     * (resize_x: width entries over src_width, resize_y: height entries over src_height), device pointers
+     * for bff_lift_scene */
+    int32_t src_height, src_width;
+    const bff_resize_tap *resize_x, *resize_y;
     /* optional cudaEvent_t handles recorded on `stream` right before the first and right after the last
      * device operation of the call (for callers that time the launch itself); NULL = none */
     void *ev_start, *ev_stop;
@@ -106,6 +123,23 @@ BFF_API const char *bff_last_error(void);
  * compute_visible_masked_pts_tensor :73, masked_counts/viewed_counts updates) with one launch
  * over all frames. Outputs are fully overwritten. */
 BFF_API int bff_lift_scene(const bff_lift_desc *desc, void *stream);
+
+/* The bilinear sampling of cv2.resize(src, (n_dst, .)) along one axis (INTER_LINEAR on float32, as OpenCV's
+ * IPP-backed builds compute it; checked against cv2.resize in tests/ and at run time by the host package):
+ *   f = (i + 0.5) * (n_src / n_dst) - 0.5 in float64; index = floor(f); weight = float32(f - index);
+ *   index < 0 -> (0, 0);  index >= n_src - 1 -> (n_src - 1, 0).
+ * Host function, `taps` is a HOST array of n_dst entries. */
+BFF_API int bff_resize_table(int32_t n_dst, int32_t n_src, bff_resize_tap *taps);
+
+/* Stand-alone form of the depth ingest of projection_2d_to_3d.py:431-436 (and :556-563) on the device:
+ * src (n_frames, src_h, src_w) raw uint16 -> dst (n_frames, dst_h, dst_w) float32 metres =
+ * cv2.resize((float)src / depth_scale, (dst_w, dst_h)): rows first blend horizontally, then vertically,
+ * each blend fmaf(s1 - s0, weight, s0). tap_x (dst_w) / tap_y (dst_h) are DEVICE copies of bff_resize_table.
+ * The scene path does not need it (BFF_DEPTH_U16_BILINEAR samples inside the lift kernel); callers that want
+ * the resized image, and the run-time check against cv2.resize, do. */
+BFF_API int bff_depth_resize(const uint16_t *src, int32_t n_frames, int32_t src_h, int32_t src_w, float depth_scale,
+                             const bff_resize_tap *tap_x, const bff_resize_tap *tap_y, int32_t dst_h, int32_t dst_w,
+                             float *dst, void *stream);
 
 /* Number of kernels bff_lift_scene launches for this description (for launch accounting). */
 BFF_API int bff_lift_scene_launches(const bff_lift_desc *desc);

@@ -166,3 +166,45 @@ ORACLE_API void oracle_rle_decode(const int64_t *counts, int64_t ncounts, int64_
 }
 
 ORACLE_API int oracle_version(void) { return 1; }
+
+/* tools/projection_2d_to_3d.py:431-436 (and :556-563) -- depth_im = imread(png).astype(float32) / 1000;
+ * depth_im = cv2.resize(depth_im, (width_2d, height_2d)).
+ * cv2.resize is OpenCV (INTER_LINEAR, float32), a dependency outside the reference tree; its IPP-backed pip
+ * builds compute, per output pixel (x, y):
+ *   f = (i + 0.5) * (n_src / n_dst) - 0.5 in float64 per axis; i0 = floor(f); w = float32(f - i0);
+ *   i0 < 0 -> (0, w = 0);  i0 >= n_src - 1 -> (n_src - 1, w = 0);  i1 = min(i0 + 1, n_src - 1)
+ *   h0 = fmaf(S[y0][x1] - S[y0][x0], wx, S[y0][x0]);  h1 = the same on row y1;  out = fmaf(h1 - h0, wy, h0)
+ * PINNED against cv2.resize itself (tests/test_oracle_golden.py::test_resize_matches_cv2, 11 size pairs up
+ * and down, bit for bit) and against the frozen cv2 output in tests/golden/resize.npz (oracle/make_golden_resize.py).
+ * src (hs, ws) f32 -> dst (hd, wd) f32. */
+static void resize_axis(int n_dst, int n_src, int *idx, float *wt) {
+    const double scale = (double)n_src / (double)n_dst;
+    for (int i = 0; i < n_dst; ++i) {
+        const double f = ((double)i + 0.5) * scale - 0.5;
+        const double fl = floor(f);
+        int k = (int)fl;
+        float w = (float)(f - fl);
+        if (k < 0) { k = 0; w = 0.0f; }
+        if (k >= n_src - 1) { k = n_src - 1; w = 0.0f; }
+        idx[i] = k;
+        wt[i] = w;
+    }
+}
+
+ORACLE_API void oracle_resize_bilinear(const float *src, int hs, int ws, float *dst, int hd, int wd) {
+    int *xi = (int *)malloc(sizeof(int) * (size_t)wd), *yi = (int *)malloc(sizeof(int) * (size_t)hd);
+    float *xw = (float *)malloc(sizeof(float) * (size_t)wd), *yw = (float *)malloc(sizeof(float) * (size_t)hd);
+    resize_axis(wd, ws, xi, xw);
+    resize_axis(hd, hs, yi, yw);
+    for (int y = 0; y < hd; ++y) {
+        const int y0 = yi[y], y1 = y0 + 1 < hs ? y0 + 1 : hs - 1;
+        const float *r0 = src + (size_t)y0 * ws, *r1 = src + (size_t)y1 * ws;
+        for (int x = 0; x < wd; ++x) {
+            const int x0 = xi[x], x1 = x0 + 1 < ws ? x0 + 1 : ws - 1;
+            const float h0 = fmaf(r0[x1] - r0[x0], xw[x], r0[x0]);
+            const float h1 = fmaf(r1[x1] - r1[x0], xw[x], r1[x0]);
+            dst[(size_t)y * wd + x] = fmaf(h1 - h0, yw[y], h0);
+        }
+    }
+    free(xi); free(yi); free(xw); free(yw);
+}

@@ -109,3 +109,12 @@ def rle_decode(rle):
     m = np.empty(length, np.uint8)
     lib().oracle_rle_decode(_p(counts), ctypes.c_int64(counts.size), ctypes.c_int64(length), _p(m))
     return m
+
+
+def resize_bilinear(src, height, width):
+    """cv2.resize(src, (width, height)) on float32 (projection_2d_to_3d.py:436) restated."""
+    src = _c(src, np.float32)
+    hs, ws = src.shape
+    dst = np.empty((int(height), int(width)), np.float32)
+    lib().oracle_resize_bilinear(_p(src), hs, ws, _p(dst), int(height), int(width))
+    return dst

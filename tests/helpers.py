@@ -77,20 +77,20 @@ def random_scene(seed, n=5000, f=7, h=60, w=80, m_per_frame=(0, 1, 2, 3), n_quer
 
 
 # ----------------------------------------------------------------------------- golden tree helpers
-def load_expected():
+def load_expected(name="e2e.pth"):
     import os
     import torch
     from conftest import GOLDEN
-    return torch.load(os.path.join(GOLDEN, "e2e.pth"), weights_only=False)
+    return torch.load(os.path.join(GOLDEN, name), weights_only=False)
 
 
-def copy_tree(tmp_path):
-    """A writable copy of tests/golden/tree (the CLIs write outputs and checkpoints under cwd)."""
+def copy_tree(tmp_path, name="tree"):
+    """A writable copy of tests/golden/<name> (the CLIs write outputs and checkpoints under cwd)."""
     import os
     import shutil
     from conftest import GOLDEN
-    dst = os.path.join(str(tmp_path), "tree")
-    shutil.copytree(os.path.join(GOLDEN, "tree"), dst)
+    dst = os.path.join(str(tmp_path), name)
+    shutil.copytree(os.path.join(GOLDEN, name), dst)
     os.makedirs(os.path.join(dst, "checkpoints"), exist_ok=True)
     return dst
 

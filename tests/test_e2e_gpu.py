@@ -51,3 +51,28 @@ def test_multi_query_run_equals_one_reference_run_per_class(cuda_dev, tmp_path, 
         for sid in ("scene0001_00", "scene0002_00", "scene0003_00"):
             got = torch.load(os.path.join(tree, out2, cls, f"{sid}.pth"), weights_only=False)
             check_against_expected(got, expected[(cfg_name, cls, "mask_3d", sid)], f"multi stage2 {cls} {sid}")
+
+
+@pytest.mark.parametrize("in_kernel", [True, False])
+def test_cli_with_depth_upsampling_matches_reference(cuda_dev, tmp_path, monkeypatch, in_kernel):
+    """The reference's default situation (configs/config.yaml:19-20): depth PNGs smaller than the masks, every frame
+    resized by cv2.resize (:436, :563). tests/golden/tree_up + e2e_up.pth come from the unmodified reference CLIs
+    (oracle/make_golden_up.py). in_kernel=True: the lift kernel samples the native uint16 depth itself
+    (BFF_DEPTH_U16_BILINEAR, gated at run time against this machine's cv2.resize); False: cv2.resize on the host."""
+    from bff_b200 import refine, scene_io, stage2
+    tree = copy_tree(tmp_path, "tree_up")
+    monkeypatch.chdir(tree)
+    monkeypatch.setattr(scene_io, "IN_KERNEL_RESIZE", in_kernel)
+    _install_fake_clip()
+    expected = load_expected("e2e_up.pth")
+    cls = "office chair"
+    assert stage2.main(["--config", "config.yaml", "--cls", cls]) == 0
+    assert refine.main(["--config", "config.yaml", "--cls", cls]) == 0
+    if in_kernel:
+        assert scene_io._resize_checked and all(scene_io._resize_checked.values()), \
+            "the in-kernel resize disagrees with this machine's cv2.resize: the fused depth path was not exercised"
+    for sid in ("scene0001_00", "scene0002_00"):
+        got2 = torch.load(os.path.join(tree, "output/mask_3d", cls, f"{sid}.pth"), weights_only=False)
+        gotf = torch.load(os.path.join(tree, "output/final_output", cls, f"{sid}.pth"), weights_only=False)
+        check_against_expected(got2, expected[("config.yaml", cls, "mask_3d", sid)], f"stage2 {sid}")
+        check_against_expected(gotf, expected[("config.yaml", cls, "final", sid)], f"final {sid}")

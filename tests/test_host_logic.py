@@ -61,3 +61,24 @@ def test_rle_runs_follow_python_slice_semantics():
     assert np.array_equal(d, m) and L == 50
     runs, length = rle.runs_for_device([r, {"length": 50, "counts": np.zeros(0, np.int64)}])
     assert length == 50 and set(runs[:, 0].tolist()) == {0}
+
+
+def test_resize_table_reproduces_cv2_resize():
+    """bff_resize_table (host function of libbff.so) applied with float32 fmaf blends == oracle.resize_bilinear
+    (itself pinned to cv2.resize in test_oracle_golden.py)."""
+    import numpy as np
+    import oracle as O
+    from bff_b200 import ops
+    rng = np.random.default_rng(3)
+    src = (rng.integers(0, 6000, (48, 64)).astype(np.uint16)).astype(np.float32) / 1000
+    for (hd, wd) in [(97, 130), (24, 31), (48, 64)]:
+        tx, ty = ops.resize_table(wd, 64), ops.resize_table(hd, 48)
+        x0, wx = tx[:, 0], tx[:, 1].copy().view(np.float32)
+        y0, wy = ty[:, 0], ty[:, 1].copy().view(np.float32)
+        x1, y1 = np.minimum(x0 + 1, 63), np.minimum(y0 + 1, 47)
+
+        def fma(a, b, c):   # exact product and sum in float64, one rounding to float32 (no double rounding at these sizes)
+            return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(np.float32)
+        h = fma(src[:, x1] - src[:, x0], np.broadcast_to(wx, (48, wd)), src[:, x0])
+        got = fma(h[y1] - h[y0], np.broadcast_to(wy[:, None], (hd, wd)), h[y0])
+        np.testing.assert_array_equal(got, O.resize_bilinear(src, hd, wd))

@@ -268,3 +268,83 @@ def test_tensor_core_intersections_equal_popc_path_and_oracle(cuda_dev, monkeypa
     got = res["umma"][0][3].cpu().numpy()[:40]
     assert np.array_equal(np.isnan(got), nan)
     np.testing.assert_array_equal(got[~nan].view(np.int32), iou_o[~nan].view(np.int32))
+
+
+# ---- depth ingest on the device: cv2.resize(depth, (W, H)) (projection_2d_to_3d.py:431-436)
+@pytest.mark.parametrize("src_hw,dst_hw", [((480, 640), (968, 1296)), ((480, 640), (240, 320)), ((48, 64), (97, 130)),
+                                           ((97, 130), (48, 64)), ((7, 5), (19, 23)), ((60, 80), (60, 80))])
+def test_depth_resize_matches_cv2_and_oracle(cuda_dev, src_hw, dst_hw):
+    import oracle as O
+    from bff_b200 import ops
+    rng = np.random.default_rng(src_hw[0] + 3 * dst_hw[1])
+    raw = rng.integers(0, 6000, (2,) + src_hw).astype(np.uint16)
+    raw[rng.random(raw.shape) < 0.03] = 0
+    raw[0, 0, 0], raw[0, -1, -1] = 65535, 1
+    got = ops.depth_resize(torch.from_numpy(raw.view(np.int16)).to(cuda_dev), dst_hw[0], dst_hw[1]).cpu().numpy()
+    for i in range(2):
+        want = O.resize_bilinear(raw[i].astype(np.float32) / 1000, dst_hw[0], dst_hw[1])
+        np.testing.assert_array_equal(got[i].view(np.int32), want.view(np.int32))
+    try:
+        import cv2
+    except ImportError:
+        return
+    want = cv2.resize(raw[1].astype(np.float32) / 1000, (dst_hw[1], dst_hw[0]))          # the reference's own call
+    np.testing.assert_array_equal(got[1].view(np.int32), want.view(np.int32))
+
+
+def _scene_from_native_depth(seed, n, f, h, w, scale, f32):
+    """A scene whose cloud is back-projected FROM smooth native-resolution uint16 depth images (so that points are
+    visible through the resized depth): random_scene's cameras and masks, new depth and points."""
+    import oracle as O
+    sc = random_scene(seed, n=n, f=f, h=h, w=w, f32_xyz=f32)
+    rng = np.random.default_rng(seed + 1)
+    hs, ws = int(h / scale), int(w / scale)
+    yy, xx = np.mgrid[0:hs, 0:ws]
+    native = np.stack([np.clip(1500 + rng.uniform(-6, 6) * xx + rng.uniform(-6, 6) * yy + 40 * np.sin(xx / 3.0 + i), 300, 9000)
+                       for i in range(f)]).astype(np.uint16)
+    native[:, ::7, ::5] = 0                                                              # holes blend into their neighbours
+    depth = np.stack([O.resize_bilinear(r.astype(np.float32) / 1000, h, w) for r in native])
+    kinv = np.linalg.inv(sc["K"])
+    pts = []
+    for i in range(f):
+        k = n // f + (1 if i < n % f else 0)
+        px, py = rng.integers(0, w, k), rng.integers(0, h, k)
+        d = depth[i, py, px].astype(np.float64) + rng.uniform(-0.12, 0.12, k)            # straddles the 0.08 m threshold
+        cam = (kinv @ np.stack([px + rng.uniform(-0.45, 0.45, k), py + rng.uniform(-0.45, 0.45, k), np.ones(k)])) * d
+        pts.append((sc["poses"][i] @ np.concatenate([cam, np.ones((1, k))]))[:3].T)
+    xyz = np.concatenate(pts)
+    sc["xyz"] = xyz.astype(np.float32).astype(np.float64) if f32 else xyz
+    sc["depth"], sc["native"] = depth, native
+    return sc
+
+
+@pytest.mark.parametrize("f32,fpc,scale", [(True, 0, 2), (False, 4, 2), (True, 0, 0.5)])
+def test_lift_with_in_kernel_resize_matches_oracle(cuda_dev, f32, fpc, scale):
+    """BFF_DEPTH_U16_BILINEAR: native uint16 depth sampled inside the lift kernel == lifting on the resized image."""
+    import oracle as O
+    from bff_b200 import ops
+    sc = _scene_from_native_depth(23, 6007, 8, 96, 128, scale, f32)
+    native, hs, ws = sc["native"], sc["native"].shape[1], sc["native"].shape[2]
+    rows_o, mc_o, vc_o = _oracle(sc)
+    assert vc_o.sum() > 200 and rows_o.sum() > 20
+    packed2d = pack_rows(sc["masks"].reshape(sc["masks"].shape[0], -1)).view(np.int32)
+    for debug in (False, True):
+        out = ops.lift_scene(_xyz_dev(sc, cuda_dev, f32), torch.from_numpy(sc["pinv"]).to(cuda_dev), sc["K"],
+                             torch.from_numpy(native.view(np.int16)).to(cuda_dev), 96, 128,
+                             masks2d=torch.from_numpy(packed2d).to(cuda_dev), mask_offset=torch.from_numpy(sc["mask_off"]).to(cuda_dev),
+                             depth_thresh=0.08, depth_range=(0.0, 65.535), frames_per_chunk=fpc, native_size=(hs, ws), debug=debug)
+        np.testing.assert_array_equal(unpack_rows(out.rows.cpu().numpy(), sc["n"]), rows_o)
+        np.testing.assert_array_equal(out.masked_counts.cpu().numpy(), mc_o)
+        np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)
+
+
+def test_lift_ignores_nan_points_in_float32_cloud(cuda_dev):
+    """NaN coordinates (never visible) must not poison the warp's culling sphere."""
+    sc = random_scene(31, n=4099, f=6)
+    sc["xyz"][5::97] = np.nan
+    sc["xyz"][40, 1] = np.inf
+    rows_o, mc_o, vc_o = _oracle(sc)
+    out = _lift(sc, cuda_dev, f32=True)
+    np.testing.assert_array_equal(unpack_rows(out.rows.cpu().numpy(), sc["n"]), rows_o)
+    np.testing.assert_array_equal(out.masked_counts.cpu().numpy(), mc_o)
+    np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)

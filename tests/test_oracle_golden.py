@@ -121,3 +121,33 @@ def test_rle_codec(G):
     for a, b in zip(lo, hi):
         d[a:b] = True
     np.testing.assert_array_equal(d, exp)
+
+
+# ---- depth ingest: cv2.resize(depth, (W, H)) (projection_2d_to_3d.py:436) restated
+def test_resize_matches_golden():
+    import oracle as O
+    R = np.load(os.path.join(GOLDEN, "resize.npz"), allow_pickle=False)
+    k = 0
+    while f"raw{k}" in R.files:
+        dst = R[f"dst{k}"]
+        got = O.resize_bilinear(R[f"raw{k}"].astype(np.float32) / 1000, dst.shape[0], dst.shape[1])
+        np.testing.assert_array_equal(got.view(np.int32), dst.view(np.int32))
+        k += 1
+    assert k == 5
+
+
+@pytest.mark.parametrize("src_hw,dst_hw", [((480, 640), (968, 1296)), ((480, 640), (480, 640)), ((480, 640), (240, 320)),
+                                           ((480, 640), (600, 800)), ((968, 1296), (480, 640)), ((480, 640), (481, 641)),
+                                           ((480, 640), (1000, 1333)), ((120, 160), (200, 300)), ((30, 40), (60, 80)),
+                                           ((480, 640), (96, 128)), ((7, 5), (19, 23))])
+def test_resize_matches_cv2(src_hw, dst_hw):
+    """The restatement against the reference's own call, live, bit for bit (cv2 of this machine)."""
+    cv2 = pytest.importorskip("cv2")
+    import oracle as O
+    rng = np.random.default_rng(src_hw[0] * 7 + dst_hw[1])
+    raw = rng.integers(0, 6000, src_hw).astype(np.uint16)
+    raw[rng.random(src_hw) < 0.02] = 0
+    depth = raw.astype(np.float32) / 1000
+    want = cv2.resize(depth, (dst_hw[1], dst_hw[0]))
+    got = O.resize_bilinear(depth, dst_hw[0], dst_hw[1])
+    np.testing.assert_array_equal(got.view(np.int32), want.view(np.int32))
