@@ -36,48 +36,71 @@ import numpy as np
 import torch
 
 WORKLOADS = {
-    # name: (N points, frames per rank, W, H, stage-1 masks, boxes)   -- BASELINE.json configs
+    # BASELINE.json configs: N points, frames PER RANK, mask size W x H, stage-1 masks, boxes, text queries,
+    # native depth size (0 = same as the masks; else the lift kernel resamples like cv2.resize, :436)
     "c1": dict(n_points=150_000, n_frames=100, width=640, height=480, n_stage1=50, n_boxes=14),
     "c2": dict(n_points=250_000, n_frames=300, width=640, height=480, n_stage1=200, n_boxes=14),
+    # configs[2]: the c2 scene with 20 concurrent text queries (shared projection, per-query votes and rows)
+    "c3": dict(n_points=250_000, n_frames=300, width=640, height=480, n_stage1=200, n_boxes=40, n_queries=20),
+    # configs[3]: 2M points, 2000 frames over 8 ranks (250 per rank), 1296x968 masks over 640x480 depth, 500 stage-1 masks
+    "c4": dict(n_points=2_000_000, n_frames=250, width=1296, height=968, depth_width=640, depth_height=480,
+               n_stage1=500, n_boxes=40, room=(20.0, 15.0, 3.0)),
     "tiny": dict(n_points=20_000, n_frames=12, width=320, height=240, n_stage1=20, n_boxes=9),
+    "tiny3": dict(n_points=20_000, n_frames=12, width=320, height=240, depth_width=160, depth_height=120,
+                  n_stage1=20, n_boxes=9, n_queries=3),
 }
 QUERY = "office chair"
 
 
+def query_names(n_queries: int):
+    """QUERY first, then other ScanNet200 class names (spaces instead of underscores, like --cls)."""
+    from bff_b200.refine import STAGE1_CLASS_NAMES
+    names = [QUERY] + [c.replace("_", " ") for c in STAGE1_CLASS_NAMES if c.replace("_", " ") != QUERY]
+    return names[:n_queries]
+
+
 # ----------------------------------------------------------------------------- synthetic inputs
 def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, seed: int = 2000):
-    """In-memory inputs of one scene in the reference's wire formats (RLE 2D masks per frame,
-    uint16 depth, float64 poses/intrinsics, RLE stage-1 masks). Frames [rank*F, (rank+1)*F) of a
+    """In-memory inputs of one scene in the reference's wire formats (RLE 2D masks per frame and query,
+    uint16 depth at its native size, float64 poses/intrinsics, RLE stage-1 masks). Frames [rank*F, (rank+1)*F) of a
     (F*world)-frame trajectory are rendered on `device` (input fabrication, untimed)."""
     from bff_b200 import synth
     from bff_b200.refine import STAGE1_CLASS_NAMES
     from bff_b200.rle import rle_encode_rows
     w = WORKLOADS[workload]
     f_rank = w["n_frames"]
+    nq = w.get("n_queries", 1)
+    queries = query_names(nq)
     n_render = f_rank if max_frames is None else min(max_frames, f_rank)   # the CPU arms only need their sample
     spec = synth.SceneSpec(n_points=w["n_points"], n_frames=f_rank * world, width=w["width"], height=w["height"],
-                           n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=seed, n_queries=1)
+                           depth_width=w.get("depth_width", 0), depth_height=w.get("depth_height", 0),
+                           n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=seed, n_queries=nq,
+                           room=w.get("room", (6.0, 5.0, 2.8)))
     sc = synth.make_scene(spec)
     lo, hi = rank * f_rank, (rank + 1) * f_rank
     hgt, wid = spec.height, spec.width
-    depth = np.zeros((f_rank, hgt, wid), np.uint16)
-    records = []
+    dh, dw = (spec.depth_height or hgt), (spec.depth_width or wid)
+    depth = np.zeros((f_rank, dh, dw), np.uint16)
+    records = [[] for _ in queries]
     for f in range(lo, lo + n_render):
         mm, obj = synth.render_frame(sc, f, device)
         depth[f - lo] = mm.cpu().numpy().astype(np.uint16)
         rng = np.random.default_rng(spec.seed * 7919 + f)
-        ms = synth.frame_masks(sc, f, obj.cpu(), 0, rng)
-        if ms:
-            records.append({"frame_id": f"{sc.frame_ids[f]}.jpg",
-                            "segmented_frame_masks": rle_encode_rows(torch.stack(ms).reshape(len(ms), -1)),
-                            "confidences": torch.as_tensor(rng.uniform(0.2, 0.45, len(ms)).astype(np.float32)),
-                            "labels": [QUERY] * len(ms)})
+        obj = obj.cpu()
+        for qi, q in enumerate(queries):
+            ms = synth.frame_masks(sc, f, obj, qi, rng)
+            if ms:
+                records[qi].append({"frame_id": f"{sc.frame_ids[f]}.jpg",
+                                    "segmented_frame_masks": rle_encode_rows(torch.stack(ms).reshape(len(ms), -1)),
+                                    "confidences": torch.as_tensor(rng.uniform(0.2, 0.45, len(ms)).astype(np.float32)),
+                                    "labels": [q] * len(ms)})
     rng = np.random.default_rng(spec.seed + 7)
-    m1, c1, conf1 = synth.stage1_masks(sc, [QUERY], STAGE1_CLASS_NAMES, rng)
+    m1, c1, conf1 = synth.stage1_masks(sc, queries, STAGE1_CLASS_NAMES, rng)
     stage1 = {"ins": rle_encode_rows(torch.from_numpy(m1)), "conf": torch.from_numpy(conf1),
               "final_class": torch.from_numpy(c1)}
     pinv = np.stack([np.linalg.inv(p) for p in sc.poses[lo:hi]])
-    return dict(spec=spec, xyz=sc.xyz, K=sc.K, poses=sc.poses[lo:hi], pinv=pinv, depth=depth, records=records,
+    return dict(spec=spec, xyz=sc.xyz, K=sc.K, poses=sc.poses[lo:hi], pinv=pinv, depth=depth, records=records[0],
+                records_by_query=records, queries=queries,
                 frame_ids=[str(i) for i in sc.frame_ids[lo:hi]], stage1=stage1, cfg=dict(synth.DEFAULT_CFG))
 
 
@@ -90,7 +113,8 @@ def fake_similarity(query: str, label: str) -> float:
 
 # ----------------------------------------------------------------------------- our arm
 class GpuScene:
-    """Host-staged (pinned) and device-resident forms of one rank's inputs + the step itself."""
+    """Host-staged (pinned) and device-resident forms of one rank's inputs + the step itself.
+    Q text queries share one lifting launch (projection, visibility, viewed counts); rows and votes are per query."""
 
     def __init__(self, inp, device, dist_ctx=None):
         from bff_b200 import lift as lift_mod, scene_io
@@ -99,17 +123,27 @@ class GpuScene:
         spec = inp["spec"]
         self.n, self.h, self.w = spec.n_points, spec.height, spec.width
         self.f = inp["depth"].shape[0]
-        q = lift_mod.QueryMasks.from_file_records(QUERY, inp["records"])
-        self.q = q
-        self.frame_ids, self.viewed, self.per_frame = lift_mod.plan_frames([q], inp["frame_ids"])
+        self.native = tuple(inp["depth"].shape[1:])                 # depth PNG size; != (h, w): resampled in the lift kernel
+        self.names = list(inp["queries"])
+        self.nq = len(self.names)
+        self.queries = [lift_mod.QueryMasks.from_file_records(nm, recs) for nm, recs in zip(self.names, inp["records_by_query"])]
+        self.q = self.queries[0]
+        self.frame_ids, self.viewed, self.per_frame = lift_mod.plan_frames(self.queries, inp["frame_ids"])
         order = {fid: i for i, fid in enumerate(inp["frame_ids"])}
         perm = [order[fid] for fid in self.frame_ids]           # mask frames first, then view-only frames
-        rles, _, offsets = lift_mod.mask_layout(self.per_frame, [q], 0, len(self.frame_ids))
+        rles, mask_query, offsets = lift_mod.mask_layout(self.per_frame, self.queries, 0, len(self.frame_ids))
         runs, length = runs_for_device(rles)
         assert length == self.h * self.w
         self.n_masks = len(rles)
-        self.conf_list, self.labels = q.flat_conf_and_labels()
-        self.conf_list = torch.tensor(self.conf_list) if self.conf_list else []   # :484-486, parsed once with the file
+        self.row_index = lift_mod.query_row_index(self.per_frame, self.queries)   # per query: its rows in file order
+        self.conf_q, self.labels_q = [], []
+        for q in self.queries:
+            c, l = q.flat_conf_and_labels()
+            self.conf_q.append(torch.tensor(c) if c else [])    # :484-486, parsed once with the file
+            self.labels_q.append(l)
+        self.conf_list, self.labels = self.conf_q[0], self.labels_q[0]
+        self.my_queries = list(range(self.nq))                  # frame-sharded runs split the queries over the ranks
+        self.workers = int(os.environ.get("BFF_QUERY_WORKERS", "2"))   # concurrent per-query chains (bff_b200/pool.py)
         s1_runs, s1_len = runs_for_device(list(inp["stage1"]["ins"]))
         assert s1_len == self.n
 
@@ -124,7 +158,12 @@ class GpuScene:
         self.host = dict(xyz=pin(x4), pinv=pin(inp["pinv"][perm]), depth=pin(inp["depth"][perm].view(np.int16)),
                          runs=pin(runs), offsets=pin(np.asarray(offsets, np.int32)),
                          viewed=pin(np.asarray(self.viewed, np.uint8)), s1_runs=pin(s1_runs))
+        if self.nq > 1:
+            self.host["mask_query"] = pin(np.asarray(mask_query, np.int32))
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
+        self.row_index_dev = None
+        if self.nq > 1 and torch.cuda.is_available():
+            self.row_index_dev = [torch.tensor(ix, dtype=torch.long, device=device) for ix in self.row_index]
         self.lift_events = None
         if torch.cuda.is_available():
             # recorded inside bff_lift_scene around its memsets + kernel: the launch itself, without host gaps
@@ -133,36 +172,67 @@ class GpuScene:
     def upload(self):
         return {k: v.to(self.dev, non_blocking=True) for k, v in self.host.items()}
 
+    def lift(self, d, masks2d, timing=False, frames_per_chunk=0):
+        from bff_b200 import ops
+        return ops.lift_scene(d["xyz"], d["pinv"], self.inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
+                              mask_offset=d["offsets"] if self.n_masks else None,
+                              mask_query=d.get("mask_query") if self.n_masks else None, n_queries=self.nq,
+                              frame_viewed=d["viewed"], depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535),
+                              native_size=self.native, frames_per_chunk=frames_per_chunk,
+                              timing_events=self.lift_events if timing else None)
+
     def step(self, d, timers=None, to_host=True):
-        """One pass of the hot path on device-resident inputs `d`. Returns the final dict; its (k,N) bool masks
-        are copied to the host (pinned) when `to_host`, else they stay in HBM like the inputs."""
+        """One pass of the hot path on device-resident inputs `d`. Returns the final dict of query 0 (all queries'
+        results are in self.last_finals); its (k,N) bool masks are copied to the host (pinned) when `to_host`,
+        else they stay in HBM like the inputs."""
         from bff_b200 import ops, refine, stage2
         inp, cfg = self.inp, self.inp["cfg"]
         ev = (lambda: None) if timers is None else (lambda: timers.append(_event()))
         ev()
         masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
         ev()
-        out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
-                             mask_offset=d["offsets"] if self.n_masks else None, frame_viewed=d["viewed"],
-                             depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535),
-                             timing_events=self.lift_events if timers is not None else None)
+        out = self.lift(d, masks2d, timing=timers is not None)
         ev()
         rows, mc, vc = out.rows, out.masked_counts, out.viewed_counts
-        conf_list, labels = self.conf_list, self.labels
-        if self.dist is not None and self.dist.world_size > 1:
+        sharded = self.dist is not None and self.dist.world_size > 1
+        if sharded:
             from bff_b200 import dist as dist_mod
             rows, mc, vc = dist_mod.exchange(self.dist, rows, self.rows_per_rank, mc, vc)
-            conf_list, labels = self.all_conf, self.all_labels
-        ev()
-        res2, _ = stage2.aggregate_and_filter(rows, conf_list, labels, mc[0], vc, self.n, cfg, keep_rows=True, to_host=to_host)
         ev()
         s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
-        p1 = refine.pass1_scene(inp["stage1"], res2, QUERY, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)
-        thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
-        final = refine.pass2_scene(p1, QUERY, cfg["refiment_iou_thres"], thr, to_host=to_host)
-        ev()
-        self.last_stage2 = res2
-        return final
+
+        def aggregate(qi):
+            if sharded:
+                conf_list, labels, idx = self.all_conf[qi], self.all_labels[qi], self.all_index_dev[qi]
+            else:
+                conf_list, labels = self.conf_q[qi], self.labels_q[qi]
+                idx = self.row_index_dev[qi] if self.row_index_dev is not None else None
+            rows_q = rows if idx is None else rows[idx]
+            res2, _ = stage2.aggregate_and_filter(rows_q, conf_list, labels, mc[qi], vc, self.n, cfg, keep_rows=True, to_host=to_host)
+            return res2
+
+        def refine_query(qi, res2):
+            name = self.names[qi]
+            p1 = refine.pass1_scene(inp["stage1"], res2, name, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)
+            thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+            return refine.pass2_scene(p1, name, cfg["refiment_iou_thres"], thr, to_host=to_host)
+
+        if len(self.my_queries) > 1 and self.workers > 1:
+            # the queries' chains are independent: run them on concurrent streams (bff_b200/pool.py); the two stage
+            # timers then cover both stages of all queries together
+            from bff_b200.pool import get_pool
+            both = get_pool(self.dev, self.workers).map(lambda qi: (lambda r2: (r2, refine_query(qi, r2)))(aggregate(qi)), self.my_queries)
+            per_query, finals = [b[0] for b in both], [b[1] for b in both]
+            ev()
+            ev()
+        else:
+            per_query = [aggregate(qi) for qi in self.my_queries]
+            ev()
+            finals = [refine_query(qi, r2) for qi, r2 in zip(self.my_queries, per_query)]
+            ev()
+        self.last_stage2 = per_query[0] if per_query else None
+        self.last_finals = finals
+        return finals[0] if finals else None
 
 
 def _event():
@@ -176,7 +246,8 @@ def lift_algorithmic_bytes(g: GpuScene) -> int:
     Depth is consumed as uint16 here (2 bytes per pixel), which is what the product path feeds."""
     n, hw = g.n, g.h * g.w
     wd = (n + 31) // 32
-    return g.f * (16 * n + 2 * hw) + g.n_masks * ((hw + 31) // 32 * 4 + 4 * wd) + 4 * n * 2
+    depth_px = g.native[0] * g.native[1]            # the uint16 depth the kernel actually reads (native size)
+    return g.f * (16 * n + 2 * depth_px) + g.n_masks * ((hw + 31) // 32 * 4 + 4 * wd) + 4 * n * (1 + g.nq)
 
 
 class ClockSampler:
@@ -374,13 +445,10 @@ def run_gpu(args):
         done[i % 2].record()
     torch.cuda.synchronize()
     e2e_pipe_ms = (time.perf_counter() - t0) * 1e3
-    d2h = 0
-    if isinstance(final["ins"], torch.Tensor):
-        d2h = final["ins"].numel() * final["ins"].element_size()
+    d2h = sum(fn["ins"].numel() * fn["ins"].element_size() for fn in g.last_finals if isinstance(fn["ins"], torch.Tensor))
     # ---- IoU kernel alone (mask-IoU pairs/s of the aggregation-sized square call)
     from bff_b200 import ops
-    rows = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], g.h, g.w,
-                          masks2d=ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w), mask_offset=d["offsets"]).rows
+    rows = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)).rows
     for _ in range(3):
         ops.mask_iou(rows)
     torch.cuda.synchronize()
@@ -414,10 +482,12 @@ def run_gpu(args):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: ScanNet200-shaped scene, {g.n} points, {g.f} frames/GPU {g.w}x{g.h}, "
-                               f"1 query, {g.n_masks} lifted 2D masks/GPU, {len(inp['stage1']['ins'])} stage-1 masks",
+                               f"{g.nq} quer{'y' if g.nq == 1 else 'ies'}, {g.n_masks} lifted 2D masks/GPU, {len(inp['stage1']['ins'])} stage-1 masks"
+                               + (f", depth {g.native[1]}x{g.native[0]} resampled in the lift kernel" if g.native != (g.h, g.w) else ""),
+                   "queries": g.nq,
                    "n_points": g.n, "frames_per_gpu": g.f, "lifted_masks_per_gpu": g.n_masks,
                    "parallelism": f"scene-parallel x{world}: one scene per GPU, no data-path collective" if world > 1 else "single GPU",
-                   "l2": "256 MB flush written between timed steps; per-step inputs are 211 MB (> 126 MB L2)"},
+                   "l2": f"256 MB flush written between timed steps; per-step inputs are {g.h2d_bytes / 1e6:.0f} MB (> 126 MB L2)"},
         "stages_ms": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
                               (stage_acc / k).round(4).tolist())),
         "lift_point_views_per_s": pv / (ms_lift * 1e-3),
@@ -451,10 +521,18 @@ def frame_sharded_run(args, ctx, dev, flush, barrier):
     inp = build_inputs(args.workload, rank, world, dev)
     g = GpuScene(inp, dev, ctx)
     gathered = [None] * world
-    dist.all_gather_object(gathered, (g.n_masks, [float(c) for c in g.conf_list], g.labels))
+    dist.all_gather_object(gathered, (g.n_masks, [[float(c) for c in cq] for cq in g.conf_q], g.labels_q, g.row_index))
     g.rows_per_rank = [x[0] for x in gathered]
-    g.all_conf = torch.tensor([c for x in gathered for c in x[1]], dtype=torch.float32)
-    g.all_labels = [l for x in gathered for l in x[2]]
+    base = np.concatenate([[0], np.cumsum(g.rows_per_rank)])
+    # per query: confidences, labels and row positions of the whole scene = rank blocks in rank order (file order)
+    g.all_conf = [torch.tensor([c for x in gathered for c in x[1][qi]], dtype=torch.float32) for qi in range(g.nq)]
+    g.all_labels = [[l for x in gathered for l in x[2][qi]] for qi in range(g.nq)]
+    g.all_index_dev = [torch.tensor([int(base[r]) + i for r, x in enumerate(gathered) for i in x[3][qi]], dtype=torch.long, device=dev)
+                       for qi in range(g.nq)]
+    if g.nq > 1:
+        g.my_queries = list(range(rank, g.nq, world))       # after the exchange every rank refines its share of the queries
+    elif g.nq == 1:
+        g.all_index_dev = [None]
     d = g.upload()
     for _ in range(2):
         g.step(d)
@@ -476,45 +554,60 @@ def frame_sharded_run(args, ctx, dev, flush, barrier):
             "frames_total": g.f * world, "lifted_masks_total": int(sum(g.rows_per_rank)),
             "stages_ms_rank0": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
                                         (stage / steps).round(4).tolist())),
+            "queries": g.nq, "queries_per_rank": len(g.my_queries),
             "collectives": "all_reduce(SUM,int32)[votes] + all_gather[packed rows], NCCL"}
 
 
 # ----------------------------------------------------------------------------- CPU baseline (oracle port)
 def cpu_frames_of(inp, n_frames):
-    """First n_frames of the rank's block as the reference's per-frame inputs (dense float32 masks/depth)."""
+    """First n_frames of the rank's block as the reference's per-frame inputs (dense float32 masks / depth at mask
+    resolution, cv2.resize like :436 when the depth PNGs are smaller). Returns (per-query mask frames, view frames)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import reference_port as RP
-    by_frame = {r["frame_id"][:-4]: r for r in inp["records"]}
+    from bff_b200 import scene_io
     hgt, wid = inp["spec"].height, inp["spec"].width
-    mask_frames, view_frames = [], []
-    for i, fid in enumerate(inp["frame_ids"][:n_frames]):
-        depth = inp["depth"][i].astype(np.float32) / 1000
-        fr = {"pose": inp["poses"][i], "depth": depth}
-        view_frames.append(fr)
-        if fid in by_frame:
-            r = by_frame[fid]
-            masks = np.stack([RP.rle_to_mask(m).reshape(hgt, wid) for m in r["segmented_frame_masks"]]).astype(np.float32)
-            mask_frames.append(dict(fr, masks=masks, conf=r["confidences"], labels=r["labels"]))
-    return mask_frames, view_frames
+    view_frames = []
+    for i in range(min(n_frames, len(inp["frame_ids"]))):
+        view_frames.append({"pose": inp["poses"][i], "depth": scene_io.depth_to_metres(inp["depth"][i], wid, hgt)})
+    per_query = []
+    for recs in inp["records_by_query"]:
+        by_frame = {r["frame_id"][:-4]: r for r in recs}
+        mask_frames = []
+        for i, fid in enumerate(inp["frame_ids"][:n_frames]):
+            if fid in by_frame:
+                r = by_frame[fid]
+                masks = np.stack([RP.rle_to_mask(m).reshape(hgt, wid) for m in r["segmented_frame_masks"]]).astype(np.float32)
+                mask_frames.append(dict(view_frames[i], masks=masks, conf=r["confidences"], labels=r["labels"]))
+        per_query.append(mask_frames)
+    return per_query, view_frames
 
 
-def cpu_step(inp, mask_frames, view_frames):
-    """The reference's path for one scene on the CPU (numpy/OpenBLAS + torch CPU, oracle/reference_port.py)."""
+def cpu_step(inp, mask_frames_by_query, view_frames):
+    """The reference's path for one scene on the CPU (numpy/OpenBLAS + torch CPU, oracle/reference_port.py): one full
+    run per text query, each projecting every frame again, exactly like one reference process per --cls."""
     import reference_port as RP
     from bff_b200.refine import STAGE1_CLASS_NAMES
     cfg = inp["cfg"]
-    res2 = RP.stage2_scene(inp["xyz"], inp["K"], mask_frames, view_frames, cfg)
-    s1 = torch.from_numpy(np.stack([RP.rle_to_mask(r) for r in inp["stage1"]["ins"]]))
-    labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
-    p1 = RP.refine_pass1(s1, labels, res2, QUERY, cfg["stage1_iou_thres"], fake_similarity)
-    thr = RP.sim_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
-    return RP.refine_pass2(p1, QUERY, cfg["refiment_iou_thres"], thr)
+    out = []
+    for name, mask_frames in zip(inp["queries"], mask_frames_by_query):
+        res2 = RP.stage2_scene(inp["xyz"], inp["K"], mask_frames, view_frames, cfg)
+        s1 = torch.from_numpy(np.stack([RP.rle_to_mask(r) for r in inp["stage1"]["ins"]]))
+        labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
+        p1 = RP.refine_pass1(s1, labels, res2, name, cfg["stage1_iou_thres"], fake_similarity)
+        thr = RP.sim_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+        out.append(RP.refine_pass2(p1, name, cfg["refiment_iou_thres"], thr))
+    return out
+
+
+def cpu_sample_frames(inp, requested):
+    """Frames in the bounded CPU sample: the reference repeats the whole frame loop per query, so Q queries get 1/Q of them."""
+    return max(4, min(requested // max(len(inp["queries"]), 1), inp["depth"].shape[0]))
 
 
 def cpu_baseline(inp, n_frames):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_frames = min(n_frames, inp["depth"].shape[0])
+    n_frames = cpu_sample_frames(inp, n_frames)
     mask_frames, view_frames = cpu_frames_of(inp, n_frames)
     t0 = time.perf_counter()
     cpu_step(inp, mask_frames, view_frames)
@@ -536,10 +629,10 @@ def run_reference(args):
     torch.set_num_threads(cores)
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # input fabrication only
     inp = build_inputs(args.workload, 0, 1, dev, max_frames=args.cpu_frames)
-    n_frames = min(args.cpu_frames, inp["depth"].shape[0])
+    n_frames = cpu_sample_frames(inp, args.cpu_frames)
     mask_frames, view_frames = cpu_frames_of(inp, n_frames)
     for _ in range(min(args.warmup, 1)):
-        cpu_step(inp, mask_frames[:2], view_frames[:2])
+        cpu_step(inp, [m[:2] for m in mask_frames], view_frames[:2])
     t0 = time.perf_counter()
     for _ in range(args.steps):
         cpu_step(inp, mask_frames, view_frames)

@@ -137,9 +137,12 @@ _ctxs = {}
 
 
 def ctx(device_index: int):
-    """One bff_ctx (stream + scratch arenas) per device, created on first use."""
-    if device_index not in _ctxs:
+    """One bff_ctx (stream + scratch arenas) per device AND host thread, created on first use: the fused pipelines
+    carve their scratch from the context's arenas, so concurrent callers (bff_b200/pool.py) each need their own."""
+    import threading
+    key = (int(device_index), threading.get_ident())
+    if key not in _ctxs:
         h = c_void_p()
         check(lib().bff_ctx_create(int(device_index), ctypes.byref(h)), "bff_ctx_create")
-        _ctxs[device_index] = h
-    return _ctxs[device_index]
+        _ctxs[key] = h
+    return _ctxs[key]

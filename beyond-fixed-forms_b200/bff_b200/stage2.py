@@ -11,6 +11,7 @@ from . import _log, aggregate, lift as lift_mod, scene_io
 from ._log import log
 
 
+QUERY_WORKERS = 2     # concurrent per-query aggregation chains of process_scene_queries (1 = sequential loop)
 FUSED = True     # bff_stage2_aggregate (C++ decisions next to the launches); False = one Python/torch call per step
 
 
@@ -109,10 +110,15 @@ def process_scene_queries(cfg, classes, scene_id: str, device):
     frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
     lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, queries, height, width,
                            want_viewed and any_masks)
-    for qi, q in enumerate(queries):
-        conf_list, labels = q.flat_conf_and_labels()
-        out[q.query] = aggregate_and_filter(lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts,
-                                            xyz.shape[0], cfg)
+    def one(qi):
+        conf_list, labels = queries[qi].flat_conf_and_labels()
+        return aggregate_and_filter(lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts,
+                                    xyz.shape[0], cfg)
+    # the per-query chains are independent: several at once on their own streams (pool.py), same results
+    from .pool import get_pool
+    results = get_pool(device, QUERY_WORKERS).map(one, range(len(queries)))
+    for q, r in zip(queries, results):
+        out[q.query] = r
     return out
 
 

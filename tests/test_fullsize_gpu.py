@@ -79,3 +79,141 @@ def test_c2_subset_exact_against_oracle(c2):
     np.testing.assert_array_equal(got_rows, rows_o)
     np.testing.assert_array_equal(full.masked_counts.cpu().numpy()[0][sel], mc_o[0])
     np.testing.assert_array_equal(full.viewed_counts.cpu().numpy()[sel], vc_o)
+
+
+# ------------------------------------------------------------------ c3: the c2 scene with 20 concurrent text queries
+@pytest.fixture(scope="module")
+def c3(cuda_dev):
+    sys.path.insert(0, ROOT)
+    import bench
+    from bff_b200 import ops
+    inp = bench.build_inputs("c3", 0, 1, cuda_dev)
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+    return inp, g, d, masks2d
+
+
+def test_c3_shared_projection_equals_one_launch_per_query(c3):
+    """BASELINE configs[2]: 20 queries lifted in ONE launch (shared projection / visibility / viewed counts, per-query
+    votes) give, for every query, exactly the rows and votes of a launch that carries only that query's masks --
+    which is what one reference process per --cls computes."""
+    from bff_b200 import ops
+    inp, g, d, masks2d = c3
+    assert g.nq == 20 and g.n == 250_000 and g.f == 300 and g.n_masks > 800
+    full = g.lift(d, masks2d)
+    mq = d["mask_query"].cpu().numpy()
+    off = d["offsets"].cpu().numpy()
+    pop = ops.rows_and_popcount(full.rows.clone()).cpu().numpy()
+    for qi in range(g.nq):                                                   # votes are one per set row bit, per query
+        assert int(pop[mq == qi].sum()) == int(full.masked_counts[qi].sum())
+    assert int(full.masked_counts.sum()) > 100_000
+    busiest = np.argsort(-np.bincount(mq, minlength=g.nq))[:3].tolist()
+    for qi in busiest:
+        sel = np.nonzero(mq == qi)[0]
+        per_frame = np.array([np.count_nonzero((sel >= off[f]) & (sel < off[f + 1])) for f in range(g.f)])
+        off_q = torch.from_numpy(np.concatenate([[0], np.cumsum(per_frame)]).astype(np.int32)).to(g.dev)
+        sel_t = torch.from_numpy(sel).to(g.dev)
+        one = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], g.h, g.w, masks2d=masks2d[sel_t], mask_offset=off_q,
+                             frame_viewed=d["viewed"], depth_range=(0.0, 65.535))
+        assert len(sel) > 10
+        assert torch.equal(one.rows, full.rows[sel_t])
+        assert torch.equal(one.masked_counts[0], full.masked_counts[qi])
+        assert torch.equal(one.viewed_counts, full.viewed_counts)
+    # the launch layout and each query's file order agree with the host bookkeeping
+    for qi in range(g.nq):
+        assert sorted(g.row_index[qi]) == np.nonzero(mq == qi)[0].tolist()
+
+
+def test_c3_subset_exact_against_oracle(c3):
+    import oracle as O
+    inp, g, d, masks2d = c3
+    full = g.lift(d, masks2d)
+    nf = 60                                                                   # first 60 planned frames, every 97th point
+    off = d["offsets"].cpu().numpy()[:nf + 1]
+    part = ops_lift_block(c3, 0, nf)
+    sel = np.arange(0, g.n, 97)[:2560]
+    perm = [inp["frame_ids"].index(fid) for fid in g.frame_ids][:nf]
+    depth = (inp["depth"][perm].astype(np.float32) / 1000).astype(np.float32)
+    masks = unpack_rows(masks2d[:off[-1]].cpu().numpy(), g.h * g.w).reshape(-1, g.h, g.w).astype(np.uint8)
+    rows_o, mc_o, vc_o = O.lift_scene(inp["xyz"][sel], inp["pinv"][perm], inp["K"], depth, 0.08, masks, off,
+                                      d["mask_query"].cpu().numpy()[:off[-1]], np.asarray(g.viewed[:nf], np.uint8), n_query=g.nq)
+    assert vc_o.sum() > 2_000 and rows_o.sum() > 300
+    np.testing.assert_array_equal(unpack_rows(part.rows.cpu().numpy(), g.n)[:, sel], rows_o)
+    np.testing.assert_array_equal(part.masked_counts.cpu().numpy()[:, sel], mc_o)
+    np.testing.assert_array_equal(part.viewed_counts.cpu().numpy()[sel], vc_o)
+    assert torch.equal(part.rows, full.rows[:off[-1]])
+
+
+def ops_lift_block(fx, lo, hi, fpc=0, depth=None, native="same"):
+    """Frames [lo, hi) of a GpuScene fixture (all queries)."""
+    from bff_b200 import ops
+    inp, g, d, masks2d = fx
+    off = d["offsets"][lo:hi + 1]
+    m0, m1 = int(off[0]), int(off[-1])
+    return ops.lift_scene(d["xyz"], d["pinv"][lo:hi], inp["K"], d["depth"][lo:hi] if depth is None else depth, g.h, g.w,
+                          masks2d=masks2d[m0:m1] if m1 > m0 else None, mask_offset=(off - off[0]).contiguous() if m1 > m0 else None,
+                          mask_query=d["mask_query"][m0:m1].contiguous() if (m1 > m0 and "mask_query" in d) else None, n_queries=g.nq,
+                          frame_viewed=d["viewed"][lo:hi], depth_range=(0.0, 65.535), frames_per_chunk=fpc,
+                          native_size=g.native if native == "same" else native)
+
+
+# ------------------------------------------------------------------ c4: one rank's share of the 2M-point / 2000-frame scene
+@pytest.fixture(scope="module")
+def c4(cuda_dev):
+    sys.path.insert(0, ROOT)
+    import bench
+    from bff_b200 import ops
+    saved = dict(bench.WORKLOADS["c4"])
+    bench.WORKLOADS["c4"]["n_frames"] = 96                                   # a 96-frame block keeps the fixture under a minute
+    try:
+        inp = bench.build_inputs("c4", 0, 1, cuda_dev)
+    finally:
+        bench.WORKLOADS["c4"] = saved
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+    return inp, g, d, masks2d
+
+
+def test_c4_in_kernel_resize_blocks_and_chunks(c4):
+    """BASELINE configs[3] shape (2M points, 1296x968 masks over 640x480 uint16 depth): the kernel's own bilinear sampling
+    equals lifting on the image bff_depth_resize writes (which equals cv2.resize, test_kernels_gpu.py); frame blocks
+    add up (the multi-GPU invariant) and chunking is invisible."""
+    from bff_b200 import ops
+    inp, g, d, _ = c4
+    assert g.n == 2_000_000 and (g.h, g.w) == (968, 1296) and g.native == (480, 640)
+    full = ops_lift_block(c4, 0, g.f)
+    assert full.rows.shape[0] > 60 and int(full.viewed_counts.sum()) > 5_000_000
+    pop = ops.rows_and_popcount(full.rows.clone())
+    assert int(pop.sum()) == int(full.masked_counts.sum()) > 50_000
+    resized = ops.depth_resize(d["depth"], g.h, g.w)                          # (F, 968, 1296) float32 on the device
+    ref = ops_lift_block(c4, 0, g.f, depth=resized, native=None)
+    assert torch.equal(ref.rows, full.rows) and torch.equal(ref.masked_counts, full.masked_counts)
+    assert torch.equal(ref.viewed_counts, full.viewed_counts)
+    del resized, ref
+    cut = 41
+    a, b = ops_lift_block(c4, 0, cut), ops_lift_block(c4, cut, g.f)
+    assert torch.equal(a.masked_counts + b.masked_counts, full.masked_counts)
+    assert torch.equal(a.viewed_counts + b.viewed_counts, full.viewed_counts)
+    assert torch.equal(torch.cat([a.rows, b.rows]), full.rows)
+    o = ops_lift_block(c4, 0, g.f, fpc=96)
+    assert torch.equal(o.rows, full.rows) and torch.equal(o.viewed_counts, full.viewed_counts)
+
+
+def test_c4_subset_exact_against_oracle(c4):
+    import oracle as O
+    inp, g, d, masks2d = c4
+    nf = 24
+    part = ops_lift_block(c4, 0, nf)
+    off = d["offsets"].cpu().numpy()[:nf + 1]
+    sel = np.arange(0, g.n, 389)[:5000]
+    perm = [inp["frame_ids"].index(fid) for fid in g.frame_ids][:nf]
+    depth = np.stack([O.resize_bilinear(inp["depth"][i].astype(np.float32) / 1000, g.h, g.w) for i in perm])
+    masks = unpack_rows(masks2d[:off[-1]].cpu().numpy(), g.h * g.w).reshape(-1, g.h, g.w).astype(np.uint8)
+    rows_o, mc_o, vc_o = O.lift_scene(inp["xyz"][sel], inp["pinv"][perm], inp["K"], depth, 0.08, masks, off,
+                                      None, np.asarray(g.viewed[:nf], np.uint8))
+    assert vc_o.sum() > 2_000 and rows_o.sum() > 50
+    np.testing.assert_array_equal(unpack_rows(part.rows.cpu().numpy(), g.n)[:, sel], rows_o)
+    np.testing.assert_array_equal(part.masked_counts.cpu().numpy()[0][sel], mc_o[0])
+    np.testing.assert_array_equal(part.viewed_counts.cpu().numpy()[sel], vc_o)

@@ -60,6 +60,33 @@ def test_fused_pipeline_equals_stepwise_and_port(cuda_dev, occurrence):
     assert torch.equal(torch.as_tensor(ap1["ious"]), torch.as_tensor(bp1["ious"])) and ap1["sims"] == bp1["sims"]
     # and the dense CPU port of the reference (oracle) on the same inputs
     mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
-    pfin = bench.cpu_step(inp, mask_frames, view_frames)
+    pfin = bench.cpu_step(inp, mask_frames, view_frames)[0]
     assert torch.equal(afin["ins"], pfin["ins"]) and list(afin["final_class"]) == list(pfin["final_class"])
     np.testing.assert_allclose(afin["conf"].numpy(), pfin["conf"].numpy(), rtol=1e-5)
+
+
+def test_concurrent_queries_equal_sequential_loop_and_port(cuda_dev, monkeypatch):
+    """Three text queries of one scene, depth PNGs at half the mask size (resampled in the lift kernel): the per-query
+    chains run on concurrent streams (bff_b200/pool.py) must give what the sequential loop gives, and both what the
+    dense CPU port of the reference computes with one full run per query (cv2.resize on every frame)."""
+    sys.path.insert(0, ROOT)
+    import bench
+    inp = bench.build_inputs("tiny3", 0, 1, cuda_dev)
+    g = bench.GpuScene(inp, cuda_dev)
+    assert g.nq == 3 and g.native == (120, 160) and (g.h, g.w) == (240, 320)
+    d = g.upload()
+    g.workers = 4
+    g.step(d)
+    pooled = list(g.last_finals)
+    g.workers = 1
+    g.step(d)
+    serial = list(g.last_finals)
+    mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
+    port = bench.cpu_step(inp, mask_frames, view_frames)
+    assert sum(isinstance(f["ins"], torch.Tensor) and f["ins"].shape[0] >= 2 for f in serial) >= 2
+    for qi in range(g.nq):
+        _same(pooled[qi], serial[qi], f"pooled vs serial, query {qi}")
+        assert list(serial[qi]["final_class"]) == list(port[qi]["final_class"])
+        if isinstance(serial[qi]["ins"], torch.Tensor):
+            assert torch.equal(serial[qi]["ins"].cpu(), port[qi]["ins"])
+            np.testing.assert_allclose(torch.as_tensor(serial[qi]["conf"]).cpu().numpy(), port[qi]["conf"].numpy(), rtol=1e-5)
