@@ -143,7 +143,7 @@ class GpuScene:
             self.labels_q.append(l)
         self.conf_list, self.labels = self.conf_q[0], self.labels_q[0]
         self.my_queries = list(range(self.nq))                  # frame-sharded runs split the queries over the ranks
-        self.workers = int(os.environ.get("BFF_QUERY_WORKERS", "2"))   # concurrent per-query chains (bff_b200/pool.py)
+        self.workers = int(os.environ.get("BFF_QUERY_WORKERS", "1"))   # concurrent per-query chains (bff_b200/pool.py)
         s1_runs, s1_len = runs_for_device(list(inp["stage1"]["ins"]))
         assert s1_len == self.n
 

@@ -355,3 +355,16 @@ def upload(dst: torch.Tensor, src_pinned: torch.Tensor, stream: Optional[torch.c
     if nbytes >= 16:
         _count()
     return dst
+
+
+def labels_to_rows(labels: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    """labels (N,) int64 CUDA, ids (G,) int64 CUDA -> (G, ceil(N/32)) int32 packed rows, bit p of row g = labels[p] == ids[g]
+    (bff_labels_to_rows; evaluator side, scannetv2_inst_eval.py:348)."""
+    labels = _cuda(labels, torch.int64, "labels").reshape(-1)
+    ids = _cuda(ids, torch.int64, "ids").reshape(-1)
+    n, g = labels.shape[0], ids.shape[0]
+    out = torch.zeros((g, words_for(n)), dtype=torch.int32, device=labels.device)
+    check(lib().bff_labels_to_rows(ptr(labels), n, ptr(ids), g, ptr(out), current_stream()), "bff_labels_to_rows")
+    if n and g:
+        _count()
+    return out

@@ -11,7 +11,7 @@ from . import _log, aggregate, lift as lift_mod, scene_io
 from ._log import log
 
 
-QUERY_WORKERS = 2     # concurrent per-query aggregation chains of process_scene_queries (1 = sequential loop)
+QUERY_WORKERS = 1     # concurrent per-query aggregation chains of process_scene_queries (1 = sequential loop)
 FUSED = True     # bff_stage2_aggregate (C++ decisions next to the launches); False = one Python/torch call per step
 
 

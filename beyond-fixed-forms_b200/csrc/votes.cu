@@ -132,3 +132,41 @@ extern "C" int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, i
     BFF_LAUNCH_CHECK("point_keep_kernel");
     return BFF_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// bff_labels_to_rows: per-point instance labels -> one packed row per listed instance id. The evaluator
+// (evaluation/eval/scannetv2_inst_eval.py:348-359) tests `gts == gt_inst["instance_id"]` once per
+// (prediction, ground-truth instance) pair; here every instance becomes a packed row once, and all
+// pred x gt intersections are one bff_mask_iou call.
+namespace bff {
+constexpr int kLabelIdsPerPass = 1024;
+__global__ void __launch_bounds__(256)
+labels_to_rows_kernel(const long long *__restrict__ labels, long long n, const long long *__restrict__ ids, int n_ids,
+                      long long words, uint32_t *__restrict__ rows) {
+    __shared__ long long s_ids[kLabelIdsPerPass];
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    const long long lab = i < n ? __ldg(labels + i) : 0;
+    const bool valid = i < n;
+    for (int base = 0; base < n_ids; base += kLabelIdsPerPass) {
+        const int cnt = min(kLabelIdsPerPass, n_ids - base);
+        __syncthreads();
+        for (int k = threadIdx.x; k < cnt; k += 256) s_ids[k] = __ldg(ids + base + k);
+        __syncthreads();
+        for (int k = 0; k < cnt; ++k) {
+            const unsigned w = __ballot_sync(0xffffffffu, valid && lab == s_ids[k]);
+            if ((threadIdx.x & 31) == 0 && valid) rows[(long long)(base + k) * words + (i >> 5)] = w;
+        }
+    }
+}
+}  // namespace bff
+
+extern "C" int bff_labels_to_rows(const int64_t *labels, int64_t n, const int64_t *ids, int32_t n_ids, uint32_t *rows, void *stream_) {
+    BFF_REQUIRE(n >= 0 && n_ids >= 0, "bff_labels_to_rows: negative size");
+    if (n == 0 || n_ids == 0) return BFF_OK;
+    BFF_REQUIRE(labels && ids && rows, "bff_labels_to_rows: null pointer");
+    bff::labels_to_rows_kernel<<<(unsigned)ceil_div64(n, 256), 256, 0, (cudaStream_t)stream_>>>(
+        (const long long *)labels, n, (const long long *)ids, n_ids, ceil_div64(n, 32), rows);
+    BFF_LAUNCH_CHECK("labels_to_rows_kernel");
+    return BFF_OK;
+}

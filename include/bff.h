@@ -183,6 +183,12 @@ BFF_API int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32
 BFF_API int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
                    uint32_t *keep, void *stream);
 
+/* Evaluator side (evaluation/eval/scannetv2_inst_eval.py:348-359): per-point encoded ground-truth labels (n) int64
+ * -> rows (n_ids, ceil(n/32)) packed, bit p of row g = (labels[p] == ids[g]). ids is a DEVICE array. Together with
+ * bff_pack_bits on the prediction masks and one bff_mask_iou call this yields every pred x gt intersection
+ * (`np.count_nonzero(np.logical_and(gts == inst_id, pred_mask))`) at once. */
+BFF_API int bff_labels_to_rows(const int64_t *labels, int64_t n, const int64_t *ids, int32_t n_ids, uint32_t *rows, void *stream);
+
 /* solve_overlapping's sequential pass (projection_2d_to_3d.py:295-299) on packed rows, in place.
  * prog (n_steps, 2) int32: step k clears from row prog[k][0] the bits of row prog[k][1]
  * (rows[dst] &= ~rows[src]) in list order; every word column runs the program independently. */
