@@ -45,7 +45,7 @@ class Stage2Desc(ctypes.Structure):
         ("iou_thres", c_float), ("min_aggregated", c_int32), ("filter_mode", c_int32), ("filter_fraction", c_double),
         ("agg_rows", c_void_p), ("cap_groups", c_int32), ("n_groups", c_void_p), ("group_first", c_void_p),
         ("group_size", c_void_p), ("group_conf", c_void_p), ("before", c_void_p), ("after", c_void_p),
-        ("members", c_void_p), ("filter_value", c_void_p),
+        ("members", c_void_p), ("filter_value", c_void_p), ("inter_pre", c_void_p), ("pop_pre", c_void_p),
     ]
 
 

@@ -154,7 +154,7 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
 
 # ----------------------------------------------------------------------------- fused C++ pipeline
 def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], mc: torch.Tensor,
-                           vc: Optional[torch.Tensor], n_points: int, cfg):
+                           vc: Optional[torch.Tensor], n_points: int, cfg, pairs=None):
     """aggregate_rows + keep_points + the overlap/AND/popcount half of filter_and_select in ONE call
     (bff_stage2_aggregate): the component search, threshold pick and overlap schedule run in C++ next to the
     kernel launches. Returns None when nothing aggregates, else
@@ -187,6 +187,12 @@ def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Seque
     d.agg_rows, d.cap_groups = _cabi.ptr(agg), cap
     d.n_groups, d.group_first, d.group_size, d.group_conf = _cabi.ptr(n_groups), _cabi.ptr(first), _cabi.ptr(size), _cabi.ptr(gconf)
     d.before, d.after, d.members, d.filter_value = _cabi.ptr(before), _cabi.ptr(after), _cabi.ptr(members), _cabi.ptr(fval)
+    if pairs is not None:       # (inter (n,n) int32, pop (n,) int32) CUDA: the all-pairs step was done elsewhere (dist.sharded_pairs)
+        inter_pre, pop_pre = pairs
+        if tuple(inter_pre.shape) != (n, n) or tuple(pop_pre.shape) != (n,) or inter_pre.dtype != torch.int32 or pop_pre.dtype != torch.int32:
+            raise ValueError("pairs must be ((n,n) int32, (n,) int32)")
+        inter_pre, pop_pre = inter_pre.contiguous(), pop_pre.contiguous()
+        d.inter_pre, d.pop_pre = _cabi.ptr(inter_pre), _cabi.ptr(pop_pre)
     _cabi.check(_cabi.lib().bff_stage2_aggregate(_cabi.ctx(rows.device.index or 0), d, _cabi.current_stream()), "bff_stage2_aggregate")
     g = int(n_groups[0])
     _cabi.launch_count += 5 + (12 if g else 0)      # kernels inside the call (popcount x2, intersect, adjacency, ...)

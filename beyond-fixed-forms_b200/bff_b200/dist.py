@@ -101,3 +101,43 @@ def lift_sharded(ctx: DistCtx, xyz: np.ndarray, intrinsics: np.ndarray, scene_2d
         rows_per_rank.append(sum(len(queries[qi].rles[fi]) for s in range(a, b) for (qi, fi) in per_frame[s]))
     rows, mc, vc = exchange(ctx, out.rows, rows_per_rank, out.masked_counts, out.viewed_counts if want_viewed else None)
     return lift_mod.LiftedScene(xyz.shape[0], lift_mod.split_rows(rows, per_frame, queries), mc, vc, f)
+
+
+PAIRS_MIN_ROWS = 512        # below this the one-GPU call is cheaper than two more collectives
+
+
+def sharded_pairs(ctx: DistCtx, rows: torch.Tensor, iou_fn: Optional[Callable] = None):
+    """All-pairs intersections of the gathered rows with the quadratic work split over the ranks: rank r computes one
+    trapezoid of the upper triangle (bff_mask_iou), the int32 blocks are all-gathered in rank order. Integer results,
+    so the assembled (n,n) matrix is bit-identical to the one-GPU call. Returns (inter (n,n) int32, pop (n,) int32)
+    for aggregate_filter_fused(pairs=...). `iou_fn(block, rows) -> (inter, pop_block)` defaults to the CUDA kernel; the
+    gloo CPU tests inject the oracle. (calculate_iou, projection_2d_to_3d.py:149-166, is O(Ins^2 N): at c4 it is
+    the step that would otherwise be repeated on every rank.)"""
+    import torch.distributed as dist
+    from . import ops
+    n = rows.shape[0]
+    world = ctx.world_size
+    # The matrix is symmetric: rank r computes rows [lo_r, hi_r) against columns [lo_r, n) only, and the boundaries
+    # balance the AREA of those trapezoids (lo_r = n (1 - sqrt(1 - r/world))), so every rank does 1/world of the
+    # upper triangle; the lower triangle is mirrored after the gather.
+    bounds = [min(n, int(round(n * (1.0 - (1.0 - r / world) ** 0.5)))) for r in range(world)] + [n]
+    lo, hi = bounds[ctx.rank], bounds[ctx.rank + 1]
+    base = max(bounds[r + 1] - bounds[r] for r in range(world))         # all_gather needs one shape: pad to the tallest block
+    block = torch.zeros((base, n), dtype=torch.int32, device=rows.device)
+    pop_b = torch.zeros((base,), dtype=torch.int32, device=rows.device)
+    if hi > lo:
+        if iou_fn is None:
+            inter, pa, _, _ = ops.mask_iou(rows[lo:hi], rows[lo:], want_iou=False)
+        else:
+            inter, pa = iou_fn(rows[lo:hi], rows[lo:])
+        block[: hi - lo, lo:] = inter
+        pop_b[: hi - lo] = pa
+    inter_all = torch.empty((world * base, n), dtype=torch.int32, device=rows.device)
+    pop_all = torch.empty((world * base,), dtype=torch.int32, device=rows.device)
+    dist.all_gather_into_tensor(inter_all, block)
+    dist.all_gather_into_tensor(pop_all, pop_b)
+    keep = torch.cat([torch.arange(r * base, r * base + bounds[r + 1] - bounds[r], device=rows.device) for r in range(world)])
+    upper = inter_all[keep]                                              # (n, n): entry (i, j) valid for j >= lo(block of i)
+    row_lo = torch.cat([torch.full((bounds[r + 1] - bounds[r],), bounds[r], dtype=torch.long, device=rows.device) for r in range(world)])
+    valid = torch.arange(n, device=rows.device)[None, :] >= row_lo[:, None]
+    return torch.where(valid, upper, upper.T).contiguous(), pop_all[keep].contiguous()

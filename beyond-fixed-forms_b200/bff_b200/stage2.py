@@ -25,7 +25,7 @@ def needs_viewed_counts(cfg) -> bool:
 
 
 def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor, vc: Optional[torch.Tensor],
-                         n_points: int, cfg, keep_rows: bool = False, to_host: bool = True):
+                         n_points: int, cfg, keep_rows: bool = False, to_host: bool = True, pairs=None):
     """Everything after the frame loop (projection_2d_to_3d.py:463-634) for one query.
     Returns (dict to save, reached_filter) -- the reference only writes its scene checkpoint when
     the filter stage is reached (:580-581)."""
@@ -37,7 +37,7 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
         return scene_io.empty_stage2(), False
     conf = conf_list if isinstance(conf_list, torch.Tensor) else torch.tensor(conf_list)    # :484-486
     if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
-        fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c)
+        fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c, pairs=pairs)
         if fused is None:
             log("No 3d masks detected after aggregation")
             return scene_io.empty_stage2(), False
@@ -83,8 +83,11 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
         frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
         lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, [q], height, width,
                                want_viewed and bool(conf_list))
+    pairs = None
+    if dist_ctx is not None and dist_ctx.world_size > 1 and lifted.rows[0].shape[0] >= dist_mod.PAIRS_MIN_ROWS:
+        pairs = dist_mod.sharded_pairs(dist_ctx, lifted.rows[0])      # the quadratic IoU step, one row block per rank
     return aggregate_and_filter(lifted.rows[0], conf_list, labels, lifted.masked_counts[0], lifted.viewed_counts,
-                                xyz.shape[0], cfg)
+                                xyz.shape[0], cfg, pairs=pairs)
 
 
 def process_scene_queries(cfg, classes, scene_id: str, device):

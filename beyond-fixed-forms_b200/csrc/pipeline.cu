@@ -104,8 +104,14 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     const size_t nn = (size_t)n * n;
 
     // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
-    PIPE_TAKE(d_inter, c->dev, int32_t, nn);
-    PIPE_TAKE(d_pop, c->dev, int32_t, n);
+    BFF_REQUIRE((d->inter_pre == nullptr) == (d->pop_pre == nullptr), "bff_stage2_aggregate: inter_pre and pop_pre come together");
+    const bool have_pairs = d->inter_pre != nullptr;
+    int32_t *d_inter = const_cast<int32_t *>(d->inter_pre), *d_pop = const_cast<int32_t *>(d->pop_pre);
+    if (!have_pairs) {
+        d_inter = c->dev.get<int32_t>(nn);
+        d_pop = c->dev.get<int32_t>(n);
+        if (!d_inter || !d_pop) return BFF_ENOMEM;
+    }
     const int stride = (n + 7) & ~7;
     const size_t adj_bytes = (size_t)n * stride;
     PIPE_TAKE(d_adj, c->dev, uint8_t, adj_bytes);
@@ -113,8 +119,10 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     int32_t *d_label = nullptr;
     int rc = upload_i32(c, std::vector<int32_t>(d->label_id, d->label_id + n), &d_label, s);
     if (rc != BFF_OK) return rc;
-    rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
-    if (rc != BFF_OK) return rc;
+    if (!have_pairs) {
+        rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
+        if (rc != BFF_OK) return rc;
+    }
     merge_adjacency_kernel<<<(unsigned)ceil_div64((int64_t)adj_bytes, 256), 256, 0, s>>>(d_inter, d_pop, d_label, n, stride, d->iou_thres, d_adj);
     BFF_LAUNCH_CHECK("merge_adjacency_kernel");
     BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));

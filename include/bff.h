@@ -258,6 +258,11 @@ typedef struct bff_stage2_desc {
     int32_t *after;             /* host (cap_groups): row sums after overlap resolution and `&= masked_points` (:596) */
     int32_t *members;           /* host (n_rows), optional: members of the kept groups, concatenated (for the log line) */
     float *filter_value;        /* host, optional: the threshold that was picked (:576) */
+    /* optional, both or neither: the all-pairs intersections (n_rows, n_rows) and row popcounts (n_rows) of `rows`,
+     * already on the device -- the frame-sharded multi-GPU path computes one row block per rank and all-gathers them
+     * (bff_b200/dist.py), so the quadratic step is not repeated on every rank. NULL: computed here. */
+    const int32_t *inter_pre;
+    const int32_t *pop_pre;
 } bff_stage2_desc;
 BFF_API int bff_stage2_aggregate(bff_ctx *ctx, const bff_stage2_desc *desc, void *stream);
 

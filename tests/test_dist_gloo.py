@@ -10,7 +10,8 @@ import pytest
 import torch
 import torch.multiprocessing as mp
 
-from helpers import pack_rows, random_scene
+import oracle as O
+from helpers import pack_rows, random_scene, unpack_rows
 
 
 def _free_port():
@@ -69,7 +70,17 @@ def _worker(rank, world, port, out_dir):
     frame_ids, viewed, per_frame = lift_mod.plan_frames([q], view_ids)
     lifted = dist_mod.lift_sharded(ctx, sc["xyz"], sc["K"], "", "", frame_ids, viewed, per_frame, [q], sc["h"], sc["w"], True,
                                    torch.device("cpu"), lift_fn=_oracle_lift_fn(sc), load_fn=_load_fn(sc))
-    torch.save({"rows": lifted.rows[0], "mc": lifted.masked_counts, "vc": lifted.viewed_counts}, os.path.join(out_dir, f"r{rank}.pth"))
+    # the all-pairs IoU with one row block per rank (dist.sharded_pairs), oracle injected for the kernel
+    import oracle as O
+    from helpers import unpack_rows
+
+    def iou_fn(block, rows):
+        a, b = unpack_rows(block.numpy(), sc["n"]), unpack_rows(rows.numpy(), sc["n"])
+        inter, _ = O.mask_iou(a, b)
+        return torch.from_numpy(inter), torch.from_numpy(a.sum(1).astype(np.int32))
+    inter, pop = dist_mod.sharded_pairs(ctx, lifted.rows[0], iou_fn=iou_fn)
+    torch.save({"rows": lifted.rows[0], "mc": lifted.masked_counts, "vc": lifted.viewed_counts, "inter": inter, "pop": pop},
+               os.path.join(out_dir, f"r{rank}.pth"))
     ctx.finalize()
 
 
@@ -88,6 +99,9 @@ def test_sharded_lift_equals_single(tmp_path, world):
         got = torch.load(os.path.join(str(tmp_path), f"r{r}.pth"))
         assert torch.equal(got["rows"], single.rows)
         assert torch.equal(got["mc"], single.masked_counts) and torch.equal(got["vc"], single.viewed_counts)
+        dense = unpack_rows(single.rows.numpy(), sc["n"])
+        inter_o, _ = O.mask_iou(dense, dense)
+        assert np.array_equal(got["inter"].numpy(), inter_o) and np.array_equal(got["pop"].numpy(), dense.sum(1))
 
 
 def test_shard_bounds_cover_everything():

@@ -90,3 +90,22 @@ def test_concurrent_queries_equal_sequential_loop_and_port(cuda_dev, monkeypatch
         if isinstance(serial[qi]["ins"], torch.Tensor):
             assert torch.equal(serial[qi]["ins"].cpu(), port[qi]["ins"])
             np.testing.assert_allclose(torch.as_tensor(serial[qi]["conf"]).cpu().numpy(), port[qi]["conf"].numpy(), rtol=1e-5)
+
+
+def test_precomputed_pairs_give_the_same_aggregation(cuda_dev):
+    """bff_stage2_aggregate with inter_pre / pop_pre (what dist.sharded_pairs assembles from the ranks' row blocks)."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from bff_b200 import ops, stage2
+    inp = bench.build_inputs("tiny", 0, 1, cuda_dev)
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+    a, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, inp["cfg"])
+    top, bottom = out.rows[:11], out.rows[11:]                                # two "rank" blocks of the all-pairs matrix
+    i0, p0, _, _ = ops.mask_iou(top, out.rows, want_iou=False)
+    i1, p1, _, _ = ops.mask_iou(bottom, out.rows, want_iou=False)
+    pairs = (torch.cat([i0, i1]), torch.cat([p0, p1]))
+    b, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, inp["cfg"], pairs=pairs)
+    assert a["ins"].shape[0] >= 2
+    _same(a, b, "precomputed pairs")
