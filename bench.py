@@ -423,8 +423,9 @@ def run_gpu(args):
     copy_stream = torch.cuda.Stream(device=dev)
     bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]   # double buffer, no allocation in the loop
     done = [None, None]
-    # which engine moves the big buffers faster is a property of the box (measured 42 vs 47 GB/s on one, 55 vs 51 on
-    # another): time both once on the largest input (untimed warm-up) and use the winner
+    # The big buffers go through the SM copy kernel even where the copy engine alone is a little faster (probe below:
+    # 42 vs 47 GB/s on one box, 55 vs 51 on another): the running step's own small H2D/D2H staging copies would otherwise
+    # queue behind a 184 MB transfer on the same engine (measured: 5.2 ms per scene with the copy engine, 4.5 with the kernel)
     big = max(g.host, key=lambda k_: g.host[k_].numel() * g.host[k_].element_size())
 
     def _time_copy(fn):
@@ -434,7 +435,7 @@ def run_gpu(args):
         return a.elapsed_time(b) / 2
     t_ce = _time_copy(lambda: bufs[0][big].copy_(g.host[big], non_blocking=True))
     t_sm = _time_copy(lambda: ops.upload(bufs[0][big], g.host[big])) if g.host[big].numel() * g.host[big].element_size() >= 16 else float("inf")
-    use_sm_copy = t_sm < t_ce
+    use_sm_copy = True
 
     def upload_async(slot):
         with torch.cuda.stream(copy_stream):

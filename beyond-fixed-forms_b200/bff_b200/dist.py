@@ -103,7 +103,7 @@ def lift_sharded(ctx: DistCtx, xyz: np.ndarray, intrinsics: np.ndarray, scene_2d
     return lift_mod.LiftedScene(xyz.shape[0], lift_mod.split_rows(rows, per_frame, queries), mc, vc, f)
 
 
-PAIRS_MIN_ROWS = 512        # below this the one-GPU call is cheaper than two more collectives
+PAIRS_MIN_ROWS = int(os.environ.get("BFF_PAIRS_MIN_ROWS", "512"))   # below this the one-GPU call is cheaper than two more collectives
 
 
 def sharded_pairs(ctx: DistCtx, rows: torch.Tensor, iou_fn: Optional[Callable] = None):

@@ -7,7 +7,7 @@ from typing import Optional
 
 import torch
 
-from . import _log, aggregate, lift as lift_mod, scene_io
+from . import _log, aggregate, lift as lift_mod, scene_io, schedule
 from ._log import log
 
 
@@ -177,6 +177,26 @@ def main(argv=None):
     ckpt = scene_io.read_checkpoint(ckpt_path)
     seg_dir = os.path.join(cfg["mask_2d_dir"], cls)
     scenes = sorted(s for s in os.listdir(seg_dir) if s.endswith("_00.pth"))  # :361-363
+    if dist_ctx is not None and dist_ctx.world_size > 1 and schedule.dist_mode(len(scenes), dist_ctx.world_size) == "scene":
+        # whole scenes per rank (longest first onto the least loaded rank), no data-path collective; rank 0 merges the
+        # checkpoint entries at the end
+        import torch.distributed as tdist
+        mine = schedule.lpt_assign([schedule.scene_cost(cfg, s[:-4]) for s in scenes], dist_ctx.world_size)[dist_ctx.rank]
+        reached = []
+        for i in mine:
+            scene_id = scenes[i][:-4]
+            result, reached_filter = process_scene(cfg, cls, scene_id, device, None)
+            scene_io.save_result(result, cfg["mask_3d_dir"], cls, scene_id)
+            if reached_filter:
+                reached.append(scene_id)
+        everyone = [None] * dist_ctx.world_size
+        tdist.all_gather_object(everyone, reached)
+        if dist_ctx.rank == 0:
+            for scene_id in sorted(x for part in everyone for x in part):
+                ckpt[scene_id] = True
+            scene_io.write_checkpoint(ckpt_path, ckpt)
+        dist_ctx.finalize()
+        return 0
     for s in scenes:
         scene_id = s[:-4]
         result, reached_filter = process_scene(cfg, cls, scene_id, device, dist_ctx)

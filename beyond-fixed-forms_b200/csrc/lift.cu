@@ -94,6 +94,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 // magnitude above fp64 rounding; NaN/inf make every comparison false, i.e. "do not cull".
 constexpr double kCullEps = 1e-9;
 
+// |n| rounded UP (float32 square root with directed rounding; an upper bound is all the test needs), times (1 + eps)
+__device__ __forceinline__ double norm_upper(double n0, double n1, double n2) {
+    const float s = __double2float_ru(n0 * n0 + n1 * n1 + n2 * n2);
+    return (double)__fsqrt_ru(s) * (1.0 + 2.0 * kCullEps) * (1.0 + 1e-6);
+}
+
 __device__ __forceinline__ void store_plane(double *dst, int fc, int k, double ax, double ay, double az, const double *P) {
     // camera-space functional a.p_cam  ->  world-space n.p + d with p_cam = R p + t (rows 0..2 of inv(pose))
     const double n0 = ax * P[0] + ay * P[4] + az * P[8];
@@ -104,22 +110,27 @@ __device__ __forceinline__ void store_plane(double *dst, int fc, int k, double a
     dst[(k + 1) * fc] = n1;
     dst[(k + 2) * fc] = n2;
     dst[(k + 3) * fc] = d + kCullEps * fabs(d);
-    dst[(k + 4) * fc] = sqrt(n0 * n0 + n1 * n1 + n2 * n2) * (1.0 + kCullEps);
+    dst[(k + 4) * fc] = norm_upper(n0, n1, n2);
 }
 
-__device__ __forceinline__ void build_frame_planes(const double *P, const LiftParams &p, double *dst, int fc) {
-    const double nz = sqrt(P[8] * P[8] + P[9] * P[9] + P[10] * P[10]) * (1.0 + kCullEps);
-    dst[0 * fc] = P[8];
-    dst[1 * fc] = P[9];
-    dst[2 * fc] = P[10];
-    dst[3 * fc] = P[11];
-    dst[4 * fc] = nz;
-    dst[5 * fc] = kCullEps * fabs(P[11]);
+// One of the five culling functionals of a frame (which = 0: camera z, 1..4: the image-border planes); the chunk's
+// frames x 5 items are spread over all threads of the CTA so that no warp waits long for the tables.
+__device__ __forceinline__ void build_frame_plane(const double *P, const LiftParams &p, double *dst, int fc, int which) {
     const double W = (double)p.width, H = (double)p.height;
-    store_plane(dst, fc, 6, p.k[0], p.k[1], p.k[2] + 1.0, P);          // q0 + z >= 0      (u >= -1)
-    store_plane(dst, fc, 11, -p.k[0], -p.k[1], W - p.k[2], P);         // W z - q0 >= 0    (u <= W)
-    store_plane(dst, fc, 16, p.k[3], p.k[4], p.k[5] + 1.0, P);         // q1 + z >= 0      (v >= -1)
-    store_plane(dst, fc, 21, -p.k[3], -p.k[4], H - p.k[5], P);         // H z - q1 >= 0    (v <= H)
+    switch (which) {
+    case 0:
+        dst[0 * fc] = P[8];
+        dst[1 * fc] = P[9];
+        dst[2 * fc] = P[10];
+        dst[3 * fc] = P[11];
+        dst[4 * fc] = norm_upper(P[8], P[9], P[10]);
+        dst[5 * fc] = kCullEps * fabs(P[11]);
+        break;
+    case 1: store_plane(dst, fc, 6, p.k[0], p.k[1], p.k[2] + 1.0, P); break;          // q0 + z >= 0      (u >= -1)
+    case 2: store_plane(dst, fc, 11, -p.k[0], -p.k[1], W - p.k[2], P); break;         // W z - q0 >= 0    (u <= W)
+    case 3: store_plane(dst, fc, 16, p.k[3], p.k[4], p.k[5] + 1.0, P); break;         // q1 + z >= 0      (v >= -1)
+    default: store_plane(dst, fc, 21, -p.k[3], -p.k[4], H - p.k[5], P); break;        // H z - q1 >= 0    (v <= H)
+    }
 }
 
 __device__ __forceinline__ double warp_min(double v) {
@@ -380,7 +391,12 @@ lift_kernel(const __grid_constant__ LiftParams p) {
 
     // ---- per-frame culling planes (one thread per frame of the chunk), see warp_may_see()
     const int fc = p.frames_per_chunk;
-    if (!DEBUG && tid < nf) build_frame_planes(s_pose + tid * 16, p, s_plane + tid, fc);
+    if (!DEBUG) {
+        for (int item = tid; item < nf * 5; item += kLiftThreads) {
+            const int fr = item % nf;
+            build_frame_plane(s_pose + fr * 16, p, s_plane + fr, fc, item / nf);
+        }
+    }
     // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible)
     double cx, cy, cz, cr;
     const bool warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr)

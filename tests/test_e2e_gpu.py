@@ -76,3 +76,30 @@ def test_cli_with_depth_upsampling_matches_reference(cuda_dev, tmp_path, monkeyp
         gotf = torch.load(os.path.join(tree, "output/final_output", cls, f"{sid}.pth"), weights_only=False)
         check_against_expected(got2, expected[("config.yaml", cls, "mask_3d", sid)], f"stage2 {sid}")
         check_against_expected(gotf, expected[("config.yaml", cls, "final", sid)], f"final {sid}")
+
+
+@pytest.mark.parametrize("mode", ["scene", "frame"])
+def test_two_rank_cli_matches_reference(cuda_dev, tmp_path, mode):
+    """torchrun, 2 ranks over NCCL, the drop-in lifting CLI on the golden tree: whole scenes per rank (LPT, config 5) and
+    frames sharded per scene (vote all-reduce, row all-gather, all-pairs IoU split over the ranks) must both write the
+    reference's files."""
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    from conftest import ROOT
+    tree = copy_tree(tmp_path)
+    expected = load_expected()
+    cls = "office chair"
+    env = dict(os.environ, BFF_DIST_MODE=mode, BFF_PAIRS_MIN_ROWS="2", PYTHONPATH=os.path.join(ROOT, "beyond-fixed-forms_b200"))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29571" if mode == "scene" else "29572", os.path.join(ROOT, "tools", "projection_2d_to_3d.py"),
+           "--config", "config.yaml", "--cls", cls]
+    r = subprocess.run(cmd, cwd=tree, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    for sid in ("scene0001_00", "scene0002_00", "scene0003_00"):
+        got2 = torch.load(os.path.join(tree, "output/mask_3d", cls, f"{sid}.pth"), weights_only=False)
+        check_against_expected(got2, expected[("config.yaml", cls, "mask_3d", sid)], f"{mode} stage2 {sid}")
+    import yaml
+    ck = yaml.safe_load(open(os.path.join(tree, "checkpoints", f"projection_2d_to_3d_checkpoint_{cls}.yaml")))
+    assert ck and all(v is True for v in ck.values())

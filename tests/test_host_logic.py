@@ -82,3 +82,29 @@ def test_resize_table_reproduces_cv2_resize():
         h = fma(src[:, x1] - src[:, x0], np.broadcast_to(wx, (48, wd)), src[:, x0])
         got = fma(h[y1] - h[y0], np.broadcast_to(wy[:, None], (hd, wd)), h[y0])
         np.testing.assert_array_equal(got, O.resize_bilinear(src, hd, wd))
+
+
+def test_lpt_scene_assignment_and_costs():
+    """Scene-parallel scheduling (BASELINE config 5): every scene exactly once, loads balanced like LPT guarantees
+    (max load <= mean + largest item), deterministic, sorted per rank; costs read from the golden tree."""
+    import os
+    import numpy as np
+    import yaml
+    from conftest import GOLDEN
+    from bff_b200 import schedule
+    rng = np.random.default_rng(0)
+    costs = (rng.uniform(4e4, 4.2e5, 312) * rng.integers(58, 544, 312)).tolist()       # SURVEY F8 ranges
+    for world in (1, 2, 8):
+        parts = schedule.lpt_assign(costs, world)
+        assert sorted(i for p in parts for i in p) == list(range(312)) and all(p == sorted(p) for p in parts)
+        loads = [sum(costs[i] for i in p) for p in parts]
+        assert max(loads) <= sum(costs) / world + max(costs)
+        assert parts == schedule.lpt_assign(costs, world)
+        if world == 8:
+            assert max(loads) / (sum(costs) / world) < 1.02                              # 312 scenes balance to within 2 %
+    assert schedule.lpt_assign([], 4) == [[], [], [], []]
+    tree = os.path.join(GOLDEN, "tree")
+    cfg = yaml.safe_load(open(os.path.join(tree, "config.yaml")))
+    cfg = {k: (os.path.join(tree, v[2:]) if isinstance(v, str) and v.startswith("./") else v) for k, v in cfg.items()}
+    assert schedule.scene_cost(cfg, "scene0001_00") == 3000 * 8 and schedule.scene_cost(cfg, "scene0002_00") == 2500 * 6
+    assert schedule.dist_mode(3, 8) == "frame" and schedule.dist_mode(312, 8) == "scene"
