@@ -341,6 +341,7 @@ def run_gpu(args):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     import torch.distributed as dist
+    numa_cpus = dist_mod.bind_to_gpu_numa(local) if world > 1 else None     # staging buffers on the GPU's own socket
     # N > 1: scenes are the independent units of the path (the reference's outermost loop, :365), so the headline
     # run gives every rank its OWN c2-shaped scene and needs no data-path collective (weak scaling); the
     # frame-sharded variant of ONE scene (NCCL all-reduce + all-gather) is measured afterwards as `frame_sharded`.
@@ -515,6 +516,7 @@ def run_gpu(args):
                        "host; scene i+1's upload overlaps scene i's compute (copy stream); wall clock over the K steps",
                 "serial_ms_per_step": ms_e2e, "serial_value": pv / (ms_e2e * 1e-3),
                 "upload_engine": "SM copy kernel (bff_upload)" if use_sm_copy else "copy engine (cudaMemcpyAsync)",
+                "numa_bound_cpus_rank0": (len(numa_cpus) if numa_cpus else None),
                 "upload_gbs_probe": {"copy_engine": round(g.host[big].numel() * g.host[big].element_size() / t_ce / 1e6, 1),
                                      "sm_kernel": round(g.host[big].numel() * g.host[big].element_size() / t_sm / 1e6, 1)}},
         "gpu_launches": int(launches),

@@ -51,6 +51,32 @@ def init_from_env(backend: Optional[str] = None) -> Optional[DistCtx]:
     return DistCtx(rank, world, local, owns)
 
 
+def bind_to_gpu_numa(device_index: int) -> Optional[list]:
+    """Pin this process (and thereby the first-touch placement of the pinned host buffers it allocates next) to the CPU
+    cores NVML reports as local to GPU `device_index`. With one rank per GPU on a multi-socket host, staging buffers on
+    the far socket make every upload cross the inter-socket link, which caps the aggregate host->device bandwidth of an
+    8-GPU box well below 8 x PCIe. Returns the CPU list, or None when NVML / affinity control is unavailable
+    (BFF_NO_NUMA_BIND=1 disables it)."""
+    if os.environ.get("BFF_NO_NUMA_BIND") == "1" or not hasattr(os, "sched_setaffinity"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(visible.split(",")[device_index]) if visible and all(v.strip().isdigit() for v in visible.split(",")) else device_index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = [w * 64 + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
 def shard_bounds(n_items: int, world_size: int, rank: int):
     """Contiguous block [lo, hi) of rank `rank`: the first (n mod world) ranks get one extra item."""
     base, extra = divmod(n_items, world_size)

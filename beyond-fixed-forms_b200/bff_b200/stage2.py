@@ -172,6 +172,8 @@ def main(argv=None):
     dist_ctx = dist_mod.init_from_env()
     device = torch.device("cuda", dist_ctx.local_rank if dist_ctx else 0)
     torch.cuda.set_device(device)
+    if dist_ctx is not None:
+        dist_mod.bind_to_gpu_numa(dist_ctx.local_rank)
     cls = args.cls
     ckpt_path = f"checkpoints/projection_2d_to_3d_checkpoint_{cls}.yaml"     # :320-322
     ckpt = scene_io.read_checkpoint(ckpt_path)

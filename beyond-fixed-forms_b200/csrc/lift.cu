@@ -29,7 +29,7 @@ namespace bff {
 
 constexpr int kLiftThreads = 256;
 #ifndef BFF_LIFT_MIN_BLOCKS
-#define BFF_LIFT_MIN_BLOCKS 6      // resident CTAs per SM the register allocation is tuned for (measured best of 4..8)
+#define BFF_LIFT_MIN_BLOCKS 7      // resident CTAs per SM the register allocation is tuned for (measured: 5: 0.259, 6: 0.251, 7: 0.243-0.247 ms at c2)
 #endif
 #ifndef BFF_LIFT_PIPE
 #define BFF_LIFT_PIPE 1            // surviving frames processed per loop iteration (1 or 2; 2 measured slower)
