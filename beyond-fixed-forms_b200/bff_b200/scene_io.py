@@ -74,6 +74,7 @@ class FrameSet:
         self.native_size = native_size
 
 
+INGEST_THREADS = int(os.environ.get("BFF_INGEST_THREADS", str(min(32, os.cpu_count() or 1))))   # frame files read in parallel
 IN_KERNEL_RESIZE = True      # False: always resize on the host with cv2.resize like the reference (:436)
 _resize_checked = {}
 
@@ -100,10 +101,22 @@ def load_frames(scene_2d_dir: str, scene_id: str, frame_ids: Sequence[str], view
                 width: int, height: int, device=None) -> FrameSet:
     f = len(frame_ids)
     pose_inv = np.empty((f, 4, 4), np.float64)
+
+    def load_one(fid):
+        return load_pose_inverse(scene_2d_dir, scene_id, fid), load_depth_raw(scene_2d_dir, scene_id, fid)
+    # PNG decoding (cv2 releases the GIL) dominates the wall time of a scene once the kernels take milliseconds:
+    # decode the frames on a thread pool; results keep the order of frame_ids
+    workers = min(INGEST_THREADS, f)
+    if workers > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=workers) as ex:
+            loaded = list(ex.map(load_one, frame_ids))
+    else:
+        loaded = [load_one(fid) for fid in frame_ids]
     raws = []
-    for i, fid in enumerate(frame_ids):
-        pose_inv[i] = load_pose_inverse(scene_2d_dir, scene_id, fid)
-        raws.append(load_depth_raw(scene_2d_dir, scene_id, fid))
+    for i, (pinv, raw) in enumerate(loaded):
+        pose_inv[i] = pinv
+        raws.append(raw)
     same = all(r.dtype == np.uint16 and r.shape == (height, width) for r in raws)
     if same:
         depth = np.stack(raws) if raws else np.zeros((0, height, width), np.uint16)

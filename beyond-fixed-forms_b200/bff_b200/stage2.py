@@ -59,13 +59,13 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
     return result, True
 
 
-def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
-    """One iteration of the scene loop (projection_2d_to_3d.py:365-634).
-    Returns (dict to save, reached_filter)."""
-    from . import dist as dist_mod
+def load_scene(cfg, cls: str, scene_id: str, device, with_frames: bool = True) -> dict:
+    """Everything process_scene reads from disk for one (class, scene): intrinsics, cloud, 2D-mask records, the frame
+    plan and (single-GPU path) the frames themselves. Pure host work apart from the cached cv2.resize gate, so the
+    scene loop runs it for scene i+1 on a background thread while scene i is on the GPU."""
+    torch.cuda.set_device(device)
     width, height = int(cfg_get(cfg, "width_2d")), int(cfg_get(cfg, "height_2d"))
     scene_2d_dir = cfg_get(cfg, "scene_2d_dir")
-    log("Working on", scene_id, "class", cls)
     intr = scene_io.load_intrinsics(scene_2d_dir, scene_id)
     xyz = scene_io.load_cloud(cfg_get(cfg, "scene_npy_dir"), scene_id)
     records = scene_io.torch_load(os.path.join(cfg_get(cfg, "mask_2d_dir"), cls, f"{scene_id}.pth"))
@@ -76,18 +76,47 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None):
     # result is unused in those cases, so computing it in the same launch changes nothing on disk
     view_ids = scene_io.list_view_frames(scene_2d_dir, scene_id, int(cfg_get(cfg, "downsample_ratio"))) if (want_viewed and conf_list) else None
     frame_ids, viewed, per_frame = lift_mod.plan_frames([q], view_ids)
-    if dist_ctx is not None and dist_ctx.world_size > 1:
-        lifted = dist_mod.lift_sharded(dist_ctx, xyz, intr, scene_2d_dir, scene_id, frame_ids, viewed, per_frame, [q],
-                                       height, width, want_viewed and bool(conf_list), device)
+    frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device) if with_frames else None
+    return dict(intr=intr, xyz=xyz, q=q, conf_list=conf_list, labels=labels, want_viewed=want_viewed, frame_ids=frame_ids,
+                viewed=viewed, per_frame=per_frame, frames=frames, width=width, height=height)
+
+
+def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None, loaded: Optional[dict] = None):
+    """One iteration of the scene loop (projection_2d_to_3d.py:365-634).
+    Returns (dict to save, reached_filter). `loaded`: the result of load_scene when it was prefetched."""
+    from . import dist as dist_mod
+    log("Working on", scene_id, "class", cls)
+    sharded = dist_ctx is not None and dist_ctx.world_size > 1
+    L = loaded if loaded is not None else load_scene(cfg, cls, scene_id, device, with_frames=not sharded)
+    xyz, q, conf_list, labels, want_viewed = L["xyz"], L["q"], L["conf_list"], L["labels"], L["want_viewed"]
+    if sharded:
+        lifted = dist_mod.lift_sharded(dist_ctx, xyz, L["intr"], cfg_get(cfg, "scene_2d_dir"), scene_id, L["frame_ids"], L["viewed"],
+                                       L["per_frame"], [q], L["height"], L["width"], want_viewed and bool(conf_list), device)
     else:
-        frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
-        lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, [q], height, width,
-                               want_viewed and bool(conf_list))
+        lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), L["intr"], L["frames"], L["per_frame"], [q], L["height"],
+                               L["width"], want_viewed and bool(conf_list))
     pairs = None
-    if dist_ctx is not None and dist_ctx.world_size > 1 and lifted.rows[0].shape[0] >= dist_mod.PAIRS_MIN_ROWS:
+    if sharded and lifted.rows[0].shape[0] >= dist_mod.PAIRS_MIN_ROWS:
         pairs = dist_mod.sharded_pairs(dist_ctx, lifted.rows[0])      # the quadratic IoU step, one row block per rank
     return aggregate_and_filter(lifted.rows[0], conf_list, labels, lifted.masked_counts[0], lifted.viewed_counts,
                                 xyz.shape[0], cfg, pairs=pairs)
+
+
+def scene_loop(cfg, cls: str, scene_ids, device):
+    """Single-GPU scene loop with the next scene's files loaded on a background thread (PNG decode, text parsing and
+    torch.load release the GIL most of the time). Yields (scene_id, result, reached_filter) in order."""
+    from concurrent.futures import ThreadPoolExecutor
+    scene_ids = list(scene_ids)
+    if not scene_ids:
+        return
+    with ThreadPoolExecutor(max_workers=1, thread_name_prefix="bff-ingest") as ex:
+        nxt = ex.submit(load_scene, cfg, cls, scene_ids[0], device)
+        for i, scene_id in enumerate(scene_ids):
+            loaded = nxt.result()
+            if i + 1 < len(scene_ids):
+                nxt = ex.submit(load_scene, cfg, cls, scene_ids[i + 1], device)
+            result, reached_filter = process_scene(cfg, cls, scene_id, device, None, loaded)
+            yield scene_id, result, reached_filter
 
 
 def process_scene_queries(cfg, classes, scene_id: str, device):
@@ -185,9 +214,7 @@ def main(argv=None):
         import torch.distributed as tdist
         mine = schedule.lpt_assign([schedule.scene_cost(cfg, s[:-4]) for s in scenes], dist_ctx.world_size)[dist_ctx.rank]
         reached = []
-        for i in mine:
-            scene_id = scenes[i][:-4]
-            result, reached_filter = process_scene(cfg, cls, scene_id, device, None)
+        for scene_id, result, reached_filter in scene_loop(cfg, cls, [scenes[i][:-4] for i in mine], device):
             scene_io.save_result(result, cfg["mask_3d_dir"], cls, scene_id)
             if reached_filter:
                 reached.append(scene_id)
@@ -198,6 +225,15 @@ def main(argv=None):
                 ckpt[scene_id] = True
             scene_io.write_checkpoint(ckpt_path, ckpt)
         dist_ctx.finalize()
+        return 0
+    if dist_ctx is None or dist_ctx.world_size == 1:
+        for scene_id, result, reached_filter in scene_loop(cfg, cls, [s[:-4] for s in scenes], device):
+            scene_io.save_result(result, cfg["mask_3d_dir"], cls, scene_id)
+            if reached_filter:
+                ckpt[scene_id] = True
+                scene_io.write_checkpoint(ckpt_path, ckpt)
+        if dist_ctx is not None:
+            dist_ctx.finalize()
         return 0
     for s in scenes:
         scene_id = s[:-4]
