@@ -641,6 +641,98 @@ def cpu_baseline(inp, n_frames):
                       "(numpy/OpenBLAS + torch CPU like the reference)"}
 
 
+# ----------------------------------------------------------------------------- files -> files (BASELINE configs[0])
+def _install_fake_clip():
+    """CLIP text similarity is an INPUT of refinement (refinement.py:93-117) and the model is not in this image: a
+    deterministic stand-in module named `clip` so that tools/refinement.py's own code path (ClipTextSimilarity) runs."""
+    import hashlib
+    import types
+
+    def vec(text):
+        g = torch.Generator().manual_seed(int.from_bytes(hashlib.sha1(text.encode()).digest()[:4], "little"))
+        return torch.randn(1, 32, generator=g) + 1.0
+
+    class Tok:
+        def __init__(self, texts):
+            self.texts = list(texts)
+
+        def to(self, *_a, **_k):
+            return self
+
+    class Model:
+        def encode_text(self, tok):
+            return torch.cat([vec(t) for t in tok.texts], dim=0)
+    m = types.ModuleType("clip")
+    m.load = lambda name, device=None: (Model(), None)
+    m.tokenize = lambda texts: Tok(texts)
+    sys.modules["clip"] = m
+
+    def sim(query, label):
+        a, b = vec(query), vec(label)
+        s_ = a @ b.T
+        return (s_ / (a.norm(dim=-1, keepdim=True) * b.norm(dim=-1, keepdim=True).T)).item()
+    return sim
+
+
+def run_cli_e2e(args):
+    """--cli-e2e: BASELINE configs[0] as a user runs it -- an on-disk tree in the reference's formats (npy cloud, pose /
+    intrinsic text, uint16 depth PNGs, RLE .pth masks), `tools/projection_2d_to_3d.py` then `tools/refinement.py` of this
+    repo in-process, files to files, wall clock; next to it the reference's path (oracle port: per-frame imread + numpy
+    projection + torch CPU aggregation/refinement) over the same tree on the host cores. Prints one JSON line."""
+    import shutil
+    import yaml
+    from bff_b200 import refine, scene_io, stage2, synth
+    dev = torch.device("cuda", 0)
+    w = WORKLOADS[args.workload]
+    root = tempfile.mkdtemp(prefix="bff_cli_")
+    n_scenes = 3
+    scenes = {}
+    for i in range(n_scenes):
+        spec = synth.SceneSpec(n_points=w["n_points"], n_frames=w["n_frames"], width=w["width"], height=w["height"],
+                               depth_width=w.get("depth_width", 0), depth_height=w.get("depth_height", 0), n_boxes=w["n_boxes"],
+                               n_stage1=w["n_stage1"], seed=3000 + i, n_queries=1, room=w.get("room", (6.0, 5.0, 2.8)))
+        scenes[f"scene{i + 1:04d}_00"] = synth.make_scene(spec)
+    cfg_path = synth.write_tree(root, scenes, [QUERY], device=dev)
+    cfg = yaml.safe_load(open(cfg_path))
+    sim = _install_fake_clip()
+    cwd = os.getcwd()
+    os.chdir(root)
+    try:
+        stage2.main(["--config", cfg_path, "--cls", QUERY])                    # warm-up pass (CUDA context, library load)
+        shutil.rmtree(os.path.join(root, "checkpoints")); os.makedirs(os.path.join(root, "checkpoints"))
+        t0 = time.perf_counter()
+        stage2.main(["--config", cfg_path, "--cls", QUERY])
+        t1 = time.perf_counter()
+        refine.main(["--config", cfg_path, "--cls", QUERY])
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        ours = {sid: scene_io.torch_load(os.path.join(cfg["final_output_dir"], QUERY, f"{sid}.pth")) for sid in scenes}
+        # ---- the reference's path over the same files (oracle port; the one CPU leg)
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from helpers import port_run_class
+        import helpers
+        helpers.fake_clip_sim = sim
+        torch.set_num_threads(os.cpu_count() or 1)
+        t3 = time.perf_counter()
+        _, finals = port_run_class(cfg, QUERY)
+        t4 = time.perf_counter()
+    finally:
+        os.chdir(cwd)
+        shutil.rmtree(root, ignore_errors=True)
+    same = all(isinstance(ours[s]["ins"], torch.Tensor) and isinstance(finals[s]["ins"], torch.Tensor)
+               and torch.equal(ours[s]["ins"].cpu(), finals[s]["ins"]) for s in scenes)
+    pv = n_scenes * w["n_points"] * w["n_frames"]
+    emit({"metric": "point-view projections/sec, files to files (both CLIs, disk in, disk out)", "value": pv / (t2 - t0),
+          "unit": "point-views/s", "n_gpus": 1, "higher_is_better": True, "data": "synthetic", "dtype": "f64",
+          "config": {"workload": f"{args.workload}: {n_scenes} scenes x {w['n_points']} points x {w['n_frames']} frames "
+                                 f"{w['width']}x{w['height']}, 1 query, on-disk tree in the reference's formats"},
+          "seconds": {"lifting_cli": t1 - t0, "refinement_cli": t2 - t1, "per_scene": (t2 - t0) / n_scenes},
+          "cpu_baseline": {"value": pv / (t4 - t3), "unit": "point-views/s", "cores": os.cpu_count(), "kind": "port",
+                           "sample": f"the same {n_scenes} scenes, whole path from the same files, {t4 - t3:.1f} s"},
+          "masks_identical_to_cpu_path": bool(same)})
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (oracle port) on the host cores, same metric and config."""
     rank = int(os.environ.get("RANK", "0"))
@@ -702,11 +794,14 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the secondary frame-sharded measurement")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
+    ap.add_argument("--cli-e2e", action="store_true", help="files-to-files run of both drop-in CLIs on an on-disk tree (configs[0]) and exit")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
-    if args.impl == "reference":
+    if args.cli_e2e:
+        run_cli_e2e(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
