@@ -348,3 +348,88 @@ def test_lift_ignores_nan_points_in_float32_cloud(cuda_dev):
     np.testing.assert_array_equal(unpack_rows(out.rows.cpu().numpy(), sc["n"]), rows_o)
     np.testing.assert_array_equal(out.masked_counts.cpu().numpy(), mc_o)
     np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)
+
+
+# ---- host-buffer entry points (what INTEGRATION.md binds: plain numpy in, numpy out, copies inside the call)
+def _lift_host(sc, depth_np, depth_kind, native=None, depth_range=(1.0, 0.0)):
+    import ctypes
+    from bff_b200 import _cabi
+    n, f = sc["n"], sc["f"]
+    x4 = np.zeros((n, 4), np.float32)
+    x4[:, :3] = sc["xyz"].astype(np.float32)
+    packed2d = np.ascontiguousarray(pack_rows(sc["masks"].reshape(sc["masks"].shape[0], -1)))
+    pinv, K, off = np.ascontiguousarray(sc["pinv"]), np.ascontiguousarray(sc["K"]), np.ascontiguousarray(sc["mask_off"])
+    rows = np.full((packed2d.shape[0], (n + 31) // 32), 0xdeadbeef, np.uint32)
+    mc, vc = np.full((1, n), -7, np.int32), np.full(n, -7, np.int32)
+    d = _cabi.LiftDesc()
+    d.xyz, d.xyz_kind, d.n_points = _cabi.ptr(x4), _cabi.BFF_XYZ_F32X4, n
+    d.pose_inv, d.intrinsics, d.n_frames = _cabi.ptr(pinv), _cabi.ptr(K), f
+    d.depth, d.depth_kind, d.depth_scale = _cabi.ptr(depth_np), depth_kind, 1000.0
+    d.height, d.width, d.depth_thresh = sc["h"], sc["w"], 0.08
+    d.depth_min, d.depth_max = depth_range
+    d.masks2d, d.mask_offset, d.n_masks, d.n_queries = _cabi.ptr(packed2d), _cabi.ptr(off), packed2d.shape[0], 1
+    d.rows, d.masked_counts, d.viewed_counts = _cabi.ptr(rows), _cabi.ptr(mc), _cabi.ptr(vc)
+    if native is not None:
+        d.src_height, d.src_width = native
+    up, down = ctypes.c_int64(), ctypes.c_int64()
+    _cabi.check(_cabi.lib().bff_lift_scene_host(_cabi.ctx(0), d, ctypes.byref(up), ctypes.byref(down)), "bff_lift_scene_host")
+    assert down.value == rows.nbytes + mc.nbytes + vc.nbytes and up.value > depth_np.nbytes
+    return rows, mc, vc
+
+
+def test_host_buffer_lift_all_depth_kinds(cuda_dev):
+    from bff_b200 import _cabi
+    sc = random_scene(41, n=5003, f=6)
+    rows_o, mc_o, vc_o = _oracle(sc)
+    raw = np.round(sc["depth"].astype(np.float64) * 1000).astype(np.uint16)
+    for depth_np, kind in ((np.ascontiguousarray(sc["depth"]), _cabi.BFF_DEPTH_F32), (raw, _cabi.BFF_DEPTH_U16)):
+        rows, mc, vc = _lift_host(sc, depth_np, kind)
+        np.testing.assert_array_equal(unpack_rows(rows, sc["n"]), rows_o)
+        np.testing.assert_array_equal(mc, mc_o)
+        np.testing.assert_array_equal(vc, vc_o)
+    # native-size depth, resize tables built inside the call (resize_x / resize_y NULL)
+    sb = _scene_from_native_depth(29, 4001, 5, 96, 128, 2, True)
+    rows_o, mc_o, vc_o = _oracle(sb)
+    rows, mc, vc = _lift_host(sb, np.ascontiguousarray(sb["native"]), _cabi.BFF_DEPTH_U16_BILINEAR, native=sb["native"].shape[1:],
+                              depth_range=(0.0, 65.535))
+    assert vc_o.sum() > 100
+    np.testing.assert_array_equal(unpack_rows(rows, sb["n"]), rows_o)
+    np.testing.assert_array_equal(mc, mc_o)
+    np.testing.assert_array_equal(vc, vc_o)
+
+
+def test_host_buffer_mask_iou(cuda_dev):
+    import ctypes
+    import oracle as O
+    from bff_b200 import _cabi
+    rng = np.random.default_rng(2)
+    n = 3333
+    a, b = rng.random((7, n)) < 0.3, rng.random((5, n)) < 0.2
+    a[3] = False
+    pa, pb = np.ascontiguousarray(pack_rows(a)), np.ascontiguousarray(pack_rows(b))
+    inter, iou = np.zeros((7, 5), np.int32), np.zeros((7, 5), np.float32)
+    popa, popb = np.zeros(7, np.int32), np.zeros(5, np.int32)
+    _cabi.check(_cabi.lib().bff_mask_iou_host(_cabi.ctx(0), _cabi.ptr(pa), 7, _cabi.ptr(pb), 5, pa.shape[1], _cabi.ptr(inter),
+                                              _cabi.ptr(popa), _cabi.ptr(popb), _cabi.ptr(iou), None, None), "bff_mask_iou_host")
+    inter_o, iou_o = O.mask_iou(a, b)
+    np.testing.assert_array_equal(inter, inter_o)
+    np.testing.assert_array_equal(popa, a.sum(1))
+    np.testing.assert_array_equal(iou.view(np.int32), iou_o.view(np.int32))          # incl. the empty row's 0/0... none here: b is never empty
+    np.testing.assert_allclose(iou, iou_o, rtol=1e-5, equal_nan=True)                 # north_star tolerance
+
+
+def test_lift_with_in_kernel_resize_edge_cases(cuda_dev):
+    """No masks / no frames / ragged N with the bilinear depth kind."""
+    from bff_b200 import ops
+    sb = _scene_from_native_depth(53, 1001, 3, 96, 128, 2, True)
+    hs, ws = sb["native"].shape[1:]
+    nat = torch.from_numpy(sb["native"].view(np.int16)).to(cuda_dev)
+    out = ops.lift_scene(_xyz_dev(sb, cuda_dev, True), torch.from_numpy(sb["pinv"]).to(cuda_dev), sb["K"], nat, 96, 128,
+                         depth_range=(0.0, 65.535), native_size=(hs, ws))
+    sb2 = dict(sb, masks=np.zeros((0, 96, 128), bool), mask_off=np.zeros(sb["f"] + 1, np.int32))
+    _, _, vc_o = _oracle(sb2)
+    assert out.rows.shape[0] == 0 and int(out.masked_counts.sum()) == 0
+    np.testing.assert_array_equal(out.viewed_counts.cpu().numpy(), vc_o)
+    z = ops.lift_scene(_xyz_dev(sb, cuda_dev, True), torch.zeros((0, 4, 4), dtype=torch.float64, device=cuda_dev), sb["K"], nat[:0], 96, 128,
+                       native_size=(hs, ws))
+    assert int(z.viewed_counts.sum()) == 0 and z.viewed_counts.shape[0] == sb["n"]
