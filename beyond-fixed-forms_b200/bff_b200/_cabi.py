@@ -74,6 +74,8 @@ SYMBOLS = {
     "bff_rows_or_reduce": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_counts_max": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "bff_vote_hist": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
+    "bff_vote_unique_table_size": (c_int64, [c_int32, c_int32]),
+    "bff_vote_unique": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
     "bff_point_keep": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
     "bff_labels_to_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_overlap_resolve": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p]),

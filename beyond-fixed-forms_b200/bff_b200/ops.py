@@ -234,6 +234,20 @@ def vote_hist(mc: torch.Tensor, vc: Optional[torch.Tensor], mc_bins: int, vc_bin
     return hist
 
 
+def vote_unique(hist: torch.Tensor, mode: int) -> torch.Tensor:
+    """Distinct values of the non-empty histogram bins, sorted: what masked_counts.unique() (mode 1) or
+    detected_ratio.unique() (mode 0, f32(mc) / (f32(vc) + 1)) returns in the reference (projection_2d_to_3d.py:512-517, :571-575)."""
+    hist = _cuda(hist, torch.int32, "hist")
+    mb, vb = hist.shape
+    tsize = int(lib().bff_vote_unique_table_size(mb, vb))
+    table = torch.empty((tsize,), dtype=torch.int32, device=hist.device)
+    vals = torch.empty((mb * vb,), dtype=torch.float32, device=hist.device)
+    cnt = torch.zeros((1,), dtype=torch.int32, device=hist.device)
+    check(lib().bff_vote_unique(ptr(hist), mb, vb, int(mode), ptr(table), tsize, ptr(vals), ptr(cnt), current_stream()), "bff_vote_unique")
+    _count(2)
+    return torch.sort(vals[: int(cnt.item())]).values
+
+
 def point_keep(mc: torch.Tensor, vc: Optional[torch.Tensor], mode: int, thr: float) -> torch.Tensor:
     mc = _cuda(mc, torch.int32, "mc").reshape(-1)
     if vc is not None:

@@ -8,7 +8,11 @@
 #include <math.h>
 #include <string.h>
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
+#include <chrono>
 #include <vector>
 
 #include "common.cuh"
@@ -17,16 +21,20 @@ namespace bff {
 
 // adjacency of the merge graph: same label AND iou > thr, IoU in float32 as calculate_iou computes it
 // (projection_2d_to_3d.py:120-122,158-165). NaN (0/0) compares false.
-// Rows of `adj` are padded to `stride` (a multiple of 8) bytes so the host can scan them 8 bytes at a time.
+// One BIT per pair: row r is `stride_words` 32-bit words (an even number, so the host walks 64-bit words), bit c of row r
+// = edge (r, c); a warp's ballot is one word.
 __global__ void merge_adjacency_kernel(const int32_t *__restrict__ inter, const int32_t *__restrict__ pop,
-                                       const int32_t *__restrict__ label, int n, int stride, float thr, uint8_t *__restrict__ adj) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (long long)n * stride) return;
-    const int r = (int)(i / stride), c = (int)(i % stride);
-    if (c >= n) { adj[i] = 0; return; }
-    const float fi = __int2float_rn(inter[(long long)r * n + c]);
-    const float un = __fsub_rn(__fadd_rn(__int2float_rn(pop[r]), __int2float_rn(pop[c])), fi);
-    adj[i] = (label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
+                                       const int32_t *__restrict__ label, int n, int stride_words, float thr, uint32_t *__restrict__ adj) {
+    const int r = blockIdx.y;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    bool e = false;
+    if (c < n) {
+        const float fi = __int2float_rn(inter[(long long)r * n + c]);
+        const float un = __fsub_rn(__fadd_rn(__int2float_rn(pop[r]), __int2float_rn(pop[c])), fi);
+        e = (label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
+    }
+    const unsigned w = __ballot_sync(0xffffffffu, e);
+    if ((threadIdx.x & 31) == 0 && (c >> 5) < stride_words) adj[(long long)r * stride_words + (c >> 5)] = w;
 }
 
 __global__ void rows_gather_kernel(const uint32_t *__restrict__ rows, long long words, const int32_t *__restrict__ idx,
@@ -36,16 +44,25 @@ __global__ void rows_gather_kernel(const uint32_t *__restrict__ rows, long long 
     out[(long long)blockIdx.y * words + w] = __ldg(rows + (long long)idx[blockIdx.y] * words + w);
 }
 
-struct UnionFind {
-    std::vector<int> parent;
-    explicit UnionFind(int n) : parent(n) { for (int i = 0; i < n; ++i) parent[i] = i; }
-    int find(int x) { while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; } return x; }
-    void unite(int a, int b) { a = find(a); b = find(b); if (a != b) { if (a < b) parent[b] = a; else parent[a] = b; } }  // root = smallest member
-};
-
 }  // namespace bff
 
 using namespace bff;
+
+// BFF_PIPE_TRACE=1: wall-clock marks inside the fused pipelines on stderr (dev aid; one getenv per call otherwise)
+struct PipeTrace {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    explicit PipeTrace(const char *what) : on(getenv("BFF_PIPE_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {
+        if (on) fprintf(stderr, "[bff trace] %s:", what);
+    }
+    void mark(const char *name) {
+        if (!on) return;
+        const auto t = std::chrono::steady_clock::now();
+        fprintf(stderr, " %s %.0fus", name, std::chrono::duration<double, std::micro>(t - t0).count());
+        t0 = t;
+    }
+    ~PipeTrace() { if (on) fprintf(stderr, "\n"); }
+};
 
 #define PIPE_TAKE(var, arena, type, count)                         \
     type *var = (arena).get<type>(count);                          \
@@ -102,6 +119,7 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     const int n = d->n_rows;
     const int64_t words = ceil_div64(d->n_points, 32);
     const size_t nn = (size_t)n * n;
+    PipeTrace tr("stage2_aggregate");
 
     // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
     BFF_REQUIRE((d->inter_pre == nullptr) == (d->pop_pre == nullptr), "bff_stage2_aggregate: inter_pre and pop_pre come together");
@@ -112,10 +130,10 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         d_pop = c->dev.get<int32_t>(n);
         if (!d_inter || !d_pop) return BFF_ENOMEM;
     }
-    const int stride = (n + 7) & ~7;
-    const size_t adj_bytes = (size_t)n * stride;
-    PIPE_TAKE(d_adj, c->dev, uint8_t, adj_bytes);
-    PIPE_TAKE(h_adj, c->pin, uint8_t, adj_bytes);
+    const int stride_words = ((n + 63) / 64) * 2;               // 32-bit words per adjacency row, whole 64-bit words
+    const size_t adj_bytes = (size_t)n * stride_words * 4;
+    PIPE_TAKE(d_adj, c->dev, uint32_t, (size_t)n * stride_words);
+    PIPE_TAKE(h_adj, c->pin, uint32_t, (size_t)n * stride_words);
     int32_t *d_label = nullptr;
     int rc = upload_i32(c, std::vector<int32_t>(d->label_id, d->label_id + n), &d_label, s);
     if (rc != BFF_OK) return rc;
@@ -123,28 +141,70 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
         if (rc != BFF_OK) return rc;
     }
-    merge_adjacency_kernel<<<(unsigned)ceil_div64((int64_t)adj_bytes, 256), 256, 0, s>>>(d_inter, d_pop, d_label, n, stride, d->iou_thres, d_adj);
+    {
+        dim3 grid((unsigned)(stride_words * 32 / 256 + 1), (unsigned)n);
+        merge_adjacency_kernel<<<grid, 256, 0, s>>>(d_inter, d_pop, d_label, n, stride_words, d->iou_thres, d_adj);
+    }
     BFF_LAUNCH_CHECK("merge_adjacency_kernel");
     BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));
+    // the point filter (:512-583) does not depend on the grouping: its first step (the maxima that size the vote
+    // histogram) rides on this synchronisation instead of paying for one of its own
+    const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
+    int32_t *h_max = nullptr;
+    if (d->filter_mode != 2) {
+        PIPE_TAKE(d_max, c->dev, int32_t, 2);
+        h_max = c->pin.get<int32_t>(2);
+        if (!h_max) return BFF_ENOMEM;
+        if ((rc = bff_counts_max(d->mc, vc, d->n_points, d_max, s)) != BFF_OK) return rc;
+        BFF_CUDA(cudaMemcpyAsync(h_max, d_max, 8, cudaMemcpyDeviceToHost, s));
+    }
+    tr.mark("enqueue1");
     BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync1");
 
     // ---- connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric, so the
     // reference's reachability lists are the components, emitted by smallest member, members ascending).
     // A node without any edge (an empty row: IoU diagonal NaN) forms no group.
-    UnionFind uf(n);
+    // Flood fill over the bit rows, 64 neighbours per step: root[i] = smallest member of i's component.
+    tr.mark("pre_cc");
+    const int w64 = stride_words / 2;
+    const uint64_t *adj64 = reinterpret_cast<const uint64_t *>(h_adj);
+    std::vector<uint64_t> visited(w64, 0), frontier(w64), next(w64);
+    std::vector<int> root(n, -1), count(n, 0);
     std::vector<char> has_edge(n, 0);
     for (int i = 0; i < n; ++i) {
-        const uint8_t *row = h_adj + (size_t)i * stride;
-        for (int j0 = 0; j0 < stride; j0 += 8) {
-            uint64_t w;
-            memcpy(&w, row + j0, 8);
-            if (!w) continue;                                   // the merge graph is sparse: skip 8 zero entries at once
-            for (int j = j0; j < j0 + 8; ++j)
-                if (row[j]) { has_edge[i] = 1; if (j > i) uf.unite(i, j); }
+        const uint64_t *row = adj64 + (size_t)i * w64;
+        uint64_t any = 0;
+        for (int w = 0; w < w64; ++w) any |= row[w];
+        has_edge[i] = any != 0;
+    }
+    for (int i = 0; i < n; ++i) {
+        if ((visited[i >> 6] >> (i & 63)) & 1) continue;
+        std::fill(frontier.begin(), frontier.end(), 0);
+        frontier[i >> 6] = 1ull << (i & 63);
+        visited[i >> 6] |= 1ull << (i & 63);
+        bool grew = true;
+        while (grew) {
+            grew = false;
+            std::fill(next.begin(), next.end(), 0);
+            for (int w = 0; w < w64; ++w) {
+                for (uint64_t m = frontier[w]; m; m &= m - 1) {
+                    const int u = w * 64 + __builtin_ctzll(m);
+                    root[u] = i;
+                    const uint64_t *row = adj64 + (size_t)u * w64;
+                    for (int k = 0; k < w64; ++k) next[k] |= row[k];
+                }
+            }
+            for (int k = 0; k < w64; ++k) {
+                next[k] &= ~visited[k];
+                visited[k] |= next[k];
+                grew |= next[k] != 0;
+            }
+            frontier.swap(next);
         }
     }
-    std::vector<int> root(n), count(n, 0);
-    for (int i = 0; i < n; ++i) { root[i] = uf.find(i); count[root[i]]++; }
+    for (int i = 0; i < n; ++i) count[root[i]]++;
+    tr.mark("cc");
     // kept groups (:203): len >= min_aggregated; roots ascending == order of smallest member
     std::vector<int> group_of_root(n, -1);
     int g = 0;
@@ -170,6 +230,7 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         }
     }
     if (d->members) memcpy(d->members, idx.data(), idx.size() * 4);
+    tr.mark("components");
 
     // ---- OR-merge the members (:214-223)
     int32_t *d_idx = nullptr, *d_seg = nullptr;
@@ -186,39 +247,56 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     PIPE_TAKE(h_before, c->pin, int32_t, g);
     BFF_CUDA(cudaMemcpyAsync(h_before, d_before, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
 
-    // ---- point filter (:512-583): the unique() over N values comes from the (masked, viewed) histogram
+    // ---- point filter (:512-583): the unique() over N values comes from the (masked, viewed) histogram, which is
+    // enqueued behind the pair overlaps so that ONE synchronisation brings both to the host
     PIPE_TAKE(d_keep, c->dev, uint32_t, words);
     float thr = 0.0f;
+    float *h_vals = nullptr, *d_vals_keep = nullptr;
+    size_t first_vals = 0;
+    int mb = 0, vb = 0;
+    if (d->filter_mode != 2) {
+        mb = h_max[0] + 1;
+        vb = vc ? h_max[1] + 1 : 1;
+        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
+        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
+        // distinct ratios straight from the non-empty bins, on the device: only they travel to the host
+        const int64_t tsize = bff_vote_unique_table_size(mb, vb);
+        PIPE_TAKE(d_table, c->dev, uint32_t, (size_t)tsize);
+        PIPE_TAKE(d_vals, c->dev, float, (size_t)mb * vb + 1);
+        h_vals = c->pin.get<float>((size_t)mb * vb + 1);
+        if (!h_vals) return BFF_ENOMEM;
+        int32_t *d_cnt = reinterpret_cast<int32_t *>(d_vals + (size_t)mb * vb);       // the count rides behind the values
+        if ((rc = bff_vote_unique(d_hist, mb, vb, d->filter_mode, d_table, tsize, d_vals, d_cnt, s)) != BFF_OK) return rc;
+        // the number of distinct values is not known yet: a first slice that nearly always suffices, the rest on demand
+        first_vals = std::min<size_t>((size_t)mb * vb, 16384);
+        BFF_CUDA(cudaMemcpyAsync(h_vals, d_vals, first_vals * 4, cudaMemcpyDeviceToHost, s));
+        BFF_CUDA(cudaMemcpyAsync(h_vals + (size_t)mb * vb, d_cnt, 4, cudaMemcpyDeviceToHost, s));
+        d_vals_keep = d_vals;
+    }
+    tr.mark("enqueue2");
+    BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps, 'before' and the histogram are on the host now
+    tr.mark("sync2");
     if (d->filter_mode == 2) {
         if ((rc = bff_point_keep(d->mc, nullptr, d->n_points, 2, 0.0f, d_keep, s)) != BFF_OK) return rc;
     } else {
-        PIPE_TAKE(d_max, c->dev, int32_t, 2);
-        PIPE_TAKE(h_max, c->pin, int32_t, 2);
-        const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
-        if ((rc = bff_counts_max(d->mc, vc, d->n_points, d_max, s)) != BFF_OK) return rc;
-        BFF_CUDA(cudaMemcpyAsync(h_max, d_max, 8, cudaMemcpyDeviceToHost, s));
-        BFF_CUDA(cudaStreamSynchronize(s));
-        const int mb = h_max[0] + 1, vb = vc ? h_max[1] + 1 : 1;
-        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
-        PIPE_TAKE(h_hist, c->pin, uint32_t, (size_t)mb * vb);
-        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
-        BFF_CUDA(cudaMemcpyAsync(h_hist, d_hist, (size_t)mb * vb * 4, cudaMemcpyDeviceToHost, s));
-        BFF_CUDA(cudaStreamSynchronize(s));
-        std::vector<float> u;
-        for (int a = 0; a < mb; ++a)
-            for (int b = 0; b < vb; ++b)
-                if (h_hist[(size_t)a * vb + b]) u.push_back(d->filter_mode == 0 ? (float)a / ((float)b + 1.0f) : (float)a);   // :571 in float32
-        std::sort(u.begin(), u.end());
-        u.erase(std::unique(u.begin(), u.end()), u.end());
-        // u[floor(p * len(u))] with p a Python float (:516-517, :575-576); out of range raises in the reference
+        int32_t n_unique;
+        memcpy(&n_unique, h_vals + (size_t)mb * vb, 4);
+        if ((size_t)n_unique > first_vals) {
+            BFF_CUDA(cudaMemcpyAsync(h_vals + first_vals, d_vals_keep + first_vals, ((size_t)n_unique - first_vals) * 4, cudaMemcpyDeviceToHost, s));
+            BFF_CUDA(cudaStreamSynchronize(s));
+        }
+        std::vector<float> u(h_vals, h_vals + n_unique);
+        // u[floor(p * len(u))] of the SORTED unique values with p a Python float (:516-517, :575-576); out of range raises in the reference
         const double pos = floor(d->filter_fraction * (double)u.size());
         BFF_REQUIRE(pos >= 0.0 && pos < (double)u.size(), "bff_stage2_aggregate: filter fraction %g selects index %g of %zu unique values",
                     d->filter_fraction, pos, u.size());
+        std::nth_element(u.begin(), u.begin() + (size_t)pos, u.end());
         thr = u[(size_t)pos];
+        if (tr.on) fprintf(stderr, " [bins %dx%d unique %zu]", mb, vb, u.size());
+        tr.mark("threshold");
         if ((rc = bff_point_keep(d->mc, vc, d->n_points, d->filter_mode, thr, d_keep, s)) != BFF_OK) return rc;
     }
     if (d->filter_value) *d->filter_value = thr;
-    BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps + 'before' are on the host now
 
     // ---- solve_overlapping's sequential schedule (:285-299): pairs i<j that overlap in the incoming rows;
     // the mask merged from MORE members keeps the shared points, ties: i loses
@@ -229,6 +307,7 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
                 if (d->group_size[i] > d->group_size[j]) { prog.push_back(j); prog.push_back(i); }
                 else { prog.push_back(i); prog.push_back(j); }
             }
+    tr.mark("schedule");
     if (!prog.empty()) {
         int32_t *d_prog = nullptr;
         if ((rc = upload_i32(c, prog, &d_prog, s)) != BFF_OK) return rc;
@@ -239,7 +318,9 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     if ((rc = bff_rows_and_popcount(d->agg_rows, g, words, d_keep, d_after, s)) != BFF_OK) return rc;
     PIPE_TAKE(h_after, c->pin, int32_t, g);
     BFF_CUDA(cudaMemcpyAsync(h_after, d_after, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+    tr.mark("enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync3");
     memcpy(d->before, h_before, (size_t)g * 4);
     memcpy(d->after, h_after, (size_t)g * 4);
     return BFF_OK;

@@ -121,6 +121,56 @@ extern "C" int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, in
     return BFF_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// bff_vote_unique: the distinct values the reference's unique() would see (projection_2d_to_3d.py:512-517 masked_counts,
+// :571-575 detected_ratio = mc / (vc + 1) in float32), from the non-empty bins of the vote histogram: every non-empty bin
+// inserts the bit pattern of its value into an open-addressing set (atomicCAS, linear probing; values are finite and
+// >= +0, so equal bits <=> equal values), a second kernel compacts the set. Order of `values` is unspecified.
+namespace bff {
+__global__ void __launch_bounds__(256)
+vote_unique_insert_kernel(const uint32_t *__restrict__ hist, int mc_bins, int vc_bins, int mode, uint32_t *__restrict__ table, uint32_t cap_mask) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= (long long)mc_bins * vc_bins || hist[i] == 0u) return;
+    const int a = (int)(i / vc_bins), b = (int)(i % vc_bins);
+    const float val = mode == 0 ? __fdiv_rn((float)a, __fadd_rn((float)b, 1.0f)) : (float)a;
+    const uint32_t bits = __float_as_uint(val);
+    uint32_t slot = (bits * 2654435761u) & cap_mask;
+    while (true) {
+        const uint32_t old = atomicCAS(table + slot, 0xffffffffu, bits);
+        if (old == 0xffffffffu || old == bits) return;
+        slot = (slot + 1u) & cap_mask;
+    }
+}
+__global__ void __launch_bounds__(256)
+vote_unique_compact_kernel(const uint32_t *__restrict__ table, uint32_t cap, float *__restrict__ values, int32_t *__restrict__ count) {
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= cap) return;
+    const uint32_t v = table[i];
+    if (v != 0xffffffffu) values[atomicAdd(count, 1)] = __uint_as_float(v);
+}
+}  // namespace bff
+
+extern "C" int64_t bff_vote_unique_table_size(int32_t mc_bins, int32_t vc_bins) {
+    int64_t cap = 1024;
+    while (cap < (int64_t)mc_bins * vc_bins * 2) cap <<= 1;
+    return cap;
+}
+
+extern "C" int bff_vote_unique(const uint32_t *hist, int32_t mc_bins, int32_t vc_bins, int32_t mode, uint32_t *table, int64_t table_size,
+                               float *values, int32_t *count, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(hist && table && values && count && mc_bins >= 1 && vc_bins >= 1 && (mode == 0 || mode == 1), "bff_vote_unique: bad arguments");
+    BFF_REQUIRE(table_size >= bff_vote_unique_table_size(mc_bins, vc_bins) && (table_size & (table_size - 1)) == 0 && table_size <= (1LL << 31),
+                "bff_vote_unique: table_size must be a power of two >= bff_vote_unique_table_size()");
+    const long long bins = (long long)mc_bins * vc_bins;
+    BFF_CUDA(cudaMemsetAsync(table, 0xff, (size_t)table_size * 4, stream));
+    BFF_CUDA(cudaMemsetAsync(count, 0, 4, stream));
+    vote_unique_insert_kernel<<<(unsigned)ceil_div64(bins, 256), 256, 0, stream>>>(hist, mc_bins, vc_bins, mode, table, (uint32_t)(table_size - 1));
+    vote_unique_compact_kernel<<<(unsigned)ceil_div64(table_size, 256), 256, 0, stream>>>(table, (uint32_t)table_size, values, count);
+    BFF_LAUNCH_CHECK("vote_unique kernels");
+    return BFF_OK;
+}
+
 extern "C" int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mode, float thr,
                               uint32_t *keep, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;

@@ -176,6 +176,14 @@ BFF_API int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, int3
 BFF_API int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, int32_t mc_bins, int32_t vc_bins,
                   uint32_t *hist, void *stream);
 
+/* The distinct values the reference's unique() sees (:512-517 masked_counts.unique(), :571-575 detected_ratio.unique()),
+ * derived on the device from the non-empty bins of bff_vote_hist: mode 0 value = f32(mc) / (f32(vc) + 1), mode 1 value =
+ * f32(mc). `table` is scratch of table_size uint32 (a power of two >= bff_vote_unique_table_size(mc_bins, vc_bins));
+ * `values` receives *count distinct floats in unspecified order (capacity mc_bins * vc_bins). */
+BFF_API int64_t bff_vote_unique_table_size(int32_t mc_bins, int32_t vc_bins);
+BFF_API int bff_vote_unique(const uint32_t *hist, int32_t mc_bins, int32_t vc_bins, int32_t mode, uint32_t *table, int64_t table_size,
+                            float *values, int32_t *count, void *stream);
+
 /* Per-point keep predicate -> packed bits keep (Wd):
  *  mode 0 (detected ratio, :571-583): keep = mc > 0 && !(f32(mc) / (f32(vc) + 1) < thr)
  *  mode 1 (occurrence, :512-522,583):  keep = mc > 0 && !(f32(mc) < thr)

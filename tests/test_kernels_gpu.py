@@ -433,3 +433,20 @@ def test_lift_with_in_kernel_resize_edge_cases(cuda_dev):
     z = ops.lift_scene(_xyz_dev(sb, cuda_dev, True), torch.zeros((0, 4, 4), dtype=torch.float64, device=cuda_dev), sb["K"], nat[:0], 96, 128,
                        native_size=(hs, ws))
     assert int(z.viewed_counts.sum()) == 0 and z.viewed_counts.shape[0] == sb["n"]
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_vote_unique_equals_torch_unique(cuda_dev, mode):
+    """bff_vote_hist + bff_vote_unique == the reference's unique() over N per-point values (:512-517, :571-575)."""
+    from bff_b200 import ops
+    rng = np.random.default_rng(17 + mode)
+    n = 200_003
+    mc = rng.integers(0, 140, n).astype(np.int32)
+    mc[rng.random(n) < 0.5] = 0
+    vc = rng.integers(0, 301, n).astype(np.int32)
+    mc_t, vc_t = torch.from_numpy(mc).to(cuda_dev), torch.from_numpy(vc).to(cuda_dev)
+    hist = ops.vote_hist(mc_t, vc_t if mode == 0 else None, int(mc.max()) + 1, int(vc.max()) + 1 if mode == 0 else 1)
+    got = ops.vote_unique(hist, mode).cpu()
+    mcf, vcf = torch.from_numpy(mc).float(), torch.from_numpy(vc).float()
+    want = (mcf / (vcf + 1)).unique() if mode == 0 else mcf.unique()
+    assert len(want) > 100 and torch.equal(got, want)
