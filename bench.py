@@ -217,7 +217,10 @@ class GpuScene:
 
         def refine_query(qi, res2):
             name = self.names[qi]
-            p1 = refine.pass1_scene(inp["stage1"], res2, name, cfg["stage1_iou_thres"], fake_similarity, self.dev, s1_rows=s1)
+            # pass 1 ORs matched stage-1 rows in place (refinement.py:248): every query starts from the decoded originals,
+            # as every reference process (one per --cls) does
+            p1 = refine.pass1_scene(inp["stage1"], res2, name, cfg["stage1_iou_thres"], fake_similarity, self.dev,
+                                    s1_rows=s1.clone() if self.nq > 1 else s1)
             thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
             return refine.pass2_scene(p1, name, cfg["refiment_iou_thres"], thr, to_host=to_host)
 
