@@ -161,8 +161,11 @@ def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Seque
     (agg_rows CUDA (G,Wd), conf_agg CPU (G,), labels_agg, groups, before (G,) int64, after (G,) int64)."""
     from . import _cabi
     n = rows.shape[0]
-    ids: dict = {}
-    label_id = np.asarray([ids.setdefault(l, len(ids)) for l in labels], dtype=np.int32)
+    if n and isinstance(labels, (list, tuple)) and labels.count(labels[0]) == n:   # one phrase for every mask (the usual case: labels = [query] * M)
+        label_id = np.zeros(n, dtype=np.int32)
+    else:
+        ids: dict = {}
+        label_id = np.asarray([ids.setdefault(l, len(ids)) for l in labels], dtype=np.int32)
     conf32 = np.ascontiguousarray(conf.numpy(), dtype=np.float32)
     if cfg["if_occurance_threshold"]:
         mode, frac = 1, float(cfg["occurance_threshold"])
