@@ -40,21 +40,21 @@ def _same(a, b, what):
     assert torch.equal(torch.as_tensor(a["conf"]), torch.as_tensor(b["conf"])), what
 
 
-@pytest.mark.parametrize("occurrence", [False, True])
-def test_fused_pipeline_equals_stepwise_and_port(cuda_dev, occurrence):
+@pytest.mark.parametrize("occurrence,seed", [(False, 2000), (True, 2000), (False, 2011), (True, 2012), (False, 2013), (False, 2014)])
+def test_fused_pipeline_equals_stepwise_and_port(cuda_dev, occurrence, seed):
     sys.path.insert(0, ROOT)
     import bench
-    inp = bench.build_inputs("tiny", 0, 1, cuda_dev)
+    inp = bench.build_inputs("tiny", 0, 1, cuda_dev, seed=seed)
     cfg = dict(inp["cfg"])
     if occurrence:
         cfg.update(if_occurance_threshold=True, if_detected_ratio_threshold=False)
     inp["cfg"] = cfg
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    assert g.n_masks > 15
+    assert g.n_masks > 8
     a2, ap1, afin = _run(inp, g, d, True, cfg)
     b2, bp1, bfin = _run(inp, g, d, False, cfg)
-    assert a2["ins"].shape[0] >= 2 and afin["ins"].shape[0] >= 2
+    assert a2["ins"].shape[0] >= 1 and afin["ins"].shape[0] >= 1
     _same(a2, b2, "stage 2")
     _same(afin, bfin, "final")
     assert torch.equal(torch.as_tensor(ap1["ious"]), torch.as_tensor(bp1["ious"])) and ap1["sims"] == bp1["sims"]
