@@ -78,6 +78,7 @@ SYMBOLS = {
     "bff_vote_unique": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
     "bff_point_keep": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
     "bff_labels_to_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
+    "bff_rows_permute": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),
     "bff_overlap_resolve": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p]),
     "bff_rows_or_into": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_int32, c_void_p]),
     "bff_rows_and_popcount": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -382,3 +382,16 @@ def labels_to_rows(labels: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
     if n and g:
         _count()
     return out
+
+
+def rows_permute(rows: torch.Tensor, src_index: torch.Tensor, n_points: int) -> torch.Tensor:
+    """out bit p of every row = rows bit src_index[p] (bff_rows_permute). rows (R,Wd) int32, src_index (N,) int32, CUDA."""
+    rows = _cuda(rows, torch.int32, "rows")
+    src_index = _cuda(src_index, torch.int32, "src_index").reshape(-1)
+    if src_index.numel() != n_points or rows.shape[1] != words_for(n_points):
+        raise ValueError("rows_permute: size mismatch")
+    out = torch.empty_like(rows)
+    check(lib().bff_rows_permute(ptr(rows), rows.shape[0], int(n_points), ptr(src_index), ptr(out), current_stream()), "bff_rows_permute")
+    if rows.shape[0] and n_points:
+        _count()
+    return out

@@ -361,3 +361,40 @@ extern "C" int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_ro
     BFF_LAUNCH_CHECK("rle_to_bits_kernel");
     return BFF_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// bff_rows_permute: out bit p of every row = in bit src_index[p]. Used to bring rows lifted on a spatially re-ordered
+// copy of the cloud (bff_b200/lift.py: Morton order, so that a warp's 32 points are neighbours and the warp-level
+// culling of lift_kernel bites) back to the cloud's own point order, which every output of the path is indexed by.
+namespace bff {
+constexpr int kPermuteRowsPerBlock = 16;
+__global__ void __launch_bounds__(256)
+rows_permute_kernel(const uint32_t *__restrict__ in, int n_rows, long long n, long long words, const int32_t *__restrict__ src,
+                    uint32_t *__restrict__ out) {
+    const long long p = (long long)blockIdx.x * 256 + threadIdx.x;
+    const bool valid = p < n;
+    const int s = valid ? __ldg(src + p) : 0;
+    const long long sw = s >> 5;
+    const int sb = s & 31;
+    const int r0 = blockIdx.y * kPermuteRowsPerBlock, r1 = min(n_rows, r0 + kPermuteRowsPerBlock);
+    for (int r = r0; r < r1; ++r) {
+        const bool bit = valid && ((__ldg(in + (long long)r * words + sw) >> sb) & 1u);
+        const unsigned w = __ballot_sync(0xffffffffu, bit);
+        if ((threadIdx.x & 31) == 0 && valid) out[(long long)r * words + (p >> 5)] = w;
+    }
+}
+}  // namespace bff
+
+extern "C" int bff_rows_permute(const uint32_t *rows_in, int32_t n_rows, int64_t n_points, const int32_t *src_index,
+                                uint32_t *rows_out, void *stream_) {
+    BFF_REQUIRE(n_rows >= 0 && n_points >= 0, "bff_rows_permute: negative size");
+    if (n_rows == 0 || n_points == 0) return BFF_OK;
+    BFF_REQUIRE(rows_in && src_index && rows_out && rows_in != rows_out, "bff_rows_permute: null or aliased pointer");
+    BFF_REQUIRE(n_points < (1LL << 31), "bff_rows_permute: too many points for int32 indices");
+    dim3 grid((unsigned)ceil_div64(n_points, 256), (unsigned)ceil_div64(n_rows, bff::kPermuteRowsPerBlock));
+    BFF_REQUIRE(grid.y <= 65535, "bff_rows_permute: too many rows");
+    bff::rows_permute_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows_in, n_rows, n_points, ceil_div64(n_points, 32), src_index, rows_out);
+    BFF_LAUNCH_CHECK("rows_permute_kernel");
+    return BFF_OK;
+}

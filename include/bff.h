@@ -197,6 +197,12 @@ BFF_API int bff_point_keep(const int32_t *mc, const int32_t *vc, int64_t n, int3
  * (`np.count_nonzero(np.logical_and(gts == inst_id, pred_mask))`) at once. */
 BFF_API int bff_labels_to_rows(const int64_t *labels, int64_t n, const int64_t *ids, int32_t n_ids, uint32_t *rows, void *stream);
 
+/* Re-index packed rows by point: rows_out bit p = rows_in bit src_index[p] for every row (src_index: device, (n_points) int32,
+ * a permutation or any gather map). The lifting host code uses it to return rows computed on a spatially sorted copy of the
+ * cloud to the cloud's own order. rows_out must not alias rows_in. */
+BFF_API int bff_rows_permute(const uint32_t *rows_in, int32_t n_rows, int64_t n_points, const int32_t *src_index,
+                             uint32_t *rows_out, void *stream);
+
 /* solve_overlapping's sequential pass (projection_2d_to_3d.py:295-299) on packed rows, in place.
  * prog (n_steps, 2) int32: step k clears from row prog[k][0] the bits of row prog[k][1]
  * (rows[dst] &= ~rows[src]) in list order; every word column runs the program independently. */

@@ -450,3 +450,38 @@ def test_vote_unique_equals_torch_unique(cuda_dev, mode):
     mcf, vcf = torch.from_numpy(mc).float(), torch.from_numpy(vc).float()
     want = (mcf / (vcf + 1)).unique() if mode == 0 else mcf.unique()
     assert len(want) > 100 and torch.equal(got, want)
+
+
+@pytest.mark.parametrize("f32", [True, False])
+def test_lift_on_reordered_cloud_returns_results_in_cloud_order(cuda_dev, monkeypatch, f32):
+    """lift.lift sorts an incoherent cloud along a Morton curve for the launch (warp-level culling needs neighbours in a
+    warp) and un-permutes rows and votes (bff_rows_permute): results equal the oracle's on the cloud as given."""
+    import oracle as O
+    from bff_b200 import lift as lift_mod, scene_io
+    from bff_b200.rle import rle_encode_rows
+    sc = random_scene(61, n=9001, f=9, f32_xyz=f32)           # random_scene points are uniformly random: no coherence at all
+    rows_o, mc_o, vc_o = _oracle(sc)
+    recs = []
+    for fr in range(sc["f"]):
+        m0, m1 = sc["mask_off"][fr], sc["mask_off"][fr + 1]
+        if m1 > m0:
+            recs.append({"frame_id": f"{fr}.jpg", "segmented_frame_masks": rle_encode_rows(torch.from_numpy(sc["masks"][m0:m1].reshape(m1 - m0, -1))),
+                         "confidences": torch.full((m1 - m0,), 0.3), "labels": ["q"] * (m1 - m0)})
+    q = lift_mod.QueryMasks.from_file_records("q", recs)
+    frame_ids, viewed, per_frame = lift_mod.plan_frames([q], [str(i) for i in range(sc["f"])])
+    idx = [int(i) for i in frame_ids]
+    frames = scene_io.FrameSet(frame_ids, sc["pinv"][idx], sc["depth"][idx], False, np.asarray(viewed, np.uint8), None)
+    xyz_dev = scene_io.cloud_for_device(sc["xyz"], cuda_dev)
+    assert lift_mod.point_order_spread(xyz_dev) > 0.5
+    got = {}
+    monkeypatch.setattr(lift_mod, "REORDER_MIN_POINT_VIEWS", 0.0)
+    for mode in ("never", "auto", "always"):
+        monkeypatch.setattr(lift_mod, "REORDER", mode)
+        L = lift_mod.lift(xyz_dev, sc["K"], frames, per_frame, [q], sc["h"], sc["w"], True)
+        got[mode] = L
+        # rows of the oracle are in launch order = frames that carry masks first (plan order == file order here)
+        np.testing.assert_array_equal(unpack_rows(L.rows[0].cpu().numpy(), sc["n"]), rows_o)
+        np.testing.assert_array_equal(L.masked_counts.cpu().numpy(), mc_o)
+        np.testing.assert_array_equal(L.viewed_counts.cpu().numpy(), vc_o)
+    order = lift_mod.morton_order(xyz_dev)
+    assert lift_mod.point_order_spread(xyz_dev[order]) < 0.25
