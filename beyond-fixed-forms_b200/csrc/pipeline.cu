@@ -352,6 +352,7 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
     const int n1 = d->n1, n2 = d->n2;
     const int64_t words = ceil_div64(d->n_points, 32);
     int rc;
+    PipeTrace tr("refine_match");
     // scratch for an (n1 x k) IoU, k <= n2
     PIPE_TAKE(d_inter, c->dev, int32_t, (size_t)n1 * n2);
     PIPE_TAKE(d_p1, c->dev, int32_t, n1);
@@ -362,7 +363,9 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
     // ---- iou(stage1, stage2), max_match = argmax over stage-1 (:208-213)
     if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_rows, n2, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
     BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    tr.mark("enqueue1");
     BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync1");
     std::vector<int32_t> mm(n2);
     for (int k = 0; k < n2; ++k) mm[k] = argmax_torch(h_iou + k, n1, n2);
 
@@ -381,7 +384,9 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
     }
     if ((rc = bff_mask_iou(d_sel, n2, d_sel, n2, words, d_ginter, d_gpop, d_gpop, d_giou, s)) != BFF_OK) return rc;
     BFF_CUDA(cudaMemcpyAsync(h_giou, d_giou, (size_t)n2 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    tr.mark("enqueue2");
     BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync2");
 
     // ---- sequential merge loop (:230-249): redirects + in-place ORs of stage-1 rows, in list order
     std::vector<int32_t> best(n2), redirect(n2, -1), or_prog;
@@ -448,7 +453,9 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
     // ---- IoU of the merged stage-1 masks with the merged stage-2 masks, final argmax (:285-290)
     if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_out, m, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
     BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * m * 4, cudaMemcpyDeviceToHost, s));
+    tr.mark("enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync3");
     for (int k = 0; k < m; ++k) {
         d->match[k] = argmax_torch(h_iou + k, n1, m);
         d->match_iou[k] = h_iou[(size_t)d->match[k] * m + k];
