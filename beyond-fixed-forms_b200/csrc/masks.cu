@@ -102,6 +102,69 @@ intersect_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *__rest
     }
 }
 
+// ------------------------------------------------------------------ intersections, few columns
+// The refinement calls are (200 stage-1 rows) x (a handful of stage-2 rows) and (few) x (few): a 64 x 64 tile would compute
+// mostly padding. Here a warp owns ONE row of A; the B rows of the current 256-word chunk sit in shared memory and every
+// lane keeps NB running sums, so A streams through exactly once. The row popcounts of both operands fall out of the same
+// pass (no separate row_popcount launches): pop_a from the A words a warp reads anyway, pop_b from the staged B words in the
+// first row block. inter / pop_a / pop_b must be zeroed; partial sums of the K-slices are added atomically.
+constexpr int kSkinnyChunk = 256;      // words of every B row staged per step
+constexpr int kSkinnyRows = 8;         // A rows (= warps) per CTA
+
+template <int NB>
+__global__ void __launch_bounds__(kSkinnyRows * 32)
+intersect_skinny_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *__restrict__ b, int n_b, long long words,
+                        long long words_per_slice, int32_t *__restrict__ inter, int32_t *__restrict__ pop_a, int32_t *__restrict__ pop_b) {
+    __shared__ uint32_t sb[NB][kSkinnyChunk];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * kSkinnyRows + warp;
+    const bool row_ok = row < n_a;
+    const uint32_t *ar = a + (long long)(row_ok ? row : 0) * words;
+    const long long w_begin = (long long)blockIdx.y * words_per_slice;
+    const long long w_end = min(words, w_begin + words_per_slice);
+    int acc[NB];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) acc[j] = 0;
+    int acc_a = 0, acc_b = 0;                       // acc_b: thread t < NB * 8 ... see below (B popcount of row t / 8)
+    for (long long w0 = w_begin; w0 < w_end; w0 += kSkinnyChunk) {
+        const int cw = (int)min((long long)kSkinnyChunk, w_end - w0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < NB * kSkinnyChunk; i += kSkinnyRows * 32) {
+            const int j = i / kSkinnyChunk, k = i % kSkinnyChunk;
+            const uint32_t v = (j < n_b && k < cw) ? __ldg(b + (long long)j * words + w0 + k) : 0u;
+            sb[j][k] = v;
+        }
+        __syncthreads();
+        if (pop_b != nullptr && blockIdx.x == 0) {   // B popcounts: once per K-slice, by the first row block
+            for (int i = threadIdx.x; i < NB * kSkinnyChunk; i += kSkinnyRows * 32) {
+                const int j = i / kSkinnyChunk;      // 256 consecutive i share j: a warp's 32 values belong to one row
+                int c = __popc(sb[j][i % kSkinnyChunk]);
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                if (lane == 0 && c && j < n_b) atomicAdd(pop_b + j, c);
+            }
+        }
+        if (row_ok) {
+#pragma unroll 2
+            for (int k = lane; k < cw; k += 32) {
+                const uint32_t va = __ldg(ar + w0 + k);
+                acc_a += __popc(va);
+#pragma unroll
+                for (int j = 0; j < NB; ++j) acc[j] += __popc(va & sb[j][k]);
+            }
+        }
+    }
+    (void)acc_b;
+    if (!row_ok) return;
+    for (int o = 16; o > 0; o >>= 1) acc_a += __shfl_xor_sync(0xffffffffu, acc_a, o);
+    if (lane == 0 && pop_a != nullptr && acc_a) atomicAdd(pop_a + row, acc_a);
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+        int v = acc[j];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0 && j < n_b && v) atomicAdd(inter + (long long)row * n_b + j, v);
+    }
+}
+
 // IoU exactly as calculate_iou (projection_2d_to_3d.py:158-165) / calculate_iou_between_stages
 // (refinement.py:82-90): union = (f32(sA) + f32(sB)) - f32(I); iou = f32(I) / union; 0/0 = NaN.
 __global__ void iou_finalize_kernel(const int32_t *__restrict__ inter, const int32_t *__restrict__ pa,
@@ -229,6 +292,32 @@ extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, i
     if (n_a == 0 || n_b == 0) return BFF_OK;
     BFF_REQUIRE(a && b, "bff_mask_iou: null rows");
     BFF_REQUIRE(!iou || (inter && pop_a && pop_b), "bff_mask_iou: iou needs inter, pop_a and pop_b buffers");
+    // few columns (the refinement shapes): one pass that also yields both popcount vectors
+    if (inter && words > 0 && n_b <= 32 && !(getenv("BFF_IOU_PATH") && getenv("BFF_IOU_PATH")[0] != 's')) {
+        const bool same_pop = pop_a != nullptr && pop_a == pop_b;           // symmetric call: one vector serves both
+        BFF_CUDA(cudaMemsetAsync(inter, 0, (size_t)n_a * n_b * 4, stream));
+        if (pop_a) BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));
+        if (pop_b && !same_pop) BFF_CUDA(cudaMemsetAsync(pop_b, 0, (size_t)n_b * 4, stream));
+        const long long row_blocks = ceil_div64(n_a, kSkinnyRows);
+        long long slices = ceil_div64((long long)kNumSMs * 4, row_blocks);
+        const long long max_slices = ceil_div64(words, kSkinnyChunk);
+        if (slices > max_slices) slices = max_slices;
+        if (slices < 1) slices = 1;
+        if (slices > 65535) slices = 65535;
+        const long long wps = ceil_div64(ceil_div64(words, slices), kSkinnyChunk) * kSkinnyChunk;
+        slices = ceil_div64(words, wps);
+        dim3 grid((unsigned)row_blocks, (unsigned)slices);
+        int32_t *pb = same_pop ? nullptr : pop_b;
+        if (n_b <= 8) intersect_skinny_kernel<8><<<grid, kSkinnyRows * 32, 0, stream>>>(a, n_a, b, n_b, words, wps, inter, pop_a, pb);
+        else if (n_b <= 16) intersect_skinny_kernel<16><<<grid, kSkinnyRows * 32, 0, stream>>>(a, n_a, b, n_b, words, wps, inter, pop_a, pb);
+        else intersect_skinny_kernel<32><<<grid, kSkinnyRows * 32, 0, stream>>>(a, n_a, b, n_b, words, wps, inter, pop_a, pb);
+        if (iou) {
+            const long long tot = (long long)n_a * n_b;
+            iou_finalize_kernel<<<(unsigned)ceil_div64(tot, 256), 256, 0, stream>>>(inter, pop_a, pop_b, n_a, n_b, iou);
+        }
+        BFF_LAUNCH_CHECK("bff_mask_iou kernels (few columns)");
+        return BFF_OK;
+    }
     if (pop_a) {
         if (words > 0) row_popcount_kernel<<<n_a, 256, 0, stream>>>(a, words, pop_a);
         else BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));

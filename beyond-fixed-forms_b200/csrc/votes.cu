@@ -136,8 +136,12 @@ vote_unique_insert_kernel(const uint32_t *__restrict__ hist, int mc_bins, int vc
     const uint32_t bits = __float_as_uint(val);
     uint32_t slot = (bits * 2654435761u) & cap_mask;
     while (true) {
-        const uint32_t old = atomicCAS(table + slot, 0xffffffffu, bits);
-        if (old == 0xffffffffu || old == bits) return;
+        uint32_t old = *reinterpret_cast<volatile uint32_t *>(table + slot);      // many bins share a value (0 / (b + 1) = 0 ...):
+        if (old == bits) return;                                                   // look before the atomic
+        if (old == 0xffffffffu) {
+            old = atomicCAS(table + slot, 0xffffffffu, bits);
+            if (old == 0xffffffffu || old == bits) return;
+        }
         slot = (slot + 1u) & cap_mask;
     }
 }

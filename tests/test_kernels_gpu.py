@@ -485,3 +485,33 @@ def test_lift_on_reordered_cloud_returns_results_in_cloud_order(cuda_dev, monkey
         np.testing.assert_array_equal(L.viewed_counts.cpu().numpy(), vc_o)
     order = lift_mod.morton_order(xyz_dev)
     assert lift_mod.point_order_spread(xyz_dev[order]) < 0.25
+
+
+@pytest.mark.parametrize("na,nb,n", [(200, 9, 250_003), (200, 1, 4099), (7, 7, 100_001), (33, 32, 12_345), (1, 17, 31), (70, 27, 257)])
+def test_few_column_intersections_equal_tile_path_and_oracle(cuda_dev, monkeypatch, na, nb, n):
+    """The one-pass kernel for the refinement shapes (<= 32 columns; intersections and BOTH popcount vectors from a single
+    read of the rows) against the tiled POPC kernel and the C oracle, rectangular and symmetric, incl. empty rows (0/0 = NaN)."""
+    import oracle as O
+    from bff_b200 import ops
+    rng = np.random.default_rng(na * 11 + nb)
+    a = rng.random((na, n)) < rng.uniform(0, 0.4, size=(na, 1))
+    b = rng.random((nb, n)) < 0.15
+    a[na // 2] = False
+    b[nb - 1] = False
+    da = torch.from_numpy(pack_rows(a).view(np.int32)).to(cuda_dev)
+    db = torch.from_numpy(pack_rows(b).view(np.int32)).to(cuda_dev)
+    res = {}
+    for path in ("skinny", "popc"):
+        monkeypatch.setenv("BFF_IOU_PATH", path)
+        res[path] = (ops.mask_iou(da, db), ops.mask_iou(db))
+    for k in range(2):
+        for t_s, t_p in zip(res["skinny"][k], res["popc"][k]):
+            assert torch.equal(torch.nan_to_num(t_s.float(), nan=-1.0), torch.nan_to_num(t_p.float(), nan=-1.0))
+    inter_o, iou_o = O.mask_iou(a, b)
+    inter, pa, pb, iou = (t.cpu().numpy() for t in res["skinny"][0])
+    np.testing.assert_array_equal(inter, inter_o)
+    np.testing.assert_array_equal(pa, a.sum(1))
+    np.testing.assert_array_equal(pb, b.sum(1))
+    nan = np.isnan(iou_o)
+    assert nan.any() and np.array_equal(np.isnan(iou), nan)
+    np.testing.assert_array_equal(iou[~nan].view(np.int32), iou_o[~nan].view(np.int32))
