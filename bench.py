@@ -424,7 +424,7 @@ def run_gpu(args):
     # already moving host -> device on a copy stream (every step still uploads all of its own inputs and
     # reads its result back inside the timed region; only the two are allowed to overlap)
     from bff_b200 import ops
-    copy_stream = torch.cuda.Stream(device=dev)
+    copy_stream = torch.cuda.Stream(device=dev, priority=-1 if args.upload.endswith('+hi') else 0)
     bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]   # double buffer, no allocation in the loop
     done = [None, None]
     # The big buffers go through the SM copy kernel even where the copy engine alone is a little faster (probe below:
@@ -439,33 +439,64 @@ def run_gpu(args):
         return a.elapsed_time(b) / 2
     t_ce = _time_copy(lambda: bufs[0][big].copy_(g.host[big], non_blocking=True))
     t_sm = _time_copy(lambda: ops.upload(bufs[0][big], g.host[big])) if g.host[big].numel() * g.host[big].element_size() >= 16 else float("inf")
-    use_sm_copy = True
+    mode = args.upload.replace("+hi", "")   # "sm" | "ce" | "ce:<MiB>" (copy engine in chunks, so that other streams' small copies interleave)
+    use_sm_copy = mode == "sm"
+    chunk = int(float(mode.split(":")[1]) * (1 << 20)) if mode.startswith("ce:") else 0
 
     def upload_async(slot):
         with torch.cuda.stream(copy_stream):
             if done[slot] is not None:
                 copy_stream.wait_event(done[slot])          # the step that last read this buffer has finished
             for k_, v_ in g.host.items():
-                if use_sm_copy and v_.numel() * v_.element_size() >= (1 << 20):
-                    ops.upload(bufs[slot][k_], v_, copy_stream)      # SM-driven copy: keeps the H2D copy engine free
+                nbytes = v_.numel() * v_.element_size()
+                if use_sm_copy and nbytes:
+                    # SM-driven copy for EVERY buffer: the H2D copy engine stays free for the running step's own small
+                    # staging copies. (A copy-engine transfer queued in this stream behind the 3.6 ms depth kernel would
+                    # wait at the head of the engine's queue and hold those copies back: 4.4 ms per scene instead of 3.8.)
+                    ops.upload(bufs[slot][k_], v_, copy_stream)
+                elif chunk and nbytes > chunk:
+                    src_b, dst_b = v_.view(-1).view(torch.uint8), bufs[slot][k_].view(-1).view(torch.uint8)
+                    for a in range(0, nbytes, chunk):
+                        dst_b[a:a + chunk].copy_(src_b[a:a + chunk], non_blocking=True)
                 else:
                     bufs[slot][k_].copy_(v_, non_blocking=True)
-            ev = torch.cuda.Event()
+            ev = torch.cuda.Event(enable_timing=diag)
             ev.record(copy_stream)
         return ev
+    diag = bool(os.environ.get("BFF_E2E_DIAG"))         # dev: print the device timeline of uploads and steps (stderr)
+    marks = []
     barrier()
+    prof = None
+    if os.environ.get("BFF_E2E_DIAG") == "2":
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
     t0 = time.perf_counter()
+    origin = _event() if diag else None
     nxt = upload_async(0)
     for i in range(args.steps):
         ev = nxt
         if i + 1 < args.steps:
             nxt = upload_async((i + 1) % 2)
         torch.cuda.current_stream().wait_event(ev)
-        final = g.step(bufs[i % 2])
-        done[i % 2] = torch.cuda.Event()
+        s_ev = _event() if diag else None
+        tm_ = [] if diag else None
+        final = g.step(bufs[i % 2], tm_)
+        done[i % 2] = torch.cuda.Event(enable_timing=diag)
         done[i % 2].record()
+        if diag:
+            marks.append((ev, s_ev, done[i % 2], (time.perf_counter() - t0) * 1e3, tm_))
     torch.cuda.synchronize()
     e2e_pipe_ms = (time.perf_counter() - t0) * 1e3
+    if prof is not None:
+        import pstats
+        prof.disable()
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(22)
+    if diag:
+        for i, (u, s0, s1, host_ms, tm_) in enumerate(marks):
+            print(f"[e2e diag] scene {i}: upload done {origin.elapsed_time(u):7.3f}  step {origin.elapsed_time(s0):7.3f} -> {origin.elapsed_time(s1):7.3f}  host returned {host_ms:7.3f}"
+                  f"  stages {[round(tm_[j].elapsed_time(tm_[j + 1]), 3) for j in range(len(tm_) - 1)]} lift {g.lift_events[0].elapsed_time(g.lift_events[1]):.3f}",
+                  file=sys.stderr)
     d2h = sum(fn["ins"].numel() * fn["ins"].element_size() for fn in g.last_finals if isinstance(fn["ins"], torch.Tensor))
     # ---- IoU kernel alone (mask-IoU pairs/s of the aggregation-sized square call)
     from bff_b200 import ops
@@ -518,7 +549,7 @@ def run_gpu(args):
                 "how": "K consecutive scenes through the host API: pinned host inputs -> device -> step -> final masks on the "
                        "host; scene i+1's upload overlaps scene i's compute (copy stream); wall clock over the K steps",
                 "serial_ms_per_step": ms_e2e, "serial_value": pv / (ms_e2e * 1e-3),
-                "upload_engine": "SM copy kernel (bff_upload)" if use_sm_copy else "copy engine (cudaMemcpyAsync)",
+                "upload_engine": "SM copy kernel (bff_upload)" if use_sm_copy else f"copy engine (cudaMemcpyAsync{', %d MiB chunks' % (chunk >> 20) if chunk else ''})",
                 "numa_bound_cpus_rank0": (len(numa_cpus) if numa_cpus else None),
                 "upload_gbs_probe": {"copy_engine": round(g.host[big].numel() * g.host[big].element_size() / t_ce / 1e6, 1),
                                      "sm_kernel": round(g.host[big].numel() * g.host[big].element_size() / t_sm / 1e6, 1)}},
@@ -798,6 +829,7 @@ def main():
     ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the secondary frame-sharded measurement")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--cli-e2e", action="store_true", help="files-to-files run of both drop-in CLIs on an on-disk tree (configs[0]) and exit")
+    ap.add_argument("--upload", default="sm", help="pipelined e2e: how scene i+1's big buffers move while scene i runs: sm | ce | ce:<MiB>")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -366,7 +366,7 @@ def upload(dst: torch.Tensor, src_pinned: torch.Tensor, stream: Optional[torch.c
         raise ValueError("size mismatch")
     st = stream if stream is not None else torch.cuda.current_stream(dst.device)
     check(lib().bff_upload(ptr(dst), c_void_p(src_pinned.data_ptr()), nbytes, c_void_p(st.cuda_stream)), "bff_upload")
-    if nbytes >= 16:
+    if nbytes:
         _count()
     return dst
 

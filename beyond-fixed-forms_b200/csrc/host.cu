@@ -254,15 +254,24 @@ extern "C" int bff_mask_iou_host(bff_ctx *c, const uint32_t *a, int32_t n_a, con
 
 // ---------------------------------------------------------------------------------------------------
 // bff_upload: SM-driven host -> device copy (see include/bff.h). 32 CTAs x 512 threads x 4 x 16-byte loads keep
-// ~1 MB of reads in flight, enough to cover PCIe latency at full link bandwidth, while leaving the copy
-// engines free for the small staging copies of a pipeline that runs concurrently.
+// 1 MB of reads in flight, enough to cover PCIe latency at full link bandwidth on every box measured (50-51 GB/s; with
+// 16 CTAs x 2 loads one box dropped to 45), while leaving the copy engines free for the small staging copies of a
+// pipeline that runs concurrently (BFF_UPLOAD_BLOCKS / BFF_UPLOAD_UNROLL: scripts/upload_bw.py).
+// Nothing here touches a copy engine (the tail bytes included): a copy-engine transfer queued behind a long kernel in
+// the upload stream would sit at the head of the engine's queue and hold back every other stream's small copies.
 namespace bff {
-__global__ void __launch_bounds__(512) upload_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, long long n16) {
+template <int UNROLL>
+__global__ void __launch_bounds__(512) upload_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, long long n16, int tail) {
     const long long stride = (long long)gridDim.x * 512;
     long long i = (long long)blockIdx.x * 512 + threadIdx.x;
-    for (; i + 3 * stride < n16; i += 4 * stride) {
-        const uint4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
-        dst[i] = a; dst[i + stride] = b; dst[i + 2 * stride] = c; dst[i + 3 * stride] = d;
+    if (blockIdx.x == 0 && (int)threadIdx.x < tail)       // the last (bytes % 16) bytes: no copy-engine call at all
+        reinterpret_cast<unsigned char *>(dst + n16)[threadIdx.x] = reinterpret_cast<const unsigned char *>(src + n16)[threadIdx.x];
+    for (; i + (UNROLL - 1) * stride < n16; i += UNROLL * stride) {
+        uint4 v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) v[u] = src[i + u * stride];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) dst[i + u * stride] = v[u];
     }
     for (; i < n16; i += stride) dst[i] = src[i];
 }
@@ -282,11 +291,15 @@ extern "C" int bff_upload(void *dst, const void *src_host, int64_t bytes, void *
         return BFF_EINVAL;
     }
     const long long n16 = bytes / 16;
-    if (n16 > 0) {
-        upload_kernel<<<32, 512, 0, s>>>(reinterpret_cast<const uint4 *>(src_dev), reinterpret_cast<uint4 *>(dst), n16);
-        BFF_LAUNCH_CHECK("upload_kernel");
-    }
-    if (bytes & 15)
-        BFF_CUDA(cudaMemcpyAsync((char *)dst + n16 * 16, (const char *)src_host + n16 * 16, (size_t)(bytes & 15), cudaMemcpyHostToDevice, s));
+    const int tail = (int)(bytes & 15);
+    static const int max_blocks = [] { const char *e = getenv("BFF_UPLOAD_BLOCKS"); const int b = e ? atoi(e) : 32; return b > 0 ? b : 32; }();
+    static const int unroll = [] { const char *e = getenv("BFF_UPLOAD_UNROLL"); return e ? atoi(e) : 4; }();
+    const int blocks = (int)std::max<long long>(1, std::min<long long>(max_blocks, (n16 + 511) / 512));
+    const uint4 *sp = reinterpret_cast<const uint4 *>(src_dev);
+    uint4 *dp = reinterpret_cast<uint4 *>(dst);
+    if (unroll == 1) upload_kernel<1><<<blocks, 512, 0, s>>>(sp, dp, n16, tail);
+    else if (unroll == 2) upload_kernel<2><<<blocks, 512, 0, s>>>(sp, dp, n16, tail);
+    else upload_kernel<4><<<blocks, 512, 0, s>>>(sp, dp, n16, tail);
+    BFF_LAUNCH_CHECK("upload_kernel");
     return BFF_OK;
 }

@@ -304,7 +304,9 @@ BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *st
  * PCIe) instead of a copy engine. Used to prefetch the next scene's depth stack while the current scene is
  * processed: a 180 MB cudaMemcpyAsync would occupy the H2D copy engine and every small staging copy of the
  * running pipeline would queue behind it. `src_host` must be page-locked (cudaHostAlloc / cudaHostRegister /
- * torch pin_memory); dst and src 16-byte aligned. */
+ * torch pin_memory); dst and src 16-byte aligned, any size (the last bytes % 16 are moved by the same kernel: the call
+ * never touches a copy engine, so small buffers can follow a large one in the same stream without parking a
+ * copy-engine transfer behind a milliseconds-long kernel, where it would stall the other streams' copies). */
 BFF_API int bff_upload(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
 
 /* out[k] = rows[idx[k]] (device gather of packed rows; idx on the HOST). */

@@ -1,4 +1,5 @@
-"""Dev tool: bandwidth of bff_upload (SM-driven zero-copy H2D) vs cudaMemcpyAsync for a 184 MB pinned buffer."""
+"""Dev tool: bandwidth of bff_upload (SM-driven zero-copy H2D) vs cudaMemcpyAsync for a 184 MB pinned buffer,
+over the kernel's grid/unroll knobs (BFF_UPLOAD_BLOCKS / BFF_UPLOAD_UNROLL are read once per process: run per setting)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "beyond-fixed-forms_b200"))
@@ -14,17 +15,6 @@ def t(fn, n=8):
     for _ in range(n): fn()
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n
-ms = t(lambda: dst.copy_(src, non_blocking=True)); print(f"cudaMemcpyAsync: {ms:.3f} ms  {src.numel()/ms/1e6:.1f} GB/s")
-ms = t(lambda: ops.upload(dst, src)); print(f"bff_upload     : {ms:.3f} ms  {src.numel()/ms/1e6:.1f} GB/s")
-# both at once: the copy engine moves the head of the buffer while the SMs pull the tail over the same link
-sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
-for frac in (0.3, 0.4, 0.5, 0.6):
-    cut = (int(src.numel() * frac) >> 12) << 12
-    def both():
-        ev = torch.cuda.Event(); ev.record()
-        sa.wait_event(ev); sb.wait_event(ev)
-        with torch.cuda.stream(sa):
-            dst[:cut].copy_(src[:cut], non_blocking=True)
-        ops.upload(dst[cut:], src[cut:], sb)
-        torch.cuda.current_stream().wait_stream(sa); torch.cuda.current_stream().wait_stream(sb)
-    ms = t(both); print(f"copy engine {frac:.1f} + SM {1-frac:.1f}: {ms:.3f} ms  {src.numel()/ms/1e6:.1f} GB/s")
+tag = f"lib={os.path.basename(os.environ.get('BFF_LIB_PATH', 'libbff.so'))} blocks={os.environ.get('BFF_UPLOAD_BLOCKS', '-')} unroll={os.environ.get('BFF_UPLOAD_UNROLL', '-')}"
+ms = t(lambda: dst.copy_(src, non_blocking=True)); ce = src.numel() / ms / 1e6
+ms = t(lambda: ops.upload(dst, src)); print(f"{tag}: cudaMemcpyAsync {ce:.1f} GB/s, bff_upload {src.numel()/ms/1e6:.1f} GB/s", flush=True)

@@ -515,3 +515,21 @@ def test_few_column_intersections_equal_tile_path_and_oracle(cuda_dev, monkeypat
     nan = np.isnan(iou_o)
     assert nan.any() and np.array_equal(np.isnan(iou), nan)
     np.testing.assert_array_equal(iou[~nan].view(np.int32), iou_o[~nan].view(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nbytes", [1, 15, 16, 17, 4096 + 5, (3 << 20) + 7])
+def test_upload_copies_every_byte_including_the_tail(cuda_dev, nbytes):
+    """bff_upload (SM-driven pinned-host -> device copy, no copy engine even for the last bytes % 16)."""
+    from bff_b200 import ops
+    g = torch.Generator().manual_seed(nbytes)
+    src = torch.randint(0, 256, (nbytes,), dtype=torch.uint8, generator=g).pin_memory()
+    dst = torch.full((nbytes + 16,), 0xAB, dtype=torch.uint8, device=cuda_dev)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    ops.upload(dst[:nbytes], src, side)
+    side.synchronize()
+    assert torch.equal(dst[:nbytes].cpu(), src)
+    assert bool((dst[nbytes:] == 0xAB).all())          # nothing written past the end
+    with pytest.raises(ValueError):
+        ops.upload(dst[:nbytes], torch.zeros(nbytes, dtype=torch.uint8))     # pageable source is refused
