@@ -253,10 +253,12 @@ extern "C" int bff_mask_iou_host(bff_ctx *c, const uint32_t *a, int32_t n_a, con
 
 
 // ---------------------------------------------------------------------------------------------------
-// bff_upload: SM-driven host -> device copy (see include/bff.h). 32 CTAs x 512 threads x 4 x 16-byte loads keep
-// 1 MB of reads in flight, enough to cover PCIe latency at full link bandwidth on every box measured (50-51 GB/s; with
-// 16 CTAs x 2 loads one box dropped to 45), while leaving the copy engines free for the small staging copies of a
-// pipeline that runs concurrently (BFF_UPLOAD_BLOCKS / BFF_UPLOAD_UNROLL: scripts/upload_bw.py).
+// bff_upload: SM-driven host -> device copy (see include/bff.h). 8 CTAs x 512 threads x 4 x 16-byte loads keep 256 KB of
+// reads in flight: enough for 50-51 GB/s over PCIe on the boxes measured (32 KB already reaches 51 GB/s on the fastest,
+// 45-48 GB/s on the slowest), and no more than needed -- every read waiting in the GPU's outbound PCIe queue also delays
+// the small copies, semaphores and completions of the pipeline that runs concurrently (measured at c2: a step that takes
+// 1.4 ms alone takes 2.5 ms next to 8 x 4, 3.9 ms next to 16 x 2, 4.2 ms next to 32 x 4, and the scene loop becomes
+// step-bound instead of upload-bound). BFF_UPLOAD_BLOCKS / BFF_UPLOAD_UNROLL override (scripts/upload_bw.py).
 // Nothing here touches a copy engine (the tail bytes included): a copy-engine transfer queued behind a long kernel in
 // the upload stream would sit at the head of the engine's queue and hold back every other stream's small copies.
 namespace bff {
@@ -292,7 +294,7 @@ extern "C" int bff_upload(void *dst, const void *src_host, int64_t bytes, void *
     }
     const long long n16 = bytes / 16;
     const int tail = (int)(bytes & 15);
-    static const int max_blocks = [] { const char *e = getenv("BFF_UPLOAD_BLOCKS"); const int b = e ? atoi(e) : 32; return b > 0 ? b : 32; }();
+    static const int max_blocks = [] { const char *e = getenv("BFF_UPLOAD_BLOCKS"); const int b = e ? atoi(e) : 8; return b > 0 ? b : 8; }();
     static const int unroll = [] { const char *e = getenv("BFF_UPLOAD_UNROLL"); return e ? atoi(e) : 4; }();
     const int blocks = (int)std::max<long long>(1, std::min<long long>(max_blocks, (n16 + 511) / 512));
     const uint4 *sp = reinterpret_cast<const uint4 *>(src_dev);

@@ -1,15 +1,17 @@
 // Mask intersections on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM).
 //
 // inter[i][j] = popcount(A_i & B_j) is the (nA x N) . (N x nB) product of 0/1 matrices. The rows stay bit-packed
-// in HBM (N/8 bytes per row); each CTA expands the 128-bit slices it needs to uint8 0/1 values on the fly,
-// straight into shared memory in the canonical K-major "interleave" (no-swizzle) UMMA layout, and one thread
-// issues 128x128x32 integer MMAs on them while the other threads expand the next slice. The int32 sums are
+// in HBM (N/8 bytes per row); each CTA expands the 128-bit slices it needs to uint8 0/1 values on the fly --
+// the B rows into shared memory in the canonical K-major "interleave" (no-swizzle) UMMA layout, the A rows
+// straight into tensor memory (tcgen05.st; lane = row, 4 K-bytes per 32-bit column) -- and one thread issues
+// 128x128x32 integer MMAs ([d_tmem], [a_tmem], b_desc) while the other threads expand the next slice. The int32 sums are
 // exact (<= N < 2^31), so the result is bit-identical to the POPC kernel (north_star: "tensor cores only if an
 // int8 mask-product formulation measurably wins" -- it does, see profiles/).
 //
 // Layout of one operand sub-tile (128 rows x 32 K-bytes, 4 KB) as the descriptor states it:
 //   byte(r, k) at (r / 8) * SBO + (k / 16) * LBO + (r % 8) * 16 + (k % 16),   LBO = 128, SBO = 256
-// A stage holds 4 such sub-tiles per operand (128 K-bits); 3 stages form the producer/MMA ring.
+// A stage holds 4 such sub-tiles (128 K-bits) of B in shared memory and 32 TMEM columns of A; 4 stages form the
+// producer/MMA ring (BFF_UMMA_A_TMEM=0 builds the earlier form with both operands in shared memory, 3 stages).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -23,8 +25,23 @@ constexpr int kStageWords = 4;            // 32-bit words of every row per stage
 constexpr int kSubTileBytes = 128 * 32;   // one operand, one MMA
 constexpr int kOperandStageBytes = kStageWords * kSubTileBytes;   // 16 KB
 constexpr int kStageBytes = 2 * kOperandStageBytes;               // A + B = 32 KB
-constexpr int kStages = 3;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024;          // + alignment slack
+#ifndef BFF_UMMA_A_TMEM
+#define BFF_UMMA_A_TMEM 1
+#endif
+// A operand in tensor memory (tcgen05.mma [d], [a_tmem], b_desc): at M = N = 128 an int8 MMA reading BOTH operands from
+// shared memory consumes 8 KB per 64 clocks = the whole 128 B/clk of the SM's shared memory, leaving nothing for the
+// producers' stores (ncu: tensor pipe 32 % busy, shared-memory wavefronts the limiter). With A expanded straight into
+// TMEM by tcgen05.st only B crosses shared memory (64 B/clk read + 64 B/clk written).
+constexpr bool kATmem = BFF_UMMA_A_TMEM != 0;
+constexpr int kStages = kATmem ? 4 : 3;
+constexpr int kSmemStageBytes = kATmem ? kOperandStageBytes : kStageBytes;      // what one ring slot holds in shared memory
+constexpr int kSmemNeeded = kStages * kSmemStageBytes + 1024;                    // + alignment slack
+// TMEM columns: 128 accumulators (+ 4 slots x 32 columns of A bytes, 4 per column) -> 256 per CTA, two CTAs fill the SM's 512;
+// the shared-memory request is padded so that a third CTA (which could only spin in tcgen05.alloc) is never resident
+constexpr int kSmemBytes = kATmem ? (kSmemNeeded > 77 * 1024 ? kSmemNeeded : 77 * 1024) : kSmemNeeded;
+constexpr int kTmemCols = kATmem ? 256 : 128;
+constexpr int kATmemCol0 = 128;           // first column of the A ring
+constexpr int kAStageCols = kStageWords * 8;
 constexpr int kProducerWarps = 8;
 constexpr int kThreads = (kProducerWarps + 1) * 32;               // + the MMA-issuing warp
 
@@ -76,8 +93,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 }
 
 // grid: x = tile column (B), y = tile row (A), z = K slice. `inter` must be zeroed; partial sums are added.
-// Warps 0..7 (256 threads) are PRODUCERS: thread t expands row t of the stage (0..127 = A, 128..255 = B) from
-// packed bits to 0/1 bytes in shared memory, running up to kStages ahead. Warp 8 is the MMA ISSUER: one lane
+// Warps 0..7 (256 threads) are PRODUCERS: thread t expands row t of the stage (0..127 = A -> TMEM lanes,
+// 128..255 = B -> shared memory) from packed bits to 0/1 bytes, running up to kStages ahead. Warp 8 is the MMA ISSUER: one lane
 // waits for a full stage, issues its 4 MMAs and commits them to the stage's `empty` barrier.
 __global__ void __launch_bounds__(kThreads)
 intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *__restrict__ b, int n_b, long long words,
@@ -99,8 +116,8 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
         mbar_init(&done_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {                                    // TMEM: 128 columns x 128 lanes of int32 accumulators
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&tmem_base_slot)), "r"((uint32_t)kTileN) : "memory");
+    if (warp == 0) {                                    // TMEM: 128 columns x 128 lanes of int32 accumulators (+ the A ring)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&tmem_base_slot)), "r"((uint32_t)kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -128,7 +145,32 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
             for (int k = 0; k < kStageWords; ++k) nxt[k] = (row_ok && (w1 + k) < w_end) ? __ldg(src + w1 + k) : 0u;
             // the MMAs that read this buffer kStages stages ago must have completed
             if (s >= kStages) mbar_wait(&empty_bar[buf], (uint32_t)(((s / kStages) - 1) & 1));
-            unsigned char *dst = smem + buf * kStageBytes + op * kOperandStageBytes + row_off;
+            if (kATmem && op == 0) {
+                // row r of A = TMEM lane r (this warp owns lanes 32 warp .. 32 warp + 31); column c of the slot holds
+                // K bytes 4c .. 4c+3 of the stage, i.e. nibble c % 8 of word c / 8
+                uint32_t e[kAStageCols];
+#pragma unroll
+                for (int k = 0; k < kStageWords; ++k)
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) e[k * 8 + q] = nibble_to_bytes((wv[k] >> (4 * q)) & 15u);
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(kATmemCol0 + buf * kAStageCols);
+                static_assert(kAStageCols == 32, "tcgen05.st below writes 32 columns");
+                asm volatile(
+                    "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                    "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+                    "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+                    ::"r"(taddr), "r"(e[0]), "r"(e[1]), "r"(e[2]), "r"(e[3]), "r"(e[4]), "r"(e[5]), "r"(e[6]), "r"(e[7]),
+                      "r"(e[8]), "r"(e[9]), "r"(e[10]), "r"(e[11]), "r"(e[12]), "r"(e[13]), "r"(e[14]), "r"(e[15]),
+                      "r"(e[16]), "r"(e[17]), "r"(e[18]), "r"(e[19]), "r"(e[20]), "r"(e[21]), "r"(e[22]), "r"(e[23]),
+                      "r"(e[24]), "r"(e[25]), "r"(e[26]), "r"(e[27]), "r"(e[28]), "r"(e[29]), "r"(e[30]), "r"(e[31])
+                    : "memory");
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full_bar[buf]);
+                continue;
+            }
+            unsigned char *dst = smem + buf * kSmemStageBytes + (kATmem ? 0 : op * kOperandStageBytes) + row_off;
 #pragma unroll
             for (int k = 0; k < kStageWords; ++k) {          // word k = the K = 32 slice of MMA k
 #pragma unroll
@@ -154,18 +196,29 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
             const int buf = s % kStages;
             mbar_wait(&full_bar[buf], (uint32_t)((s / kStages) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t a_base = smem_addr(smem + buf * kStageBytes);
-            const uint32_t b_base = a_base + kOperandStageBytes;
+            const uint32_t a_base = smem_addr(smem + buf * kSmemStageBytes);
+            const uint32_t b_base = kATmem ? a_base : a_base + kOperandStageBytes;
 #pragma unroll
             for (int k = 0; k < kStageWords; ++k) {
-                const uint64_t da = make_desc(a_base + k * kSubTileBytes), db = make_desc(b_base + k * kSubTileBytes);
+                const uint64_t db = make_desc(b_base + k * kSubTileBytes);
                 const uint32_t accumulate = (s > 0 || k > 0) ? 1u : 0u;
-                asm volatile(
-                    "{\n\t.reg .pred p;\n\t"
-                    "setp.ne.b32 p, %4, 0;\n\t"
-                    "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-                    ::"r"(tmem_base), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
-                    : "memory");
+                if (kATmem) {
+                    const uint32_t a_tmem = tmem_base + (uint32_t)(kATmemCol0 + buf * kAStageCols + k * 8);
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\t"
+                        "setp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+                        ::"r"(tmem_base), "r"(a_tmem), "l"(db), "r"(idesc), "r"(accumulate)
+                        : "memory");
+                } else {
+                    const uint64_t da = make_desc(a_base + k * kSubTileBytes);
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\t"
+                        "setp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                        ::"r"(tmem_base), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+                        : "memory");
+                }
             }
             // arrives on the barrier when the MMAs issued so far have finished reading shared memory
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(&empty_bar[buf])) : "memory");
@@ -209,7 +262,7 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTileN) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols) : "memory");
 }
 
 // Enqueue the tensor-core intersection. Returns a cudaError_t-compatible int (0 = ok).
