@@ -162,6 +162,34 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync1");
 
+    // ---- point filter (:512-583), first half: the unique() over N values comes from the (masked, viewed) histogram.
+    // It depends on the maxima only, so it is enqueued BEFORE the host searches the components: the device builds the
+    // histogram and its distinct ratios while the host walks the graph, and the next synchronisation brings them along.
+    float thr = 0.0f;
+    float *h_vals = nullptr, *d_vals_keep = nullptr;
+    size_t first_vals = 0;
+    int mb = 0, vb = 0;
+    if (d->filter_mode != 2) {
+        mb = h_max[0] + 1;
+        vb = vc ? h_max[1] + 1 : 1;
+        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
+        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
+        // distinct ratios straight from the non-empty bins, on the device: only they travel to the host
+        const int64_t tsize = bff_vote_unique_table_size(mb, vb);
+        PIPE_TAKE(d_table, c->dev, uint32_t, (size_t)tsize);
+        PIPE_TAKE(d_vals, c->dev, float, (size_t)mb * vb + 1);
+        h_vals = c->pin.get<float>((size_t)mb * vb + 1);
+        if (!h_vals) return BFF_ENOMEM;
+        int32_t *d_cnt = reinterpret_cast<int32_t *>(d_vals + (size_t)mb * vb);       // the count rides behind the values
+        if ((rc = bff_vote_unique(d_hist, mb, vb, d->filter_mode, d_table, tsize, d_vals, d_cnt, s)) != BFF_OK) return rc;
+        // the number of distinct values is not known yet: a first slice that nearly always suffices, the rest on demand
+        first_vals = std::min<size_t>((size_t)mb * vb, 16384);
+        BFF_CUDA(cudaMemcpyAsync(h_vals, d_vals, first_vals * 4, cudaMemcpyDeviceToHost, s));
+        BFF_CUDA(cudaMemcpyAsync(h_vals + (size_t)mb * vb, d_cnt, 4, cudaMemcpyDeviceToHost, s));
+        d_vals_keep = d_vals;
+    }
+    tr.mark("enqueue_votes");
+
     // ---- connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric, so the
     // reference's reachability lists are the components, emitted by smallest member, members ascending).
     // A node without any edge (an empty row: IoU diagonal NaN) forms no group.
@@ -212,6 +240,7 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         if (root[r] == r && has_edge[r] && count[r] >= d->min_aggregated) group_of_root[r] = g++;
     *d->n_groups = g;
     if (d->filter_value) *d->filter_value = 0.0f;
+    if (g == 0 || g > d->cap_groups) BFF_CUDA(cudaStreamSynchronize(s));     // the vote copies still target this context's pinned arena
     if (g == 0) return BFF_OK;
     BFF_REQUIRE(g <= d->cap_groups, "bff_stage2_aggregate: %d groups exceed cap_groups %d", g, d->cap_groups);
     std::vector<int32_t> seg(g + 1, 0), idx;
@@ -247,35 +276,25 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     PIPE_TAKE(h_before, c->pin, int32_t, g);
     BFF_CUDA(cudaMemcpyAsync(h_before, d_before, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
 
-    // ---- point filter (:512-583): the unique() over N values comes from the (masked, viewed) histogram, which is
-    // enqueued behind the pair overlaps so that ONE synchronisation brings both to the host
     PIPE_TAKE(d_keep, c->dev, uint32_t, words);
-    float thr = 0.0f;
-    float *h_vals = nullptr, *d_vals_keep = nullptr;
-    size_t first_vals = 0;
-    int mb = 0, vb = 0;
-    if (d->filter_mode != 2) {
-        mb = h_max[0] + 1;
-        vb = vc ? h_max[1] + 1 : 1;
-        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
-        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
-        // distinct ratios straight from the non-empty bins, on the device: only they travel to the host
-        const int64_t tsize = bff_vote_unique_table_size(mb, vb);
-        PIPE_TAKE(d_table, c->dev, uint32_t, (size_t)tsize);
-        PIPE_TAKE(d_vals, c->dev, float, (size_t)mb * vb + 1);
-        h_vals = c->pin.get<float>((size_t)mb * vb + 1);
-        if (!h_vals) return BFF_ENOMEM;
-        int32_t *d_cnt = reinterpret_cast<int32_t *>(d_vals + (size_t)mb * vb);       // the count rides behind the values
-        if ((rc = bff_vote_unique(d_hist, mb, vb, d->filter_mode, d_table, tsize, d_vals, d_cnt, s)) != BFF_OK) return rc;
-        // the number of distinct values is not known yet: a first slice that nearly always suffices, the rest on demand
-        first_vals = std::min<size_t>((size_t)mb * vb, 16384);
-        BFF_CUDA(cudaMemcpyAsync(h_vals, d_vals, first_vals * 4, cudaMemcpyDeviceToHost, s));
-        BFF_CUDA(cudaMemcpyAsync(h_vals + (size_t)mb * vb, d_cnt, 4, cudaMemcpyDeviceToHost, s));
-        d_vals_keep = d_vals;
-    }
     tr.mark("enqueue2");
     BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps, 'before' and the histogram are on the host now
     tr.mark("sync2");
+    // ---- solve_overlapping's sequential schedule (:285-299): pairs i<j that overlap in the incoming rows; the mask
+    // merged from MORE members keeps the shared points, ties: i loses. Enqueued before the host picks the vote threshold.
+    std::vector<int32_t> prog;
+    for (int i = 0; i < g; ++i)
+        for (int j = i + 1; j < g; ++j)
+            if (h_ginter[(size_t)i * g + j] > 0) {
+                if (d->group_size[i] > d->group_size[j]) { prog.push_back(j); prog.push_back(i); }
+                else { prog.push_back(i); prog.push_back(j); }
+            }
+    tr.mark("schedule");
+    if (!prog.empty()) {
+        int32_t *d_prog = nullptr;
+        if ((rc = upload_i32(c, prog, &d_prog, s)) != BFF_OK) return rc;
+        if ((rc = bff_overlap_resolve(d->agg_rows, g, words, d_prog, (int32_t)(prog.size() / 2), s)) != BFF_OK) return rc;
+    }
     if (d->filter_mode == 2) {
         if ((rc = bff_point_keep(d->mc, nullptr, d->n_points, 2, 0.0f, d_keep, s)) != BFF_OK) return rc;
     } else {
@@ -298,21 +317,6 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     }
     if (d->filter_value) *d->filter_value = thr;
 
-    // ---- solve_overlapping's sequential schedule (:285-299): pairs i<j that overlap in the incoming rows;
-    // the mask merged from MORE members keeps the shared points, ties: i loses
-    std::vector<int32_t> prog;
-    for (int i = 0; i < g; ++i)
-        for (int j = i + 1; j < g; ++j)
-            if (h_ginter[(size_t)i * g + j] > 0) {
-                if (d->group_size[i] > d->group_size[j]) { prog.push_back(j); prog.push_back(i); }
-                else { prog.push_back(i); prog.push_back(j); }
-            }
-    tr.mark("schedule");
-    if (!prog.empty()) {
-        int32_t *d_prog = nullptr;
-        if ((rc = upload_i32(c, prog, &d_prog, s)) != BFF_OK) return rc;
-        if ((rc = bff_overlap_resolve(d->agg_rows, g, words, d_prog, (int32_t)(prog.size() / 2), s)) != BFF_OK) return rc;
-    }
     // ---- ins &= masked_points, row sums 'after' (:594-596)
     PIPE_TAKE(d_after, c->dev, int32_t, g);
     if ((rc = bff_rows_and_popcount(d->agg_rows, g, words, d_keep, d_after, s)) != BFF_OK) return rc;
