@@ -261,6 +261,31 @@ unpack_bits_kernel(const uint32_t *__restrict__ packed, long long n, long long w
     dense[(long long)row * n + i] = (uint8_t)((__ldg(packed + (long long)row * words + (i >> 5)) >> (i & 31)) & 1u);
 }
 
+// The (rows, n) byte matrix as ONE flat array: a thread writes 16 consecutive bytes with one store. A chunk inside one
+// row takes its 16 bits from at most two packed words; the few chunks that straddle a row end go byte by byte.
+__device__ __forceinline__ uint32_t spread4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+__global__ void __launch_bounds__(256)
+unpack_bits_wide_kernel(const uint32_t *__restrict__ packed, long long n, long long words, long long total, uint4 *__restrict__ dense16) {
+    const long long j0 = ((long long)blockIdx.x * 256 + threadIdx.x) * 16;
+    if (j0 >= total) return;
+    const long long row = j0 / n, i0 = j0 - row * n;
+    if (i0 + 16 <= n && j0 + 16 <= total) {
+        const uint32_t *src = packed + row * words + (i0 >> 5);
+        const int sh = (int)(i0 & 31);
+        const uint32_t lo = __ldg(src);
+        const uint32_t hi = sh > 16 ? __ldg(src + 1) : 0u;      // sh > 16: bits sh..sh+15 reach into the next word (i0 + 16 <= n keeps it inside the row)
+        const uint32_t v = __funnelshift_r(lo, hi, sh) & 0xffffu;
+        dense16[j0 >> 4] = make_uint4(spread4(v & 15u), spread4((v >> 4) & 15u), spread4((v >> 8) & 15u), spread4(v >> 12));
+        return;
+    }
+    uint8_t *out = reinterpret_cast<uint8_t *>(dense16);
+    for (long long j = j0; j < j0 + 16 && j < total; ++j) {
+        const long long r = j / n, i = j - r * n;
+        out[j] = (uint8_t)((__ldg(packed + r * words + (i >> 5)) >> (i & 31)) & 1u);
+    }
+}
+
 // ------------------------------------------------------------------ RLE -> bits
 // One warp per run [lo, hi) of row r: lanes stride over the touched words and OR their part in.
 __global__ void __launch_bounds__(256)
@@ -431,8 +456,13 @@ extern "C" int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n
     BFF_REQUIRE(dense && packed, "bff_unpack_bits: null pointer");
     BFF_REQUIRE(n_rows <= 65535, "bff_unpack_bits: too many rows");
     const long long words = ceil_div64(n, 32);
-    dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_rows);
-    unpack_bits_kernel<<<grid, 256, 0, stream>>>(packed, n, words, dense);
+    const long long total = (long long)n_rows * n;
+    if ((reinterpret_cast<uintptr_t>(dense) & 15) == 0 && n >= 16 && ceil_div64(total, 16 * 256) <= 0x7fffffffLL) {
+        unpack_bits_wide_kernel<<<(unsigned)ceil_div64(total, 16 * 256), 256, 0, stream>>>(packed, n, words, total, reinterpret_cast<uint4 *>(dense));
+    } else {
+        dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_rows);
+        unpack_bits_kernel<<<grid, 256, 0, stream>>>(packed, n, words, dense);
+    }
     BFF_LAUNCH_CHECK("unpack_bits_kernel");
     return BFF_OK;
 }

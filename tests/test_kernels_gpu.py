@@ -533,3 +533,25 @@ def test_upload_copies_every_byte_including_the_tail(cuda_dev, nbytes):
     assert bool((dst[nbytes:] == 0xAB).all())          # nothing written past the end
     with pytest.raises(ValueError):
         ops.upload(dst[:nbytes], torch.zeros(nbytes, dtype=torch.uint8))     # pageable source is refused
+
+
+@pytest.mark.gpu
+def test_unpack_bits_wide_store_path_on_ragged_rows(cuda_dev):
+    """bff_unpack_bits writes 16 bytes per thread over the flattened (rows, n) matrix: chunks that straddle a row end,
+    shifts into the next packed word, n < 16 (byte kernel) and an output that is not 16-byte aligned."""
+    from bff_b200 import ops
+    rng = np.random.default_rng(11)
+    for rows, n in ((1, 16), (3, 17), (7, 47), (4, 48), (5, 1023), (9, 250000), (2, 15), (6, 33), (3, 100003)):
+        d = rng.random((rows, n)) < 0.5
+        p = torch.from_numpy(pack_rows(d).view(np.int32)).to(cuda_dev)
+        np.testing.assert_array_equal(ops.unpack_bits(p, n).cpu().numpy(), d, err_msg=f"{rows}x{n}")
+    # raw entry point with a misaligned destination
+    from bff_b200 import _cabi
+    rows, n = 3, 77
+    d = rng.random((rows, n)) < 0.5
+    p = torch.from_numpy(pack_rows(d).view(np.int32)).to(cuda_dev)
+    buf = torch.full((rows * n + 32,), 7, dtype=torch.uint8, device=cuda_dev)
+    out = buf[3:3 + rows * n]
+    _cabi.check(_cabi.lib().bff_unpack_bits(_cabi.ptr(p), rows, n, _cabi.ptr(out), _cabi.current_stream()), "bff_unpack_bits")
+    np.testing.assert_array_equal(out.cpu().numpy().reshape(rows, n), d.astype(np.uint8))
+    assert bool((buf[:3] == 7).all()) and bool((buf[3 + rows * n:] == 7).all())
