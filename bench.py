@@ -201,13 +201,16 @@ class GpuScene:
         ev()
         s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
 
-        def aggregate(qi):
+        def job(qi):
             if sharded:
                 conf_list, labels, idx = self.all_conf[qi], self.all_labels[qi], self.all_index_dev[qi]
             else:
                 conf_list, labels = self.conf_q[qi], self.labels_q[qi]
                 idx = self.row_index_dev[qi] if self.row_index_dev is not None else None
-            rows_q = rows if idx is None else rows[idx]
+            return (rows if idx is None else rows[idx], conf_list, labels, mc[qi], vc, self.n)
+
+        def aggregate(qi):
+            rows_q, conf_list, labels = job(qi)[:3]
             pairs = None
             if sharded and self.nq == 1 and rows_q.shape[0] >= dist_mod.PAIRS_MIN_ROWS:
                 pairs = dist_mod.sharded_pairs(self.dist, rows_q)    # all-pairs IoU: one row block per rank + all-gather
@@ -233,9 +236,24 @@ class GpuScene:
             ev()
             ev()
         else:
-            per_query = [aggregate(qi) for qi in self.my_queries]
+            if len(self.my_queries) > 1 and os.environ.get("BFF_AGG_BATCH", "1") != "0":
+                # all queries advance phase by phase inside ONE bff_stage2_aggregate_batch call (shared synchronisations)
+                per_query = [r for r, _ in stage2.aggregate_and_filter_batch([job(qi) for qi in self.my_queries], cfg, keep_rows=True,
+                                                                             to_host=to_host)]
+            else:
+                per_query = [aggregate(qi) for qi in self.my_queries]
             ev()
-            finals = [refine_query(qi, r2) for qi, r2 in zip(self.my_queries, per_query)]
+            if len(self.my_queries) > 1 and os.environ.get("BFF_AGG_BATCH", "1") != "0":
+                # pass 1 of all queries in ONE bff_refine_match_batch call; every query ORs into its own copy of the stage-1 rows
+                names = [self.names[qi] for qi in self.my_queries]
+                p1s = refine.pass1_scene_batch(inp["stage1"], per_query, names, cfg["stage1_iou_thres"], fake_similarity, self.dev,
+                                               [s1.clone() for _ in names])
+                finals = []
+                for name, p1 in zip(names, p1s):
+                    thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
+                    finals.append(refine.pass2_scene(p1, name, cfg["refiment_iou_thres"], thr, to_host=to_host))
+            else:
+                finals = [refine_query(qi, r2) for qi, r2 in zip(self.my_queries, per_query)]
             ev()
         self.last_stage2 = per_query[0] if per_query else None
         self.last_finals = finals

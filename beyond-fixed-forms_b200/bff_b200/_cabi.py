@@ -86,7 +86,9 @@ SYMBOLS = {
     "bff_unpack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_rle_to_bits": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_stage2_aggregate": (c_int, [c_void_p, POINTER(Stage2Desc), c_void_p]),
+    "bff_stage2_aggregate_batch": (c_int, [c_void_p, POINTER(Stage2Desc), c_int32, c_void_p]),
     "bff_refine_match": (c_int, [c_void_p, POINTER(RefineDesc), c_void_p]),
+    "bff_refine_match_batch": (c_int, [c_void_p, POINTER(RefineDesc), c_int32, c_void_p]),
     "bff_upload": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "bff_rows_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),

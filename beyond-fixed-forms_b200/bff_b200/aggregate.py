@@ -14,7 +14,7 @@ from typing import List, Optional, Sequence, Tuple
 import numpy as np
 import torch
 
-from . import ops
+from . import _log, ops
 from ._log import log
 
 
@@ -153,6 +153,68 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
 
 
 # ----------------------------------------------------------------------------- fused C++ pipeline
+class _FusedJob:
+    """Inputs, descriptor and host output buffers of one bff_stage2_aggregate job (kept alive until the call returns)."""
+
+    def __init__(self, rows, conf, labels, mc, vc, n_points, cfg, pairs=None):
+        from . import _cabi
+        n = rows.shape[0]
+        self.labels, self.n = labels, n
+        if n and isinstance(labels, (list, tuple)) and labels.count(labels[0]) == n:   # one phrase for every mask (the usual case: labels = [query] * M)
+            label_id = np.zeros(n, dtype=np.int32)
+        else:
+            ids: dict = {}
+            label_id = np.asarray([ids.setdefault(l, len(ids)) for l in labels], dtype=np.int32)
+        conf32 = np.ascontiguousarray(conf.numpy(), dtype=np.float32)
+        if cfg["if_occurance_threshold"]:
+            mode, frac = 1, float(cfg["occurance_threshold"])
+        elif cfg["if_detected_ratio_threshold"]:
+            mode, frac = 0, float(cfg["detected_ratio_threshold"])
+        else:
+            mode, frac = 2, 0.0
+        self.mode = mode
+        cap = n // max(int(cfg["min_aggragated_masks"]), 1) + 1
+        self.agg = torch.empty((cap, rows.shape[1]), dtype=torch.int32, device=rows.device)
+        self.n_groups = np.zeros(1, np.int32)
+        self.first, self.size = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+        self.gconf = np.zeros(cap, np.float32)
+        self.before, self.after = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+        self.members = np.zeros(n, np.int32)
+        self.fval = np.zeros(1, np.float32)
+        mc = mc.reshape(-1)
+        self.keep = (rows, conf32, label_id, mc, vc)         # referenced by raw pointers below
+        d = self.desc = _cabi.Stage2Desc()
+        d.rows, d.n_rows, d.n_points = _cabi.ptr(rows), n, int(n_points)
+        d.conf, d.label_id, d.mc, d.vc = _cabi.ptr(conf32), _cabi.ptr(label_id), _cabi.ptr(mc), _cabi.ptr(vc if mode == 0 else None)
+        d.iou_thres = float(np.float32(cfg["iou_thres"]))
+        d.min_aggregated, d.filter_mode, d.filter_fraction = int(cfg["min_aggragated_masks"]), mode, frac
+        d.agg_rows, d.cap_groups = _cabi.ptr(self.agg), cap
+        d.n_groups, d.group_first, d.group_size, d.group_conf = (_cabi.ptr(self.n_groups), _cabi.ptr(self.first), _cabi.ptr(self.size),
+                                                                 _cabi.ptr(self.gconf))
+        d.before, d.after, d.members, d.filter_value = _cabi.ptr(self.before), _cabi.ptr(self.after), _cabi.ptr(self.members), _cabi.ptr(self.fval)
+        if pairs is not None:       # (inter (n,n) int32, pop (n,) int32) CUDA: the all-pairs step was done elsewhere (dist.sharded_pairs)
+            inter_pre, pop_pre = pairs
+            if tuple(inter_pre.shape) != (n, n) or tuple(pop_pre.shape) != (n,) or inter_pre.dtype != torch.int32 or pop_pre.dtype != torch.int32:
+                raise ValueError("pairs must be ((n,n) int32, (n,) int32)")
+            self.pairs = (inter_pre.contiguous(), pop_pre.contiguous())
+            d.inter_pre, d.pop_pre = _cabi.ptr(self.pairs[0]), _cabi.ptr(self.pairs[1])
+
+    def result(self):
+        from . import _cabi
+        g = int(self.n_groups[0])
+        _cabi.launch_count += 5 + (12 if g else 0)      # kernels inside the call (popcount x2, intersect, adjacency, ...)
+        if g == 0:
+            log("masks_to_be_merged", [])
+            return None
+        off = np.concatenate([[0], np.cumsum(self.size[:g])])
+        groups = [self.members[off[k]:off[k + 1]].tolist() for k in range(g)]
+        log("masks_to_be_merged", groups)
+        if self.mode != 2 and _log.VERBOSE:
+            log("detected_ratio_thres_value" if self.mode == 0 else "occurance_thres_value", torch.tensor(self.fval[0]))
+        return (self.agg[:g], torch.from_numpy(self.gconf[:g].copy()), [self.labels[int(i)] for i in self.first[:g]], groups,
+                torch.from_numpy(self.before[:g].astype(np.int64)), torch.from_numpy(self.after[:g].astype(np.int64)))
+
+
 def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], mc: torch.Tensor,
                            vc: Optional[torch.Tensor], n_points: int, cfg, pairs=None):
     """aggregate_rows + keep_points + the overlap/AND/popcount half of filter_and_select in ONE call
@@ -160,55 +222,24 @@ def aggregate_filter_fused(rows: torch.Tensor, conf: torch.Tensor, labels: Seque
     kernel launches. Returns None when nothing aggregates, else
     (agg_rows CUDA (G,Wd), conf_agg CPU (G,), labels_agg, groups, before (G,) int64, after (G,) int64)."""
     from . import _cabi
-    n = rows.shape[0]
-    if n and isinstance(labels, (list, tuple)) and labels.count(labels[0]) == n:   # one phrase for every mask (the usual case: labels = [query] * M)
-        label_id = np.zeros(n, dtype=np.int32)
-    else:
-        ids: dict = {}
-        label_id = np.asarray([ids.setdefault(l, len(ids)) for l in labels], dtype=np.int32)
-    conf32 = np.ascontiguousarray(conf.numpy(), dtype=np.float32)
-    if cfg["if_occurance_threshold"]:
-        mode, frac = 1, float(cfg["occurance_threshold"])
-    elif cfg["if_detected_ratio_threshold"]:
-        mode, frac = 0, float(cfg["detected_ratio_threshold"])
-    else:
-        mode, frac = 2, 0.0
-    cap = n // max(int(cfg["min_aggragated_masks"]), 1) + 1
-    agg = torch.empty((cap, rows.shape[1]), dtype=torch.int32, device=rows.device)
-    n_groups = np.zeros(1, np.int32)
-    first, size = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
-    gconf = np.zeros(cap, np.float32)
-    before, after = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
-    members = np.zeros(n, np.int32)
-    fval = np.zeros(1, np.float32)
-    mc = mc.reshape(-1)
-    d = _cabi.Stage2Desc()
-    d.rows, d.n_rows, d.n_points = _cabi.ptr(rows), n, int(n_points)
-    d.conf, d.label_id, d.mc, d.vc = _cabi.ptr(conf32), _cabi.ptr(label_id), _cabi.ptr(mc), _cabi.ptr(vc if mode == 0 else None)
-    d.iou_thres = float(np.float32(cfg["iou_thres"]))
-    d.min_aggregated, d.filter_mode, d.filter_fraction = int(cfg["min_aggragated_masks"]), mode, frac
-    d.agg_rows, d.cap_groups = _cabi.ptr(agg), cap
-    d.n_groups, d.group_first, d.group_size, d.group_conf = _cabi.ptr(n_groups), _cabi.ptr(first), _cabi.ptr(size), _cabi.ptr(gconf)
-    d.before, d.after, d.members, d.filter_value = _cabi.ptr(before), _cabi.ptr(after), _cabi.ptr(members), _cabi.ptr(fval)
-    if pairs is not None:       # (inter (n,n) int32, pop (n,) int32) CUDA: the all-pairs step was done elsewhere (dist.sharded_pairs)
-        inter_pre, pop_pre = pairs
-        if tuple(inter_pre.shape) != (n, n) or tuple(pop_pre.shape) != (n,) or inter_pre.dtype != torch.int32 or pop_pre.dtype != torch.int32:
-            raise ValueError("pairs must be ((n,n) int32, (n,) int32)")
-        inter_pre, pop_pre = inter_pre.contiguous(), pop_pre.contiguous()
-        d.inter_pre, d.pop_pre = _cabi.ptr(inter_pre), _cabi.ptr(pop_pre)
-    _cabi.check(_cabi.lib().bff_stage2_aggregate(_cabi.ctx(rows.device.index or 0), d, _cabi.current_stream()), "bff_stage2_aggregate")
-    g = int(n_groups[0])
-    _cabi.launch_count += 5 + (12 if g else 0)      # kernels inside the call (popcount x2, intersect, adjacency, ...)
-    if g == 0:
-        log("masks_to_be_merged", [])
-        return None
-    off = np.concatenate([[0], np.cumsum(size[:g])])
-    groups = [members[off[k]:off[k + 1]].tolist() for k in range(g)]
-    log("masks_to_be_merged", groups)
-    if mode != 2:
-        log("detected_ratio_thres_value" if mode == 0 else "occurance_thres_value", torch.tensor(fval[0]))
-    return (agg[:g], torch.from_numpy(gconf[:g].copy()), [labels[int(i)] for i in first[:g]], groups,
-            torch.from_numpy(before[:g].astype(np.int64)), torch.from_numpy(after[:g].astype(np.int64)))
+    job = _FusedJob(rows, conf, labels, mc, vc, n_points, cfg, pairs)
+    _cabi.check(_cabi.lib().bff_stage2_aggregate(_cabi.ctx(rows.device.index or 0), job.desc, _cabi.current_stream()), "bff_stage2_aggregate")
+    return job.result()
+
+
+def aggregate_filter_fused_batch(jobs, cfg):
+    """aggregate_filter_fused for several queries of one scene in ONE call (bff_stage2_aggregate_batch): the phases of all
+    jobs share their stream synchronisations. jobs: [(rows, conf, labels, mc, vc, n_points), ...] on one device.
+    Returns one aggregate_filter_fused result per job (log lines come out job by job, in order)."""
+    from . import _cabi
+    if not jobs:
+        return []
+    prepared = [_FusedJob(*j, cfg) for j in jobs]
+    descs = (_cabi.Stage2Desc * len(prepared))(*[p.desc for p in prepared])       # copies the structs; the buffers stay owned by `prepared`
+    dev = jobs[0][0].device
+    _cabi.check(_cabi.lib().bff_stage2_aggregate_batch(_cabi.ctx(dev.index or 0), descs, len(prepared), _cabi.current_stream()),
+                "bff_stage2_aggregate_batch")
+    return [p.result() for p in prepared]
 
 
 def select_rows(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[str], before64: torch.Tensor,

@@ -103,36 +103,78 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
             "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
 
 
+class _RefineJob:
+    """Descriptor and host output buffers of one bff_refine_match job."""
+
+    def __init__(self, s1, s2, s2_conf, n_points, stage1_iou_thres):
+        from . import _cabi
+        n1, n2 = s1.shape[0], s2.shape[0]
+        self.s1, self.s2, self.n_points = s1, s2, n_points
+        self.conf32 = np.ascontiguousarray(s2_conf.numpy(), dtype=np.float32)
+        self.s2_out = torch.empty_like(s2)
+        self.n2_out = np.zeros(1, np.int32)
+        self.conf_out, self.match_iou = np.zeros(n2, np.float32), np.zeros(n2, np.float32)
+        self.match, self.best_log = np.zeros(n2, np.int32), np.zeros(n2, np.int32)
+        d = self.desc = _cabi.RefineDesc()
+        d.s1_rows, d.n1, d.s2_rows, d.n2, d.n_points = _cabi.ptr(s1), n1, _cabi.ptr(s2), n2, int(n_points)
+        d.s2_conf, d.stage1_iou_thres = _cabi.ptr(self.conf32), float(np.float32(stage1_iou_thres))
+        d.s2_out, d.n2_out, d.s2_conf_out = _cabi.ptr(self.s2_out), _cabi.ptr(self.n2_out), _cabi.ptr(self.conf_out)
+        d.match, d.match_iou, d.best_match_log = _cabi.ptr(self.match), _cabi.ptr(self.match_iou), _cabi.ptr(self.best_log)
+
+    def result(self, labels, query, q_, sim_fn, device) -> dict:
+        from . import _cabi
+        _cabi.launch_count += 14
+        s1 = self.s1
+        m = int(self.n2_out[0])
+        mm = self.match[:m]
+        if _log.VERBOSE:                     # the reference prints a list of 0-d tensors; do not build them for nobody
+            log("DEBUG best_match_after_iou_check", [torch.tensor(int(b)) for b in self.best_log])
+        matched = set(int(k) for k in mm)
+        other = [i for i, l in enumerate(labels) if l == q_ and i not in matched]      # :293
+        matched_labels = [labels[int(k)] for k in mm]
+        sims = [float(sim_fn(query, l)) for l in matched_labels]                       # :297-302
+        ious = torch.from_numpy(self.match_iou[:m].copy())
+        log("iou for matched labels", ious)
+        log("Matched labels:", matched_labels)
+        log("Clip similarities:", sims)
+        mm_dev = torch.from_numpy(mm.astype(np.int64)).to(device)
+        return {"ious": ious, "sims": sims, "m1": s1[mm_dev], "m2": self.s2_out[:m], "conf2": torch.from_numpy(self.conf_out[:m].copy()),
+                "n_points": self.n_points, "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+
+
 def _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:
     """The matching part of pass 1 (refinement.py:208-290) in one call: bff_refine_match."""
     from . import _cabi
-    n1, n2 = s1.shape[0], s2.shape[0]
-    conf32 = np.ascontiguousarray(s2_conf.numpy(), dtype=np.float32)
-    s2_out = torch.empty_like(s2)
-    n2_out = np.zeros(1, np.int32)
-    conf_out, match_iou = np.zeros(n2, np.float32), np.zeros(n2, np.float32)
-    match, best_log = np.zeros(n2, np.int32), np.zeros(n2, np.int32)
-    d = _cabi.RefineDesc()
-    d.s1_rows, d.n1, d.s2_rows, d.n2, d.n_points = _cabi.ptr(s1), n1, _cabi.ptr(s2), n2, int(n_points)
-    d.s2_conf, d.stage1_iou_thres = _cabi.ptr(conf32), float(np.float32(stage1_iou_thres))
-    d.s2_out, d.n2_out, d.s2_conf_out = _cabi.ptr(s2_out), _cabi.ptr(n2_out), _cabi.ptr(conf_out)
-    d.match, d.match_iou, d.best_match_log = _cabi.ptr(match), _cabi.ptr(match_iou), _cabi.ptr(best_log)
-    _cabi.check(_cabi.lib().bff_refine_match(_cabi.ctx(s1.device.index or 0), d, _cabi.current_stream()), "bff_refine_match")
-    _cabi.launch_count += 14
-    m = int(n2_out[0])
-    mm = match[:m]
-    log("DEBUG best_match_after_iou_check", [torch.tensor(int(b)) for b in best_log])
-    matched = set(int(k) for k in mm)
-    other = [i for i, l in enumerate(labels) if l == q_ and i not in matched]      # :293
-    matched_labels = [labels[int(k)] for k in mm]
-    sims = [float(sim_fn(query, l)) for l in matched_labels]                       # :297-302
-    ious = torch.from_numpy(match_iou[:m].copy())
-    log("iou for matched labels", ious)
-    log("Matched labels:", matched_labels)
-    log("Clip similarities:", sims)
-    mm_dev = torch.from_numpy(mm.astype(np.int64)).to(device)
-    return {"ious": ious, "sims": sims, "m1": s1[mm_dev], "m2": s2_out[:m], "conf2": torch.from_numpy(conf_out[:m].copy()),
-            "n_points": n_points, "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+    job = _RefineJob(s1, s2, s2_conf, n_points, stage1_iou_thres)
+    _cabi.check(_cabi.lib().bff_refine_match(_cabi.ctx(s1.device.index or 0), job.desc, _cabi.current_stream()), "bff_refine_match")
+    return job.result(labels, query, q_, sim_fn, device)
+
+
+def pass1_scene_batch(stage1: dict, stage2_list: Sequence[dict], queries: Sequence[str], stage1_iou_thres: float,
+                      sim_fn: Callable[[str, str], float], device, s1_rows_list: Sequence[torch.Tensor]) -> list:
+    """pass1_scene for several queries of ONE scene: the fused jobs go through one bff_refine_match_batch call and share
+    its synchronisations. `s1_rows_list[k]` is query k's OWN copy of the decoded stage-1 rows (pass 1 ORs into them,
+    refinement.py:248; every reference process starts from the file). Returns one pass1_scene dict per query."""
+    from . import _cabi
+    n_points = int(stage1["ins"][0]["length"]) if len(stage1["ins"]) else 0
+    labels = [STAGE1_CLASS_NAMES[i] for i in torch.as_tensor(stage1["final_class"]).tolist()]
+    out = [None] * len(queries)
+    at, jobs = [], []
+    for k, (stage2, query) in enumerate(zip(stage2_list, queries)):
+        fused = FUSED and len(stage2["conf"]) and isinstance(stage2["conf"], torch.Tensor) and stage2["conf"].dtype == torch.float32
+        if not fused:
+            out[k] = pass1_scene(stage1, stage2, query, stage1_iou_thres, sim_fn, device, s1_rows=s1_rows_list[k])
+            continue
+        s2 = stage2["rows"] if "rows" in stage2 else ops.pack_bits(stage2["ins"].to(device))
+        at.append(k)
+        jobs.append(_RefineJob(s1_rows_list[k], s2, stage2["conf"], n_points, stage1_iou_thres))
+    if jobs:
+        descs = (_cabi.RefineDesc * len(jobs))(*[j.desc for j in jobs])
+        _cabi.check(_cabi.lib().bff_refine_match_batch(_cabi.ctx(jobs[0].s1.device.index or 0), descs, len(jobs), _cabi.current_stream()),
+                    "bff_refine_match_batch")
+        for k, j in zip(at, jobs):
+            out[k] = j.result(labels, queries[k], queries[k].replace(" ", "_"), sim_fn, device)
+    return out
 
 
 def similarity_threshold(all_sims: Sequence[Sequence[float]], percentile: float) -> float:

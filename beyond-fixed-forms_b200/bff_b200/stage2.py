@@ -24,29 +24,36 @@ def needs_viewed_counts(cfg) -> bool:
     return (not cfg_get(cfg, "if_occurance_threshold")) and bool(cfg_get(cfg, "if_detected_ratio_threshold"))
 
 
+_CFG_KEYS = ("iou_thres", "min_aggragated_masks", "if_occurance_threshold", "occurance_threshold",
+             "if_detected_ratio_threshold", "detected_ratio_threshold", "remove_filtered_masks", "remove_small_masks")
+
+
+def _finish_fused(fused, n_points: int, c, keep_rows: bool, to_host: bool):
+    """Row filter + saved dict for one bff_stage2_aggregate result (projection_2d_to_3d.py:592-634)."""
+    if fused is None:
+        log("No 3d masks detected after aggregation")
+        return scene_io.empty_stage2(), False
+    agg, conf_agg, labels_agg, groups, before64, after64 = fused
+    log("before filtering", torch.Size([agg.shape[0], n_points]))
+    result, out_rows = aggregate.select_rows(agg, conf_agg, labels_agg, before64, after64, n_points, c, to_host)
+    if keep_rows:
+        result["rows"] = out_rows        # packed CUDA rows for an in-process refinement (never saved)
+    return result, True
+
+
 def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor, vc: Optional[torch.Tensor],
                          n_points: int, cfg, keep_rows: bool = False, to_host: bool = True, pairs=None):
     """Everything after the frame loop (projection_2d_to_3d.py:463-634) for one query.
     Returns (dict to save, reached_filter) -- the reference only writes its scene checkpoint when
     the filter stage is reached (:580-581)."""
-    c = {k: cfg_get(cfg, k) for k in ("iou_thres", "min_aggragated_masks", "if_occurance_threshold", "occurance_threshold",
-                                      "if_detected_ratio_threshold", "detected_ratio_threshold", "remove_filtered_masks",
-                                      "remove_small_masks")}
+    c = {k: cfg_get(cfg, k) for k in _CFG_KEYS}
     if len(conf_list) == 0:
         log("No 3d masks detected in backprojection!")
         return scene_io.empty_stage2(), False
     conf = conf_list if isinstance(conf_list, torch.Tensor) else torch.tensor(conf_list)    # :484-486
     if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
         fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c, pairs=pairs)
-        if fused is None:
-            log("No 3d masks detected after aggregation")
-            return scene_io.empty_stage2(), False
-        agg, conf_agg, labels_agg, groups, before64, after64 = fused
-        log("before filtering", torch.Size([agg.shape[0], n_points]))
-        result, out_rows = aggregate.select_rows(agg, conf_agg, labels_agg, before64, after64, n_points, c, to_host)
-        if keep_rows:
-            result["rows"] = out_rows        # packed CUDA rows for an in-process refinement (never saved)
-        return result, True
+        return _finish_fused(fused, n_points, c, keep_rows, to_host)
     agg, conf_agg, labels_agg, groups = aggregate.aggregate_rows(rows, conf, labels, c["iou_thres"], c["min_aggragated_masks"])
     if agg is None:
         log("No 3d masks detected after aggregation")
@@ -57,6 +64,26 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
     if keep_rows:
         result["rows"] = out_rows
     return result, True
+
+
+def aggregate_and_filter_batch(jobs, cfg, keep_rows: bool = False, to_host: bool = True):
+    """aggregate_and_filter for several queries of one scene: jobs = [(rows, conf_list, labels, mc, vc, n_points), ...].
+    The fused jobs go through ONE bff_stage2_aggregate_batch call (shared synchronisations); a job the fused path does
+    not take (nothing lifted, non-float32 confidences, min_aggragated_masks < 1) is handled on its own.
+    Returns [(dict to save, reached_filter), ...] in job order, equal to one aggregate_and_filter call per job."""
+    c = {k: cfg_get(cfg, k) for k in _CFG_KEYS}
+    out = [None] * len(jobs)
+    fused_at, fused_jobs = [], []
+    for k, (rows, conf_list, labels, mc, vc, n_points) in enumerate(jobs):
+        conf = conf_list if isinstance(conf_list, torch.Tensor) else (torch.tensor(conf_list) if len(conf_list) else None)
+        if conf is not None and len(conf_list) and FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
+            fused_at.append(k)
+            fused_jobs.append((rows, conf, labels, mc, vc, n_points))
+        else:
+            out[k] = aggregate_and_filter(rows, conf_list, labels, mc, vc, n_points, cfg, keep_rows, to_host)
+    for k, fused in zip(fused_at, aggregate.aggregate_filter_fused_batch(fused_jobs, c)):
+        out[k] = _finish_fused(fused, jobs[k][5], c, keep_rows, to_host)
+    return out
 
 
 def load_scene(cfg, cls: str, scene_id: str, device, with_frames: bool = True) -> dict:
@@ -142,13 +169,16 @@ def process_scene_queries(cfg, classes, scene_id: str, device):
     frames = scene_io.load_frames(scene_2d_dir, scene_id, frame_ids, viewed, width, height, device)
     lifted = lift_mod.lift(scene_io.cloud_for_device(xyz, device), intr, frames, per_frame, queries, height, width,
                            want_viewed and any_masks)
-    def one(qi):
+    def job(qi):
         conf_list, labels = queries[qi].flat_conf_and_labels()
-        return aggregate_and_filter(lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts,
-                                    xyz.shape[0], cfg)
-    # the per-query chains are independent: several at once on their own streams (pool.py), same results
-    from .pool import get_pool
-    results = get_pool(device, QUERY_WORKERS).map(one, range(len(queries)))
+        return (lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts, xyz.shape[0])
+    if QUERY_WORKERS > 1:
+        # the per-query chains are independent: several at once on their own streams (pool.py), same results
+        from .pool import get_pool
+        results = get_pool(device, QUERY_WORKERS).map(lambda qi: aggregate_and_filter(*job(qi), cfg), range(len(queries)))
+    else:
+        # default: all queries advance phase by phase inside one call and share its synchronisations
+        results = aggregate_and_filter_batch([job(qi) for qi in range(len(queries))], cfg)
     for q, r in zip(queries, results):
         out[q.query] = r
     return out

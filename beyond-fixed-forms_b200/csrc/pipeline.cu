@@ -102,10 +102,28 @@ extern "C" int bff_rows_gather(bff_ctx *c, const uint32_t *rows, int64_t words, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// bff_stage2_aggregate
-extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *stream_) {
-    cudaStream_t s = (cudaStream_t)stream_;
-    BFF_REQUIRE(c && d, "bff_stage2_aggregate: null argument");
+// bff_stage2_aggregate / bff_stage2_aggregate_batch
+//
+// One query's aggregation is four phases with a stream synchronisation between them (each hands small device results
+// to a host decision). The batch entry runs every phase for ALL jobs before it synchronises, so Q concurrent queries
+// pay three synchronisations together instead of three each, and their small kernels queue back to back.
+namespace {
+struct AggJob {
+    const bff_stage2_desc *d = nullptr;
+    int n = 0, g = 0, stride_words = 0;
+    int64_t words = 0;
+    const int32_t *vc = nullptr;
+    uint32_t *h_adj = nullptr;
+    int32_t *h_max = nullptr;
+    float *h_vals = nullptr, *d_vals_keep = nullptr;
+    size_t first_vals = 0;
+    int mb = 0, vb = 0;
+    int32_t *h_ginter = nullptr, *h_before = nullptr, *h_after = nullptr;
+    uint32_t *d_keep = nullptr;
+};
+
+int agg_check(const bff_stage2_desc *d) {
+    BFF_REQUIRE(d, "bff_stage2_aggregate: null argument");
     BFF_REQUIRE(d->n_rows > 0 && d->n_points > 0, "bff_stage2_aggregate: empty input (the caller handles 'nothing lifted')");
     BFF_REQUIRE(d->rows && d->conf && d->label_id && d->mc && d->agg_rows && d->n_groups && d->group_first && d->group_size &&
                     d->group_conf && d->before && d->after,
@@ -113,16 +131,17 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
     BFF_REQUIRE(d->min_aggregated >= 1, "bff_stage2_aggregate: min_aggregated must be >= 1");
     BFF_REQUIRE(d->filter_mode >= 0 && d->filter_mode <= 2 && (d->filter_mode != 0 || d->vc), "bff_stage2_aggregate: bad filter mode");
     BFF_REQUIRE(d->n_rows <= 46340, "bff_stage2_aggregate: too many rows");
-    BFF_CUDA(cudaSetDevice(c->device));
-    c->dev.reset();
-    c->pin.reset();
-    const int n = d->n_rows;
-    const int64_t words = ceil_div64(d->n_points, 32);
-    const size_t nn = (size_t)n * n;
-    PipeTrace tr("stage2_aggregate");
-
-    // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
     BFF_REQUIRE((d->inter_pre == nullptr) == (d->pop_pre == nullptr), "bff_stage2_aggregate: inter_pre and pop_pre come together");
+    return BFF_OK;
+}
+
+// phase 1 (enqueue): all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122),
+// and the maxima that size the vote histogram
+int agg_phase1(bff_ctx *c, AggJob &j, cudaStream_t s) {
+    const bff_stage2_desc *d = j.d;
+    const int n = j.n = d->n_rows;
+    j.words = ceil_div64(d->n_points, 32);
+    const size_t nn = (size_t)n * n;
     const bool have_pairs = d->inter_pre != nullptr;
     int32_t *d_inter = const_cast<int32_t *>(d->inter_pre), *d_pop = const_cast<int32_t *>(d->pop_pre);
     if (!have_pairs) {
@@ -130,73 +149,74 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         d_pop = c->dev.get<int32_t>(n);
         if (!d_inter || !d_pop) return BFF_ENOMEM;
     }
-    const int stride_words = ((n + 63) / 64) * 2;               // 32-bit words per adjacency row, whole 64-bit words
-    const size_t adj_bytes = (size_t)n * stride_words * 4;
-    PIPE_TAKE(d_adj, c->dev, uint32_t, (size_t)n * stride_words);
-    PIPE_TAKE(h_adj, c->pin, uint32_t, (size_t)n * stride_words);
+    j.stride_words = ((n + 63) / 64) * 2;                 // 32-bit words per adjacency row, whole 64-bit words
+    const size_t adj_bytes = (size_t)n * j.stride_words * 4;
+    PIPE_TAKE(d_adj, c->dev, uint32_t, (size_t)n * j.stride_words);
+    j.h_adj = c->pin.get<uint32_t>((size_t)n * j.stride_words);
+    if (!j.h_adj) return BFF_ENOMEM;
     int32_t *d_label = nullptr;
     int rc = upload_i32(c, std::vector<int32_t>(d->label_id, d->label_id + n), &d_label, s);
     if (rc != BFF_OK) return rc;
     if (!have_pairs) {
-        rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s);
+        rc = bff_mask_iou(d->rows, n, d->rows, n, j.words, d_inter, d_pop, d_pop, nullptr, s);
         if (rc != BFF_OK) return rc;
     }
     {
-        dim3 grid((unsigned)(stride_words * 32 / 256 + 1), (unsigned)n);
-        merge_adjacency_kernel<<<grid, 256, 0, s>>>(d_inter, d_pop, d_label, n, stride_words, d->iou_thres, d_adj);
+        dim3 grid((unsigned)(j.stride_words * 32 / 256 + 1), (unsigned)n);
+        merge_adjacency_kernel<<<grid, 256, 0, s>>>(d_inter, d_pop, d_label, n, j.stride_words, d->iou_thres, d_adj);
     }
     BFF_LAUNCH_CHECK("merge_adjacency_kernel");
-    BFF_CUDA(cudaMemcpyAsync(h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaMemcpyAsync(j.h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));
     // the point filter (:512-583) does not depend on the grouping: its first step (the maxima that size the vote
     // histogram) rides on this synchronisation instead of paying for one of its own
-    const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
-    int32_t *h_max = nullptr;
+    j.vc = d->filter_mode == 0 ? d->vc : nullptr;
     if (d->filter_mode != 2) {
         PIPE_TAKE(d_max, c->dev, int32_t, 2);
-        h_max = c->pin.get<int32_t>(2);
-        if (!h_max) return BFF_ENOMEM;
-        if ((rc = bff_counts_max(d->mc, vc, d->n_points, d_max, s)) != BFF_OK) return rc;
-        BFF_CUDA(cudaMemcpyAsync(h_max, d_max, 8, cudaMemcpyDeviceToHost, s));
+        j.h_max = c->pin.get<int32_t>(2);
+        if (!j.h_max) return BFF_ENOMEM;
+        if ((rc = bff_counts_max(d->mc, j.vc, d->n_points, d_max, s)) != BFF_OK) return rc;
+        BFF_CUDA(cudaMemcpyAsync(j.h_max, d_max, 8, cudaMemcpyDeviceToHost, s));
     }
-    tr.mark("enqueue1");
-    BFF_CUDA(cudaStreamSynchronize(s));
-    tr.mark("sync1");
+    return BFF_OK;
+}
 
-    // ---- point filter (:512-583), first half: the unique() over N values comes from the (masked, viewed) histogram.
-    // It depends on the maxima only, so it is enqueued BEFORE the host searches the components: the device builds the
-    // histogram and its distinct ratios while the host walks the graph, and the next synchronisation brings them along.
-    float thr = 0.0f;
-    float *h_vals = nullptr, *d_vals_keep = nullptr;
-    size_t first_vals = 0;
-    int mb = 0, vb = 0;
-    if (d->filter_mode != 2) {
-        mb = h_max[0] + 1;
-        vb = vc ? h_max[1] + 1 : 1;
-        PIPE_TAKE(d_hist, c->dev, uint32_t, (size_t)mb * vb);
-        if ((rc = bff_vote_hist(d->mc, vc, d->n_points, mb, vb, d_hist, s)) != BFF_OK) return rc;
-        // distinct ratios straight from the non-empty bins, on the device: only they travel to the host
-        const int64_t tsize = bff_vote_unique_table_size(mb, vb);
-        PIPE_TAKE(d_table, c->dev, uint32_t, (size_t)tsize);
-        PIPE_TAKE(d_vals, c->dev, float, (size_t)mb * vb + 1);
-        h_vals = c->pin.get<float>((size_t)mb * vb + 1);
-        if (!h_vals) return BFF_ENOMEM;
-        int32_t *d_cnt = reinterpret_cast<int32_t *>(d_vals + (size_t)mb * vb);       // the count rides behind the values
-        if ((rc = bff_vote_unique(d_hist, mb, vb, d->filter_mode, d_table, tsize, d_vals, d_cnt, s)) != BFF_OK) return rc;
-        // the number of distinct values is not known yet: a first slice that nearly always suffices, the rest on demand
-        first_vals = std::min<size_t>((size_t)mb * vb, 16384);
-        BFF_CUDA(cudaMemcpyAsync(h_vals, d_vals, first_vals * 4, cudaMemcpyDeviceToHost, s));
-        BFF_CUDA(cudaMemcpyAsync(h_vals + (size_t)mb * vb, d_cnt, 4, cudaMemcpyDeviceToHost, s));
-        d_vals_keep = d_vals;
-    }
-    tr.mark("enqueue_votes");
+// phase 2a (enqueue, needs the maxima): point filter (:512-583), first half -- the unique() over N values comes from the
+// (masked, viewed) histogram. Enqueued BEFORE the host searches the components: the device builds the histogram and
+// its distinct ratios while the host walks the graph, and the next synchronisation brings them along.
+int agg_phase2_votes(bff_ctx *c, AggJob &j, cudaStream_t s) {
+    const bff_stage2_desc *d = j.d;
+    if (d->filter_mode == 2) return BFF_OK;
+    int rc;
+    j.mb = j.h_max[0] + 1;
+    j.vb = j.vc ? j.h_max[1] + 1 : 1;
+    const size_t bins = (size_t)j.mb * j.vb;
+    PIPE_TAKE(d_hist, c->dev, uint32_t, bins);
+    if ((rc = bff_vote_hist(d->mc, j.vc, d->n_points, j.mb, j.vb, d_hist, s)) != BFF_OK) return rc;
+    // distinct ratios straight from the non-empty bins, on the device: only they travel to the host
+    const int64_t tsize = bff_vote_unique_table_size(j.mb, j.vb);
+    PIPE_TAKE(d_table, c->dev, uint32_t, (size_t)tsize);
+    PIPE_TAKE(d_vals, c->dev, float, bins + 1);
+    j.h_vals = c->pin.get<float>(bins + 1);
+    if (!j.h_vals) return BFF_ENOMEM;
+    int32_t *d_cnt = reinterpret_cast<int32_t *>(d_vals + bins);       // the count rides behind the values
+    if ((rc = bff_vote_unique(d_hist, j.mb, j.vb, d->filter_mode, d_table, tsize, d_vals, d_cnt, s)) != BFF_OK) return rc;
+    // the number of distinct values is not known yet: a first slice that nearly always suffices, the rest on demand
+    j.first_vals = std::min<size_t>(bins, 16384);
+    BFF_CUDA(cudaMemcpyAsync(j.h_vals, d_vals, j.first_vals * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaMemcpyAsync(j.h_vals + bins, d_cnt, 4, cudaMemcpyDeviceToHost, s));
+    j.d_vals_keep = d_vals;
+    return BFF_OK;
+}
 
-    // ---- connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric, so the
-    // reference's reachability lists are the components, emitted by smallest member, members ascending).
-    // A node without any edge (an empty row: IoU diagonal NaN) forms no group.
-    // Flood fill over the bit rows, 64 neighbours per step: root[i] = smallest member of i's component.
-    tr.mark("pre_cc");
-    const int w64 = stride_words / 2;
-    const uint64_t *adj64 = reinterpret_cast<const uint64_t *>(h_adj);
+// phase 2b (host + enqueue): connected components (find_unconnected_subgraphs_tensor :250-274; the graph is symmetric,
+// so the reference's reachability lists are the components, emitted by smallest member, members ascending). A node
+// without any edge (an empty row: IoU diagonal NaN) forms no group. Then the OR-merge and the pair overlaps.
+int agg_phase2_groups(bff_ctx *c, AggJob &j, cudaStream_t s) {
+    const bff_stage2_desc *d = j.d;
+    const int n = j.n;
+    // flood fill over the bit rows, 64 neighbours per step: root[i] = smallest member of i's component
+    const int w64 = j.stride_words / 2;
+    const uint64_t *adj64 = reinterpret_cast<const uint64_t *>(j.h_adj);
     std::vector<uint64_t> visited(w64, 0), frontier(w64), next(w64);
     std::vector<int> root(n, -1), count(n, 0);
     std::vector<char> has_edge(n, 0);
@@ -232,15 +252,14 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         }
     }
     for (int i = 0; i < n; ++i) count[root[i]]++;
-    tr.mark("cc");
     // kept groups (:203): len >= min_aggregated; roots ascending == order of smallest member
     std::vector<int> group_of_root(n, -1);
     int g = 0;
     for (int r = 0; r < n; ++r)
         if (root[r] == r && has_edge[r] && count[r] >= d->min_aggregated) group_of_root[r] = g++;
+    j.g = g;
     *d->n_groups = g;
     if (d->filter_value) *d->filter_value = 0.0f;
-    if (g == 0 || g > d->cap_groups) BFF_CUDA(cudaStreamSynchronize(s));     // the vote copies still target this context's pinned arena
     if (g == 0) return BFF_OK;
     BFF_REQUIRE(g <= d->cap_groups, "bff_stage2_aggregate: %d groups exceed cap_groups %d", g, d->cap_groups);
     std::vector<int32_t> seg(g + 1, 0), idx;
@@ -259,75 +278,129 @@ extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *
         }
     }
     if (d->members) memcpy(d->members, idx.data(), idx.size() * 4);
-    tr.mark("components");
 
     // ---- OR-merge the members (:214-223)
+    int rc;
     int32_t *d_idx = nullptr, *d_seg = nullptr;
     if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
     if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
-    if ((rc = bff_rows_or_reduce(d->rows, words, d_idx, d_seg, g, d->agg_rows, s)) != BFF_OK) return rc;
+    if ((rc = bff_rows_or_reduce(d->rows, j.words, d_idx, d_seg, g, d->agg_rows, s)) != BFF_OK) return rc;
 
     // ---- pair overlaps of the merged rows + row sums 'before' (:285-291, :592), issued now, read later
     PIPE_TAKE(d_ginter, c->dev, int32_t, (size_t)g * g);
     PIPE_TAKE(d_before, c->dev, int32_t, g);
-    PIPE_TAKE(h_ginter, c->pin, int32_t, (size_t)g * g);
-    if ((rc = bff_mask_iou(d->agg_rows, g, d->agg_rows, g, words, d_ginter, d_before, d_before, nullptr, s)) != BFF_OK) return rc;
-    BFF_CUDA(cudaMemcpyAsync(h_ginter, d_ginter, (size_t)g * g * 4, cudaMemcpyDeviceToHost, s));
-    PIPE_TAKE(h_before, c->pin, int32_t, g);
-    BFF_CUDA(cudaMemcpyAsync(h_before, d_before, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+    j.h_ginter = c->pin.get<int32_t>((size_t)g * g);
+    j.h_before = c->pin.get<int32_t>(g);
+    j.d_keep = c->dev.get<uint32_t>(j.words);
+    if (!j.h_ginter || !j.h_before || !j.d_keep) return BFF_ENOMEM;
+    if ((rc = bff_mask_iou(d->agg_rows, g, d->agg_rows, g, j.words, d_ginter, d_before, d_before, nullptr, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(j.h_ginter, d_ginter, (size_t)g * g * 4, cudaMemcpyDeviceToHost, s));
+    BFF_CUDA(cudaMemcpyAsync(j.h_before, d_before, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+    return BFF_OK;
+}
 
-    PIPE_TAKE(d_keep, c->dev, uint32_t, words);
-    tr.mark("enqueue2");
-    BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps, 'before' and the histogram are on the host now
-    tr.mark("sync2");
+// phase 3 (host + enqueue; pair overlaps, 'before' and the distinct vote ratios are on the host now)
+int agg_phase3(bff_ctx *c, AggJob &j, cudaStream_t s, PipeTrace &tr) {
+    const bff_stage2_desc *d = j.d;
+    const int g = j.g;
+    if (g == 0) return BFF_OK;
+    int rc;
     // ---- solve_overlapping's sequential schedule (:285-299): pairs i<j that overlap in the incoming rows; the mask
     // merged from MORE members keeps the shared points, ties: i loses. Enqueued before the host picks the vote threshold.
     std::vector<int32_t> prog;
     for (int i = 0; i < g; ++i)
-        for (int j = i + 1; j < g; ++j)
-            if (h_ginter[(size_t)i * g + j] > 0) {
-                if (d->group_size[i] > d->group_size[j]) { prog.push_back(j); prog.push_back(i); }
-                else { prog.push_back(i); prog.push_back(j); }
+        for (int k = i + 1; k < g; ++k)
+            if (j.h_ginter[(size_t)i * g + k] > 0) {
+                if (d->group_size[i] > d->group_size[k]) { prog.push_back(k); prog.push_back(i); }
+                else { prog.push_back(i); prog.push_back(k); }
             }
-    tr.mark("schedule");
     if (!prog.empty()) {
         int32_t *d_prog = nullptr;
         if ((rc = upload_i32(c, prog, &d_prog, s)) != BFF_OK) return rc;
-        if ((rc = bff_overlap_resolve(d->agg_rows, g, words, d_prog, (int32_t)(prog.size() / 2), s)) != BFF_OK) return rc;
+        if ((rc = bff_overlap_resolve(d->agg_rows, g, j.words, d_prog, (int32_t)(prog.size() / 2), s)) != BFF_OK) return rc;
     }
+    float thr = 0.0f;
     if (d->filter_mode == 2) {
-        if ((rc = bff_point_keep(d->mc, nullptr, d->n_points, 2, 0.0f, d_keep, s)) != BFF_OK) return rc;
+        if ((rc = bff_point_keep(d->mc, nullptr, d->n_points, 2, 0.0f, j.d_keep, s)) != BFF_OK) return rc;
     } else {
+        const size_t bins = (size_t)j.mb * j.vb;
         int32_t n_unique;
-        memcpy(&n_unique, h_vals + (size_t)mb * vb, 4);
-        if ((size_t)n_unique > first_vals) {
-            BFF_CUDA(cudaMemcpyAsync(h_vals + first_vals, d_vals_keep + first_vals, ((size_t)n_unique - first_vals) * 4, cudaMemcpyDeviceToHost, s));
+        memcpy(&n_unique, j.h_vals + bins, 4);
+        if ((size_t)n_unique > j.first_vals) {
+            BFF_CUDA(cudaMemcpyAsync(j.h_vals + j.first_vals, j.d_vals_keep + j.first_vals, ((size_t)n_unique - j.first_vals) * 4,
+                                     cudaMemcpyDeviceToHost, s));
             BFF_CUDA(cudaStreamSynchronize(s));
         }
-        std::vector<float> u(h_vals, h_vals + n_unique);
+        std::vector<float> u(j.h_vals, j.h_vals + n_unique);
         // u[floor(p * len(u))] of the SORTED unique values with p a Python float (:516-517, :575-576); out of range raises in the reference
         const double pos = floor(d->filter_fraction * (double)u.size());
         BFF_REQUIRE(pos >= 0.0 && pos < (double)u.size(), "bff_stage2_aggregate: filter fraction %g selects index %g of %zu unique values",
                     d->filter_fraction, pos, u.size());
         std::nth_element(u.begin(), u.begin() + (size_t)pos, u.end());
         thr = u[(size_t)pos];
-        if (tr.on) fprintf(stderr, " [bins %dx%d unique %zu]", mb, vb, u.size());
-        tr.mark("threshold");
-        if ((rc = bff_point_keep(d->mc, vc, d->n_points, d->filter_mode, thr, d_keep, s)) != BFF_OK) return rc;
+        if (tr.on) fprintf(stderr, " [bins %dx%d unique %zu]", j.mb, j.vb, u.size());
+        if ((rc = bff_point_keep(d->mc, j.vc, d->n_points, d->filter_mode, thr, j.d_keep, s)) != BFF_OK) return rc;
     }
     if (d->filter_value) *d->filter_value = thr;
 
     // ---- ins &= masked_points, row sums 'after' (:594-596)
     PIPE_TAKE(d_after, c->dev, int32_t, g);
-    if ((rc = bff_rows_and_popcount(d->agg_rows, g, words, d_keep, d_after, s)) != BFF_OK) return rc;
-    PIPE_TAKE(h_after, c->pin, int32_t, g);
-    BFF_CUDA(cudaMemcpyAsync(h_after, d_after, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
-    tr.mark("enqueue3");
+    if ((rc = bff_rows_and_popcount(d->agg_rows, g, j.words, j.d_keep, d_after, s)) != BFF_OK) return rc;
+    j.h_after = c->pin.get<int32_t>(g);
+    if (!j.h_after) return BFF_ENOMEM;
+    BFF_CUDA(cudaMemcpyAsync(j.h_after, d_after, (size_t)g * 4, cudaMemcpyDeviceToHost, s));
+    return BFF_OK;
+}
+
+// All phases for `n_jobs` queries. On an error the stream is drained before returning: copies into the pinned arena may
+// still be in flight and the next call reuses that arena.
+int agg_run(bff_ctx *c, const bff_stage2_desc *descs, int n_jobs, cudaStream_t s) {
+    int rc = BFF_OK;
+    for (int q = 0; q < n_jobs; ++q)
+        if ((rc = agg_check(descs + q)) != BFF_OK) return rc;
+    BFF_CUDA(cudaSetDevice(c->device));
+    c->dev.reset();
+    c->pin.reset();
+    PipeTrace tr(n_jobs == 1 ? "stage2_aggregate" : "stage2_aggregate_batch");
+    std::vector<AggJob> jobs(n_jobs);
+    for (int q = 0; q < n_jobs; ++q) jobs[q].d = descs + q;
+#define AGG_ALL(call)                                                      \
+    for (int q = 0; q < n_jobs && rc == BFF_OK; ++q) rc = (call);          \
+    if (rc != BFF_OK) { cudaStreamSynchronize(s); return rc; }
+    AGG_ALL(agg_phase1(c, jobs[q], s));
+    tr.mark("enqueue1");
+    BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync1");
+    AGG_ALL(agg_phase2_votes(c, jobs[q], s));
+    tr.mark("enqueue_votes");
+    AGG_ALL(agg_phase2_groups(c, jobs[q], s));
+    tr.mark("components+enqueue2");
+    BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps, 'before' and the histograms are on the host now
+    tr.mark("sync2");
+    AGG_ALL(agg_phase3(c, jobs[q], s, tr));
+    tr.mark("threshold+enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync3");
-    memcpy(d->before, h_before, (size_t)g * 4);
-    memcpy(d->after, h_after, (size_t)g * 4);
+#undef AGG_ALL
+    for (const AggJob &j : jobs)
+        if (j.g > 0) {
+            memcpy(j.d->before, j.h_before, (size_t)j.g * 4);
+            memcpy(j.d->after, j.h_after, (size_t)j.g * 4);
+        }
     return BFF_OK;
+}
+}  // namespace
+
+extern "C" int bff_stage2_aggregate(bff_ctx *c, const bff_stage2_desc *d, void *stream_) {
+    BFF_REQUIRE(c && d, "bff_stage2_aggregate: null argument");
+    return agg_run(c, d, 1, (cudaStream_t)stream_);
+}
+
+extern "C" int bff_stage2_aggregate_batch(bff_ctx *c, const bff_stage2_desc *descs, int32_t n_jobs, void *stream_) {
+    BFF_REQUIRE(c && n_jobs >= 0, "bff_stage2_aggregate_batch: bad arguments");
+    if (n_jobs == 0) return BFF_OK;
+    BFF_REQUIRE(descs, "bff_stage2_aggregate_batch: null descriptors");
+    return agg_run(c, descs, n_jobs, (cudaStream_t)stream_);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -343,66 +416,90 @@ static int argmax_torch(const float *v, int n, int stride) {
     return best;
 }
 
-extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stream_) {
-    cudaStream_t s = (cudaStream_t)stream_;
-    BFF_REQUIRE(c && d, "bff_refine_match: null argument");
+// Like the aggregation, one job is phases separated by stream synchronisations; the batch entry runs each phase for all
+// jobs (queries of one scene, each with its OWN copy of the stage-1 rows -- pass 1 modifies them in place) before it waits.
+namespace {
+struct RefineJob {
+    const bff_refine_desc *d = nullptr;
+    int n1 = 0, n2 = 0, m = 0;
+    int64_t words = 0;
+    int32_t *d_inter = nullptr, *d_p1 = nullptr, *d_p2 = nullptr;
+    float *d_iou = nullptr, *h_iou = nullptr, *h_giou = nullptr;
+    std::vector<int32_t> mm;
+};
+
+int refine_check(const bff_refine_desc *d) {
+    BFF_REQUIRE(d, "bff_refine_match: null argument");
     BFF_REQUIRE(d->n1 > 0 && d->n2 > 0 && d->n_points > 0, "bff_refine_match: empty input (the caller handles empty stages)");
     BFF_REQUIRE(d->s1_rows && d->s2_rows && d->s2_conf && d->s2_out && d->n2_out && d->s2_conf_out && d->match && d->match_iou,
                 "bff_refine_match: null pointer");
     BFF_REQUIRE(d->n2 <= 65535, "bff_refine_match: too many stage-2 masks");
-    BFF_CUDA(cudaSetDevice(c->device));
-    c->dev.reset();
-    c->pin.reset();
-    const int n1 = d->n1, n2 = d->n2;
-    const int64_t words = ceil_div64(d->n_points, 32);
-    int rc;
-    PipeTrace tr("refine_match");
+    return BFF_OK;
+}
+
+// phase 1 (enqueue): iou(stage1, stage2) (:208-213)
+int refine_phase1(bff_ctx *c, RefineJob &j, cudaStream_t s) {
+    const bff_refine_desc *d = j.d;
+    const int n1 = j.n1 = d->n1, n2 = j.n2 = d->n2;
+    j.words = ceil_div64(d->n_points, 32);
     // scratch for an (n1 x k) IoU, k <= n2
-    PIPE_TAKE(d_inter, c->dev, int32_t, (size_t)n1 * n2);
-    PIPE_TAKE(d_p1, c->dev, int32_t, n1);
-    PIPE_TAKE(d_p2, c->dev, int32_t, n2);
-    PIPE_TAKE(d_iou, c->dev, float, (size_t)n1 * n2);
-    PIPE_TAKE(h_iou, c->pin, float, (size_t)n1 * n2);
+    j.d_inter = c->dev.get<int32_t>((size_t)n1 * n2);
+    j.d_p1 = c->dev.get<int32_t>(n1);
+    j.d_p2 = c->dev.get<int32_t>(n2);
+    j.d_iou = c->dev.get<float>((size_t)n1 * n2);
+    j.h_iou = c->pin.get<float>((size_t)n1 * n2);
+    if (!j.d_inter || !j.d_p1 || !j.d_p2 || !j.d_iou || !j.h_iou) return BFF_ENOMEM;
+    int rc;
+    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_rows, n2, j.words, j.d_inter, j.d_p1, j.d_p2, j.d_iou, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(j.h_iou, j.d_iou, (size_t)n1 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    return BFF_OK;
+}
 
-    // ---- iou(stage1, stage2), max_match = argmax over stage-1 (:208-213)
-    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_rows, n2, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
-    BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * n2 * 4, cudaMemcpyDeviceToHost, s));
-    tr.mark("enqueue1");
-    BFF_CUDA(cudaStreamSynchronize(s));
-    tr.mark("sync1");
-    std::vector<int32_t> mm(n2);
-    for (int k = 0; k < n2; ++k) mm[k] = argmax_torch(h_iou + k, n1, n2);
-
-    // ---- IoU among the matched stage-1 masks, diagonal zeroed, thresholded (:217-224)
+// phase 2 (host + enqueue): max_match = argmax over stage-1; IoU among the matched stage-1 masks (:217-224)
+int refine_phase2(bff_ctx *c, RefineJob &j, cudaStream_t s) {
+    const bff_refine_desc *d = j.d;
+    const int n1 = j.n1, n2 = j.n2;
+    const int64_t words = j.words;
+    int rc;
+    j.mm.resize(n2);
+    for (int k = 0; k < n2; ++k) j.mm[k] = argmax_torch(j.h_iou + k, n1, n2);
     PIPE_TAKE(d_sel, c->dev, uint32_t, (size_t)n2 * words);
     PIPE_TAKE(d_ginter, c->dev, int32_t, (size_t)n2 * n2);
     PIPE_TAKE(d_gpop, c->dev, int32_t, n2);
     PIPE_TAKE(d_giou, c->dev, float, (size_t)n2 * n2);
-    PIPE_TAKE(h_giou, c->pin, float, (size_t)n2 * n2);
+    j.h_giou = c->pin.get<float>((size_t)n2 * n2);
+    if (!j.h_giou) return BFF_ENOMEM;
     int32_t *d_mm = nullptr;
-    if ((rc = upload_i32(c, mm, &d_mm, s)) != BFF_OK) return rc;
+    if ((rc = upload_i32(c, j.mm, &d_mm, s)) != BFF_OK) return rc;
     {
         dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n2);
         rows_gather_kernel<<<grid, 256, 0, s>>>(d->s1_rows, words, d_mm, d_sel);
         BFF_LAUNCH_CHECK("rows_gather_kernel");
     }
     if ((rc = bff_mask_iou(d_sel, n2, d_sel, n2, words, d_ginter, d_gpop, d_gpop, d_giou, s)) != BFF_OK) return rc;
-    BFF_CUDA(cudaMemcpyAsync(h_giou, d_giou, (size_t)n2 * n2 * 4, cudaMemcpyDeviceToHost, s));
-    tr.mark("enqueue2");
-    BFF_CUDA(cudaStreamSynchronize(s));
-    tr.mark("sync2");
+    BFF_CUDA(cudaMemcpyAsync(j.h_giou, d_giou, (size_t)n2 * n2 * 4, cudaMemcpyDeviceToHost, s));
+    return BFF_OK;
+}
 
+// phase 3 (host + enqueue): the sequential merge loop, the stage-2 merges and the final IoU
+int refine_phase3(bff_ctx *c, RefineJob &j, cudaStream_t s) {
+    const bff_refine_desc *d = j.d;
+    const int n1 = j.n1, n2 = j.n2;
+    const int64_t words = j.words;
+    const std::vector<int32_t> &mm = j.mm;
+    const float *h_giou = j.h_giou;
+    int rc;
     // ---- sequential merge loop (:230-249): redirects + in-place ORs of stage-1 rows, in list order
     std::vector<int32_t> best(n2), redirect(n2, -1), or_prog;
     for (int i = 0; i < n2; ++i) {
         if (redirect[i] != -1) { best[i] = mm[redirect[i]]; continue; }
         best[i] = mm[i];
-        for (int j = 0; j < n2; ++j) {
-            if (j == i) continue;                                            // diagonal set to 0 (:219)
-            if (h_giou[(size_t)i * n2 + j] > d->stage1_iou_thres) {
-                redirect[j] = i;
+        for (int k = 0; k < n2; ++k) {
+            if (k == i) continue;                                            // diagonal set to 0 (:219)
+            if (h_giou[(size_t)i * n2 + k] > d->stage1_iou_thres) {
+                redirect[k] = i;
                 or_prog.push_back(mm[i]);
-                or_prog.push_back(mm[j]);
+                or_prog.push_back(mm[k]);
             }
         }
     }
@@ -441,7 +538,7 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
         keep.push_back(merged); keep_conf.push_back(sum / (float)cnt); keep_best.push_back(u);
         cur.swap(keep); cur_conf.swap(keep_conf); cur_best.swap(keep_best);
     }
-    const int m = (int)cur.size();
+    const int m = j.m = (int)cur.size();
     *d->n2_out = m;
     std::vector<int32_t> idx, seg(m + 1, 0);
     for (int k = 0; k < m; ++k) {
@@ -454,15 +551,56 @@ extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stre
     if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
     if ((rc = bff_rows_or_reduce(d->s2_rows, words, d_idx, d_seg, m, d->s2_out, s)) != BFF_OK) return rc;
 
-    // ---- IoU of the merged stage-1 masks with the merged stage-2 masks, final argmax (:285-290)
-    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_out, m, words, d_inter, d_p1, d_p2, d_iou, s)) != BFF_OK) return rc;
-    BFF_CUDA(cudaMemcpyAsync(h_iou, d_iou, (size_t)n1 * m * 4, cudaMemcpyDeviceToHost, s));
+    // ---- IoU of the merged stage-1 masks with the merged stage-2 masks (:285-290)
+    if ((rc = bff_mask_iou(d->s1_rows, n1, d->s2_out, m, words, j.d_inter, j.d_p1, j.d_p2, j.d_iou, s)) != BFF_OK) return rc;
+    BFF_CUDA(cudaMemcpyAsync(j.h_iou, j.d_iou, (size_t)n1 * m * 4, cudaMemcpyDeviceToHost, s));
+    return BFF_OK;
+}
+
+int refine_run(bff_ctx *c, const bff_refine_desc *descs, int n_jobs, cudaStream_t s) {
+    int rc = BFF_OK;
+    for (int q = 0; q < n_jobs; ++q)
+        if ((rc = refine_check(descs + q)) != BFF_OK) return rc;
+    BFF_CUDA(cudaSetDevice(c->device));
+    c->dev.reset();
+    c->pin.reset();
+    PipeTrace tr(n_jobs == 1 ? "refine_match" : "refine_match_batch");
+    std::vector<RefineJob> jobs(n_jobs);
+    for (int q = 0; q < n_jobs; ++q) jobs[q].d = descs + q;
+#define REFINE_ALL(call)                                                   \
+    for (int q = 0; q < n_jobs && rc == BFF_OK; ++q) rc = (call);          \
+    if (rc != BFF_OK) { cudaStreamSynchronize(s); return rc; }
+    REFINE_ALL(refine_phase1(c, jobs[q], s));
+    tr.mark("enqueue1");
+    BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync1");
+    REFINE_ALL(refine_phase2(c, jobs[q], s));
+    tr.mark("enqueue2");
+    BFF_CUDA(cudaStreamSynchronize(s));
+    tr.mark("sync2");
+    REFINE_ALL(refine_phase3(c, jobs[q], s));
     tr.mark("enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync3");
-    for (int k = 0; k < m; ++k) {
-        d->match[k] = argmax_torch(h_iou + k, n1, m);
-        d->match_iou[k] = h_iou[(size_t)d->match[k] * m + k];
-    }
+#undef REFINE_ALL
+    // final argmax (:288) and the matched IoU (:308)
+    for (const RefineJob &j : jobs)
+        for (int k = 0; k < j.m; ++k) {
+            j.d->match[k] = argmax_torch(j.h_iou + k, j.n1, j.m);
+            j.d->match_iou[k] = j.h_iou[(size_t)j.d->match[k] * j.m + k];
+        }
     return BFF_OK;
+}
+}  // namespace
+
+extern "C" int bff_refine_match(bff_ctx *c, const bff_refine_desc *d, void *stream_) {
+    BFF_REQUIRE(c && d, "bff_refine_match: null argument");
+    return refine_run(c, d, 1, (cudaStream_t)stream_);
+}
+
+extern "C" int bff_refine_match_batch(bff_ctx *c, const bff_refine_desc *descs, int32_t n_jobs, void *stream_) {
+    BFF_REQUIRE(c && n_jobs >= 0, "bff_refine_match_batch: bad arguments");
+    if (n_jobs == 0) return BFF_OK;
+    BFF_REQUIRE(descs, "bff_refine_match_batch: null descriptors");
+    return refine_run(c, descs, n_jobs, (cudaStream_t)stream_);
 }

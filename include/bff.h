@@ -279,6 +279,10 @@ typedef struct bff_stage2_desc {
     const int32_t *pop_pre;
 } bff_stage2_desc;
 BFF_API int bff_stage2_aggregate(bff_ctx *ctx, const bff_stage2_desc *desc, void *stream);
+/* The same for `n_jobs` independent queries of one scene (descs[0..n_jobs)): every phase is enqueued for all jobs before
+ * the stream is synchronised, so Q concurrent queries share three synchronisations instead of paying three each.
+ * Results are identical to n_jobs separate calls. */
+BFF_API int bff_stage2_aggregate_batch(bff_ctx *ctx, const bff_stage2_desc *descs, int32_t n_jobs, void *stream);
 
 /* pass 1 of tools/refinement.py for one scene (:208-290): stage-1 / stage-2 matching, the in-place stage-1
  * OR-merges, merging of stage-2 masks that share a stage-1 match, and the final IoU + argmax. */
@@ -299,6 +303,9 @@ typedef struct bff_refine_desc {
     int32_t *best_match_log;    /* host (n2), optional: best_match_after_iou_check before merging (:252) */
 } bff_refine_desc;
 BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *stream);
+/* The same for `n_jobs` independent jobs (queries of one scene; every job needs its own copy of the stage-1 rows, which
+ * pass 1 modifies): phases are enqueued for all jobs before the stream is synchronised. Results equal n_jobs separate calls. */
+BFF_API int bff_refine_match_batch(bff_ctx *ctx, const bff_refine_desc *descs, int32_t n_jobs, void *stream);
 
 /* Host -> device copy done by a small kernel that reads PINNED host memory directly (zero-copy loads over
  * PCIe) instead of a copy engine. Used to prefetch the next scene's depth stack while the current scene is

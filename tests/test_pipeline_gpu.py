@@ -109,3 +109,67 @@ def test_precomputed_pairs_give_the_same_aggregation(cuda_dev):
     b, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, inp["cfg"], pairs=pairs)
     assert a["ins"].shape[0] >= 2
     _same(a, b, "precomputed pairs")
+
+
+def test_batched_aggregation_equals_one_call_per_query(cuda_dev):
+    """bff_stage2_aggregate_batch (all queries advance phase by phase, shared synchronisations) against one
+    bff_stage2_aggregate call per query; with an empty query and one whose masks never reach min_aggragated_masks."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from bff_b200 import ops, stage2
+    inp = bench.build_inputs("tiny3", 0, 1, cuda_dev)
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+    cfg = inp["cfg"]
+    jobs = []
+    for qi in range(g.nq):
+        idx = g.row_index_dev[qi] if g.row_index_dev is not None else None
+        jobs.append((out.rows if idx is None else out.rows[idx], g.conf_q[qi], g.labels_q[qi], out.masked_counts[qi], out.viewed_counts, g.n))
+    jobs.append((None, [], [], None, None, g.n))                                  # nothing lifted for this query
+    rows0, conf0, labels0 = jobs[0][:3]
+    jobs.append((rows0[:2], conf0[:2], labels0[:2], out.masked_counts[0], out.viewed_counts, g.n))   # too few masks to aggregate
+    single = [stage2.aggregate_and_filter(*j, cfg) for j in jobs]
+    batch = stage2.aggregate_and_filter_batch(jobs, cfg)
+    assert len(batch) == len(jobs)
+    assert sum(r[1] for r in single) >= 2 and not single[-2][1]
+    for k, (a, b) in enumerate(zip(single, batch)):
+        assert a[1] == b[1], f"job {k}: reached_filter differs"
+        _same(a[0], b[0], f"batch vs single, job {k}")
+
+
+def test_batched_refinement_pass1_equals_one_call_per_query(cuda_dev):
+    """bff_refine_match_batch against one bff_refine_match call per query (each on its own copy of the stage-1 rows),
+    with a query whose stage 2 is empty."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from bff_b200 import ops, refine, scene_io, stage2
+    inp = bench.build_inputs("tiny3", 0, 1, cuda_dev)
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    cfg = inp["cfg"]
+    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+    s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), g.n)
+    res2 = []
+    for qi in range(g.nq):
+        idx = g.row_index_dev[qi] if g.row_index_dev is not None else None
+        r, _ = stage2.aggregate_and_filter(out.rows if idx is None else out.rows[idx], g.conf_q[qi], g.labels_q[qi], out.masked_counts[qi],
+                                           out.viewed_counts, g.n, cfg, keep_rows=True)
+        res2.append(r)
+    res2.append(scene_io.empty_stage2())
+    names = list(g.names) + [g.names[0]]
+    single = [refine.pass1_scene(inp["stage1"], r, nm, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev, s1_rows=s1.clone())
+              for r, nm in zip(res2, names)]
+    batch = refine.pass1_scene_batch(inp["stage1"], res2, names, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev,
+                                     [s1.clone() for _ in names])
+    assert sum(len(p["sims"]) > 0 for p in single) >= 2
+    for k, (a, b) in enumerate(zip(single, batch)):
+        assert a["sims"] == b["sims"], k
+        assert torch.equal(torch.as_tensor(a["ious"]), torch.as_tensor(b["ious"])), k
+        assert torch.equal(a["other"], b["other"]), k
+        if a["m1"] is not None:
+            assert torch.equal(a["m1"], b["m1"]) and torch.equal(a["m2"], b["m2"]), k
+            assert torch.equal(torch.as_tensor(a["conf2"]), torch.as_tensor(b["conf2"])), k
+        fa = refine.pass2_scene(a, names[k], cfg["refiment_iou_thres"], 0.0)
+        fb = refine.pass2_scene(b, names[k], cfg["refiment_iou_thres"], 0.0)
+        _same(fa, fb, f"pass 2 after batched pass 1, query {k}")
