@@ -64,4 +64,11 @@ struct bff_ctx {
     size_t ws_bytes;
     bff::Arena dev;         // pipeline scratch on the device
     bff::Arena pin;         // pipeline scratch in pinned host memory
+    // side streams of the batched pipelines (created on first use): job q runs on lane q % n_lanes between a fork from
+    // and a join into the caller's stream, so the small kernels of independent jobs overlap
+    static constexpr int kMaxLanes = 8;
+    cudaStream_t lane[kMaxLanes];
+    cudaEvent_t lane_done[kMaxLanes];
+    cudaEvent_t fork_ev;
+    int n_lanes;
 };

@@ -102,6 +102,8 @@ extern "C" void bff_ctx_destroy(bff_ctx *c) {
     if (c->ws) cudaFree(c->ws);
     c->dev.release();
     c->pin.release();
+    for (int i = 0; i < c->n_lanes; ++i) { cudaStreamDestroy(c->lane[i]); cudaEventDestroy(c->lane_done[i]); }
+    if (c->n_lanes) cudaEventDestroy(c->fork_ev);
     cudaStreamDestroy(c->stream);
     delete c;
 }

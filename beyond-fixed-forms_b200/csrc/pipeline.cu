@@ -101,6 +101,50 @@ extern "C" int bff_rows_gather(bff_ctx *c, const uint32_t *rows, int64_t words, 
     return BFF_OK;
 }
 
+// Side streams for the batched pipelines. With several jobs, job q is enqueued on lane q % n between fork() (the lanes
+// wait for what is already on the caller's stream) and join() (the caller's stream waits for the lanes); one job keeps
+// its lane through all phases. A single job, or BFF_BATCH_LANES=0, runs on the caller's stream.
+struct Lanes {
+    bff_ctx *c;
+    cudaStream_t main;
+    int n = 0;
+    int init(bff_ctx *ctx, cudaStream_t s, int n_jobs) {
+        c = ctx;
+        main = s;
+        static const int want = [] { const char *e = getenv("BFF_BATCH_LANES"); const int v = e ? atoi(e) : 4; return v < 0 ? 0 : (v > bff_ctx::kMaxLanes ? bff_ctx::kMaxLanes : v); }();
+        if (n_jobs < 2 || want < 2) return BFF_OK;
+        if (c->n_lanes == 0) {
+            BFF_CUDA(cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
+            for (int i = 0; i < bff_ctx::kMaxLanes; ++i) {
+                BFF_CUDA(cudaStreamCreateWithFlags(&c->lane[i], cudaStreamNonBlocking));
+                BFF_CUDA(cudaEventCreateWithFlags(&c->lane_done[i], cudaEventDisableTiming));
+                c->n_lanes = i + 1;
+            }
+        }
+        n = want < n_jobs ? want : n_jobs;
+        return BFF_OK;
+    }
+    cudaStream_t of(int q) const { return n ? c->lane[q % n] : main; }
+    int fork() {
+        if (!n) return BFF_OK;
+        BFF_CUDA(cudaEventRecord(c->fork_ev, main));
+        for (int i = 0; i < n; ++i) BFF_CUDA(cudaStreamWaitEvent(c->lane[i], c->fork_ev, 0));
+        return BFF_OK;
+    }
+    int join() {
+        if (!n) return BFF_OK;
+        for (int i = 0; i < n; ++i) {
+            BFF_CUDA(cudaEventRecord(c->lane_done[i], c->lane[i]));
+            BFF_CUDA(cudaStreamWaitEvent(main, c->lane_done[i], 0));
+        }
+        return BFF_OK;
+    }
+    void drain() {                               // error path: nothing may still be writing into the pinned arena
+        for (int i = 0; i < n; ++i) cudaStreamSynchronize(c->lane[i]);
+        cudaStreamSynchronize(main);
+    }
+};
+
 // ------------------------------------------------------------------------------------------------
 // bff_stage2_aggregate / bff_stage2_aggregate_batch
 //
@@ -364,24 +408,33 @@ int agg_run(bff_ctx *c, const bff_stage2_desc *descs, int n_jobs, cudaStream_t s
     PipeTrace tr(n_jobs == 1 ? "stage2_aggregate" : "stage2_aggregate_batch");
     std::vector<AggJob> jobs(n_jobs);
     for (int q = 0; q < n_jobs; ++q) jobs[q].d = descs + q;
+    Lanes lanes;
+    if ((rc = lanes.init(c, s, n_jobs)) != BFF_OK) return rc;
 #define AGG_ALL(call)                                                      \
     for (int q = 0; q < n_jobs && rc == BFF_OK; ++q) rc = (call);          \
-    if (rc != BFF_OK) { cudaStreamSynchronize(s); return rc; }
-    AGG_ALL(agg_phase1(c, jobs[q], s));
+    if (rc != BFF_OK) { lanes.drain(); return rc; }
+#define AGG_STEP(call)                                                     \
+    if ((rc = (call)) != BFF_OK) { lanes.drain(); return rc; }
+    AGG_STEP(lanes.fork());
+    AGG_ALL(agg_phase1(c, jobs[q], lanes.of(q)));
+    AGG_STEP(lanes.join());
     tr.mark("enqueue1");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync1");
-    AGG_ALL(agg_phase2_votes(c, jobs[q], s));
+    AGG_ALL(agg_phase2_votes(c, jobs[q], lanes.of(q)));
     tr.mark("enqueue_votes");
-    AGG_ALL(agg_phase2_groups(c, jobs[q], s));
+    AGG_ALL(agg_phase2_groups(c, jobs[q], lanes.of(q)));
+    AGG_STEP(lanes.join());
     tr.mark("components+enqueue2");
     BFF_CUDA(cudaStreamSynchronize(s));      // pair overlaps, 'before' and the histograms are on the host now
     tr.mark("sync2");
-    AGG_ALL(agg_phase3(c, jobs[q], s, tr));
+    AGG_ALL(agg_phase3(c, jobs[q], lanes.of(q), tr));
+    AGG_STEP(lanes.join());
     tr.mark("threshold+enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync3");
 #undef AGG_ALL
+#undef AGG_STEP
     for (const AggJob &j : jobs)
         if (j.g > 0) {
             memcpy(j.d->before, j.h_before, (size_t)j.g * 4);
@@ -567,22 +620,31 @@ int refine_run(bff_ctx *c, const bff_refine_desc *descs, int n_jobs, cudaStream_
     PipeTrace tr(n_jobs == 1 ? "refine_match" : "refine_match_batch");
     std::vector<RefineJob> jobs(n_jobs);
     for (int q = 0; q < n_jobs; ++q) jobs[q].d = descs + q;
+    Lanes lanes;
+    if ((rc = lanes.init(c, s, n_jobs)) != BFF_OK) return rc;
 #define REFINE_ALL(call)                                                   \
     for (int q = 0; q < n_jobs && rc == BFF_OK; ++q) rc = (call);          \
-    if (rc != BFF_OK) { cudaStreamSynchronize(s); return rc; }
-    REFINE_ALL(refine_phase1(c, jobs[q], s));
+    if (rc != BFF_OK) { lanes.drain(); return rc; }
+#define REFINE_STEP(call)                                                  \
+    if ((rc = (call)) != BFF_OK) { lanes.drain(); return rc; }
+    REFINE_STEP(lanes.fork());
+    REFINE_ALL(refine_phase1(c, jobs[q], lanes.of(q)));
+    REFINE_STEP(lanes.join());
     tr.mark("enqueue1");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync1");
-    REFINE_ALL(refine_phase2(c, jobs[q], s));
+    REFINE_ALL(refine_phase2(c, jobs[q], lanes.of(q)));
+    REFINE_STEP(lanes.join());
     tr.mark("enqueue2");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync2");
-    REFINE_ALL(refine_phase3(c, jobs[q], s));
+    REFINE_ALL(refine_phase3(c, jobs[q], lanes.of(q)));
+    REFINE_STEP(lanes.join());
     tr.mark("enqueue3");
     BFF_CUDA(cudaStreamSynchronize(s));
     tr.mark("sync3");
 #undef REFINE_ALL
+#undef REFINE_STEP
     // final argmax (:288) and the matched IoU (:308)
     for (const RefineJob &j : jobs)
         for (int k = 0; k < j.m; ++k) {
