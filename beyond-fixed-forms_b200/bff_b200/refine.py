@@ -192,8 +192,11 @@ def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float, to_hos
     out = {"ins": [], "conf": [], "final_class": []}
     n_other = p1["other"].shape[0]
     kept, from_s1 = [], []
-    for k, iou in enumerate(p1["ious"]):
-        if iou > iou_thres:                      # float32 tensor element vs python float, like the reference (:360)
+    ious = p1["ious"]
+    # float32 tensor element vs python float, like the reference (:360); one vectorised compare when the IoUs are a tensor
+    above = (ious > iou_thres).tolist() if isinstance(ious, torch.Tensor) and ious.dim() == 1 else [bool(iou > iou_thres) for iou in ious]
+    for k, hit in enumerate(above):
+        if hit:
             if p1["sims"][k] < sim_thres:
                 continue
             kept.append(k)
@@ -207,10 +210,15 @@ def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float, to_hos
     out["final_class"] = [query] * total
     parts = [p1["other"]] if n_other else []
     if kept:
-        dev = p1["m2"].device
-        k_dev = torch.tensor(kept, dtype=torch.long, device=dev)
-        s1_flag = torch.tensor(from_s1, dtype=torch.bool, device=dev).unsqueeze(1)
-        parts.append(torch.where(s1_flag, p1["m1"][k_dev], p1["m2"][k_dev]))
+        m1, m2 = p1["m1"], p1["m2"]
+        if len(kept) == m2.shape[0] and not any(from_s1):
+            parts.append(m2)                     # every pair keeps its stage-2 mask: no index upload, no gather
+        elif len(kept) == m1.shape[0] and all(from_s1):
+            parts.append(m1)
+        else:
+            # one upload: row k of the result = row kept[k] of m1 (stage-1 mask) or of m2, taken from their concatenation
+            pick = torch.tensor([k if f else k + m1.shape[0] for k, f in zip(kept, from_s1)], dtype=torch.long).to(m2.device)
+            parts.append(torch.cat([m1, m2])[pick])
     rows = torch.cat(parts) if len(parts) > 1 else parts[0]
     ins = ops.unpack_bits(rows, p1["n_points"])
     out["ins"] = ops.to_host(ins) if to_host else ins
