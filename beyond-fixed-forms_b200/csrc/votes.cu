@@ -128,13 +128,16 @@ extern "C" int bff_vote_hist(const int32_t *mc, const int32_t *vc, int64_t n, in
 // >= +0, so equal bits <=> equal values), a second kernel compacts the set. Order of `values` is unspecified.
 namespace bff {
 __global__ void __launch_bounds__(256)
-vote_unique_insert_kernel(const uint32_t *__restrict__ hist, int mc_bins, int vc_bins, int mode, uint32_t *__restrict__ table, uint32_t cap_mask) {
+vote_unique_insert_kernel(const uint32_t *__restrict__ hist, int mc_bins, int vc_bins, int mode, uint32_t *__restrict__ table, uint32_t cap_mask,
+                          int hash_shift) {
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
     if (i >= (long long)mc_bins * vc_bins || hist[i] == 0u) return;
     const int a = (int)(i / vc_bins), b = (int)(i % vc_bins);
     const float val = mode == 0 ? __fdiv_rn((float)a, __fadd_rn((float)b, 1.0f)) : (float)a;
     const uint32_t bits = __float_as_uint(val);
-    uint32_t slot = (bits * 2654435761u) & cap_mask;
+    // Fibonacci hashing: the TOP bits of the product. (Ratios of small integers have all-zero low mantissa bits, and the low
+    // bits of a product depend on the low bits of the factors only: masking them instead piles every value into a few slots.)
+    uint32_t slot = (bits * 2654435761u) >> hash_shift;
     while (true) {
         uint32_t old = *reinterpret_cast<volatile uint32_t *>(table + slot);      // many bins share a value (0 / (b + 1) = 0 ...):
         if (old == bits) return;                                                   // look before the atomic
@@ -169,7 +172,8 @@ extern "C" int bff_vote_unique(const uint32_t *hist, int32_t mc_bins, int32_t vc
     const long long bins = (long long)mc_bins * vc_bins;
     BFF_CUDA(cudaMemsetAsync(table, 0xff, (size_t)table_size * 4, stream));
     BFF_CUDA(cudaMemsetAsync(count, 0, 4, stream));
-    vote_unique_insert_kernel<<<(unsigned)ceil_div64(bins, 256), 256, 0, stream>>>(hist, mc_bins, vc_bins, mode, table, (uint32_t)(table_size - 1));
+    vote_unique_insert_kernel<<<(unsigned)ceil_div64(bins, 256), 256, 0, stream>>>(hist, mc_bins, vc_bins, mode, table, (uint32_t)(table_size - 1),
+                                                                                     32 - (int)(63 - __builtin_clzll((unsigned long long)table_size)));
     vote_unique_compact_kernel<<<(unsigned)ceil_div64(table_size, 256), 256, 0, stream>>>(table, (uint32_t)table_size, values, count);
     BFF_LAUNCH_CHECK("vote_unique kernels");
     return BFF_OK;
