@@ -178,15 +178,36 @@ __global__ void iou_finalize_kernel(const int32_t *__restrict__ inter, const int
 }
 
 // ------------------------------------------------------------------ segmented OR
-__global__ void rows_or_reduce_kernel(const uint32_t *__restrict__ rows, long long words,
-                                      const int32_t *__restrict__ idx, const int32_t *__restrict__ seg,
-                                      uint32_t *__restrict__ out) {
+__global__ void __launch_bounds__(256)
+rows_or_reduce_kernel(const uint32_t *__restrict__ rows, long long words,
+                      const int32_t *__restrict__ idx, const int32_t *__restrict__ seg,
+                      uint32_t *__restrict__ out) {
+    // the group's member list goes through shared memory so that the row loads do not wait for an index load each,
+    // and eight of them are in flight per thread
+    __shared__ int32_t s_idx[256];
     const int g = blockIdx.y;
-    const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= words) return;
+    const long long w = (long long)blockIdx.x * 256 + threadIdx.x;
+    const bool live = w < words;
+    const int k0 = seg[g], k1 = seg[g + 1];
     uint32_t v = 0;
-    for (int k = seg[g]; k < seg[g + 1]; ++k) v |= __ldg(rows + (long long)idx[k] * words + w);
-    out[(long long)g * words + w] = v;
+    for (int base = k0; base < k1; base += 256) {
+        const int cnt = min(256, k1 - base);
+        __syncthreads();
+        if ((int)threadIdx.x < cnt) s_idx[threadIdx.x] = __ldg(idx + base + threadIdx.x);
+        __syncthreads();
+        if (live) {
+            int k = 0;
+            for (; k + 8 <= cnt; k += 8) {
+                uint32_t t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) t[u] = __ldg(rows + (long long)s_idx[k + u] * words + w);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v |= t[u];
+            }
+            for (; k < cnt; ++k) v |= __ldg(rows + (long long)s_idx[k] * words + w);
+        }
+    }
+    if (live) out[(long long)g * words + w] = v;
 }
 
 // ------------------------------------------------------------------ overlap resolution
@@ -219,12 +240,15 @@ row_program_kernel(uint32_t *__restrict__ rows, int n_rows, long long words,
 }
 
 // ------------------------------------------------------------------ AND keep + popcount
+constexpr int kAndPopWordsPerBlock = 2048;        // a row is cut into pieces so that a handful of rows still fills the GPU
 __global__ void __launch_bounds__(256)
 rows_and_popcount_kernel(uint32_t *__restrict__ rows, long long words, const uint32_t *__restrict__ keep,
                          int32_t *__restrict__ pop) {
-    uint32_t *r = rows + (long long)blockIdx.x * words;
+    uint32_t *r = rows + (long long)blockIdx.y * words;
+    const long long w0 = (long long)blockIdx.x * kAndPopWordsPerBlock;
+    const long long w1 = min(words, w0 + kAndPopWordsPerBlock);
     int s = 0;
-    for (long long w = threadIdx.x; w < words; w += 256) {
+    for (long long w = w0 + threadIdx.x; w < w1; w += 256) {
         uint32_t v = r[w];
         if (keep != nullptr) {
             v &= __ldg(keep + w);
@@ -239,7 +263,7 @@ rows_and_popcount_kernel(uint32_t *__restrict__ rows, long long words, const uin
     if (threadIdx.x == 0 && pop != nullptr) {
         int t = 0;
         for (int i = 0; i < 8; ++i) t += red[i];
-        pop[blockIdx.x] = t;
+        if (t) atomicAdd(pop + blockIdx.y, t);          // pop is zeroed by the host wrapper
     }
 }
 
@@ -431,7 +455,10 @@ extern "C" int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t wor
         return BFF_OK;
     }
     BFF_REQUIRE(rows, "bff_rows_and_popcount: null rows");
-    rows_and_popcount_kernel<<<n_rows, 256, 0, stream>>>(rows, words, keep, pop);
+    BFF_REQUIRE(n_rows <= 65535, "bff_rows_and_popcount: too many rows");
+    if (pop) BFF_CUDA(cudaMemsetAsync(pop, 0, (size_t)n_rows * 4, stream));
+    dim3 grid((unsigned)ceil_div64(words, kAndPopWordsPerBlock), (unsigned)n_rows);
+    rows_and_popcount_kernel<<<grid, 256, 0, stream>>>(rows, words, keep, pop);
     BFF_LAUNCH_CHECK("rows_and_popcount_kernel");
     return BFF_OK;
 }

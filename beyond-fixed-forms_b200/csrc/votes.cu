@@ -8,7 +8,17 @@ namespace bff {
 __global__ void __launch_bounds__(256)
 counts_max_kernel(const int32_t *__restrict__ mc, const int32_t *__restrict__ vc, long long n, int32_t *__restrict__ out2) {
     int m0 = 0, m1 = 0;
-    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    // 16-byte loads over the aligned body, scalar tail; ONE atomic pair per CTA (all CTAs hit the same two words)
+    const long long n4 = ((reinterpret_cast<uintptr_t>(mc) | reinterpret_cast<uintptr_t>(vc)) & 15) == 0 ? n / 4 : 0;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+        const int4 a = __ldg(reinterpret_cast<const int4 *>(mc) + i);
+        m0 = max(m0, max(max(a.x, a.y), max(a.z, a.w)));
+        if (vc != nullptr) {
+            const int4 b = __ldg(reinterpret_cast<const int4 *>(vc) + i);
+            m1 = max(m1, max(max(b.x, b.y), max(b.z, b.w)));
+        }
+    }
+    for (long long i = n4 * 4 + (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
         m0 = max(m0, __ldg(mc + i));
         if (vc != nullptr) m1 = max(m1, __ldg(vc + i));
     }
@@ -16,7 +26,11 @@ counts_max_kernel(const int32_t *__restrict__ mc, const int32_t *__restrict__ vc
         m0 = max(m0, __shfl_down_sync(0xffffffffu, m0, o));
         m1 = max(m1, __shfl_down_sync(0xffffffffu, m1, o));
     }
-    if ((threadIdx.x & 31) == 0) {
+    __shared__ int s0[8], s1[8];
+    if ((threadIdx.x & 31) == 0) { s0[threadIdx.x >> 5] = m0; s1[threadIdx.x >> 5] = m1; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { m0 = max(m0, s0[w]); m1 = max(m1, s1[w]); }
         if (m0 > 0) atomicMax(out2, m0);
         if (m1 > 0) atomicMax(out2 + 1, m1);
     }
@@ -97,8 +111,8 @@ extern "C" int bff_counts_max(const int32_t *mc, const int32_t *vc, int64_t n, i
     BFF_CUDA(cudaMemsetAsync(out2, 0, 8, stream));
     if (n == 0) return BFF_OK;
     BFF_REQUIRE(mc, "bff_counts_max: null counts");
-    long long blocks = ceil_div64(n, 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    long long blocks = ceil_div64(n, 256 * 4);
+    if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
     counts_max_kernel<<<(unsigned)blocks, 256, 0, stream>>>(mc, vc, n, out2);
     BFF_LAUNCH_CHECK("counts_max_kernel");
     return BFF_OK;
