@@ -445,9 +445,11 @@ def run_gpu(args):
     copy_stream = torch.cuda.Stream(device=dev, priority=-1 if args.upload.endswith('+hi') else 0)
     bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]   # double buffer, no allocation in the loop
     done = [None, None]
-    # The big buffers go through the SM copy kernel even where the copy engine alone is a little faster (probe below:
-    # 42 vs 47 GB/s on one box, 55 vs 51 on another): the running step's own small H2D/D2H staging copies would otherwise
-    # queue behind a 184 MB transfer on the same engine (measured: 5.2 ms per scene with the copy engine, 4.5 with the kernel)
+    # The next scene's buffers move on the H2D copy engine (55 GB/s here, against 46-51 GB/s for an SM copy kernel that
+    # shares SMs and the PCIe request queue with the running step). That only works because the running step never
+    # touches that engine: its own small staging copies go through bff_upload (pipeline.cu upload_i32, ops.small_to_device);
+    # a single cudaMemcpyAsync H2D inside the step would wait for the whole 184 MB transfer (measured before that change:
+    # 4.8-5.2 ms per scene with the copy engine, 4.4 ms with the kernel; now 3.55 ms vs 3.95 ms).
     big = max(g.host, key=lambda k_: g.host[k_].numel() * g.host[k_].element_size())
 
     def _time_copy(fn):
@@ -468,9 +470,9 @@ def run_gpu(args):
             for k_, v_ in g.host.items():
                 nbytes = v_.numel() * v_.element_size()
                 if use_sm_copy and nbytes:
-                    # SM-driven copy for EVERY buffer: the H2D copy engine stays free for the running step's own small
-                    # staging copies. (A copy-engine transfer queued in this stream behind the 3.6 ms depth kernel would
-                    # wait at the head of the engine's queue and hold those copies back: 4.4 ms per scene instead of 3.8.)
+                    # --upload sm: EVERY buffer through the SM copy kernel. (Mixing is the worst choice: a copy-engine
+                    # transfer queued in this stream behind a milliseconds-long copy kernel waits at the head of the
+                    # engine's queue and holds back every other stream's copies.)
                     ops.upload(bufs[slot][k_], v_, copy_stream)
                 elif chunk and nbytes > chunk:
                     src_b, dst_b = v_.view(-1).view(torch.uint8), bufs[slot][k_].view(-1).view(torch.uint8)
@@ -847,7 +849,7 @@ def main():
     ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the secondary frame-sharded measurement")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--cli-e2e", action="store_true", help="files-to-files run of both drop-in CLIs on an on-disk tree (configs[0]) and exit")
-    ap.add_argument("--upload", default="sm", help="pipelined e2e: how scene i+1's big buffers move while scene i runs: sm | ce | ce:<MiB>")
+    ap.add_argument("--upload", default="ce", help="pipelined e2e: how scene i+1's buffers move while scene i runs: ce (copy engine) | sm (bff_upload kernel) | ce:<MiB>")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

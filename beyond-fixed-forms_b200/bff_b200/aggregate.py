@@ -146,7 +146,7 @@ def filter_and_select(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Seq
     sel = (after64 > cfg["remove_small_masks"]) & (after64 > cfg["remove_filtered_masks"] * before64)
     idx = torch.nonzero(sel).reshape(-1)
     # every row kept (the usual case): the buffer itself, no index upload and no gather
-    out_rows = agg if idx.numel() == agg.shape[0] else agg[idx.to(agg.device)]
+    out_rows = agg if idx.numel() == agg.shape[0] else agg[ops.small_to_device(idx, agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
     result = {"ins": ops.to_host(ins) if to_host else ins, "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}
@@ -249,7 +249,7 @@ def select_rows(agg: torch.Tensor, conf_agg: torch.Tensor, labels_agg: Sequence[
     sel = (after64 > cfg["remove_small_masks"]) & (after64 > cfg["remove_filtered_masks"] * before64)
     idx = torch.nonzero(sel).reshape(-1)
     # every row kept (the usual case): the buffer itself, no index upload and no gather
-    out_rows = agg if idx.numel() == agg.shape[0] else agg[idx.to(agg.device)]
+    out_rows = agg if idx.numel() == agg.shape[0] else agg[ops.small_to_device(idx, agg.device)]
     ins = ops.unpack_bits(out_rows, n_points)
     log("after filtering", ins.shape)
     return {"ins": ops.to_host(ins) if to_host else ins, "conf": conf_agg[sel], "final_class": [labels_agg[i] for i in idx.tolist()]}, out_rows

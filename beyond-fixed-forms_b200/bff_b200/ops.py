@@ -371,6 +371,36 @@ def upload(dst: torch.Tensor, src_pinned: torch.Tensor, stream: Optional[torch.c
     return dst
 
 
+_STAGE_BYTES = 1 << 20
+_stage_rings: dict = {}
+
+
+def small_to_device(t: torch.Tensor, device) -> torch.Tensor:
+    """Small CPU tensor -> CUDA tensor through a pinned staging ring and bff_upload (an SM copy kernel on the current
+    stream) instead of a copy-engine transfer: index vectors of a few bytes must not queue behind a scene-sized
+    cudaMemcpyAsync that another stream has put on the H2D engine. Falls back to `.to(device)` for large tensors."""
+    import threading
+    device = torch.device(device)
+    t = t.contiguous()
+    nbytes = t.numel() * t.element_size()
+    if nbytes == 0 or nbytes > _STAGE_BYTES // 8 or device.type != "cuda":
+        return t.to(device)
+    key = (device.index or 0, threading.get_ident())
+    ring = _stage_rings.get(key)
+    if ring is None:
+        ring = _stage_rings[key] = [torch.empty(_STAGE_BYTES, dtype=torch.uint8).pin_memory(), 0]
+    need = (nbytes + 255) & ~255
+    if ring[1] + need > _STAGE_BYTES:
+        ring[1] = 0               # wrap: the oldest slots were consumed thousands of uploads (and several stream syncs) ago
+    slot = ring[0][ring[1]:ring[1] + nbytes]
+    ring[1] += need
+    slot.copy_(t.reshape(-1).view(torch.uint8))
+    out = torch.empty(t.shape, dtype=t.dtype, device=device)
+    check(lib().bff_upload(ptr(out), c_void_p(slot.data_ptr()), nbytes, current_stream()), "bff_upload")
+    _count()
+    return out
+
+
 def labels_to_rows(labels: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
     """labels (N,) int64 CUDA, ids (G,) int64 CUDA -> (G, ceil(N/32)) int32 packed rows, bit p of row g = labels[p] == ids[g]
     (bff_labels_to_rows; evaluator side, scannetv2_inst_eval.py:348)."""

@@ -54,7 +54,7 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
         log("Empty stage 2 mask")
         other = [i for i, l in enumerate(labels) if l == q_]
         return {"ious": [], "sims": [], "m1": None, "m2": None, "conf2": [], "n_points": n_points,
-                "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+                "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
     s2 = stage2["rows"] if "rows" in stage2 else ops.pack_bits(stage2["ins"].to(device))
     s2_conf = stage2["conf"]
     if FUSED and s2_conf.dtype == torch.float32:
@@ -100,7 +100,7 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
     log("Matched labels:", matched_labels)
     log("Clip similarities:", sims)
     return {"ious": ious, "sims": sims, "m1": s1[mm.to(device)], "m2": s2, "conf2": s2_conf, "n_points": n_points,
-            "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+            "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
 
 
 class _RefineJob:
@@ -137,9 +137,9 @@ class _RefineJob:
         log("iou for matched labels", ious)
         log("Matched labels:", matched_labels)
         log("Clip similarities:", sims)
-        mm_dev = torch.from_numpy(mm.astype(np.int64)).to(device)
+        mm_dev = ops.small_to_device(torch.from_numpy(mm.astype(np.int64)), device)
         return {"ious": ious, "sims": sims, "m1": s1[mm_dev], "m2": self.s2_out[:m], "conf2": torch.from_numpy(self.conf_out[:m].copy()),
-                "n_points": self.n_points, "other": s1[torch.tensor(other, dtype=torch.long, device=device)] if other else s1[:0]}
+                "n_points": self.n_points, "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
 
 
 def _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:
@@ -217,8 +217,8 @@ def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float, to_hos
             parts.append(m1)
         else:
             # one upload: row k of the result = row kept[k] of m1 (stage-1 mask) or of m2, taken from their concatenation
-            pick = torch.tensor([k if f else k + m1.shape[0] for k, f in zip(kept, from_s1)], dtype=torch.long).to(m2.device)
-            parts.append(torch.cat([m1, m2])[pick])
+            pick = torch.tensor([k if f else k + m1.shape[0] for k, f in zip(kept, from_s1)], dtype=torch.long)
+            parts.append(torch.cat([m1, m2])[ops.small_to_device(pick, m2.device)])
     rows = torch.cat(parts) if len(parts) > 1 else parts[0]
     ins = ops.unpack_bits(rows, p1["n_points"])
     out["ins"] = ops.to_host(ins) if to_host else ins

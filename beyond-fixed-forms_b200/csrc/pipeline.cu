@@ -74,8 +74,11 @@ static int upload_i32(bff_ctx *c, const std::vector<int32_t> &v, int32_t **dev_o
     int32_t *d = c->dev.get<int32_t>(n);
     if (!h || !d) return BFF_ENOMEM;
     if (!v.empty()) {
+        // staged through the pinned arena and pulled over by the SM copy kernel, NOT a copy-engine transfer: while the
+        // next scene's depth stack occupies the H2D engine (3.4 ms per 184 MB) a cudaMemcpyAsync here would wait for it
         memcpy(h, v.data(), v.size() * 4);
-        BFF_CUDA(cudaMemcpyAsync(d, h, v.size() * 4, cudaMemcpyHostToDevice, s));
+        const int rc = bff_upload(d, h, (int64_t)v.size() * 4, s);
+        if (rc != BFF_OK) return rc;
     }
     *dev_out = d;
     return BFF_OK;
