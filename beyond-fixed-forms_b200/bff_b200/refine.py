@@ -137,9 +137,11 @@ class _RefineJob:
         log("iou for matched labels", ious)
         log("Matched labels:", matched_labels)
         log("Clip similarities:", sims)
-        mm_dev = ops.small_to_device(torch.from_numpy(mm.astype(np.int64)), device)
-        return {"ious": ious, "sims": sims, "m1": s1[mm_dev], "m2": self.s2_out[:m], "conf2": torch.from_numpy(self.conf_out[:m].copy()),
-                "n_points": self.n_points, "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
+        # matched rows and the class's other rows: one index upload, one gather
+        pick = ops.small_to_device(torch.from_numpy(np.concatenate([mm.astype(np.int64), np.asarray(other, dtype=np.int64)])), device)
+        sel = s1[pick]
+        return {"ious": ious, "sims": sims, "m1": sel[:m], "m2": self.s2_out[:m], "conf2": torch.from_numpy(self.conf_out[:m].copy()),
+                "n_points": self.n_points, "other": sel[m:]}
 
 
 def _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:

@@ -329,8 +329,12 @@ int agg_phase2_groups(bff_ctx *c, AggJob &j, cudaStream_t s) {
     // ---- OR-merge the members (:214-223)
     int rc;
     int32_t *d_idx = nullptr, *d_seg = nullptr;
-    if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
-    if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
+    {   // members and segment bounds travel together: one staging copy instead of two
+        const size_t n_idx = idx.size();
+        idx.insert(idx.end(), seg.begin(), seg.end());
+        if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
+        d_seg = d_idx + n_idx;
+    }
     if ((rc = bff_rows_or_reduce(d->rows, j.words, d_idx, d_seg, g, d->agg_rows, s)) != BFF_OK) return rc;
 
     // ---- pair overlaps of the merged rows + row sums 'before' (:285-291, :592), issued now, read later
@@ -603,8 +607,12 @@ int refine_phase3(bff_ctx *c, RefineJob &j, cudaStream_t s) {
         d->s2_conf_out[k] = cur_conf[k];
     }
     int32_t *d_idx = nullptr, *d_seg = nullptr;
-    if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
-    if ((rc = upload_i32(c, seg, &d_seg, s)) != BFF_OK) return rc;
+    {   // members and segment bounds travel together: one staging copy instead of two
+        const size_t n_idx = idx.size();
+        idx.insert(idx.end(), seg.begin(), seg.end());
+        if ((rc = upload_i32(c, idx, &d_idx, s)) != BFF_OK) return rc;
+        d_seg = d_idx + n_idx;
+    }
     if ((rc = bff_rows_or_reduce(d->s2_rows, words, d_idx, d_seg, m, d->s2_out, s)) != BFF_OK) return rc;
 
     // ---- IoU of the merged stage-1 masks with the merged stage-2 masks (:285-290)
