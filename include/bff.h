@@ -307,13 +307,12 @@ BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *st
  * pass 1 modifies): phases are enqueued for all jobs before the stream is synchronised. Results equal n_jobs separate calls. */
 BFF_API int bff_refine_match_batch(bff_ctx *ctx, const bff_refine_desc *descs, int32_t n_jobs, void *stream);
 
-/* Host -> device copy done by a small kernel that reads PINNED host memory directly (zero-copy loads over
- * PCIe) instead of a copy engine. Used to prefetch the next scene's depth stack while the current scene is
- * processed: a 180 MB cudaMemcpyAsync would occupy the H2D copy engine and every small staging copy of the
- * running pipeline would queue behind it. `src_host` must be page-locked (cudaHostAlloc / cudaHostRegister /
- * torch pin_memory); dst and src 16-byte aligned, any size (the last bytes % 16 are moved by the same kernel: the call
- * never touches a copy engine, so small buffers can follow a large one in the same stream without parking a
- * copy-engine transfer behind a milliseconds-long kernel, where it would stall the other streams' copies). */
+/* Host -> device copy done by a small kernel that reads PINNED host memory directly (zero-copy loads over PCIe) instead
+ * of a copy engine; the last bytes % 16 are moved by the same kernel, so the call never touches a copy engine. The fused
+ * pipelines stage their small host vectors through it: while a scene-sized cudaMemcpyAsync of the NEXT scene occupies the
+ * H2D engine (3.4 ms per 184 MB), a few-byte cudaMemcpyAsync of the running pipeline would wait for all of it. It also
+ * serves as a bulk upload (50 GB/s) where the engines must stay free. `src_host` must be page-locked (cudaHostAlloc /
+ * cudaHostRegister / torch pin_memory); dst and src 16-byte aligned, any size. */
 BFF_API int bff_upload(void *dst_dev, const void *src_host, int64_t bytes, void *stream);
 
 /* out[k] = rows[idx[k]] (device gather of packed rows; idx on the HOST). */
