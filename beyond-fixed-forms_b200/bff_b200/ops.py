@@ -391,7 +391,9 @@ def small_to_device(t: torch.Tensor, device) -> torch.Tensor:
         ring = _stage_rings[key] = [torch.empty(_STAGE_BYTES, dtype=torch.uint8).pin_memory(), 0]
     need = (nbytes + 255) & ~255
     if ring[1] + need > _STAGE_BYTES:
-        ring[1] = 0               # wrap: the oldest slots were consumed thousands of uploads (and several stream syncs) ago
+        # wrap (once per ~4000 index vectors): an upload kernel that has not run yet may still read the oldest slots
+        torch.cuda.synchronize(device)
+        ring[1] = 0
     slot = ring[0][ring[1]:ring[1] + nbytes]
     ring[1] += need
     slot.copy_(t.reshape(-1).view(torch.uint8))

@@ -555,3 +555,25 @@ def test_unpack_bits_wide_store_path_on_ragged_rows(cuda_dev):
     _cabi.check(_cabi.lib().bff_unpack_bits(_cabi.ptr(p), rows, n, _cabi.ptr(out), _cabi.current_stream()), "bff_unpack_bits")
     np.testing.assert_array_equal(out.cpu().numpy().reshape(rows, n), d.astype(np.uint8))
     assert bool((buf[:3] == 7).all()) and bool((buf[3 + rows * n:] == 7).all())
+
+
+@pytest.mark.gpu
+def test_small_to_device_ring_wraps_without_losing_data(cuda_dev):
+    """ops.small_to_device (pinned staging ring + bff_upload): values survive the ring wrapping under a busy stream."""
+    from bff_b200 import ops
+    rng = np.random.default_rng(5)
+    busy = torch.empty(64 << 20, dtype=torch.uint8, device=cuda_dev)
+    outs, wants = [], []
+    for k in range(40):                                   # 40 x 100 KB > the 1 MB ring: wraps several times
+        busy.fill_(k & 255)                               # keeps the stream ahead of the host
+        a = torch.from_numpy(rng.integers(0, 1 << 40, 12800 + k, dtype=np.int64))
+        outs.append(ops.small_to_device(a, cuda_dev))
+        wants.append(a)
+    outs.append(ops.small_to_device(torch.tensor([], dtype=torch.long), cuda_dev))
+    wants.append(torch.tensor([], dtype=torch.long))
+    big = torch.arange(1 << 18, dtype=torch.int64)        # above the ring's per-upload limit: plain .to()
+    outs.append(ops.small_to_device(big, cuda_dev))
+    wants.append(big)
+    torch.cuda.synchronize()
+    for o, w in zip(outs, wants):
+        assert o.device.type == "cuda" and torch.equal(o.cpu(), w)
