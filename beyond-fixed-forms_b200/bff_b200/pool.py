@@ -83,4 +83,5 @@ def get_pool(device, workers: int = 2) -> QueryPool:
 # Measured on a B200 (bench.py --workload c3: 20 queries, 1351 lifted masks): 17.9 ms per scene with the sequential loop,
 # 14.3 ms with 2 workers, 19.0 with 4, 17.1 with 8; with two ranks on one host (2 workers each) 27 ms. Beyond the C calls
 # the Python glue of the chains contends for the GIL, so the gain is small and not stable: callers default to 1 worker
-# (BFF_QUERY_WORKERS / stage2.QUERY_WORKERS opt in). The real fix is one C++ call driving all chains.
+# (BFF_QUERY_WORKERS / stage2.QUERY_WORKERS opt in). The default for several queries is the batched pipelines instead
+# (bff_stage2_aggregate_batch / bff_refine_match_batch: one C++ call drives every query's phases, 6.9 ms per scene at c3).
