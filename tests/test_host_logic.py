@@ -108,3 +108,24 @@ def test_lpt_scene_assignment_and_costs():
     cfg = {k: (os.path.join(tree, v[2:]) if isinstance(v, str) and v.startswith("./") else v) for k, v in cfg.items()}
     assert schedule.scene_cost(cfg, "scene0001_00") == 3000 * 8 and schedule.scene_cost(cfg, "scene0002_00") == 2500 * 6
     assert schedule.dist_mode(3, 8) == "frame" and schedule.dist_mode(312, 8) == "scene"
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the CPU arm the driver runs beside ours): one JSON line with the contract's keys, the
+    same metric/unit as the GPU arm, a cpu_baseline describing the run and an e2e object without transfers."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--cpu-frames", "2", "--workload", "tiny"], capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "point-views/s" and d["higher_is_better"] is True
+    assert d["metric"].startswith("point-view projections/sec") and d["value"] > 0 and d["n_gpus"] == 1
+    assert d["steps"] == 1 and d["warmup"] == 0 and d["scaling"] == "weak" and d["vs_baseline"] is None
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
