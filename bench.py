@@ -161,9 +161,24 @@ class GpuScene:
         if self.nq > 1:
             self.host["mask_query"] = pin(np.asarray(mask_query, np.int32))
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
+        # device-resident decisions (bff_b200/devpipe.py): per query the lifted rows' confidences and the two stage-1 tables
+        # (is the label the query's class; CLIP-style similarity of query and label -- an INPUT of the path) travel with
+        # the scene's other inputs
+        from bff_b200 import devpipe
+        from bff_b200.refine import STAGE1_CLASS_NAMES
+        self.device_decisions = os.environ.get("BFF_DEVICE_DECISIONS", "1") != "0"
+        s1_labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
+        for qi, name in enumerate(self.names):
+            q_ = name.replace(" ", "_")
+            sims = {}
+            self.host[f"conf{qi}"] = pin(self.conf_q[qi].numpy() if len(self.conf_q[qi]) else np.zeros(1, np.float32))
+            self.host[f"isq{qi}"] = pin(np.asarray([l == q_ for l in s1_labels], np.uint8))
+            self.host[f"sim{qi}"] = pin(np.asarray([sims[l] if l in sims else sims.setdefault(l, fake_similarity(name, l)) for l in s1_labels], np.float64))
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
         self.row_index_dev = None
         if self.nq > 1 and torch.cuda.is_available():
             self.row_index_dev = [torch.tensor(ix, dtype=torch.long, device=device) for ix in self.row_index]
+            self.row_index_dev32 = [t.to(torch.int32) for t in self.row_index_dev]
         self.lift_events = None
         if torch.cuda.is_available():
             # recorded inside bff_lift_scene around its memsets + kernel: the launch itself, without host gaps
@@ -188,6 +203,9 @@ class GpuScene:
         from bff_b200 import ops, refine, stage2
         inp, cfg = self.inp, self.inp["cfg"]
         ev = (lambda: None) if timers is None else (lambda: timers.append(_event()))
+        if self.device_decisions and not (self.dist is not None and self.dist.world_size > 1) and cfg["min_aggragated_masks"] >= 1:
+            self._timing = timers is not None
+            return self.step_device(d, ev, to_host)
         ev()
         masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
         ev()
@@ -258,6 +276,51 @@ class GpuScene:
         self.last_stage2 = per_query[0] if per_query else None
         self.last_finals = finals
         return finals[0] if finals else None
+
+
+def _step_device(self, d, ev, to_host=True):
+    """The same step with every decision taken on the device (bff_stage2_device / bff_refine_device): the whole chain
+    lift -> aggregate -> filter -> refine is enqueued without a host round trip; the only synchronisation is the one
+    that brings the final counts back, after the last kernel."""
+    from bff_b200 import devpipe, ops
+    inp, cfg = self.inp, self.inp["cfg"]
+    ev()
+    masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+    ev()
+    out = self.lift(d, masks2d, timing=getattr(self, "_timing", False))
+    ev()
+    ev()                                                         # (no exchange on one GPU)
+    n1 = len(inp["stage1"]["ins"])
+    s1 = ops.rle_to_bits_dev(d["s1_runs"], n1, self.n)
+    wd = s1.shape[1]
+    s2s = []
+    for qi in self.my_queries:
+        rows_q = out.rows if self.row_index_dev is None else ops.rows_gather(out.rows, self.row_index_dev32[qi])
+        if rows_q.shape[0] == 0:                                 # nothing lifted for this query (:465-478): known on the host
+            s2s.append(None)
+            continue
+        s2s.append(devpipe.stage2_device(rows_q, d[f"conf{qi}"], self.labels_q[qi], out.masked_counts[qi], out.viewed_counts, self.n, cfg,
+                                         mc_cap=rows_q.shape[0], vc_cap=self.f))
+    ev()
+    rfs = []
+    for qi, s2 in zip(self.my_queries, s2s):
+        s1_q = s1.clone() if len(self.my_queries) > 1 else s1   # pass 1 ORs matched stage-1 rows in place (refinement.py:248)
+        if s2 is None:
+            rows2, n2, conf2 = torch.zeros((1, wd), dtype=torch.int32, device=self.dev), 0, torch.zeros((1,), dtype=torch.float32, device=self.dev)
+        else:
+            rows2, n2, conf2 = s2.out_rows, s2.n_selected_dev, s2.selected_conf_dev
+        rf = devpipe.refine_device(s1_q, rows2, n2, conf2, d[f"isq{qi}"], d[f"sim{qi}"], self.n, cfg, self.names[qi], select_mode=1)
+        rf.enqueue_unpack()
+        rfs.append(rf)
+    finals = [rf.final(to_host) for rf in rfs]
+    ev()
+    self.last_stage2_dev = s2s[0] if s2s else None
+    self.last_refine_dev = rfs[0] if rfs else None
+    self.last_finals = finals
+    return finals[0] if finals else None
+
+
+GpuScene.step_device = _step_device
 
 
 def _event():

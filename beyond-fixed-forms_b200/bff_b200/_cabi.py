@@ -59,6 +59,43 @@ class RefineDesc(ctypes.Structure):
     ]
 
 
+class Stage2DevDesc(ctypes.Structure):
+    """struct bff_stage2_dev_desc (include/bff.h)."""
+    _fields_ = [
+        ("rows", c_void_p), ("n_rows", c_int32), ("n_points", c_int64),
+        ("conf", c_void_p), ("label_id", c_void_p), ("mc", c_void_p), ("vc", c_void_p),
+        ("n_vote_points", c_int64), ("vote_point0", c_int64),
+        ("iou_thres", c_float), ("min_aggregated", c_int32), ("filter_mode", c_int32), ("filter_fraction", c_double),
+        ("small_is_float", c_int32), ("ratio_is_float", c_int32), ("small_i", c_int64), ("ratio_i", c_int64),
+        ("small_f", c_float), ("ratio_f", c_float), ("mc_cap", c_int32), ("vc_cap", c_int32),
+        ("out_rows", c_void_p), ("cap_groups", c_int32), ("result", c_void_p), ("comm", c_void_p),
+    ]
+
+
+class RefineDevDesc(ctypes.Structure):
+    """struct bff_refine_dev_desc (include/bff.h)."""
+    _fields_ = [
+        ("s1_rows", c_void_p), ("n1", c_int32), ("s2_rows", c_void_p), ("n2_dev", c_void_p), ("n2_host", c_int32),
+        ("cap2", c_int32), ("n_points", c_int64), ("s2_conf", c_void_p), ("stage1_iou_thres", c_float),
+        ("is_query", c_void_p), ("sim", c_void_p), ("select_mode", c_int32), ("sim_percentile", c_double),
+        ("sim_thres", c_double), ("refine_iou_thres", c_float),
+        ("s2_out", c_void_p), ("final_rows", c_void_p), ("result", c_void_p), ("comm", c_void_p),
+    ]
+
+
+# word offsets of the device result blocks (include/bff.h enums)
+S2R_N_GROUPS, S2R_N_SELECTED, S2R_N_OVERLAP, S2R_N_UNIQUE, S2R_ERROR, S2R_FILTER_VALUE, S2R_MC_MAX, S2R_VC_MAX, S2R_HEADER = 0, 1, 2, 3, 4, 5, 6, 7, 16
+RFR_N2_IN, RFR_N2_OUT, RFR_N_OR, RFR_N_OTHER, RFR_N_FINAL, RFR_ERROR, RFR_SIM_THRES, RFR_HEADER = 0, 1, 2, 3, 4, 5, 6, 16
+
+
+def stage2_dev_result_words(n_rows: int, cap: int) -> int:
+    return S2R_HEADER + 7 * cap + (cap + 1) + n_rows
+
+
+def refine_dev_result_words(n1: int, cap2: int) -> int:
+    return RFR_HEADER + 8 * cap2 + (cap2 + 1) + n1 + 2 * (n1 + cap2)
+
+
 # name -> (restype, argtypes); every symbol include/bff.h declares
 SYMBOLS = {
     "bff_version": (c_int, []),
@@ -71,6 +108,7 @@ SYMBOLS = {
     "bff_visibility": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_double, c_void_p, c_void_p]),
     "bff_mask_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "bff_mask_iou": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bff_set_iou_path": (c_int, [c_int32]),
     "bff_rows_or_reduce": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_counts_max": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "bff_vote_hist": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
@@ -91,6 +129,18 @@ SYMBOLS = {
     "bff_refine_match_batch": (c_int, [c_void_p, POINTER(RefineDesc), c_int32, c_void_p]),
     "bff_upload": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "bff_rows_gather": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
+    "bff_stage2_device": (c_int, [c_void_p, POINTER(Stage2DevDesc), c_void_p]),
+    "bff_refine_device": (c_int, [c_void_p, POINTER(RefineDevDesc), c_void_p]),
+    "bff_refine_select_device": (c_int, [c_void_p, POINTER(RefineDevDesc), c_double, c_void_p]),
+    "bff_rows_gather_dev": (c_int, [c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
+    "bff_unpack_bits_dc": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_comm_unique_id": (c_int, [c_void_p]),
+    "bff_comm_create": (c_int, [c_int, c_int, c_int, c_void_p, POINTER(c_void_p)]),
+    "bff_comm_destroy": (None, [c_void_p]),
+    "bff_comm_rank": (c_int, [c_void_p]),
+    "bff_comm_world": (c_int, [c_void_p]),
+    "bff_comm_allreduce_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
+    "bff_comm_allgather_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),
     "bff_ctx_destroy": (None, [c_void_p]),
     "bff_lift_scene_host": (c_int, [c_void_p, POINTER(LiftDesc), POINTER(c_int64), POINTER(c_int64)]),

@@ -416,6 +416,18 @@ def labels_to_rows(labels: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def rows_gather(rows: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """rows[idx] for packed rows with the int32 index vector already on the device (bff_rows_gather_dev): one kernel of
+    this library, no ATen indexing kernel and no synchronisation."""
+    rows = _cuda(rows, torch.int32, "rows")
+    idx = _cuda(idx, torch.int32, "idx").reshape(-1)
+    out = torch.empty((idx.numel(), rows.shape[1]), dtype=torch.int32, device=rows.device)
+    check(lib().bff_rows_gather_dev(ptr(rows), rows.shape[1], ptr(idx), idx.numel(), ptr(out), current_stream()), "bff_rows_gather_dev")
+    if idx.numel() and rows.shape[1]:
+        _count()
+    return out
+
+
 def rows_permute(rows: torch.Tensor, src_index: torch.Tensor, n_points: int) -> torch.Tensor:
     """out bit p of every row = rows bit src_index[p] (bff_rows_permute). rows (R,Wd) int32, src_index (N,) int32, CUDA."""
     rows = _cuda(rows, torch.int32, "rows")

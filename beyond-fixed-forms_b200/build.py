@@ -43,7 +43,7 @@ def build(force: bool = False, verbose: bool = False, defines=(), out: str = OUT
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [f"-D{d}" for d in defines]
-    cmd += ["-o", out] + sources()
+    cmd += ["-o", out] + sources() + ["-ldl"]
     subprocess.check_call(cmd)
     return out
 

@@ -48,11 +48,27 @@ struct Arena {
     int n_blocks = 0, cur = 0;
     size_t off = 0;
     bool pinned_host = false;
-    void reset() { cur = 0; off = 0; }
+    unsigned generation = 0;           // bumped whenever reserve() moved the block (cached CUDA graphs hold its pointers)
+    void reset();                      // recycle; several blocks are first merged into one (after a device synchronisation)
     void *take(size_t bytes);          // nullptr on allocation failure (error text set)
     void release();
+    // One contiguous block of at least `bytes` (the device-resident pipelines carve all their scratch from it with a
+    // layout computed up front). Growing synchronises the device, frees everything and allocates anew, so no pointer
+    // handed out earlier survives a growth; returns BFF_OK / BFF_ENOMEM.
+    int reserve(size_t bytes);
+    unsigned char *base() const { return n_blocks ? blocks[0].p : nullptr; }
     template <typename T> T *get(size_t count) { return reinterpret_cast<T *>(take(count * sizeof(T))); }
 };
+
+// internal launchers shared between translation units (kernels are only launchable from the file that defines them)
+int launch_merge_adjacency(const int32_t *inter, const int32_t *pop, const int32_t *label, int n, int stride_words, float thr,
+                           uint32_t *adj, cudaStream_t s);
+int launch_set_i32(int32_t *dst, int32_t value, cudaStream_t s);
+// Sum (op 0) / max (op 1) of int32 buffers over the ranks of `comm` on `s`; a null communicator is a single GPU: no-op.
+int comm_allreduce_i32(bff_comm *comm, int32_t *buf, size_t count, int op, cudaStream_t s);
+static inline int comm_allreduce_sum_i32(bff_comm *comm, int32_t *buf, size_t count, cudaStream_t s) {
+    return comm ? comm_allreduce_i32(comm, buf, count, 0, s) : BFF_OK;
+}
 
 }  // namespace bff
 

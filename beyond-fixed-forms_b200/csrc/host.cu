@@ -54,6 +54,46 @@ void *Arena::take(size_t bytes) {
     off = bytes;
     return p;
 }
+void Arena::reset() {
+    cur = 0;
+    off = 0;
+    if (n_blocks <= 1) return;
+    // a call outgrew the first block: one block of twice the total instead of a growing list (the list is capped, and a
+    // skipped block is wasted for the rest of a call). Nothing of the previous call may still be running on the old blocks.
+    size_t total = 0;
+    for (int i = 0; i < n_blocks; ++i) total += blocks[i].cap;
+    cudaDeviceSynchronize();
+    release();
+    unsigned char *p = nullptr;
+    const size_t cap = 2 * total;
+    const cudaError_t e = pinned_host ? cudaMallocHost(&p, cap) : cudaMalloc(&p, cap);
+    if (e != cudaSuccess) {              // fall back to on-demand blocks
+        cudaGetLastError();
+        return;
+    }
+    blocks[0] = {p, cap};
+    n_blocks = 1;
+}
+int Arena::reserve(size_t bytes) {
+    cur = 0;
+    off = 0;
+    if (n_blocks == 1 && blocks[0].cap >= bytes) return BFF_OK;
+    cudaDeviceSynchronize();
+    release();
+    size_t cap = bytes + bytes / 4;
+    if (cap < ((size_t)32 << 20)) cap = (size_t)32 << 20;
+    unsigned char *p = nullptr;
+    const cudaError_t e = pinned_host ? cudaMallocHost(&p, cap) : cudaMalloc(&p, cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("bff arena: cannot allocate %zu bytes of %s memory", cap, pinned_host ? "pinned host" : "device");
+        return BFF_ENOMEM;
+    }
+    blocks[0] = {p, cap};
+    n_blocks = 1;
+    ++generation;
+    return BFF_OK;
+}
 void Arena::release() {
     for (int i = 0; i < n_blocks; ++i) {
         if (pinned_host) cudaFreeHost(blocks[i].p);

@@ -6,6 +6,8 @@
 // each entry point and in include/bff.h.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "iou_umma.cuh"
 
@@ -13,11 +15,21 @@ namespace bff {
 
 // Row counts from which the tcgen05 (int8 tensor core) intersection beats the POPC kernel: the tensor path
 // works on 128 x 128 row tiles, so small operands (the 200 x 7 refinement calls) stay on the CUDA cores.
-// BFF_IOU_PATH=popc|umma forces one path (used by the tests to cross-check them).
+// bff_set_iou_path (or BFF_IOU_PATH=skinny|popc|umma, read once) forces one path: the tests cross-check them.
+static std::atomic<int> g_iou_path{-1};        // 0 automatic, 1 few-column kernel, 2 POPC tiles, 3 tcgen05
+static int iou_path() {
+    int p = g_iou_path.load(std::memory_order_relaxed);
+    if (p < 0) {
+        const char *e = getenv("BFF_IOU_PATH");
+        p = !e ? 0 : e[0] == 's' ? 1 : e[0] == 'p' ? 2 : e[0] == 'u' ? 3 : 0;
+        g_iou_path.store(p, std::memory_order_relaxed);
+    }
+    return p;
+}
 static int iou_use_umma(int n_a, int n_b, long long words) {
-    const char *e = getenv("BFF_IOU_PATH");
-    if (e && e[0] == 'p') return 0;
-    if (e && e[0] == 'u') return 1;
+    const int p = iou_path();
+    if (p == 2) return 0;
+    if (p == 3) return 1;
     return n_a >= 96 && n_b >= 96 && words >= 64;
 }
 
@@ -334,6 +346,12 @@ rle_to_bits_kernel(const int32_t *__restrict__ runs, long long n_runs, long long
 
 using namespace bff;
 
+extern "C" int bff_set_iou_path(int32_t path) {
+    BFF_REQUIRE(path >= 0 && path <= 3, "bff_set_iou_path: 0 automatic, 1 few-column, 2 POPC tiles, 3 tcgen05");
+    g_iou_path.store(path, std::memory_order_relaxed);
+    return BFF_OK;
+}
+
 extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
                             int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou, void *stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -342,7 +360,7 @@ extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, i
     BFF_REQUIRE(a && b, "bff_mask_iou: null rows");
     BFF_REQUIRE(!iou || (inter && pop_a && pop_b), "bff_mask_iou: iou needs inter, pop_a and pop_b buffers");
     // few columns (the refinement shapes): one pass that also yields both popcount vectors
-    if (inter && words > 0 && n_b <= 32 && !(getenv("BFF_IOU_PATH") && getenv("BFF_IOU_PATH")[0] != 's')) {
+    if (inter && words > 0 && n_b <= 32 && iou_path() <= 1) {
         const bool same_pop = pop_a != nullptr && pop_a == pop_b;           // symmetric call: one vector serves both
         BFF_CUDA(cudaMemsetAsync(inter, 0, (size_t)n_a * n_b * 4, stream));
         if (pop_a) BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));

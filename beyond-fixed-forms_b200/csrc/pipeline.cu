@@ -31,7 +31,7 @@ __global__ void merge_adjacency_kernel(const int32_t *__restrict__ inter, const 
     if (c < n) {
         const float fi = __int2float_rn(inter[(long long)r * n + c]);
         const float un = __fsub_rn(__fadd_rn(__int2float_rn(pop[r]), __int2float_rn(pop[c])), fi);
-        e = (label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
+        e = (label == nullptr || label[r] == label[c]) && (__fdiv_rn(fi, un) > thr);
     }
     const unsigned w = __ballot_sync(0xffffffffu, e);
     if ((threadIdx.x & 31) == 0 && (c >> 5) < stride_words) adj[(long long)r * stride_words + (c >> 5)] = w;
@@ -42,6 +42,22 @@ __global__ void rows_gather_kernel(const uint32_t *__restrict__ rows, long long 
     const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= words) return;
     out[(long long)blockIdx.y * words + w] = __ldg(rows + (long long)idx[blockIdx.y] * words + w);
+}
+
+__global__ void set_i32_kernel(int32_t *dst, int32_t value) { *dst = value; }
+
+int launch_merge_adjacency(const int32_t *inter, const int32_t *pop, const int32_t *label, int n, int stride_words, float thr,
+                           uint32_t *adj, cudaStream_t s) {
+    dim3 grid((unsigned)(stride_words * 32 / 256 + 1), (unsigned)n);
+    merge_adjacency_kernel<<<grid, 256, 0, s>>>(inter, pop, label, n, stride_words, thr, adj);
+    BFF_LAUNCH_CHECK("merge_adjacency_kernel");
+    return BFF_OK;
+}
+
+int launch_set_i32(int32_t *dst, int32_t value, cudaStream_t s) {
+    set_i32_kernel<<<1, 1, 0, s>>>(dst, value);
+    BFF_LAUNCH_CHECK("set_i32_kernel");
+    return BFF_OK;
 }
 
 }  // namespace bff
@@ -208,11 +224,7 @@ int agg_phase1(bff_ctx *c, AggJob &j, cudaStream_t s) {
         rc = bff_mask_iou(d->rows, n, d->rows, n, j.words, d_inter, d_pop, d_pop, nullptr, s);
         if (rc != BFF_OK) return rc;
     }
-    {
-        dim3 grid((unsigned)(j.stride_words * 32 / 256 + 1), (unsigned)n);
-        merge_adjacency_kernel<<<grid, 256, 0, s>>>(d_inter, d_pop, d_label, n, j.stride_words, d->iou_thres, d_adj);
-    }
-    BFF_LAUNCH_CHECK("merge_adjacency_kernel");
+    if ((rc = launch_merge_adjacency(d_inter, d_pop, d_label, n, j.stride_words, d->iou_thres, d_adj, s)) != BFF_OK) return rc;
     BFF_CUDA(cudaMemcpyAsync(j.h_adj, d_adj, adj_bytes, cudaMemcpyDeviceToHost, s));
     // the point filter (:512-583) does not depend on the grouping: its first step (the maxima that size the vote
     // histogram) rides on this synchronisation instead of paying for one of its own

@@ -160,6 +160,10 @@ BFF_API int bff_mask_gather(const int64_t *pix, const uint32_t *vis, int64_t n, 
  * inter / pop_a / pop_b / iou may each be NULL. */
 BFF_API int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, int32_t n_b, int64_t words,
                  int32_t *inter, int32_t *pop_a, int32_t *pop_b, float *iou, void *stream);
+/* Which intersection kernel bff_mask_iou takes: 0 automatic (<= 32 columns: one-pass kernel; >= 96 rows on both sides:
+ * tcgen05 int8; else POPC tiles), 1 / 2 / 3 force one of them (the tests cross-check the three; all are bit-exact).
+ * Process-wide; the initial value comes from the environment variable BFF_IOU_PATH (skinny|popc|umma), read once. */
+BFF_API int bff_set_iou_path(int32_t path);
 
 /* Replaces the OR-merges of merge_masks (projection_2d_to_3d.py:214-223) and refinement.py:248,269:
  * out[g] = OR over k in [seg[g], seg[g+1]) of rows[idx[k]].  rows (n_rows, words), out (n_groups, words). */
@@ -306,6 +310,132 @@ BFF_API int bff_refine_match(bff_ctx *ctx, const bff_refine_desc *desc, void *st
 /* The same for `n_jobs` independent jobs (queries of one scene; every job needs its own copy of the stage-1 rows, which
  * pass 1 modifies): phases are enqueued for all jobs before the stream is synchronised. Results equal n_jobs separate calls. */
 BFF_API int bff_refine_match_batch(bff_ctx *ctx, const bff_refine_desc *descs, int32_t n_jobs, void *stream);
+
+/* ---- device-resident pipelines: the same two stages with EVERY decision taken by small kernels on the device, so a
+ * call only enqueues work on `stream`: no stream synchronisation, no host round trip, CUDA-graph capturable. Counts that
+ * the host versions return (groups, selected rows, matches ...) live in a device RESULT BLOCK that later kernels read
+ * through pointers; the caller copies the block to the host when (and if) it wants the numbers. Buffers whose row count
+ * is only known on the device are sized by their upper bound (`cap_*`). The decisions are bit-identical to
+ * bff_stage2_aggregate / bff_refine_match (tests/test_devpipe_gpu.py compares both and the oracle port).
+ *
+ * Point-sharded multi-GPU form (comm != NULL): every rank passes the SAME rows / masks restricted to its own contiguous
+ * slice of the points (a multiple of 32 points; `n_points` = slice length), the additive integer results (intersections,
+ * popcounts) are summed over the ranks with ncclAllReduce on `stream`, and every rank takes the same decisions. ---- */
+typedef struct bff_comm bff_comm;
+/* The library's own NCCL communicator (libnccl is resolved with dlopen when the first of these is called, so single-GPU
+ * users never need it): rank 0 obtains 128 id bytes, the caller distributes them (torch.distributed broadcast), every
+ * rank creates its communicator on its device. All-reduce op: 0 = sum, 1 = max. */
+BFF_API int bff_comm_unique_id(void *id128);
+BFF_API int bff_comm_create(int device, int rank, int world, const void *id128, bff_comm **out);
+BFF_API void bff_comm_destroy(bff_comm *comm);
+BFF_API int bff_comm_rank(const bff_comm *comm);
+BFF_API int bff_comm_world(const bff_comm *comm);
+BFF_API int bff_comm_allreduce_i32(bff_comm *comm, int32_t *buf, int64_t count, int32_t op, void *stream);
+BFF_API int bff_comm_allgather_bytes(bff_comm *comm, const void *send, void *recv, int64_t bytes_per_rank, void *stream);
+
+/* Result block of bff_stage2_device: int32 words, R = n_rows, C = cap_groups. */
+enum {
+    BFF_S2R_N_GROUPS = 0,      /* aggregated masks that passed min_aggregated (:203) */
+    BFF_S2R_N_SELECTED = 1,    /* rows that passed the row filter (:601-623) = rows of out_rows */
+    BFF_S2R_N_OVERLAP = 2,     /* steps of solve_overlapping's schedule (:285-299) */
+    BFF_S2R_N_UNIQUE = 3,      /* distinct vote values the threshold was picked from (:514,:573) */
+    BFF_S2R_ERROR = 4,         /* bit 0: filter fraction selects an index outside the unique list (the reference raises
+                                  IndexError); bit 1: a scratch bound (mc_cap / vc_cap / cap_groups) was exceeded */
+    BFF_S2R_FILTER_VALUE = 5,  /* float32 bits of the picked threshold (:516,:576) */
+    BFF_S2R_MC_MAX = 6,
+    BFF_S2R_VC_MAX = 7,
+    BFF_S2R_HEADER = 16
+    /* then, in this order: group_first (C), group_size (C), group_conf (C, float32 bits), before (C), after (C),
+       selected (C: group index of every selected row), selected_conf (C, float32 bits), seg (C + 1), members (R) */
+};
+static inline int64_t bff_stage2_dev_result_words(int32_t n_rows, int32_t cap_groups) {
+    return BFF_S2R_HEADER + 7 * (int64_t)cap_groups + (cap_groups + 1) + n_rows;
+}
+
+typedef struct bff_stage2_dev_desc {
+    const uint32_t *rows;       /* device (n_rows, Wd) lifted rows in file order (:481) */
+    int32_t n_rows;
+    int64_t n_points;           /* points of this rank's slice (single GPU: all of them); Wd = ceil(n_points / 32) */
+    const float *conf;          /* DEVICE (n_rows) float32 confidences (:484-486) */
+    const int32_t *label_id;    /* DEVICE (n_rows), equal ids <=> equal label strings (:169-187); NULL = one label for all */
+    const int32_t *mc;          /* device (n_vote_points) masked_counts of this query, ALL points */
+    const int32_t *vc;          /* device (n_vote_points) viewed_counts; required for filter_mode 0 */
+    int64_t n_vote_points;      /* points the vote threshold is taken over (= n_points on a single GPU) */
+    int64_t vote_point0;        /* first point of this rank's slice inside mc / vc (0 on a single GPU) */
+    float iou_thres;            /* cfg.iou_thres as float32 */
+    int32_t min_aggregated;     /* cfg.min_aggragated_masks, >= 1 */
+    int32_t filter_mode;        /* 0 detected ratio, 1 occurrence, 2 none */
+    double filter_fraction;
+    /* row filter (:601-623) with torch's promotion rules: `after > small` is an int64 compare for a Python int and a
+       float32 compare for a Python float; `after > ratio * before` multiplies in float32 for a Python float */
+    int32_t small_is_float; int32_t ratio_is_float;
+    int64_t small_i; int64_t ratio_i;
+    float small_f; float ratio_f;
+    int32_t mc_cap, vc_cap;     /* upper bounds of the counts (masks of the query, viewed frames): size the histogram scratch */
+    /* outputs (device) */
+    uint32_t *out_rows;         /* (cap_groups, Wd): the selected rows after overlap resolution and the point filter */
+    int32_t cap_groups;         /* >= n_rows / min_aggregated */
+    int32_t *result;            /* bff_stage2_dev_result_words(n_rows, cap_groups) int32 */
+    bff_comm *comm;             /* NULL = single GPU */
+} bff_stage2_dev_desc;
+BFF_API int bff_stage2_device(bff_ctx *ctx, const bff_stage2_dev_desc *desc, void *stream);
+
+/* Result block of bff_refine_device: int32 words, n1 stage-1 masks, C = cap2. */
+enum {
+    BFF_RFR_N2_IN = 0,         /* stage-2 masks that came in */
+    BFF_RFR_N2_OUT = 1,        /* after merging the ones that share a stage-1 match (:258-281) */
+    BFF_RFR_N_OR = 2,          /* in-place stage-1 ORs of the merge loop (:248) */
+    BFF_RFR_N_OTHER = 3,       /* unmatched stage-1 masks of the query's class (:293) */
+    BFF_RFR_N_FINAL = 4,       /* rows of final_rows (pass 2, :330-412) */
+    BFF_RFR_ERROR = 5,         /* bit 0: similarity percentile selects an index outside the unique list (IndexError) */
+    BFF_RFR_SIM_THRES = 6,     /* float64 bits (2 words) of the similarity threshold that was applied */
+    BFF_RFR_HEADER = 16
+    /* then, in this order: sims (2 C, float64 bits: :297-302; the block must be 8-byte aligned), first_match (C: argmax of
+       :211), best (C: best_match_after_iou_check :252), match (C: :288), match_iou (C, float32 bits: :308), conf_out (C,
+       float32 bits), idx2 (C), seg2 (C + 1), other (n1), final_src (n1 + C: < n1 = stage-1 row, else n1 + row of s2_out),
+       final_conf (n1 + C, float32 bits) */
+};
+static inline int64_t bff_refine_dev_result_words(int32_t n1, int32_t cap2) {
+    return BFF_RFR_HEADER + 8 * (int64_t)cap2 + (cap2 + 1) + n1 + 2 * ((int64_t)n1 + cap2);
+}
+
+typedef struct bff_refine_dev_desc {
+    uint32_t *s1_rows;          /* device (n1, Wd) stage-1 masks, MODIFIED in place like the reference (:248) */
+    int32_t n1;
+    const uint32_t *s2_rows;    /* device (cap2, Wd) stage-2 masks, the first n2 rows are used */
+    const int32_t *n2_dev;      /* device: number of stage-2 masks (e.g. &result[BFF_S2R_N_SELECTED] of bff_stage2_device);
+                                   NULL = n2_host */
+    int32_t n2_host;
+    int32_t cap2;               /* upper bound of n2 */
+    int64_t n_points;           /* of this rank's slice */
+    const float *s2_conf;       /* DEVICE (cap2) */
+    float stage1_iou_thres;     /* cfg.stage1_iou_thres as float32 */
+    const uint8_t *is_query;    /* device (n1): stage-1 label == query with underscores (:293) */
+    const double *sim;          /* device (n1): text similarity of the query and stage-1 mask i's label (:297-302) */
+    int32_t select_mode;        /* 0: pass 1 only (the caller applies a global threshold later with bff_refine_select_device);
+                                   1: threshold = sorted(set(sims of THIS scene))[int(len * percentile)] (:317-324 for one scene),
+                                      0 when nothing matched; 2: threshold = sim_thres */
+    double sim_percentile;      /* cfg.refinment_sim_percentile */
+    double sim_thres;
+    float refine_iou_thres;     /* cfg.refiment_iou_thres as float32 */
+    /* outputs (device) */
+    uint32_t *s2_out;           /* (cap2, Wd) stage-2 rows after merging */
+    uint32_t *final_rows;       /* (n1 + cap2, Wd): rows of the saved masks, N_FINAL used (select_mode != 0); may be NULL with mode 0 */
+    int32_t *result;            /* bff_refine_dev_result_words(n1, cap2) int32 */
+    bff_comm *comm;
+} bff_refine_dev_desc;
+BFF_API int bff_refine_device(bff_ctx *ctx, const bff_refine_dev_desc *desc, void *stream);
+/* Pass 2 alone (refinement.py:330-412) on the state bff_refine_device(select_mode 0) left in `result`, with the global
+ * threshold of :317-324 that the caller computed over all scenes of the class. */
+BFF_API int bff_refine_select_device(bff_ctx *ctx, const bff_refine_dev_desc *desc, double sim_thres, void *stream);
+
+/* out[k] = rows[idx[k]], k < n_idx, with the index vector on the DEVICE: no staging copy, no synchronisation, any
+ * number of rows (bff_rows_gather takes a host vector and waits for its staging copy). */
+BFF_API int bff_rows_gather_dev(const uint32_t *rows, int64_t words, const int32_t *idx_dev, int32_t n_idx, uint32_t *out, void *stream);
+
+/* bff_unpack_bits for a row count that lives on the device: rows [0, min(*n_rows_dev, cap_rows)) are expanded,
+ * `dense` has room for cap_rows rows. */
+BFF_API int bff_unpack_bits_dc(const uint32_t *packed, const int32_t *n_rows_dev, int32_t cap_rows, int64_t n, uint8_t *dense, void *stream);
 
 /* Host -> device copy done by a small kernel that reads PINNED host memory directly (zero-copy loads over PCIe) instead
  * of a copy engine; the last bytes % 16 are moved by the same kernel, so the call never touches a copy engine. The fused

@@ -256,9 +256,13 @@ def test_tensor_core_intersections_equal_popc_path_and_oracle(cuda_dev, monkeypa
     da = torch.from_numpy(pack_rows(a).view(np.int32)).to(cuda_dev)
     db = torch.from_numpy(pack_rows(b).view(np.int32)).to(cuda_dev)
     res = {}
-    for path in ("umma", "popc"):
-        monkeypatch.setenv("BFF_IOU_PATH", path)
-        res[path] = (ops.mask_iou(da, db), ops.mask_iou(da))
+    from bff_b200 import _cabi
+    try:
+        for path, code in (("umma", 3), ("popc", 2)):
+            _cabi.check(_cabi.lib().bff_set_iou_path(code), "bff_set_iou_path")
+            res[path] = (ops.mask_iou(da, db), ops.mask_iou(da))
+    finally:
+        _cabi.lib().bff_set_iou_path(0)
     for k in range(2):
         for t_u, t_p in zip(res["umma"][k], res["popc"][k]):
             assert torch.equal(torch.nan_to_num(t_u.float(), nan=-1.0), torch.nan_to_num(t_p.float(), nan=-1.0))
@@ -501,9 +505,13 @@ def test_few_column_intersections_equal_tile_path_and_oracle(cuda_dev, monkeypat
     da = torch.from_numpy(pack_rows(a).view(np.int32)).to(cuda_dev)
     db = torch.from_numpy(pack_rows(b).view(np.int32)).to(cuda_dev)
     res = {}
-    for path in ("skinny", "popc"):
-        monkeypatch.setenv("BFF_IOU_PATH", path)
-        res[path] = (ops.mask_iou(da, db), ops.mask_iou(db))
+    from bff_b200 import _cabi
+    try:
+        for path, code in (("skinny", 1), ("popc", 2)):
+            _cabi.check(_cabi.lib().bff_set_iou_path(code), "bff_set_iou_path")
+            res[path] = (ops.mask_iou(da, db), ops.mask_iou(db))
+    finally:
+        _cabi.lib().bff_set_iou_path(0)
     for k in range(2):
         for t_s, t_p in zip(res["skinny"][k], res["popc"][k]):
             assert torch.equal(torch.nan_to_num(t_s.float(), nan=-1.0), torch.nan_to_num(t_p.float(), nan=-1.0))
