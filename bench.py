@@ -60,7 +60,7 @@ def query_names(n_queries: int):
 
 
 # ----------------------------------------------------------------------------- synthetic inputs
-def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, seed: int = 2000):
+def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, seed: int = 2000, strong: bool = False):
     """In-memory inputs of one scene in the reference's wire formats (RLE 2D masks per frame and query,
     uint16 depth at its native size, float64 poses/intrinsics, RLE stage-1 masks). Frames [rank*F, (rank+1)*F) of a
     (F*world)-frame trajectory are rendered on `device` (input fabrication, untimed)."""
@@ -69,15 +69,20 @@ def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, 
     from bff_b200.rle import rle_encode_rows
     w = WORKLOADS[workload]
     f_rank = w["n_frames"]
+    if strong:
+        # ONE scene of w["n_frames"] frames, rank r takes the contiguous block shard_bounds gives it (strong scaling)
+        from bff_b200.dist import shard_bounds
+        s_lo, s_hi = shard_bounds(w["n_frames"], world, rank)
+        f_rank = s_hi - s_lo
     nq = w.get("n_queries", 1)
     queries = query_names(nq)
     n_render = f_rank if max_frames is None else min(max_frames, f_rank)   # the CPU arms only need their sample
-    spec = synth.SceneSpec(n_points=w["n_points"], n_frames=f_rank * world, width=w["width"], height=w["height"],
+    spec = synth.SceneSpec(n_points=w["n_points"], n_frames=w["n_frames"] if strong else f_rank * world, width=w["width"], height=w["height"],
                            depth_width=w.get("depth_width", 0), depth_height=w.get("depth_height", 0),
                            n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=seed, n_queries=nq,
                            room=w.get("room", (6.0, 5.0, 2.8)))
     sc = synth.make_scene(spec)
-    lo, hi = rank * f_rank, (rank + 1) * f_rank
+    lo, hi = (s_lo, s_hi) if strong else (rank * f_rank, (rank + 1) * f_rank)
     hgt, wid = spec.height, spec.width
     dh, dw = (spec.depth_height or hgt), (spec.depth_width or wid)
     depth = np.zeros((f_rank, dh, dw), np.uint16)
@@ -154,6 +159,11 @@ class GpuScene:
         assert np.array_equal(x32.astype(np.float64), inp["xyz"])
         x4 = np.zeros((self.n, 4), np.float32)
         x4[:, :3] = x32
+        self.plan = None
+        if dist_ctx is not None and dist_ctx.world_size > 1:
+            from bff_b200.dist import ShardPlan
+            self.plan = ShardPlan(self.n, dist_ctx.world_size, dist_ctx.rank)
+            x4 = self.plan.padded_cloud(x4)        # NaN points behind the cloud: every point slice has the same width
         # host side (pinned): exactly what bff's loaders hand to the device
         self.host = dict(xyz=pin(x4), pinv=pin(inp["pinv"][perm]), depth=pin(inp["depth"][perm].view(np.int16)),
                          runs=pin(runs), offsets=pin(np.asarray(offsets, np.int32)),
@@ -203,8 +213,10 @@ class GpuScene:
         from bff_b200 import ops, refine, stage2
         inp, cfg = self.inp, self.inp["cfg"]
         ev = (lambda: None) if timers is None else (lambda: timers.append(_event()))
+        self._timing = timers is not None
+        if self.dist is not None and self.dist.world_size > 1 and getattr(self, "comm", None) is not None:
+            return self.step_sharded(d, ev, to_host)
         if self.device_decisions and not (self.dist is not None and self.dist.world_size > 1) and cfg["min_aggragated_masks"] >= 1:
-            self._timing = timers is not None
             return self.step_device(d, ev, to_host)
         ev()
         masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
@@ -323,6 +335,57 @@ def _step_device(self, d, ev, to_host=True):
 GpuScene.step_device = _step_device
 
 
+def _step_sharded(self, d, ev, to_host=True):
+    """One scene on G GPUs: rank r lifts its block of the frames over all points (rows written in G column slices), ONE
+    exchange hands every rank all rows restricted to its slice of the points plus the all-reduced votes, then every rank
+    runs the device-resident pipelines on its slice; their additive integer results are all-reduced inside the calls
+    and all ranks take the same decisions (bff_b200/dist.py). No host round trip before the final counts."""
+    from bff_b200 import devpipe, dist as dist_mod, ops
+    inp, cfg, plan, comm = self.inp, self.inp["cfg"], self.plan, self.comm
+    sw, world = plan.slice_words, plan.world
+    ev()
+    masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+    ev()
+    votes = torch.empty((self.nq + 1, plan.n_padded), dtype=torch.int32, device=self.dev)
+    out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
+                         mask_offset=d["offsets"] if self.n_masks else None, mask_query=d.get("mask_query") if self.n_masks else None,
+                         n_queries=self.nq, frame_viewed=d["viewed"], depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535),
+                         native_size=self.native, row_slices=(world, sw), votes=votes,
+                         timing_events=self.lift_events if getattr(self, "_timing", False) else None)
+    ev()
+    comm.allreduce_(votes)
+    rows = comm.exchange_rows(out.rows, self.rows_per_rank)
+    ev()
+    n1 = len(inp["stage1"]["ins"])
+    s1 = ops.rows_slice(ops.rle_to_bits_dev(d["s1_runs"], n1, self.n), plan.rank * sw, sw)
+    s2s = []
+    for qi in range(self.nq):
+        rows_q = rows if self.all_index_dev32[qi] is None else ops.rows_gather(rows, self.all_index_dev32[qi])
+        if rows_q.shape[0] == 0:
+            s2s.append(None)
+            continue
+        s2s.append(devpipe.stage2_device(rows_q, self.all_conf_dev[qi], self.all_labels[qi], votes[qi], votes[self.nq], plan.slice_points, cfg,
+                                         mc_cap=rows_q.shape[0], vc_cap=self.f_total, vote_point0=plan.point0, n_vote_points=self.n,
+                                         comm=comm.handle))
+    ev()
+    rfs = []
+    for qi, s2 in enumerate(s2s):
+        s1_q = s1.clone() if self.nq > 1 else s1
+        if s2 is None:
+            rows2, n2, conf2 = torch.zeros((1, sw), dtype=torch.int32, device=self.dev), 0, torch.zeros((1,), dtype=torch.float32, device=self.dev)
+        else:
+            rows2, n2, conf2 = s2.out_rows, s2.n_selected_dev, s2.selected_conf_dev
+        rfs.append(devpipe.refine_device(s1_q, rows2, n2, conf2, d[f"isq{qi}"], d[f"sim{qi}"], plan.slice_points, cfg, self.names[qi],
+                                         select_mode=1, comm=comm.handle))
+    finals = [dist_mod.gather_final(comm, plan, rf, to_host and plan.rank == 0) for rf in rfs]
+    ev()
+    self.last_finals = finals
+    return finals[0] if finals else None
+
+
+GpuScene.step_sharded = _step_sharded
+
+
 def _event():
     e = torch.cuda.Event(enable_timing=True)
     e.record()
@@ -430,8 +493,6 @@ def run_gpu(args):
     # run gives every rank its OWN c2-shaped scene and needs no data-path collective (weak scaling); the
     # frame-sharded variant of ONE scene (NCCL all-reduce + all-gather) is measured afterwards as `frame_sharded`.
     # (every rank fabricates the same seeded scene, so per-GPU work is identical by construction)
-    inp = build_inputs(args.workload, 0, 1, dev)
-    g = GpuScene(inp, dev, None)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
     def barrier():
@@ -439,6 +500,18 @@ def run_gpu(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if world > 1 and args.sharded_only:
+        fs = frame_sharded_run(args, ctx, dev, flush, barrier)
+        if rank == 0:
+            emit({"metric": "point-view projections/sec (whole lifting+aggregation+refinement step)", "value": fs["value"], "unit": "point-views/s",
+                  "n_gpus": world, "steps": fs["steps"], "warmup": args.warmup, "ms_per_step": fs["ms_per_step"], "higher_is_better": True,
+                  "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                  "config": {"workload": f"{args.workload}: one scene sharded over {world} GPUs"}, "frame_sharded": fs})
+        ctx.finalize()
+        return
+    inp = build_inputs(args.workload, 0, 1, dev)
+    g = GpuScene(inp, dev, None)
 
     d = g.upload()
     torch.cuda.synchronize()
@@ -643,6 +716,24 @@ def run_gpu(args):
         "clocks": clocks,
     }
     if fs is not None:
+        # N > 1: the measured headline is ONE scene sharded over the N GPUs (strong scaling: the scene and therefore the
+        # total work is fixed); the N independent replicas measured above (one scene per GPU, no collective) are kept as
+        # the secondary `replicas`
+        line["replicas"] = {k_: line[k_] for k_ in ("value", "unit", "ms_per_step", "stages_ms", "e2e", "gpu_launches", "lift_point_views_per_s")}
+        line["replicas"]["what"] = f"{world} independent {args.workload} scenes, one per GPU, no data-path collective (weak scaling)"
+        pv1 = g.n * fs["frames_total"]
+        line.update({"value": fs["value"], "ms_per_step": fs["ms_per_step"], "scaling": "strong", "steps": fs["steps"],
+                     "stages_ms": fs["stages_ms_rank0"], "lift_point_views_per_s": pv1 / (fs["lift_ms_per_launch_max"] * 1e-3)})
+        line["config"]["parallelism"] = (f"ONE {args.workload} scene on {world} GPUs: frame-sharded lifting ({fs['frames_total']} frames split), one exchange "
+                                         "(row slices + vote all-reduce over NCCL/NVLink), point-sharded aggregation + refinement")
+        line["config"]["frames_per_gpu"] = fs["frames_total"] / world
+        line["e2e"] = {"value": pv1 / (fs["e2e_ms_per_step"] * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": fs["h2d_bytes_per_step"],
+                       "d2h_bytes_per_step": fs["d2h_bytes_per_step"], "ms_per_step": fs["e2e_ms_per_step"],
+                       "how": "every rank uploads its frames' inputs from pinned host memory, the sharded step, final masks on rank 0's host; wall clock, max over ranks"}
+        alg_r = fs["lift_algorithmic_bytes_per_rank"]
+        ach = alg_r / (fs["lift_ms_per_launch_max"] * 1e-3) / 1e9
+        line["roofline"].update({"achieved": ach, "frac": ach / peak, "algorithmic_bytes_per_launch": alg_r, "ms_per_launch": fs["lift_ms_per_launch_max"],
+                                 "traffic": None, "note": "per-rank launch over this rank's frames"})
         line["frame_sharded"] = fs
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(inp, args.cpu_frames)
@@ -651,50 +742,101 @@ def run_gpu(args):
         ctx.finalize()
 
 
-def frame_sharded_run(args, ctx, dev, flush, barrier):
-    """ONE scene of F x world frames, rank r lifting frames [r F, (r+1) F) (weak scaling in frames), then the one
-    exchange step (int32 vote all-reduce + rank-ordered row all-gather over NCCL) and aggregation/refinement on
-    every rank. Returns the secondary result object; max over ranks."""
+def frame_sharded_run(args, ctx, dev, flush, barrier, workload=None, steps=None):
+    """STRONG scaling of ONE scene over the G ranks: rank r lifts its block of the scene's frames, one exchange (grouped
+    NCCL send/recv of row slices + int32 vote all-reduce), then the point-sharded device-resident pipelines (int32
+    all-reduces of the intersection matrices inside). Rank 0 also runs the same scene alone (the 1-GPU step of this
+    very run) for the speed-up, and the final masks of both are compared bit for bit. Max over ranks."""
     import torch.distributed as dist
+    from bff_b200 import dist as dist_mod
+    workload = workload or args.workload
     rank, world = ctx.rank, ctx.world_size
-    inp = build_inputs(args.workload, rank, world, dev)
+    inp = build_inputs(workload, rank, world, dev, strong=True)
     g = GpuScene(inp, dev, ctx)
     gathered = [None] * world
-    dist.all_gather_object(gathered, (g.n_masks, [[float(c) for c in cq] for cq in g.conf_q], g.labels_q, g.row_index))
+    dist.all_gather_object(gathered, (g.n_masks, [[float(c) for c in cq] for cq in g.conf_q], g.labels_q, g.row_index, g.f))
     g.rows_per_rank = [x[0] for x in gathered]
+    g.f_total = int(sum(x[4] for x in gathered))
     base = np.concatenate([[0], np.cumsum(g.rows_per_rank)])
     # per query: confidences, labels and row positions of the whole scene = rank blocks in rank order (file order)
-    g.all_conf = [torch.tensor([c for x in gathered for c in x[1][qi]], dtype=torch.float32) for qi in range(g.nq)]
+    g.all_conf_dev = [torch.tensor([c for x in gathered for c in x[1][qi]], dtype=torch.float32).to(dev) for qi in range(g.nq)]
     g.all_labels = [[l for x in gathered for l in x[2][qi]] for qi in range(g.nq)]
-    g.all_index_dev = [torch.tensor([int(base[r]) + i for r, x in enumerate(gathered) for i in x[3][qi]], dtype=torch.long, device=dev)
-                       for qi in range(g.nq)]
-    if g.nq > 1:
-        g.my_queries = list(range(rank, g.nq, world))       # after the exchange every rank refines its share of the queries
-    elif g.nq == 1:
-        g.all_index_dev = [None]
+    g.all_index_dev32 = [torch.tensor([int(base[r]) + i for r, x in enumerate(gathered) for i in x[3][qi]], dtype=torch.int32, device=dev)
+                         for qi in range(g.nq)]
+    if g.nq == 1:
+        g.all_index_dev32 = [None]
+    torch.cuda.synchronize()
+    g.comm = dist_mod.Comm(ctx, dev.index or 0)
     d = g.upload()
-    for _ in range(2):
-        g.step(d)
-    steps = max(1, min(args.steps, 5))
+    for _ in range(3):
+        final = g.step(d)
+    steps = steps or max(1, min(args.steps, 10))
     tot, stage = 0.0, np.zeros(5)
     barrier()
     for _ in range(steps):
         flush.fill_(1)
         barrier()
         tm = []
-        g.step(d, tm)
+        final = g.step(d, tm, to_host=False)
         torch.cuda.synchronize()
         stage += np.asarray([tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)])
         tot += tm[0].elapsed_time(tm[-1])
-    t = torch.tensor([tot], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.cpu()) / steps
-    return {"value": g.n * g.f * world / (ms * 1e-3), "unit": "point-views/s", "ms_per_step": ms, "steps": steps,
-            "frames_total": g.f * world, "lifted_masks_total": int(sum(g.rows_per_rank)),
+    finals_sharded = list(g.last_finals)
+    # ---- end to end: every rank uploads ITS frames' inputs from pinned host memory, the step, final masks to rank 0's host
+    e2e = 0.0
+    for _ in range(steps):
+        flush.fill_(1)
+        barrier()
+        t0 = time.perf_counter()
+        g.step(g.upload(), to_host=True)
+        torch.cuda.synchronize()
+        e2e += (time.perf_counter() - t0) * 1e3
+    d2h = sum(fn["ins"].numel() * fn["ins"].element_size() for fn in g.last_finals if isinstance(fn["ins"], torch.Tensor)) if rank == 0 else 0
+    barrier()
+    t = torch.tensor([tot, e2e, float(g.h2d_bytes), g.lift_events[0].elapsed_time(g.lift_events[1])], dtype=torch.float64, device=dev)
+    tmax = t.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    ms, e2e_ms, h2d_total, lift_ms_max = float(tmax[0]) / steps, float(tmax[1]) / steps, float(t[2]), float(tmax[3])
+    torch.cuda.synchronize()
+    # ---- the same scene on ONE GPU (rank 0, the others wait): speed-up and bit-exact parity of the final masks
+    single_ms, same = None, None
+    if rank == 0:
+        inp1 = build_inputs(workload, 0, 1, dev, strong=True)
+        g1 = GpuScene(inp1, dev, None)
+        d1 = g1.upload()
+        for _ in range(3):
+            g1.step(d1)
+        t1 = 0.0
+        for _ in range(steps):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            tm = []
+            g1.step(d1, tm, to_host=False)
+            torch.cuda.synchronize()
+            t1 += tm[0].elapsed_time(tm[-1])
+        single_ms = t1 / steps
+
+        def same_final(a, b):
+            if isinstance(a["ins"], list) or isinstance(b["ins"], list):
+                return isinstance(a["ins"], list) and isinstance(b["ins"], list)
+            return a["ins"].shape == b["ins"].shape and torch.equal(a["ins"].cpu(), b["ins"].cpu()) and \
+                torch.equal(torch.as_tensor(a["conf"]), torch.as_tensor(b["conf"]))
+        same = all(same_final(a, b) for a, b in zip(finals_sharded, g1.last_finals)) and len(finals_sharded) == len(g1.last_finals)
+        if not same:
+            raise AssertionError("frame-sharded final masks differ from the single-GPU result of the same scene")
+    barrier()
+    g.comm.close()
+    return {"value": g.n * g.f_total / (ms * 1e-3), "unit": "point-views/s", "ms_per_step": ms, "steps": steps, "scaling": "strong",
+            "workload": workload, "frames_total": g.f_total, "lifted_masks_total": int(sum(g.rows_per_rank)),
             "stages_ms_rank0": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
                                         (stage / steps).round(4).tolist())),
-            "queries": g.nq, "queries_per_rank": len(g.my_queries),
-            "collectives": "all_reduce(SUM,int32)[votes] + all_gather[packed rows] + all_gather[int32 IoU row blocks], NCCL"}
+            "e2e_ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d_total), "d2h_bytes_per_step": int(d2h),
+            "lift_ms_per_launch_max": lift_ms_max, "lift_algorithmic_bytes_per_rank": lift_algorithmic_bytes(g),
+            "queries": g.nq, "single_gpu_ms_same_scene": single_ms, "speedup_vs_single_gpu": (single_ms / ms) if single_ms else None,
+            "final_masks_identical_to_single_gpu": same,
+            "collectives": "int32 all-reduce [votes], grouped send/recv [row slices], int32 all-reduces [intersections, popcounts] "
+                           "inside the point-sharded pipelines; own NCCL communicator (bff_comm)"}
 
 
 # ----------------------------------------------------------------------------- CPU baseline (oracle port)
@@ -909,7 +1051,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-frames", type=int, default=40, help="frames in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the secondary frame-sharded measurement")
+    ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the frame-sharded (strong scaling) measurement")
+    ap.add_argument("--sharded-only", action="store_true", help="N>1: only the sharded scene (with its single-GPU cross-check), no replicas")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--cli-e2e", action="store_true", help="files-to-files run of both drop-in CLIs on an on-disk tree (configs[0]) and exit")
     ap.add_argument("--upload", default="ce", help="pipelined e2e: how scene i+1's buffers move while scene i runs: ce (copy engine) | sm (bff_upload kernel) | ce:<MiB>")

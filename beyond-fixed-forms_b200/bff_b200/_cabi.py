@@ -34,6 +34,7 @@ class LiftDesc(ctypes.Structure):
         ("frames_per_chunk", c_int32), ("reserved", c_int32),
         ("src_height", c_int32), ("src_width", c_int32), ("resize_x", c_void_p), ("resize_y", c_void_p),
         ("ev_start", c_void_p), ("ev_stop", c_void_p),
+        ("n_row_slices", c_int32), ("reserved2", c_int32), ("row_slice_words", c_int64),
     ]
 
 
@@ -141,6 +142,9 @@ SYMBOLS = {
     "bff_comm_world": (c_int, [c_void_p]),
     "bff_comm_allreduce_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "bff_comm_allgather_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "bff_comm_exchange_rows": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
+    "bff_rows_slice": (c_int, [c_void_p, c_int32, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
+    "bff_rows_unslice": (c_int, [c_void_p, c_int32, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
     "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),
     "bff_ctx_destroy": (None, [c_void_p]),
     "bff_lift_scene_host": (c_int, [c_void_p, POINTER(LiftDesc), POINTER(c_int64), POINTER(c_int64)]),

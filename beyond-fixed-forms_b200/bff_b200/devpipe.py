@@ -97,7 +97,7 @@ class Stage2Dev:
 
 def stage2_device(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], mc: torch.Tensor, vc: Optional[torch.Tensor],
                   n_points: int, cfg, mc_cap: Optional[int] = None, vc_cap: int = 0, label_id: Optional[torch.Tensor] = None,
-                  vote_point0: int = 0, comm=None) -> Stage2Dev:
+                  vote_point0: int = 0, n_vote_points: Optional[int] = None, comm=None) -> Stage2Dev:
     """aggregate + point filter + solve_overlapping + row filter of one query's lifted rows, enqueued without any
     synchronisation. rows (n,Wd) int32 CUDA; conf (n,) float32 CUDA; mc / vc int32 CUDA vote vectors (over ALL points
     when the rows are one rank's point slice: then `vote_point0` is the slice's first point and `n_points` its length);
@@ -122,7 +122,7 @@ def stage2_device(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str],
     d = _cabi.Stage2DevDesc()
     d.rows, d.n_rows, d.n_points = ptr(rows), n, int(n_points)
     d.conf, d.label_id, d.mc, d.vc = ptr(conf), ptr(label_id), ptr(mc), ptr(vc if mode == 0 else None)
-    d.n_vote_points, d.vote_point0 = int(mc.numel()), int(vote_point0)
+    d.n_vote_points, d.vote_point0 = int(mc.numel() if n_vote_points is None else n_vote_points), int(vote_point0)
     d.iou_thres, d.min_aggregated, d.filter_mode, d.filter_fraction = float(np.float32(cfg["iou_thres"])), min_agg, mode, frac
     d.small_is_float, d.small_i, d.small_f = _scalar_kind(cfg["remove_small_masks"])
     d.ratio_is_float, d.ratio_i, d.ratio_f = _scalar_kind(cfg["remove_filtered_masks"])

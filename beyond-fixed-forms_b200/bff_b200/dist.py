@@ -129,6 +129,115 @@ def lift_sharded(ctx: DistCtx, xyz: np.ndarray, intrinsics: np.ndarray, scene_2d
     return lift_mod.LiftedScene(xyz.shape[0], lift_mod.split_rows(rows, per_frame, queries), mc, vc, f)
 
 
+# ----------------------------------------------------------------------------- frame-sharded lift -> point-sharded pipelines
+# Frames are independent only up to the votes and the lifted rows; everything after the frame loop (the all-pairs IoU,
+# merges, filters, refinement) is element-wise over POINTS plus tiny decisions. So the work is handed over once: rank r
+# lifts its block of frames over ALL points, writing its rows in G column slices (ops.lift_scene(row_slices=...)); one
+# grouped send/recv gives every rank ALL rows of the scene restricted to ITS contiguous slice of the points; the votes are
+# all-reduced. From there every rank runs the device-resident pipelines (devpipe.py) on its slice, the additive integer
+# results (intersections, popcounts) are all-reduced inside those calls, and every rank takes the same decisions. No
+# rank ever holds or computes the whole quadratic step. The cloud is padded with NaN points (never visible) to
+# G * slice_words * 32 points so that all slices have the same width.
+@dataclasses.dataclass
+class ShardPlan:
+    n_points: int
+    world: int
+    rank: int
+
+    @property
+    def words(self) -> int:
+        return (self.n_points + 31) // 32
+
+    @property
+    def slice_words(self) -> int:
+        return max(1, -(-self.words // self.world))
+
+    @property
+    def n_padded(self) -> int:
+        return self.world * self.slice_words * 32
+
+    @property
+    def slice_points(self) -> int:
+        return self.slice_words * 32
+
+    @property
+    def point0(self) -> int:
+        return self.rank * self.slice_points
+
+    def padded_cloud(self, xyz4: np.ndarray) -> np.ndarray:
+        """(N,4) float32 -> (n_padded,4) with NaN points behind the cloud (a NaN point is never visible)."""
+        out = np.full((self.n_padded, 4), np.nan, np.float32)
+        out[: xyz4.shape[0]] = xyz4
+        out[:, 3] = 0.0
+        return out
+
+
+class Comm:
+    """The library's own NCCL communicator (bff_comm): created from torch.distributed's process group, which carries
+    the 128-byte unique id from rank 0 to the others."""
+
+    def __init__(self, ctx: DistCtx, device_index: int):
+        import ctypes
+        import torch.distributed as dist
+        from . import _cabi
+        self.ctx = ctx
+        ident = ctypes.create_string_buffer(128)
+        if ctx.rank == 0:
+            _cabi.check(_cabi.lib().bff_comm_unique_id(ident), "bff_comm_unique_id")
+        box = [bytes(ident.raw)]
+        dist.broadcast_object_list(box, src=0)
+        self._id = ctypes.create_string_buffer(box[0], 128)
+        h = ctypes.c_void_p()
+        _cabi.check(_cabi.lib().bff_comm_create(int(device_index), ctx.rank, ctx.world_size, self._id, ctypes.byref(h)), "bff_comm_create")
+        self.handle = h
+
+    def allreduce_(self, t: torch.Tensor, op: int = 0) -> torch.Tensor:
+        from . import _cabi
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise TypeError("allreduce_ needs a contiguous int32 tensor")
+        _cabi.check(_cabi.lib().bff_comm_allreduce_i32(self.handle, _cabi.ptr(t), t.numel(), op, _cabi.current_stream()), "bff_comm_allreduce_i32")
+        return t
+
+    def exchange_rows(self, rows_sliced: torch.Tensor, rows_per_rank: Sequence[int]) -> torch.Tensor:
+        """(G, n_local, slice_words) -> (sum(rows_per_rank), slice_words): all rows of the scene, this rank's points."""
+        from . import _cabi
+        g, n_local, sw = rows_sliced.shape
+        rpr = np.asarray(rows_per_rank, np.int32)
+        out = torch.empty((int(rpr.sum()), sw), dtype=torch.int32, device=rows_sliced.device)
+        _cabi.check(_cabi.lib().bff_comm_exchange_rows(self.handle, _cabi.ptr(rows_sliced), n_local, _cabi.ptr(rpr), sw, _cabi.ptr(out),
+                                                       _cabi.current_stream()), "bff_comm_exchange_rows")
+        return out
+
+    def allgather_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        """(k, slice_words) on every rank -> (G, k, slice_words) on every rank."""
+        from . import _cabi
+        rows = rows.contiguous()
+        out = torch.empty((self.ctx.world_size,) + tuple(rows.shape), dtype=rows.dtype, device=rows.device)
+        _cabi.check(_cabi.lib().bff_comm_allgather_bytes(self.handle, _cabi.ptr(rows), _cabi.ptr(out), rows.numel() * rows.element_size(),
+                                                         _cabi.current_stream()), "bff_comm_allgather_bytes")
+        return out
+
+    def close(self):
+        from . import _cabi
+        if self.handle:
+            _cabi.lib().bff_comm_destroy(self.handle)
+            self.handle = None
+
+
+def gather_final(comm: Comm, plan: ShardPlan, rf, to_host: bool = True) -> dict:
+    """Final dict of a point-sharded bff_refine_device call: every rank holds its column slice of the saved rows (the
+    decisions, hence the counts, are the same everywhere); the slices are all-gathered and re-assembled into (k, N) bool."""
+    from . import ops
+    h = rf.header()
+    k = h["n_final"]
+    if k == 0:
+        return {"ins": [], "conf": [], "final_class": []}
+    slices = comm.allgather_rows(rf.final_rows[:k])
+    rows = ops.rows_unslice(slices, plan.words)
+    ins = ops.unpack_bits(rows, plan.n_points)
+    return {"ins": ops.to_host(ins) if to_host else ins, "conf": torch.from_numpy(h["final_conf"].copy()), "final_class": [rf.query] * k}
+
+
 PAIRS_MIN_ROWS = int(os.environ.get("BFF_PAIRS_MIN_ROWS", "512"))   # below this the one-GPU call is cheaper than two more collectives
 
 

@@ -47,7 +47,8 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
                depth_scale: float = 1000.0, depth_range: Optional[Sequence[float]] = None,
                want_rows: bool = True, want_counts: bool = True, want_viewed: bool = True,
                debug: bool = False, frames_per_chunk: int = 0, timing_events=None,
-               native_size: Optional[Sequence[int]] = None) -> LiftOutput:
+               native_size: Optional[Sequence[int]] = None, row_slices: Optional[Sequence[int]] = None,
+               votes: Optional[torch.Tensor] = None) -> LiftOutput:
     """One launch over all frames of a scene (bff_lift_scene).
 
     xyz         (N,4) float32 [x,y,z,_] or (N,3) float64, CUDA
@@ -57,6 +58,9 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
                 native_size=(Hs,Ws) != (H,W): (F,Hs,Ws) raw sensor units sampled in the kernel exactly like
                 cv2.resize(depth, (W,H)) (projection_2d_to_3d.py:436) -- BFF_DEPTH_U16_BILINEAR
     masks2d     (sumM, ceil(H*W/32)) int32 packed 2D masks in frame order; mask_offset (F+1,) int32
+    row_slices  (G, slice_words): rows come back as (G, sumM, slice_words) -- the words of every row cut into G column
+                slices, slice-major (the send layout of the point-sharded multi-GPU exchange, dist.py)
+    votes       optional (Q+1, N) int32 CUDA buffer that receives [masked_counts | viewed_counts] (one all-reduce)
     Returns packed rows (sumM, Wd) int32, masked_counts (Q,N) int32, viewed_counts (N,) int32."""
     dev = xyz.device
     if xyz.dtype == torch.float32:
@@ -108,9 +112,22 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     if frame_viewed is not None:
         frame_viewed = _cuda(frame_viewed, torch.uint8, "frame_viewed")
     wd = words_for(n)
-    rows = torch.empty((n_masks, wd), dtype=torch.int32, device=dev) if want_rows else None
-    mc = torch.empty((n_queries, n), dtype=torch.int32, device=dev) if want_counts else None
-    vc = torch.empty((n,), dtype=torch.int32, device=dev) if want_viewed else None
+    if row_slices is not None:
+        g_sl, sw = int(row_slices[0]), int(row_slices[1])
+        if g_sl * sw < wd:
+            raise ValueError("row slices do not cover the row")
+        rows = torch.empty((g_sl, n_masks, sw), dtype=torch.int32, device=dev) if want_rows else None
+    else:
+        rows = torch.empty((n_masks, wd), dtype=torch.int32, device=dev) if want_rows else None
+    if votes is not None:
+        if votes.dtype != torch.int32 or tuple(votes.shape) != (n_queries + 1, n) or not votes.is_contiguous() or not votes.is_cuda:
+            raise ValueError("votes must be a contiguous (Q+1, N) int32 CUDA tensor")
+        mc, vc = votes[:n_queries], votes[n_queries]
+        if not want_viewed:
+            vc.zero_()
+    else:
+        mc = torch.empty((n_queries, n), dtype=torch.int32, device=dev) if want_counts else None
+        vc = torch.empty((n,), dtype=torch.int32, device=dev) if want_viewed else None
     pix = torch.empty((f, n, 2), dtype=torch.int64, device=dev) if debug else None
     vis = torch.empty((f, wd), dtype=torch.int32, device=dev) if debug else None
     d = LiftDesc()
@@ -124,8 +141,10 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
         d.depth_min, d.depth_max = float(depth_range[0]), float(depth_range[1])
     d.masks2d, d.mask_offset, d.mask_query = ptr(masks2d), ptr(mask_offset), ptr(mask_query)
     d.n_masks, d.n_queries, d.frame_viewed = n_masks, int(n_queries), ptr(frame_viewed)
-    d.rows, d.masked_counts, d.viewed_counts = ptr(rows), ptr(mc), ptr(vc)
+    d.rows, d.masked_counts, d.viewed_counts = ptr(rows), ptr(mc), ptr(vc if (want_viewed or votes is None) else None)
     d.debug_pix, d.debug_vis = ptr(pix), ptr(vis)
+    if row_slices is not None:
+        d.n_row_slices, d.row_slice_words = g_sl, sw
     d.frames_per_chunk = int(frames_per_chunk)
     if taps is not None:
         d.src_height, d.src_width, d.resize_x, d.resize_y = hs, ws, ptr(taps[0]), ptr(taps[1])
@@ -424,6 +443,27 @@ def rows_gather(rows: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     out = torch.empty((idx.numel(), rows.shape[1]), dtype=torch.int32, device=rows.device)
     check(lib().bff_rows_gather_dev(ptr(rows), rows.shape[1], ptr(idx), idx.numel(), ptr(out), current_stream()), "bff_rows_gather_dev")
     if idx.numel() and rows.shape[1]:
+        _count()
+    return out
+
+
+def rows_slice(rows: torch.Tensor, word0: int, slice_words: int) -> torch.Tensor:
+    """Words [word0, word0 + slice_words) of every packed row, zero beyond the row (bff_rows_slice)."""
+    rows = _cuda(rows, torch.int32, "rows")
+    out = torch.empty((rows.shape[0], int(slice_words)), dtype=torch.int32, device=rows.device)
+    check(lib().bff_rows_slice(ptr(rows), rows.shape[0], rows.shape[1], int(word0), int(slice_words), ptr(out), current_stream()), "bff_rows_slice")
+    if rows.shape[0] and slice_words:
+        _count()
+    return out
+
+
+def rows_unslice(slices: torch.Tensor, words: int) -> torch.Tensor:
+    """(G, R, slice_words) column slices -> (R, words) rows (bff_rows_unslice)."""
+    slices = _cuda(slices, torch.int32, "slices")
+    g, r, sw = slices.shape
+    out = torch.empty((r, int(words)), dtype=torch.int32, device=slices.device)
+    check(lib().bff_rows_unslice(ptr(slices), g, r, sw, int(words), ptr(out), current_stream()), "bff_rows_unslice")
+    if r and words:
         _count()
     return out
 

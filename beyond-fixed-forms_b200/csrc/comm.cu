@@ -24,6 +24,10 @@ struct NcclApi {
     int (*CommDestroy)(nccl_comm_t) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
     int (*AllGather)(const void *, void *, size_t, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void *, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
     int (*GetVersion)(int *) = nullptr;
 };
@@ -54,6 +58,10 @@ int load_nccl() {
     BFF_NCCL_SYM(CommDestroy, "ncclCommDestroy");
     BFF_NCCL_SYM(AllReduce, "ncclAllReduce");
     BFF_NCCL_SYM(AllGather, "ncclAllGather");
+    BFF_NCCL_SYM(Send, "ncclSend");
+    BFF_NCCL_SYM(Recv, "ncclRecv");
+    BFF_NCCL_SYM(GroupStart, "ncclGroupStart");
+    BFF_NCCL_SYM(GroupEnd, "ncclGroupEnd");
     BFF_NCCL_SYM(GetErrorString, "ncclGetErrorString");
     BFF_NCCL_SYM(GetVersion, "ncclGetVersion");
 #undef BFF_NCCL_SYM
@@ -137,5 +145,36 @@ extern "C" int bff_comm_allgather_bytes(bff_comm *c, const void *send, void *rec
         return BFF_OK;
     }
     BFF_NCCL(g_nccl.AllGather(send, recv, (size_t)bytes_per_rank, kNcclUint8, c->comm, (cudaStream_t)stream));
+    return BFF_OK;
+}
+
+extern "C" int bff_comm_exchange_rows(bff_comm *c, const uint32_t *send, int32_t n_local_rows, const int32_t *rows_per_rank,
+                                      int64_t slice_words, uint32_t *recv, void *stream_) {
+    cudaStream_t s = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_local_rows >= 0 && slice_words >= 0 && rows_per_rank, "bff_comm_exchange_rows: bad arguments");
+    const int world = c ? c->world : 1, rank = c ? c->rank : 0;
+    BFF_REQUIRE(rows_per_rank[rank] == n_local_rows, "bff_comm_exchange_rows: rows_per_rank[%d] = %d, but %d local rows", rank, rows_per_rank[rank], n_local_rows);
+    long long total = 0, row0_self = 0;
+    for (int p = 0; p < world; ++p) {
+        BFF_REQUIRE(rows_per_rank[p] >= 0, "bff_comm_exchange_rows: negative row count");
+        if (p == rank) row0_self = total;
+        total += rows_per_rank[p];
+    }
+    if (total == 0 || slice_words == 0) return BFF_OK;
+    BFF_REQUIRE(recv && (send || n_local_rows == 0), "bff_comm_exchange_rows: null buffer");
+    const size_t block = (size_t)n_local_rows * slice_words;          // words of one outgoing slice
+    if (n_local_rows)
+        BFF_CUDA(cudaMemcpyAsync(recv + row0_self * slice_words, send + (size_t)rank * block, block * 4, cudaMemcpyDeviceToDevice, s));
+    if (world == 1) return BFF_OK;
+    BFF_NCCL(g_nccl.GroupStart());
+    long long row0 = 0;
+    for (int p = 0; p < world; ++p) {
+        if (p != rank) {
+            if (n_local_rows) BFF_NCCL(g_nccl.Send(send + (size_t)p * block, block * 4, kNcclUint8, p, c->comm, s));
+            if (rows_per_rank[p]) BFF_NCCL(g_nccl.Recv(recv + row0 * slice_words, (size_t)rows_per_rank[p] * slice_words * 4, kNcclUint8, p, c->comm, s));
+        }
+        row0 += rows_per_rank[p];
+    }
+    BFF_NCCL(g_nccl.GroupEnd());
     return BFF_OK;
 }

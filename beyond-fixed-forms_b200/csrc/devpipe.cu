@@ -57,54 +57,95 @@ __device__ __forceinline__ float iou_f32(int inter, int pa, int pb) {
 
 // ------------------------------------------------------------------------------------------------ components
 // find_unconnected_subgraphs_tensor + the group bookkeeping of merge_masks (projection_2d_to_3d.py:190-274) on the BIT
-// adjacency of the merge graph: min-label propagation (every node takes the smallest label among its neighbours, then
-// all labels are compressed to their roots) until nothing changes; the label of a component is its smallest member =
-// the node at which the reference emits it. Kept groups (>= min_agg members, and the root has an edge at all: a node
-// without any edge is an empty lifted row, which the reference turns into []) are numbered in root order, members
-// ascending; conf = sequential float32 sum in index order / len (:220-224).
-// scratch: 2 n int32 (member counts per root, keep flags).
+// adjacency of the merge graph. Union-find in shared memory: every set bit (i, j > i) is an edge whose two trees are
+// joined by hooking the LARGER root under the smaller one (atomicCAS on the root's parent slot; a failed CAS means the
+// root was hooked meanwhile and the search continues from its new parent), so a root is always the smallest node of its
+// tree and, when all edges are in, of its component = the node at which the reference emits the component. One pass
+// over the edges, independent of the graph's diameter (a first version propagated minimum labels along the edges and
+// took 135 us for the elongated components of c2 -- an object seen from many frames is a long chain of overlapping
+// partial views). Kept groups (>= min_agg members, and the root has an edge at all: a node without any edge is an empty
+// lifted row, which the reference turns into []) are numbered in root order, members ascending; conf = sequential
+// float32 sum in index order / len (:220-224). scratch: 2 n int32 (member counts per root, keep flags).
+__device__ __forceinline__ int uf_find(volatile int *par, int x) {
+    int r = x, p;
+    while ((p = par[r]) != r) r = p;
+    if (x != r && par[x] != r) par[x] = r;      // parents only ever point to smaller nodes of the same tree: any ancestor is valid
+    return r;
+}
+
 __global__ void __launch_bounds__(kDecT)
 components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int min_agg, const float *__restrict__ conf, int cap,
                   int32_t *__restrict__ res, int32_t *__restrict__ scratch) {
     extern __shared__ int s_lab_raw[];
     volatile int *lab = s_lab_raw;
     __shared__ int s_scan[34];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     int32_t *cnt = scratch, *flag = scratch + n;
     int32_t *group_first = res + BFF_S2R_HEADER, *group_size = group_first + cap;
     float *group_conf = reinterpret_cast<float *>(group_size + cap);
     int32_t *seg = res + BFF_S2R_HEADER + 7 * (size_t)cap, *members = seg + cap + 1;
-    for (int i = tid; i < n; i += kDecT) { lab[i] = i; cnt[i] = 0; }
-    __syncthreads();
-    while (true) {
-        int changed = 0;
-        for (int i = warp; i < n; i += kDecT / 32) {
-            const int cur = lab[i];
-            int best = cur;
-            const uint32_t *row = adj + (size_t)i * stride_words;
-            for (int w = lane; w < stride_words; w += 32) {
-                uint32_t bits = __ldg(row + w);
-                while (bits) {
-                    const int j = w * 32 + __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    best = min(best, lab[j]);        // a stale read is still a label of this component
-                }
-            }
-            best = __reduce_min_sync(0xffffffffu, best);
-            if (best < cur) {
-                if (lane == 0) lab[i] = best;
-                changed = 1;
-            }
-        }
-        if (!__syncthreads_or(changed)) break;
-        // labels only decrease and lab[x] <= x, so every chain ends in a root (lab[r] == r); roots do not move here
-        for (int i = tid; i < n; i += kDecT) {
-            int l = lab[i], r = lab[l];
-            while (r != l) { l = r; r = lab[l]; }
-            lab[i] = l;
-        }
-        __syncthreads();
+    float *s_conf = reinterpret_cast<float *>(s_lab_raw + n);      // the confidences, staged once: the member walk below must not
+    for (int i = tid; i < n; i += kDecT) {                          // wait for a global load per member (a 100-member group cost 35 us)
+        lab[i] = i;
+        cnt[i] = 0;
+        s_conf[i] = __ldg(conf + i);
     }
+    __syncthreads();
+    // hook(u, v): join the trees of u and v
+    auto hook = [&](int u, int v) {
+        int ru = uf_find(lab, u), rv = uf_find(lab, v);
+        while (ru != rv) {
+            const int hi = max(ru, rv), lo = min(ru, rv);
+            const int old = atomicCAS(s_lab_raw + hi, hi, lo);
+            if (old == hi) break;
+            ru = uf_find(lab, old);
+            rv = uf_find(lab, lo);
+        }
+    };
+    // every tree a star: pointer jumping until nothing moves (a hooked chain of d nodes takes log2 d rounds)
+    auto flatten = [&]() {
+        while (true) {
+            int moved = 0;
+            for (int i = tid; i < n; i += kDecT) {
+                const int p = lab[i], gp = lab[p];
+                if (gp != p) { lab[i] = gp; moved = 1; }
+            }
+            if (!__syncthreads_or(moved)) break;
+        }
+    };
+    // pass 1: every node with its first larger neighbour -- n edges build most of the forest. (Hooking ALL edges costs
+    // two root searches per edge; the merge graph of c2 has 30k edges in dense cliques, lanes with full adjacency words
+    // hold up their warps, and that pass alone took 90 us.)
+    for (int i = tid; i < n; i += kDecT) {
+        const uint32_t *row = adj + (size_t)i * stride_words;
+        for (int w = (i + 1) >> 5; w < stride_words; ++w) {
+            uint32_t bits = __ldg(row + w);
+            if (w * 32 <= i) bits &= ~((2u << (i - w * 32)) - 1u);     // bits j <= i of the word that holds the diagonal
+            if (bits) {
+                hook(i, w * 32 + __ffs(bits) - 1);
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    flatten();
+    // pass 2: all edges of the upper triangle (the graph is symmetric), but an edge whose ends carry the same label after
+    // pass 1 is inside one tree for good and costs one shared-memory read; only the others search and hook
+    const long long items = (long long)n * stride_words;
+    for (long long it = tid; it < items; it += kDecT) {
+        const int i = (int)(it / stride_words), w = (int)(it % stride_words);
+        if (w * 32 + 31 <= i) continue;
+        uint32_t bits = __ldg(adj + it);
+        if (w * 32 <= i) bits &= ~((2u << (i - w * 32)) - 1u);
+        const int li = lab[i];
+        while (bits) {
+            const int j = w * 32 + __ffs(bits) - 1;
+            bits &= bits - 1;
+            if (lab[j] != li) hook(i, j);
+        }
+    }
+    __syncthreads();
+    flatten();
     for (int i = tid; i < n; i += kDecT) atomicAdd(&cnt[lab[i]], 1);
     __syncthreads();
     // kept roots in ascending order: thread t owns the nodes [t per, (t + 1) per)
@@ -142,14 +183,16 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
         else seg[g] = m_total;
     }
     __syncthreads();
+    const int *root_of = s_lab_raw;                                 // final now: plain (pipelined) shared-memory reads
     for (int gi = tid; gi < g; gi += kDecT) {
         const int r = group_first[gi];
         int pos = seg[gi];
         float acc = 0.0f;
+#pragma unroll 4
         for (int i = r; i < n; ++i)
-            if (lab[i] == r) {
+            if (root_of[i] == r) {
                 members[pos++] = i;
-                acc = __fadd_rn(acc, __ldg(conf + i));
+                acc = __fadd_rn(acc, s_conf[i]);
             }
         group_conf[gi] = __fdiv_rn(acc, __int2float_rn(group_size[gi]));
     }
@@ -292,13 +335,29 @@ intersect_dc_kernel(const uint32_t *__restrict__ a, const int32_t *__restrict__ 
 }
 
 // rows[dst] = OR_INTO ? rows[dst] | rows[src] : rows[dst] & ~rows[src] for the *n_steps (dst, src) pairs of prog, in
-// order; every thread owns one word column (solve_overlapping :295-299, refinement.py:248)
+// order; every thread owns one word column (solve_overlapping :295-299, refinement.py:248). With at most kProgRows rows
+// (n_rows_dev given) the column is loaded into shared memory once, the program replayed there and the column written
+// back: every step through global memory instead is a dependent load-modify-store chain.
+constexpr int kProgRows = 64;
 template <bool OR_INTO>
 __global__ void __launch_bounds__(128)
-row_program_dc_kernel(uint32_t *__restrict__ rows, long long words, const int32_t *__restrict__ prog, const int32_t *__restrict__ n_steps) {
+row_program_dc_kernel(uint32_t *__restrict__ rows, long long words, const int32_t *__restrict__ prog, const int32_t *__restrict__ n_steps,
+                      const int32_t *__restrict__ n_rows_dev) {
+    __shared__ uint32_t s_col[kProgRows][128];
     const long long w = (long long)blockIdx.x * 128 + threadIdx.x;
-    if (w >= words) return;
     const int n = *n_steps;
+    if (w >= words || n == 0) return;
+    const int nr = n_rows_dev ? *n_rows_dev : kProgRows + 1;
+    if (nr <= kProgRows) {
+        for (int r = 0; r < nr; ++r) s_col[r][threadIdx.x] = rows[(long long)r * words + w];
+        for (int k = 0; k < n; ++k) {
+            const int dst = __ldg(prog + 2 * k), src = __ldg(prog + 2 * k + 1);
+            const uint32_t d = s_col[dst][threadIdx.x], s = s_col[src][threadIdx.x];
+            s_col[dst][threadIdx.x] = OR_INTO ? (d | s) : (d & ~s);
+        }
+        for (int r = 0; r < nr; ++r) rows[(long long)r * words + w] = s_col[r][threadIdx.x];
+        return;
+    }
     for (int k = 0; k < n; ++k) {
         const int dst = prog[2 * k], src = prog[2 * k + 1];
         const uint32_t d = rows[(long long)dst * words + w], s = rows[(long long)src * words + w];
@@ -379,12 +438,12 @@ __device__ __forceinline__ void vote_layout(const int32_t *d_max, int mode, int 
 
 __global__ void __launch_bounds__(256)
 vote_prepare_kernel(const int32_t *__restrict__ d_max, int mode, long long hist_cap, long long table_cap, uint32_t *__restrict__ hist,
-                    uint32_t *__restrict__ table, int32_t *__restrict__ res) {
+                    uint32_t *__restrict__ table, int32_t *__restrict__ n_values, int32_t *__restrict__ res) {
     int mb, vb;
     long long bins, tsize;
     vote_layout(d_max, mode, mb, vb, bins, tsize);
     if (bins > hist_cap || tsize > table_cap) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&res[BFF_S2R_ERROR], 2);
+        if (blockIdx.x == 0 && threadIdx.x == 0) { atomicOr(&res[BFF_S2R_ERROR], 2); *n_values = 0; }
         return;
     }
     const long long stride = (long long)gridDim.x * 256;
@@ -392,7 +451,7 @@ vote_prepare_kernel(const int32_t *__restrict__ d_max, int mode, long long hist_
         if (i < bins) hist[i] = 0u;
         table[i] = kEmptySlot;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) { res[BFF_S2R_MC_MAX] = d_max[0]; res[BFF_S2R_VC_MAX] = d_max[1]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { res[BFF_S2R_MC_MAX] = d_max[0]; res[BFF_S2R_VC_MAX] = d_max[1]; *n_values = 0; }
 }
 
 __global__ void __launch_bounds__(256)
@@ -461,28 +520,32 @@ vote_unique_insert_dc_kernel(const uint32_t *__restrict__ hist, const int32_t *_
     }
 }
 
-// u[floor(p * len(u))] of the sorted distinct values (:516-517, :575-576; p a Python float: double arithmetic), by an
-// 8-bit radix select over the occupied slots of the set. One CTA.
-__global__ void __launch_bounds__(kDecT)
-vote_select_kernel(const uint32_t *__restrict__ table, const int32_t *__restrict__ d_max, int mode, long long hist_cap, long long table_cap,
-                   double fraction, float *__restrict__ d_thr, int32_t *__restrict__ res) {
-    __shared__ int s_hist[256];
-    __shared__ int s_scan[34];
-    __shared__ uint32_t s_prefix;
-    __shared__ long long s_k;
+// the occupied slots of the set, compacted (order irrelevant: the select below ranks them)
+__global__ void __launch_bounds__(256)
+vote_compact_dc_kernel(const uint32_t *__restrict__ table, const int32_t *__restrict__ d_max, int mode, long long hist_cap, long long table_cap,
+                       uint32_t *__restrict__ values, int32_t *__restrict__ n_values) {
     int mb, vb;
     long long bins, tsize;
     vote_layout(d_max, mode, mb, vb, bins, tsize);
-    if (bins > hist_cap || tsize > table_cap) {
-        if (threadIdx.x == 0) *d_thr = 0.0f;
-        return;
+    if (bins > hist_cap || tsize > table_cap) return;
+    const long long stride = (long long)gridDim.x * 256;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < tsize; i += stride) {
+        const uint32_t v = table[i];
+        if (v != kEmptySlot) values[atomicAdd(n_values, 1)] = v;
     }
-    int c = 0;
-    for (long long i = threadIdx.x; i < tsize; i += kDecT) c += table[i] != kEmptySlot;
-    int n_u;
-    block_excl_scan(c, s_scan, &n_u);
+}
+
+// u[floor(p * len(u))] of the sorted distinct values (:516-517, :575-576; p a Python float: double arithmetic), by an
+// 8-bit radix select over the compacted bit patterns. One CTA.
+__global__ void __launch_bounds__(kDecT)
+vote_select_kernel(const uint32_t *__restrict__ values, const int32_t *__restrict__ n_values, double fraction, float *__restrict__ d_thr,
+                   int32_t *__restrict__ res) {
+    __shared__ int s_hist[256];
+    __shared__ uint32_t s_prefix;
+    __shared__ long long s_k;
+    const int n_u = *n_values;
     const double pos = floor(fraction * (double)n_u);
-    if (!(pos >= 0.0 && pos < (double)n_u)) {                 // the reference raises IndexError here
+    if (!(pos >= 0.0 && pos < (double)n_u)) {                 // the reference raises IndexError here (also: a scratch bound was hit)
         if (threadIdx.x == 0) {
             atomicOr(&res[BFF_S2R_ERROR], 1);
             res[BFF_S2R_N_UNIQUE] = n_u;
@@ -496,17 +559,33 @@ vote_select_kernel(const uint32_t *__restrict__ table, const int32_t *__restrict
         for (int i = threadIdx.x; i < 256; i += kDecT) s_hist[i] = 0;
         __syncthreads();
         const uint32_t prefix = s_prefix;
-        for (long long i = threadIdx.x; i < tsize; i += kDecT) {
-            const uint32_t v = table[i];
-            if (v != kEmptySlot && (v & mask) == prefix) atomicAdd(&s_hist[(v >> shift) & 255u], 1);
+        for (int i = threadIdx.x; i < n_u; i += kDecT) {
+            const uint32_t v = values[i];
+            if ((v & mask) == prefix) atomicAdd(&s_hist[(v >> shift) & 255u], 1);
         }
         __syncthreads();
-        if (threadIdx.x == 0) {
-            long long k = s_k;
-            int b = 0;
-            while (b < 255 && k >= s_hist[b]) { k -= s_hist[b]; ++b; }
-            s_k = k;
-            s_prefix = prefix | ((uint32_t)b << shift);
+        if (threadIdx.x < 32) {
+            // the bucket that holds the k-th value: lane l owns buckets 8 l .. 8 l + 7
+            const int lane = threadIdx.x;
+            int own = 0;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) own += s_hist[lane * 8 + b];
+            int inc = own;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            const long long k = s_k;
+            const unsigned holds = __ballot_sync(0xffffffffu, k < inc);     // inclusive sums grow with the lane: first lane past k
+            const int owner = holds ? __ffs(holds) - 1 : 31;
+            if (lane == owner) {
+                long long kk = k - (inc - own);
+                int b = lane * 8;
+                while (b < lane * 8 + 7 && kk >= s_hist[b]) { kk -= s_hist[b]; ++b; }
+                s_k = kk;
+                s_prefix = prefix | ((uint32_t)b << shift);
+            }
         }
         mask |= 255u << shift;
         __syncthreads();
@@ -634,9 +713,13 @@ struct RefineLayout {
 // best = best_match_after_iou_check: masks whose match nobody shares keep their order; every match shared by several
 // masks yields ONE merged mask (members ascending, float32 conf = sequential sum / count) and the merged masks follow
 // in ascending order of the match, because the reference appends them while walking torch.unique(best).
-// scratch: n1 int32 (how many stage-2 masks chose stage-1 mask u). dynamic shared memory: cap2 int32.
+// scratch: n1 int32 (how many stage-2 masks chose stage-1 mask u). dynamic shared memory: cap2 int32 + kMergeStage
+// int32; with m <= kMergeDim the m x m intersections, the popcounts and the first matches are staged there, so that the
+// sequential loop of warp 0 does not wait for a chain of global loads per row.
+constexpr int kMergeDim = 96;
+constexpr int kMergeStage = kMergeDim * kMergeDim + 2 * kMergeDim;
 __global__ void __launch_bounds__(kDecT)
-refine_merge_kernel(RefineLayout L, const int32_t *__restrict__ n2_dev, const int32_t *__restrict__ ginter, int ld, const int32_t *__restrict__ gpop,
+refine_merge_kernel(RefineLayout L, const int32_t *__restrict__ n2_dev, const int32_t *__restrict__ ginter_g, int ld_g, const int32_t *__restrict__ gpop_g,
                     float thr, const float *__restrict__ s2_conf, int32_t *__restrict__ res, int32_t *__restrict__ or_prog,
                     int32_t *__restrict__ scratch) {
     extern __shared__ int s_redirect[];
@@ -644,7 +727,15 @@ refine_merge_kernel(RefineLayout L, const int32_t *__restrict__ n2_dev, const in
     __shared__ int s_nor;
     const int tid = threadIdx.x, lane = tid & 31;
     const int m = *n2_dev;
-    const int32_t *mm = res + L.first_match();
+    const int32_t *ginter = ginter_g, *gpop = gpop_g, *mm = res + L.first_match();
+    int ld = ld_g;
+    if (m <= kMergeDim) {
+        int *st = s_redirect + L.cap2;
+        for (int i = tid; i < m * m; i += kDecT) st[i] = ginter_g[(long long)(i / m) * ld_g + (i % m)];
+        for (int i = tid; i < m; i += kDecT) { st[m * m + i] = gpop_g[i]; st[m * m + m + i] = mm[i]; }
+        ginter = st; gpop = st + m * m; mm = st + m * m + m;
+        ld = m;
+    }
     int32_t *best = res + L.best();
     float *conf_out = reinterpret_cast<float *>(res + L.conf_out());
     int32_t *idx2 = res + L.idx2(), *seg2 = res + L.seg2();
@@ -832,6 +923,23 @@ refine_select_kernel(RefineLayout L, int mode, double percentile, double given_t
     }
 }
 
+// ------------------------------------------------------------------------------------------------ column slices
+__global__ void __launch_bounds__(256)
+rows_slice_kernel(const uint32_t *__restrict__ rows, long long words, long long word0, long long slice_words, uint32_t *__restrict__ out) {
+    const long long w = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (w >= slice_words) return;
+    const long long src = word0 + w;
+    out[(long long)blockIdx.y * slice_words + w] = src < words ? __ldg(rows + (long long)blockIdx.y * words + src) : 0u;
+}
+
+__global__ void __launch_bounds__(256)
+rows_unslice_kernel(const uint32_t *__restrict__ slices, int n_rows, long long slice_words, long long words, uint32_t *__restrict__ out) {
+    const long long w = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (w >= words) return;
+    const long long p = w / slice_words;
+    out[(long long)blockIdx.y * words + w] = __ldg(slices + (p * n_rows + blockIdx.y) * slice_words + (w - p * slice_words));
+}
+
 // ------------------------------------------------------------------------------------------------ unpack, device-side row count
 __device__ __forceinline__ uint32_t spread4_dc(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
 
@@ -911,10 +1019,9 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     BFF_REQUIRE(d->rows && d->conf && d->mc && d->out_rows && d->result, "bff_stage2_device: null pointer");
     BFF_REQUIRE(d->min_aggregated >= 1, "bff_stage2_device: min_aggregated must be >= 1");
     BFF_REQUIRE(d->filter_mode >= 0 && d->filter_mode <= 2 && (d->filter_mode != 0 || d->vc), "bff_stage2_device: bad filter mode");
-    BFF_REQUIRE(d->n_rows <= 46340, "bff_stage2_device: too many rows");
+    BFF_REQUIRE(d->n_rows <= 25000, "bff_stage2_device: too many rows (the component search keeps 8 bytes per row in shared memory)");
     BFF_REQUIRE(d->cap_groups >= d->n_rows / d->min_aggregated && d->cap_groups >= 1, "bff_stage2_device: cap_groups %d below n_rows / min_aggregated", d->cap_groups);
-    BFF_REQUIRE(d->n_vote_points >= 0 && d->vote_point0 >= 0 && d->vote_point0 + d->n_points <= std::max<int64_t>(d->n_vote_points, d->n_points),
-                "bff_stage2_device: vote slice outside the vote vectors");
+    BFF_REQUIRE(d->n_vote_points >= 0 && d->vote_point0 >= 0, "bff_stage2_device: negative vote offsets");
     BFF_REQUIRE(d->mc_cap >= 0 && d->vc_cap >= 0, "bff_stage2_device: negative count bounds");
     BFF_CUDA(cudaSetDevice(c->device));
     const int n = d->n_rows, cap = d->cap_groups;
@@ -929,7 +1036,8 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     const long long prog_cap = std::max<long long>(1, (long long)cap * (cap - 1) / 2);
 
     int32_t *d_inter = nullptr, *d_pop = nullptr, *d_scratch = nullptr, *d_ginter = nullptr, *d_prog = nullptr, *d_max = nullptr;
-    uint32_t *d_adj = nullptr, *d_agg = nullptr, *d_hist = nullptr, *d_table = nullptr, *d_keep = nullptr;
+    uint32_t *d_adj = nullptr, *d_agg = nullptr, *d_hist = nullptr, *d_table = nullptr, *d_keep = nullptr, *d_vals = nullptr;
+    int32_t *d_nvals = nullptr;
     float *d_thr = nullptr;
     for (int pass = 0; pass < 2; ++pass) {
         Take t(pass ? c->dev.base() : nullptr);
@@ -942,6 +1050,8 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
         d_max = t.get<int32_t>(2);
         d_hist = t.get<uint32_t>((size_t)hist_cap);
         d_table = t.get<uint32_t>((size_t)table_cap);
+        d_vals = t.get<uint32_t>((size_t)hist_cap);
+        d_nvals = t.get<int32_t>(1);
         d_thr = t.get<float>(1);
         d_keep = t.get<uint32_t>((size_t)words);
         if (pass == 0) {
@@ -963,7 +1073,8 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     if ((rc = launch_merge_adjacency(d_inter, d_pop, d->label_id, n, stride_words, d->iou_thres, d_adj, s)) != BFF_OK) return rc;
     // ---- connected components, groups, confidences (:190-274)
     {
-        const size_t smem = (size_t)n * 4;
+        const size_t smem = (size_t)n * 8;                   // labels + confidences
+        BFF_REQUIRE(smem <= 200 * 1024, "bff_stage2_device: %d rows need %zu bytes of shared memory for the component search", n, smem);
         if (smem > 48 * 1024) BFF_CUDA(cudaFuncSetAttribute((const void *)components_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         components_kernel<<<1, kDecT, smem, s>>>(d_adj, n, stride_words, d->min_aggregated, d->conf, cap, res, d_scratch);
         BFF_LAUNCH_CHECK("components_kernel");
@@ -984,17 +1095,18 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     }
     overlap_program_kernel<<<1, kDecT, 0, s>>>(d_ginter, cap, cap, res, d_prog);
     BFF_LAUNCH_CHECK("overlap_program_kernel");
-    row_program_dc_kernel<false><<<(unsigned)ceil_div64(words, 128), 128, 0, s>>>(d_agg, words, d_prog, res + BFF_S2R_N_OVERLAP);
+    row_program_dc_kernel<false><<<(unsigned)ceil_div64(words, 128), 128, 0, s>>>(d_agg, words, d_prog, res + BFF_S2R_N_OVERLAP, res + BFF_S2R_N_GROUPS);
     BFF_LAUNCH_CHECK("row_program_dc_kernel");
     // ---- point filter (:512-583)
     const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
     if (d->filter_mode != 2) {
         if ((rc = bff_counts_max(d->mc, vc, n_votes, d_max, s)) != BFF_OK) return rc;
-        vote_prepare_kernel<<<kNumSMs, 256, 0, s>>>(d_max, d->filter_mode, hist_cap, table_cap, d_hist, d_table, res);
+        vote_prepare_kernel<<<kNumSMs, 256, 0, s>>>(d_max, d->filter_mode, hist_cap, table_cap, d_hist, d_table, d_nvals, res);
         long long blocks = std::min<long long>(ceil_div64(n_votes, 256), kNumSMs * 4);
         vote_hist_dc_kernel<<<(unsigned)std::max<long long>(blocks, 1), 256, 0, s>>>(d->mc, vc, n_votes, d_max, d->filter_mode, hist_cap, table_cap, d_hist);
         vote_unique_insert_dc_kernel<<<kNumSMs, 256, 0, s>>>(d_hist, d_max, d->filter_mode, hist_cap, table_cap, d_table);
-        vote_select_kernel<<<1, kDecT, 0, s>>>(d_table, d_max, d->filter_mode, hist_cap, table_cap, d->filter_fraction, d_thr, res);
+        vote_compact_dc_kernel<<<kNumSMs, 256, 0, s>>>(d_table, d_max, d->filter_mode, hist_cap, table_cap, d_vals, d_nvals);
+        vote_select_kernel<<<1, kDecT, 0, s>>>(d_vals, d_nvals, d->filter_fraction, d_thr, res);
         BFF_LAUNCH_CHECK("vote threshold kernels");
     } else {
         BFF_CUDA(cudaMemsetAsync(d_thr, 0, 4, s));
@@ -1099,12 +1211,13 @@ extern "C" int bff_refine_device(bff_ctx *c, const bff_refine_dev_desc *d, void 
     if ((rc = comm_allreduce_sum_i32(d->comm, d_giou, giou_words, s)) != BFF_OK) return rc;
     // ---- the sequential merge loop (:230-249) and the stage-2 merges (:258-281)
     {
-        const size_t smem = (size_t)cap2 * 4;
+        const size_t smem = ((size_t)cap2 + kMergeStage) * 4;
+        BFF_REQUIRE(smem <= 200 * 1024, "bff_refine_device: cap2 too large");
         if (smem > 40 * 1024) BFF_CUDA(cudaFuncSetAttribute((const void *)refine_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         refine_merge_kernel<<<1, kDecT, smem, s>>>(L, n2, d_ginter, cap2, d_gpop, d->stage1_iou_thres, d->s2_conf, res, d_prog, d_scratch);
         BFF_LAUNCH_CHECK("refine_merge_kernel");
     }
-    row_program_dc_kernel<true><<<(unsigned)ceil_div64(words, 128), 128, 0, s>>>(d->s1_rows, words, d_prog, res + BFF_RFR_N_OR);
+    row_program_dc_kernel<true><<<(unsigned)ceil_div64(words, 128), 128, 0, s>>>(d->s1_rows, words, d_prog, res + BFF_RFR_N_OR, nullptr);
     BFF_LAUNCH_CHECK("row_program_dc_kernel");
     {
         dim3 grid((unsigned)ceil_div64(words, 256), loop_rows(cap2));
@@ -1153,5 +1266,27 @@ extern "C" int bff_unpack_bits_dc(const uint32_t *packed, const int32_t *n_rows_
     const long long blocks = wide ? ceil_div64(total, 16 * 256) : std::min<long long>(ceil_div64(total, 256), (long long)kNumSMs * 32);
     unpack_bits_dc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(packed, n_rows_dev, cap_rows, n, words, dense, wide);
     BFF_LAUNCH_CHECK("unpack_bits_dc_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_rows_slice(const uint32_t *rows, int32_t n_rows, int64_t words, int64_t word0, int64_t slice_words, uint32_t *out, void *stream_) {
+    BFF_REQUIRE(n_rows >= 0 && words >= 0 && word0 >= 0 && slice_words >= 0, "bff_rows_slice: negative size");
+    if (n_rows == 0 || slice_words == 0) return BFF_OK;
+    BFF_REQUIRE(rows && out, "bff_rows_slice: null pointer");
+    BFF_REQUIRE(n_rows <= 65535, "bff_rows_slice: too many rows");
+    dim3 grid((unsigned)ceil_div64(slice_words, 256), (unsigned)n_rows);
+    rows_slice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows, words, word0, slice_words, out);
+    BFF_LAUNCH_CHECK("rows_slice_kernel");
+    return BFF_OK;
+}
+
+extern "C" int bff_rows_unslice(const uint32_t *slices, int32_t world, int32_t n_rows, int64_t slice_words, int64_t words, uint32_t *out, void *stream_) {
+    BFF_REQUIRE(world >= 1 && n_rows >= 0 && slice_words > 0 && words >= 0 && (int64_t)world * slice_words >= words, "bff_rows_unslice: bad sizes");
+    if (n_rows == 0 || words == 0) return BFF_OK;
+    BFF_REQUIRE(slices && out, "bff_rows_unslice: null pointer");
+    BFF_REQUIRE(n_rows <= 65535, "bff_rows_unslice: too many rows");
+    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_rows);
+    rows_unslice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(slices, n_rows, slice_words, words, out);
+    BFF_LAUNCH_CHECK("rows_unslice_kernel");
     return BFF_OK;
 }

@@ -74,6 +74,12 @@ struct LiftParams {
     float depth_rcp;       // 1 / depth_scale in float32
     int fast_div;          // x / depth_scale == the 3-operation sequence of depth_value() for every uint16 x (checked on the host)
     int atomic_flush;      // >1 frame chunk: counts are combined with atomics
+    // Row layout. One block: row m at rows + m * row_stride (row_stride = Wd). Sliced (n_slices > 1, the point-sharded
+    // multi-GPU exchange): the words of every row are cut into n_slices column slices of row_stride words each and stored
+    // slice-major, [slice][row][word in slice], so that slice p of ALL rows is one contiguous block to send to rank p.
+    long long row_stride;
+    long long slice_rows;  // rows per slice block (= n_masks)
+    int n_slices;
 };
 
 __device__ __forceinline__ long long f64_to_i64_numpy(double v) {
@@ -374,6 +380,12 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     }
     int cnt_mask = 0, cnt_view = 0;
     const long long word_idx = pt >> 5;
+    // where this warp's word of row 0 lives (a warp = 32 consecutive points = one word, hence one slice)
+    long long row_base = word_idx;
+    if (p.n_slices > 1) {
+        const long long slice = word_idx / p.row_stride;
+        row_base = slice * p.slice_rows * p.row_stride + (word_idx - slice * p.row_stride);
+    }
 
     // wait for the poses
     {
@@ -460,7 +472,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             if (m0 >= m1) continue;
             // masks of a frame are consecutive rows of both the packed 2D masks and the packed output rows
             const uint32_t *mp = p.masks2d + ((long long)m0 * p.mask_words + (pidx >> 5));
-            uint32_t *rp = p.rows != nullptr ? p.rows + ((long long)m0 * p.words + word_idx) : nullptr;
+            uint32_t *rp = p.rows != nullptr ? p.rows + ((long long)m0 * p.row_stride + row_base) : nullptr;
             const int sh = pidx & 31;
             for (int m = m0; m < m1; ++m) {
                 bool bit = false;
@@ -469,7 +481,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
                 const unsigned w = __ballot_sync(0xffffffffu, bit);
                 if (rp != nullptr) {
                     if (w != 0u && lane == 0) *rp = w;
-                    rp += p.words;
+                    rp += p.row_stride;
                 }
                 if (MULTI_Q) {
                     if (bit) s_acc[(p.mask_query ? p.mask_query[m] : 0) * kLiftThreads + tid] += 1;
@@ -596,8 +608,11 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     const long long n = d->n_points;
     if (d->ev_start) BFF_CUDA(cudaEventRecord((cudaEvent_t)d->ev_start, stream));
     // outputs are fully overwritten: zero them first (rows get only their non-zero words stored)
+    const int n_slices = d->n_row_slices > 1 ? d->n_row_slices : 1;
+    const long long row_stride = n_slices > 1 ? d->row_slice_words : words;
+    if (n_slices > 1) BFF_REQUIRE(d->row_slice_words > 0 && (long long)n_slices * d->row_slice_words >= words, "bff_lift_scene: %d row slices of %lld words do not cover %lld words", n_slices, (long long)d->row_slice_words, words);
     if (d->rows && d->n_masks > 0 && words > 0)
-        BFF_CUDA(cudaMemsetAsync(d->rows, 0, (size_t)d->n_masks * words * 4, stream));
+        BFF_CUDA(cudaMemsetAsync(d->rows, 0, (size_t)d->n_masks * (size_t)n_slices * row_stride * 4, stream));
     if (d->masked_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->masked_counts, 0, (size_t)d->n_queries * n * 4, stream));
     if (d->viewed_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->viewed_counts, 0, (size_t)n * 4, stream));
     if (n == 0 || d->n_frames == 0) {
@@ -631,6 +646,7 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
         p.src_w = d->src_width; p.src_h = d->src_height;
     }
     p.n_points = n; p.words = words;
+    p.row_stride = row_stride; p.slice_rows = d->n_masks; p.n_slices = n_slices;
     p.mask_words = ceil_div64((long long)d->height * d->width, 32);
     p.n_frames = d->n_frames;
     int fc = d->frames_per_chunk > 0 ? d->frames_per_chunk : auto_frames_per_chunk(n, d->n_frames);

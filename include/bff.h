@@ -113,6 +113,13 @@ typedef struct bff_lift_desc {
     /* optional cudaEvent_t handles recorded on `stream` right before the first and right after the last
      * device operation of the call (for callers that time the launch itself); NULL = none */
     void *ev_start, *ev_stop;
+    /* Row layout for the point-sharded multi-GPU exchange. n_row_slices <= 1: rows is (n_masks, Wd). n_row_slices = G > 1:
+     * the words of every row are cut into G column slices of row_slice_words words (G * row_slice_words >= Wd, the tail of
+     * the last slice stays 0) and rows is (G, n_masks, row_slice_words): slice p of ALL rows is one contiguous block, which
+     * is what rank p receives (bff_comm_exchange_rows). A warp owns one word of every row, so the layout costs nothing. */
+    int32_t n_row_slices;
+    int32_t reserved2;
+    int64_t row_slice_words;
 } bff_lift_desc;
 
 BFF_API int bff_version(void);
@@ -332,6 +339,16 @@ BFF_API int bff_comm_rank(const bff_comm *comm);
 BFF_API int bff_comm_world(const bff_comm *comm);
 BFF_API int bff_comm_allreduce_i32(bff_comm *comm, int32_t *buf, int64_t count, int32_t op, void *stream);
 BFF_API int bff_comm_allgather_bytes(bff_comm *comm, const void *send, void *recv, int64_t bytes_per_rank, void *stream);
+/* The one bulk exchange of the frame-sharded -> point-sharded hand-over: `send` is this rank's lifted rows in the sliced
+ * layout of bff_lift_desc (world, n_local_rows, slice_words); slice p goes to rank p, which stores the blocks of all ranks
+ * in rank order: `recv` is (sum of rows_per_rank, slice_words) = every lifted row of the scene in file order, restricted
+ * to this rank's points. rows_per_rank: HOST array (world). One grouped ncclSend/ncclRecv; the own block is a local copy. */
+BFF_API int bff_comm_exchange_rows(bff_comm *comm, const uint32_t *send, int32_t n_local_rows, const int32_t *rows_per_rank,
+                                   int64_t slice_words, uint32_t *recv, void *stream);
+/* Column slices of packed rows: out (n_rows, slice_words) = words [word0, word0 + slice_words) of rows (n_rows, words),
+ * zero beyond `words`; and the inverse for results: in (world, n_rows, slice_words) -> out (n_rows, words). */
+BFF_API int bff_rows_slice(const uint32_t *rows, int32_t n_rows, int64_t words, int64_t word0, int64_t slice_words, uint32_t *out, void *stream);
+BFF_API int bff_rows_unslice(const uint32_t *slices, int32_t world, int32_t n_rows, int64_t slice_words, int64_t words, uint32_t *out, void *stream);
 
 /* Result block of bff_stage2_device: int32 words, R = n_rows, C = cap_groups. */
 enum {
@@ -360,8 +377,9 @@ typedef struct bff_stage2_dev_desc {
     const int32_t *label_id;    /* DEVICE (n_rows), equal ids <=> equal label strings (:169-187); NULL = one label for all */
     const int32_t *mc;          /* device (n_vote_points) masked_counts of this query, ALL points */
     const int32_t *vc;          /* device (n_vote_points) viewed_counts; required for filter_mode 0 */
-    int64_t n_vote_points;      /* points the vote threshold is taken over (= n_points on a single GPU) */
-    int64_t vote_point0;        /* first point of this rank's slice inside mc / vc (0 on a single GPU) */
+    int64_t n_vote_points;      /* points the vote threshold is taken over (0 = n_points, the single-GPU case) */
+    int64_t vote_point0;        /* first point of this rank's slice inside mc / vc (0 on a single GPU); mc / vc hold at
+                                   least max(n_vote_points, vote_point0 + n_points) entries (padding points vote 0) */
     float iou_thres;            /* cfg.iou_thres as float32 */
     int32_t min_aggregated;     /* cfg.min_aggragated_masks, >= 1 */
     int32_t filter_mode;        /* 0 detected ratio, 1 occurrence, 2 none */

@@ -18,14 +18,14 @@ CFG = {"iou_thres": 0.2, "min_aggragated_masks": 2, "if_occurance_threshold": Fa
        "stage1_iou_thres": 0.1, "refinment_sim_percentile": 0.2, "refiment_iou_thres": 0.45}
 
 
-def _object_rows(rng, n_rows, n, n_obj, noise=0.08, empty=2, dup=2):
+def _object_rows(rng, n_rows, n, n_obj, noise=0.08, empty=2, dup=2, span=(40, 6)):
     """Rows that are noisy copies of a few 'objects' (unions of intervals), so that IoUs spread over (0, 1]; plus empty
     rows (NaN diagonal) and exact duplicates (IoU 1, ties)."""
     objs = np.zeros((n_obj, n), bool)
     for o in objs:
         for _ in range(rng.integers(1, 4)):
             a = rng.integers(0, n)
-            o[a:a + rng.integers(n // 40, n // 6)] = True
+            o[a:a + rng.integers(n // span[0], n // span[1])] = True
     rows = objs[rng.integers(0, n_obj, n_rows)].copy()
     rows ^= rng.random(rows.shape) < noise * rng.random((n_rows, 1))
     rows &= rng.random(rows.shape) < rng.uniform(0.3, 1.0, (n_rows, 1))          # partial views of an object
@@ -36,7 +36,7 @@ def _object_rows(rng, n_rows, n, n_obj, noise=0.08, empty=2, dup=2):
     return rows
 
 
-def _same(a, b, what):
+def _same(a, b, what, exact_conf=True):
     assert list(a["final_class"]) == list(b["final_class"]), what
     if isinstance(a["ins"], list) or isinstance(b["ins"], list):
         assert isinstance(a["ins"], list) and isinstance(b["ins"], list) and len(a["ins"]) == len(b["ins"]) == 0, what
@@ -44,7 +44,11 @@ def _same(a, b, what):
     assert a["ins"].shape == b["ins"].shape, what
     if a["ins"].numel():
         assert torch.equal(a["ins"].cpu().bool(), b["ins"].cpu().bool()), what
-    assert torch.equal(torch.as_tensor(a["conf"]).float(), torch.as_tensor(b["conf"]).float()), what
+    ca, cb = torch.as_tensor(a["conf"]).float(), torch.as_tensor(b["conf"]).float()
+    if exact_conf:
+        assert torch.equal(ca, cb), what
+    else:       # torch's mean() of a few float32 values is not the sequential sum (ATen's 4-accumulator / 8-lane order)
+        np.testing.assert_allclose(ca.numpy(), cb.numpy(), rtol=1e-6, err_msg=what)
 
 
 @pytest.mark.parametrize("seed", list(range(12)))
@@ -94,17 +98,19 @@ def test_stage2_device_many_rows_takes_the_tensor_core_and_global_histogram_path
     from bff_b200 import devpipe, stage2
     rng = np.random.default_rng(n_rows)
     n = 50021
-    rows = _object_rows(rng, n_rows, n, 40, empty=3, dup=3)
+    rows = _object_rows(rng, n_rows, n, 40, noise=0.02, empty=3, dup=3, span=(400, 150))
     labels = ["chair"] * n_rows
     conf = torch.from_numpy(rng.uniform(0.2, 0.45, n_rows).astype(np.float32))
     mc = torch.from_numpy(rows.sum(0).astype(np.int32))
-    vc = torch.from_numpy((rows.sum(0) + rng.integers(0, 200, n)).astype(np.int32))
+    vc = rows.sum(0) + rng.integers(0, 9, n)
+    vc[rng.integers(0, n, 200)] += rng.integers(300, 900, 200)                # a few points seen very often: a wide histogram
+    vc = torch.from_numpy(vc.astype(np.int32))
     assert (int(mc.max()) + 1) * (int(vc.max()) + 1) > 8192
     d_rows = torch.from_numpy(pack_rows(rows).view(np.int32)).to(cuda_dev)
     want, _ = stage2.aggregate_and_filter(d_rows, conf, labels, mc.to(cuda_dev), vc.to(cuda_dev), n, CFG)
     s2 = devpipe.stage2_device(d_rows, conf.to(cuda_dev), labels, mc.to(cuda_dev), vc.to(cuda_dev), n, CFG, mc_cap=n_rows, vc_cap=int(vc.max()))
     got, _ = s2.saved_dict()
-    assert got["ins"].shape[0] >= 3
+    assert got["ins"].shape[0] >= 2
     _same(got, want, "device vs host decisions")
 
 
@@ -154,7 +160,7 @@ def test_refine_device_equals_host_decisions_on_random_masks(cuda_dev, seed):
             refine.FUSED = True
         thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
         res[fused] = (p1, thr, refine.pass2_scene(p1, query, cfg["refiment_iou_thres"], thr))
-    _same(res[True][2], res[False][2], "host fused vs step-by-step")
+    _same(res[True][2], res[False][2], "host fused vs step-by-step", exact_conf=False)
     # device decisions: stage-2 rows in a buffer with spare capacity, the count on the device
     cap2 = n2 + int(rng.integers(1, 5))
     buf = torch.zeros((cap2, d_s1.shape[1]), dtype=torch.int32, device=cuda_dev)
