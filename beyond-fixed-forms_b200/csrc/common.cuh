@@ -87,4 +87,9 @@ struct bff_ctx {
     cudaEvent_t lane_done[kMaxLanes];
     cudaEvent_t fork_ev;
     int n_lanes;
+    // side stream of the device-resident pipelines (created on first use): the vote-threshold chain does not depend on
+    // the intersection chain until the point filter is applied, so it runs next to it
+    cudaStream_t side;
+    cudaEvent_t side_fork, side_join;
+    int has_side;
 };

@@ -8,6 +8,7 @@
 // round trip, capturable in a CUDA graph. Every decision kernel cites the reference lines it mirrors and is compared
 // bit for bit with the host version in tests/test_devpipe_gpu.py.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -65,7 +66,8 @@ __device__ __forceinline__ float iou_f32(int inter, int pa, int pb) {
 // took 135 us for the elongated components of c2 -- an object seen from many frames is a long chain of overlapping
 // partial views). Kept groups (>= min_agg members, and the root has an edge at all: a node without any edge is an empty
 // lifted row, which the reference turns into []) are numbered in root order, members ascending; conf = sequential
-// float32 sum in index order / len (:220-224). scratch: 2 n int32 (member counts per root, keep flags).
+// float32 sum in index order / len (:220-224). scratch: 2 n int32 (member counts per root, keep flags) + n x stride_words
+// (member bit rows of the intermediate labels).
 __device__ __forceinline__ int uf_find(volatile int *par, int x) {
     int r = x, p;
     while ((p = par[r]) != r) r = p;
@@ -113,35 +115,41 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
             if (!__syncthreads_or(moved)) break;
         }
     };
-    // pass 1: every node with its first larger neighbour -- n edges build most of the forest. (Hooking ALL edges costs
-    // two root searches per edge; the merge graph of c2 has 30k edges in dense cliques, lanes with full adjacency words
-    // hold up their warps, and that pass alone took 90 us.)
+    // pass 1: every node points at its smallest neighbour (or itself): one read per node, no atomics, no search. A clique
+    // collapses onto its smallest member at once, an elongated component (an object seen from many frames is a chain of
+    // overlapping partial views) becomes a shallow forest.
     for (int i = tid; i < n; i += kDecT) {
         const uint32_t *row = adj + (size_t)i * stride_words;
-        for (int w = (i + 1) >> 5; w < stride_words; ++w) {
-            uint32_t bits = __ldg(row + w);
-            if (w * 32 <= i) bits &= ~((2u << (i - w * 32)) - 1u);     // bits j <= i of the word that holds the diagonal
+        int best = i;
+        for (int w = 0; w <= (i >> 5); ++w) {
+            const uint32_t bits = __ldg(row + w);
             if (bits) {
-                hook(i, w * 32 + __ffs(bits) - 1);
+                best = min(i, w * 32 + __ffs(bits) - 1);
                 break;
             }
         }
+        lab[i] = best;
     }
     __syncthreads();
     flatten();
-    // pass 2: all edges of the upper triangle (the graph is symmetric), but an edge whose ends carry the same label after
-    // pass 1 is inside one tree for good and costs one shared-memory read; only the others search and hook
+    // member bit rows of the labels so far: bit i of row lab[i]
+    uint32_t *mem = reinterpret_cast<uint32_t *>(scratch + 2 * (size_t)n);
     const long long items = (long long)n * stride_words;
+    for (long long it = tid; it < items; it += kDecT) mem[it] = 0u;
+    __syncthreads();
+    for (int i = tid; i < n; i += kDecT) atomicOr(mem + (size_t)lab[i] * stride_words + (i >> 5), 1u << (i & 31));
+    __syncthreads();
+    // pass 2: a word of row i may only hold members of i's own tree; whatever else it holds is an edge into another tree
+    // and is joined exactly (root search + hook). One AND per word instead of one label read per edge: the merge graph of
+    // c2 has 30k edges in dense cliques, and walking them bit by bit (lanes with full words holding up their warps) took
+    // 55k warp instructions, hooking all of them 90 us.
     for (long long it = tid; it < items; it += kDecT) {
         const int i = (int)(it / stride_words), w = (int)(it % stride_words);
-        if (w * 32 + 31 <= i) continue;
-        uint32_t bits = __ldg(adj + it);
-        if (w * 32 <= i) bits &= ~((2u << (i - w * 32)) - 1u);
-        const int li = lab[i];
+        uint32_t bits = __ldg(adj + it) & ~mem[(size_t)lab[i] * stride_words + w];
         while (bits) {
             const int j = w * 32 + __ffs(bits) - 1;
             bits &= bits - 1;
-            if (lab[j] != li) hook(i, j);
+            hook(i, j);
         }
     }
     __syncthreads();
@@ -1043,7 +1051,7 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
         Take t(pass ? c->dev.base() : nullptr);
         d_inter = t.get<int32_t>((size_t)n * n + n);          // intersections, then the row popcounts (one all-reduce)
         d_adj = t.get<uint32_t>((size_t)n * stride_words);
-        d_scratch = t.get<int32_t>(2 * (size_t)n);
+        d_scratch = t.get<int32_t>(2 * (size_t)n + (size_t)n * stride_words);
         d_agg = t.get<uint32_t>((size_t)cap * words);
         d_ginter = t.get<int32_t>((size_t)cap * cap);
         d_prog = t.get<int32_t>(2 * (size_t)prog_cap);
@@ -1066,6 +1074,39 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     int32_t *r_seg = res + BFF_S2R_HEADER + 7 * (size_t)cap, *r_members = r_seg + cap + 1;
     int rc;
     BFF_CUDA(cudaMemsetAsync(res, 0, res_words * 4, s));
+
+    // ---- point filter (:512-583) on the side stream: maxima -> histogram -> distinct values -> threshold -> keep bits.
+    // Nothing of it depends on the grouping, so it runs next to the intersection chain (BFF_DEVPIPE_SIDE=0: in line).
+    const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
+    static const bool use_side = [] { const char *e = getenv("BFF_DEVPIPE_SIDE"); return !(e && e[0] == '0'); }();
+    cudaStream_t vs = s;
+    if (use_side) {
+        if (!c->has_side) {
+            BFF_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+            BFF_CUDA(cudaEventCreateWithFlags(&c->side_fork, cudaEventDisableTiming));
+            BFF_CUDA(cudaEventCreateWithFlags(&c->side_join, cudaEventDisableTiming));
+            c->has_side = 1;
+        }
+        vs = c->side;
+        BFF_CUDA(cudaEventRecord(c->side_fork, s));
+        BFF_CUDA(cudaStreamWaitEvent(vs, c->side_fork, 0));
+    }
+    if (d->filter_mode != 2) {
+        if ((rc = bff_counts_max(d->mc, vc, n_votes, d_max, vs)) != BFF_OK) return rc;
+        vote_prepare_kernel<<<kNumSMs, 256, 0, vs>>>(d_max, d->filter_mode, hist_cap, table_cap, d_hist, d_table, d_nvals, res);
+        long long blocks = std::min<long long>(ceil_div64(n_votes, 256), kNumSMs * 4);
+        vote_hist_dc_kernel<<<(unsigned)std::max<long long>(blocks, 1), 256, 0, vs>>>(d->mc, vc, n_votes, d_max, d->filter_mode, hist_cap, table_cap, d_hist);
+        vote_unique_insert_dc_kernel<<<kNumSMs, 256, 0, vs>>>(d_hist, d_max, d->filter_mode, hist_cap, table_cap, d_table);
+        vote_compact_dc_kernel<<<kNumSMs, 256, 0, vs>>>(d_table, d_max, d->filter_mode, hist_cap, table_cap, d_vals, d_nvals);
+        vote_select_kernel<<<1, kDecT, 0, vs>>>(d_vals, d_nvals, d->filter_fraction, d_thr, res);
+        BFF_LAUNCH_CHECK("vote threshold kernels");
+    } else {
+        BFF_CUDA(cudaMemsetAsync(d_thr, 0, 4, vs));
+    }
+    point_keep_dc_kernel<<<(unsigned)ceil_div64(words * 32, 256), 256, 0, vs>>>(d->mc + d->vote_point0, vc ? vc + d->vote_point0 : nullptr, d->n_points,
+                                                                                words, d->filter_mode, d_thr, d_keep);
+    BFF_LAUNCH_CHECK("point_keep_dc_kernel");
+    if (use_side) BFF_CUDA(cudaEventRecord(c->side_join, vs));
 
     // ---- all-pairs intersections -> thresholded merge graph (calculate_iou :149-166, aggregate :113-122)
     if ((rc = bff_mask_iou(d->rows, n, d->rows, n, words, d_inter, d_pop, d_pop, nullptr, s)) != BFF_OK) return rc;
@@ -1097,24 +1138,8 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     BFF_LAUNCH_CHECK("overlap_program_kernel");
     row_program_dc_kernel<false><<<(unsigned)ceil_div64(words, 128), 128, 0, s>>>(d_agg, words, d_prog, res + BFF_S2R_N_OVERLAP, res + BFF_S2R_N_GROUPS);
     BFF_LAUNCH_CHECK("row_program_dc_kernel");
-    // ---- point filter (:512-583)
-    const int32_t *vc = d->filter_mode == 0 ? d->vc : nullptr;
-    if (d->filter_mode != 2) {
-        if ((rc = bff_counts_max(d->mc, vc, n_votes, d_max, s)) != BFF_OK) return rc;
-        vote_prepare_kernel<<<kNumSMs, 256, 0, s>>>(d_max, d->filter_mode, hist_cap, table_cap, d_hist, d_table, d_nvals, res);
-        long long blocks = std::min<long long>(ceil_div64(n_votes, 256), kNumSMs * 4);
-        vote_hist_dc_kernel<<<(unsigned)std::max<long long>(blocks, 1), 256, 0, s>>>(d->mc, vc, n_votes, d_max, d->filter_mode, hist_cap, table_cap, d_hist);
-        vote_unique_insert_dc_kernel<<<kNumSMs, 256, 0, s>>>(d_hist, d_max, d->filter_mode, hist_cap, table_cap, d_table);
-        vote_compact_dc_kernel<<<kNumSMs, 256, 0, s>>>(d_table, d_max, d->filter_mode, hist_cap, table_cap, d_vals, d_nvals);
-        vote_select_kernel<<<1, kDecT, 0, s>>>(d_vals, d_nvals, d->filter_fraction, d_thr, res);
-        BFF_LAUNCH_CHECK("vote threshold kernels");
-    } else {
-        BFF_CUDA(cudaMemsetAsync(d_thr, 0, 4, s));
-    }
-    point_keep_dc_kernel<<<(unsigned)ceil_div64(words * 32, 256), 256, 0, s>>>(d->mc + d->vote_point0, vc ? vc + d->vote_point0 : nullptr, d->n_points,
-                                                                               words, d->filter_mode, d_thr, d_keep);
-    BFF_LAUNCH_CHECK("point_keep_dc_kernel");
     // ---- ins &= masked_points, row sums 'after' (:594-596), row filter (:601-623), selected rows
+    if (use_side) BFF_CUDA(cudaStreamWaitEvent(s, c->side_join, 0));
     {
         dim3 grid((unsigned)ceil_div64(words, kAndPopWords), loop_rows(cap));
         rows_and_popcount_dc_kernel<<<grid, 256, 0, s>>>(d_agg, words, d_keep, res + BFF_S2R_N_GROUPS, r_after);

@@ -144,6 +144,7 @@ extern "C" void bff_ctx_destroy(bff_ctx *c) {
     c->pin.release();
     for (int i = 0; i < c->n_lanes; ++i) { cudaStreamDestroy(c->lane[i]); cudaEventDestroy(c->lane_done[i]); }
     if (c->n_lanes) cudaEventDestroy(c->fork_ev);
+    if (c->has_side) { cudaStreamDestroy(c->side); cudaEventDestroy(c->side_fork); cudaEventDestroy(c->side_join); }
     cudaStreamDestroy(c->stream);
     delete c;
 }

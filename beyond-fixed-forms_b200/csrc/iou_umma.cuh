@@ -43,6 +43,7 @@ constexpr int kTmemCols = kATmem ? 256 : 128;
 constexpr int kATmemCol0 = 128;           // first column of the A ring
 constexpr int kAStageCols = kStageWords * 8;
 constexpr int kProducerWarps = 8;
+constexpr int kPrefetch = 3;              // stages of packed words held in registers ahead of the expansion
 constexpr int kThreads = (kProducerWarps + 1) * 32;               // + the MMA-issuing warp
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -85,8 +86,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
-// 4 bits -> 4 bytes of 0/1: n + (n << 7) + (n << 14) + (n << 21) puts bit i at bit 8 i (no two terms overlap)
-__device__ __forceinline__ uint32_t nibble_to_bytes(uint32_t n) { return (n * 0x00204081u) & 0x01010101u; }
+// Expansion of one packed word into 32 bytes of 0/1, four K-bytes at a time: bytes (v >> p) & 0x01010101 hold bits p, p + 8,
+// p + 16, p + 24 of the word. That is NOT the natural bit order -- and it does not have to be: the dot product over K is
+// invariant under any permutation of K that A and B share, and both operands are expanded by this same function. Two
+// instructions per four K-bytes (shift, mask) instead of four (nibble extract, multiply by 0x00204081, mask).
+__device__ __forceinline__ uint32_t plane_to_bytes(uint32_t v, int p) { return (v >> p) & 0x01010101u; }
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
@@ -98,7 +102,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 // waits for a full stage, issues its 4 MMAs and commits them to the stage's `empty` barrier.
 __global__ void __launch_bounds__(kThreads)
 intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *__restrict__ b, int n_b, long long words,
-                      long long words_per_slice, int symmetric, int32_t *__restrict__ inter) {
+                      long long words_per_slice, int symmetric, int32_t *__restrict__ inter, int32_t *__restrict__ pop_a,
+                      int32_t *__restrict__ pop_b) {
     const int bi = blockIdx.y, bj = blockIdx.x;
     if (symmetric && bj < bi) return;                 // mirrored from the upper triangle
     extern __shared__ unsigned char smem_raw[];
@@ -132,17 +137,35 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
         const bool row_ok = grow < (op == 0 ? n_a : n_b);
         const uint32_t *src = (op == 0 ? a : b) + (long long)grow * words;
         const uint32_t row_off = (uint32_t)((r >> 3) * 256 + (r & 7) * 16);
-        uint32_t nxt[kStageWords];
+        // Row popcounts ride along: a producer thread sees every word of its row in this K slice anyway. Each row must be
+        // counted by exactly one tile column / row: the A rows by the CTAs of the first tile column they meet (bj == 0, or
+        // the diagonal tile of a symmetric call), the B rows by the first tile row (bi == 0; symmetric: pop_b == pop_a).
+        int32_t *pop_out = nullptr;
+        if (op == 0 && pop_a != nullptr && (symmetric ? bj == bi : bj == 0)) pop_out = pop_a;
+        if (op == 1 && pop_b != nullptr && !symmetric && bi == 0) pop_out = pop_b;
+        int pop_acc = 0;
+        // the packed words of the next kPrefetch stages travel in registers: one stage of expansion is shorter than a trip
+        // to L2, so a single stage of look-ahead left the producers waiting for their loads
+        uint32_t pre[kPrefetch][kStageWords];
 #pragma unroll
-        for (int k = 0; k < kStageWords; ++k) nxt[k] = (row_ok && (w_begin + k) < w_end) ? __ldg(src + w_begin + k) : 0u;
-        for (int s = 0; s < n_stages; ++s) {
+        for (int u = 0; u < kPrefetch; ++u)
+#pragma unroll
+            for (int k = 0; k < kStageWords; ++k) {
+                const long long w = w_begin + (long long)u * kStageWords + k;
+                pre[u][k] = (row_ok && w < w_end) ? __ldg(src + w) : 0u;
+            }
+        for (int s0 = 0; s0 < n_stages; s0 += kPrefetch) {
+#pragma unroll
+          for (int u = 0; u < kPrefetch; ++u) {
+            const int s = s0 + u;
+            if (s >= n_stages) break;
             const int buf = s % kStages;
             uint32_t wv[kStageWords];
 #pragma unroll
-            for (int k = 0; k < kStageWords; ++k) wv[k] = nxt[k];
-            const long long w1 = w_begin + (long long)(s + 1) * kStageWords;      // prefetch the next stage's words
+            for (int k = 0; k < kStageWords; ++k) { wv[k] = pre[u][k]; pop_acc += __popc(wv[k]); }
+            const long long w1 = w_begin + (long long)(s + kPrefetch) * kStageWords;      // this slot's next occupant
 #pragma unroll
-            for (int k = 0; k < kStageWords; ++k) nxt[k] = (row_ok && (w1 + k) < w_end) ? __ldg(src + w1 + k) : 0u;
+            for (int k = 0; k < kStageWords; ++k) pre[u][k] = (row_ok && (w1 + k) < w_end) ? __ldg(src + w1 + k) : 0u;
             // the MMAs that read this buffer kStages stages ago must have completed
             if (s >= kStages) mbar_wait(&empty_bar[buf], (uint32_t)(((s / kStages) - 1) & 1));
             if (kATmem && op == 0) {
@@ -152,7 +175,7 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
 #pragma unroll
                 for (int k = 0; k < kStageWords; ++k)
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) e[k * 8 + q] = nibble_to_bytes((wv[k] >> (4 * q)) & 15u);
+                    for (int q = 0; q < 8; ++q) e[k * 8 + q] = plane_to_bytes(wv[k], q);
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(kATmemCol0 + buf * kAStageCols);
                 static_assert(kAStageCols == 32, "tcgen05.st below writes 32 columns");
                 asm volatile(
@@ -174,13 +197,12 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
 #pragma unroll
             for (int k = 0; k < kStageWords; ++k) {          // word k = the K = 32 slice of MMA k
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {                // 16 bits -> one 16-byte K chunk
-                    const uint32_t v = wv[k] >> (16 * h);
+                for (int h = 0; h < 2; ++h) {                // planes 4 h .. 4 h + 3 -> one 16-byte K chunk (same order as A)
                     uint4 o;
-                    o.x = nibble_to_bytes(v & 15u);
-                    o.y = nibble_to_bytes((v >> 4) & 15u);
-                    o.z = nibble_to_bytes((v >> 8) & 15u);
-                    o.w = nibble_to_bytes((v >> 12) & 15u);
+                    o.x = plane_to_bytes(wv[k], 4 * h);
+                    o.y = plane_to_bytes(wv[k], 4 * h + 1);
+                    o.z = plane_to_bytes(wv[k], 4 * h + 2);
+                    o.w = plane_to_bytes(wv[k], 4 * h + 3);
                     *reinterpret_cast<uint4 *>(dst + k * kSubTileBytes + h * 128) = o;
                 }
             }
@@ -188,7 +210,9 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&full_bar[buf]);
+          }
         }
+        if (pop_out != nullptr && row_ok && pop_acc) atomicAdd(pop_out + grow, pop_acc);
     } else if (lane == 0) {
         // ---------------- MMA issuer (one thread)
         const uint32_t idesc = make_idesc();
@@ -266,11 +290,14 @@ intersect_umma_kernel(const uint32_t *__restrict__ a, int n_a, const uint32_t *_
 }
 
 // Enqueue the tensor-core intersection. Returns a cudaError_t-compatible int (0 = ok).
+// pop_a / pop_b (may be NULL; symmetric: pop_b ignored) must be zeroed like `inter`: the K slices add their parts.
 inline cudaError_t launch_intersect(const uint32_t *a, int n_a, const uint32_t *b, int n_b, long long words, int symmetric,
-                                    int32_t *inter, int num_sms, cudaStream_t stream) {
+                                    int32_t *inter, int32_t *pop_a, int32_t *pop_b, int num_sms, cudaStream_t stream) {
     const int ta = (n_a + kTileM - 1) / kTileM, tb = (n_b + kTileN - 1) / kTileN;
     long long tiles = symmetric ? (long long)ta * (ta + 1) / 2 : (long long)ta * tb;
-    long long slices = ((long long)num_sms * 2 + tiles - 1) / tiles;            // ~2 CTAs per SM in flight
+    // Two CTAs fit an SM (TMEM columns, shared memory): as many K slices as fill those slots ONCE. Rounding up (20 slices
+    // x 15 tiles = 300 CTAs on 296 slots at c2) left four CTAs for a second wave, i.e. doubled the kernel time.
+    long long slices = ((long long)num_sms * 2) / tiles;
     const long long max_slices = (words + 4 * kStageWords - 1) / (4 * kStageWords);
     if (slices > max_slices) slices = max_slices;
     if (slices < 1) slices = 1;
@@ -280,7 +307,7 @@ inline cudaError_t launch_intersect(const uint32_t *a, int n_a, const uint32_t *
     cudaError_t e = cudaFuncSetAttribute((const void *)intersect_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (e != cudaSuccess) return e;
     dim3 grid((unsigned)tb, (unsigned)ta, (unsigned)slices);
-    intersect_umma_kernel<<<grid, kThreads, kSmemBytes, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter);
+    intersect_umma_kernel<<<grid, kThreads, kSmemBytes, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter, pop_a, pop_b);
     return cudaGetLastError();
 }
 

@@ -27,20 +27,26 @@
 
 namespace bff {
 
-constexpr int kLiftThreads = 256;
-#ifndef BFF_LIFT_MIN_BLOCKS
-#define BFF_LIFT_MIN_BLOCKS 7      // resident CTAs per SM the register allocation is tuned for (measured: 5: 0.259, 6: 0.251, 7: 0.243-0.247 ms at c2)
+#ifndef BFF_LIFT_THREADS
+#define BFF_LIFT_THREADS 256
 #endif
-#ifndef BFF_LIFT_PIPE
-#define BFF_LIFT_PIPE 1            // surviving frames processed per loop iteration (1 or 2; 2 measured slower)
+constexpr int kLiftThreads = BFF_LIFT_THREADS;
+#ifndef BFF_LIFT_MIN_BLOCKS
+#define BFF_LIFT_MIN_BLOCKS 6      // resident CTAs per SM the register allocation is tuned for. r02, c2, 30 frames per chunk:
+                                   // 4: 0.276, 5: 0.237, 6: 0.224-0.230 (40 registers, 12 bytes spilled), 7/8: 0.241 ms (32 registers,
+                                   // x/y/z and the counters live in local memory); 128-thread CTAs: 0.239 ms
+#endif
+#ifndef BFF_LIFT_PREFETCH
+#define BFF_LIFT_PREFETCH 0        // software pipeline over the surviving frames (next frame's depth gather in flight): measured
+                                   // 0.239 ms against 0.226 ms without at c2 -- the extra live registers cost more than the gather latency
 #endif
 constexpr int kMaxFramesPerChunk = 256;   // <= kLiftThreads: one thread prepares one frame's culling planes
 // Per-frame culling data in shared memory (structure of arrays, index [k * fc + frame]):
 //   0..5   camera-z as a function of the world point: n(3), d, |n|(1+eps), eps|d|
 //   6..25  four image-border planes (left, right, top, bottom), each n(3), d(+slack), |n|(1+eps)
 constexpr int kPlaneDoubles = 26;
-constexpr int kFrameSmemBytes = 128 + kPlaneDoubles * 8 + 8;   // + mask offset and viewed flag (2 ints)
-constexpr int kChunkSmemExtra = 8;                              // the (fc+1)-th mask offset, padded
+constexpr int kFrameSmemBytes = 128 + kPlaneDoubles * 8 + 8 + 16;   // + depth offset (int64) + frame record (int4)
+constexpr int kChunkSmemExtra = 16;                                  // alignment of the records
 
 struct LiftParams {
     const void *xyz;
@@ -267,7 +273,7 @@ __device__ __forceinline__ bool locate_pixel(const LiftParams &p, const double *
         const double v = __ddiv_rn(q1, Z);
         xr = rint(u); yr = rint(v);          // np.round: half to even (:47)
     }
-    if (DEBUG) {
+    if (DEBUG && p.dbg_pix != nullptr) {
         long long *o = p.dbg_pix + ((long long)f * p.n_points + pt) * 2;
         o[0] = f64_to_i64_numpy(xr);
         o[1] = f64_to_i64_numpy(yr);
@@ -312,17 +318,17 @@ __device__ __forceinline__ bff_resize_tap load_tap(const bff_resize_tap *t) {
     return r;
 }
 
-// raw depth word of an in-image pixel: the uint16 / float32 bits, or the float32 bits of the sampled value
+// raw depth word of an in-image pixel: the uint16 / float32 bits, or the float32 bits of the sampled value.
+// frame_off = first element of the frame inside the depth stack (frame index x elements per frame).
 template <int DEPTH_KIND>
-__device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, int f, int pix, int px, int py) {
+__device__ __forceinline__ unsigned load_depth_raw(const LiftParams &p, long long frame_off, int pix, int px, int py) {
     if (DEPTH_KIND == BFF_DEPTH_U16_BILINEAR) {
-        const unsigned short *img = reinterpret_cast<const unsigned short *>(p.depth) + (long long)f * p.hw;
+        const unsigned short *img = reinterpret_cast<const unsigned short *>(p.depth) + frame_off;
         return __float_as_uint(bilinear_sample(img, p.src_w, p.src_h, load_tap(p.tap_x + px), load_tap(p.tap_y + py),
                                                p.depth_scale, p.depth_rcp, p.fast_div));
     }
-    const long long off = (long long)f * p.hw + pix;
-    if (DEPTH_KIND == BFF_DEPTH_U16) return (unsigned)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + off);
-    return __ldg(reinterpret_cast<const unsigned *>(p.depth) + off);
+    if (DEPTH_KIND == BFF_DEPTH_U16) return (unsigned)__ldg(reinterpret_cast<const unsigned short *>(p.depth) + frame_off + pix);
+    return __ldg(reinterpret_cast<const unsigned *>(p.depth) + frame_off + pix);
 }
 
 template <int DEPTH_KIND>
@@ -331,21 +337,25 @@ __device__ __forceinline__ float depth_value(unsigned raw, const LiftParams &p) 
     return __uint_as_float(raw);
 }
 
+// Shared memory of one CTA (dynamic): per frame of the chunk 16 doubles of inverse pose, kPlaneDoubles culling doubles
+// (SoA), the frame's first element in the depth stack (int64) and one int4 {first mask, end mask, counts-as-viewed, -}.
 template <int XYZ_KIND, int DEPTH_KIND, bool MULTI_Q, bool DEBUG>
 __global__ void __launch_bounds__(kLiftThreads, BFF_LIFT_MIN_BLOCKS)
 lift_kernel(const __grid_constant__ LiftParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int fc = p.frames_per_chunk;
     double *s_pose = reinterpret_cast<double *>(smem_raw);                       // fc x 16 doubles
-    double *s_plane = s_pose + (size_t)p.frames_per_chunk * 16;                   // kPlaneDoubles x fc (SoA)
-    int32_t *s_moff = reinterpret_cast<int32_t *>(s_plane + (size_t)p.frames_per_chunk * kPlaneDoubles);  // fc + 2 mask offsets
-    int32_t *s_view = s_moff + p.frames_per_chunk + 2;                                                   // fc viewed flags
-    int32_t *s_acc = s_view + p.frames_per_chunk;                                                        // Q x blockDim (MULTI_Q)
+    double *s_plane = s_pose + (size_t)fc * 16;                                   // kPlaneDoubles x fc (SoA)
+    long long *s_doff = reinterpret_cast<long long *>(s_plane + (size_t)fc * kPlaneDoubles);   // fc
+    int4 *s_frame = reinterpret_cast<int4 *>(s_doff + fc + (fc & 1));             // fc (16-byte aligned)
+    int32_t *s_acc = reinterpret_cast<int32_t *>(s_frame + fc);                   // Q x blockDim (MULTI_Q)
     __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ double s_sphere[kLiftThreads / 32][4];
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
-    const int f0 = blockIdx.y * p.frames_per_chunk;
-    const int nf = min(p.frames_per_chunk, p.n_frames - f0);
+    const int f0 = blockIdx.y * fc;
+    const int nf = min(fc, p.n_frames - f0);
 
     // ---- stage the chunk's inverse poses in shared memory: one bulk async copy (TMA)
     if (tid == 0) {
@@ -386,6 +396,16 @@ lift_kernel(const __grid_constant__ LiftParams p) {
         const long long slice = word_idx / p.row_stride;
         row_base = slice * p.slice_rows * p.row_stride + (word_idx - slice * p.row_stride);
     }
+    // per-frame records (do not need the poses)
+    for (int i = tid; i < nf; i += kLiftThreads) {
+        int4 fr;
+        fr.x = p.mask_offset != nullptr ? __ldg(p.mask_offset + f0 + i) : 0;
+        fr.y = p.mask_offset != nullptr ? __ldg(p.mask_offset + f0 + i + 1) : 0;
+        fr.z = (p.frame_viewed == nullptr || __ldg(p.frame_viewed + f0 + i)) ? 1 : 0;
+        fr.w = 0;
+        s_frame[i] = fr;
+        s_doff[i] = (long long)(f0 + i) * p.hw;
+    }
 
     // wait for the poses
     {
@@ -401,88 +421,104 @@ lift_kernel(const __grid_constant__ LiftParams p) {
         }
     }
 
-    // ---- per-frame culling planes (one thread per frame of the chunk), see warp_may_see()
-    const int fc = p.frames_per_chunk;
+    // ---- per-frame culling planes (5 functionals per frame spread over the CTA), see warp_may_see()
     if (!DEBUG) {
         for (int item = tid; item < nf * 5; item += kLiftThreads) {
             const int fr = item % nf;
             build_frame_plane(s_pose + fr * 16, p, s_plane + fr, fc, item / nf);
         }
     }
-    // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible)
-    double cx, cy, cz, cr;
-    const bool warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr)
-                                                             : warp_sphere(valid, x, y, z, cx, cy, cz, cr);
-    for (int i = tid; i <= nf; i += kLiftThreads) {
-        s_moff[i] = p.mask_offset != nullptr ? __ldg(p.mask_offset + f0 + i) : 0;
-        if (i < nf) s_view[i] = (p.frame_viewed == nullptr || __ldg(p.frame_viewed + f0 + i)) ? 1 : 0;
+    // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible);
+    // parked in shared memory: it is read once per 32-frame batch and would otherwise hold 8 registers for the whole loop
+    bool warp_has_points;
+    {
+        double cx, cy, cz, cr;
+        warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr) : warp_sphere(valid, x, y, z, cx, cy, cz, cr);
+        if (lane == 0) {
+            double *sp = s_sphere[tid >> 5];
+            sp[0] = cx; sp[1] = cy; sp[2] = cz; sp[3] = cr;
+        }
     }
     __syncthreads();
+    const bool has_rows = p.rows != nullptr;
 
     for (int fb = 0; fb < nf; fb += 32) {
-      // lane l decides for frame fb + l whether ANY point of this warp can be visible in it
-      unsigned todo;
-      {
-          const int fl = fb + lane;
-          bool see = fl < nf && warp_has_points;
-          if (!DEBUG && see) see = warp_may_see(s_plane + fl, fc, cx, cy, cz, cr, p.z_lo, p.z_hi);
-          todo = __ballot_sync(0xffffffffu, see);
-      }
-      if (p.dbg_vis != nullptr && lane == 0 && pt < p.n_points) {
-          // frames skipped below still owe their (all-zero) visibility word
-          for (unsigned m = ~todo; m != 0u; m &= m - 1u) {
-              const int fl = fb + __ffs(m) - 1;
-              if (fl < nf) p.dbg_vis[(long long)(f0 + fl) * p.words + word_idx] = 0u;
-          }
-      }
-      // Two surviving frames per iteration: both depth gathers are in flight before either is consumed
-      // (the gather -> compare -> mask gather chain is latency bound, the frames are independent).
-      while (todo != 0u) {
-        const int flA = fb + __ffs(todo) - 1;
-        todo &= todo - 1u;
-        const bool hasB = BFF_LIFT_PIPE > 1 && todo != 0u;
-        const int flB = hasB ? fb + __ffs(todo) - 1 : flA;
-        if (hasB) todo &= todo - 1u;
-        double ZA, ZB = 0.0;
-        int pixA, pixB = 0, pxA, pyA, pxB = 0, pyB = 0;
-        const bool inA = locate_pixel<DEBUG>(p, s_pose + flA * 16, f0 + flA, x, y, z, valid, pt, ZA, pixA, pxA, pyA);
-        const unsigned rawA = inA ? load_depth_raw<DEPTH_KIND>(p, f0 + flA, pixA, pxA, pyA) : 0u;
-        bool inB = false;
-        unsigned rawB = 0u;
-        if (hasB) {
-            inB = locate_pixel<DEBUG>(p, s_pose + flB * 16, f0 + flB, x, y, z, valid, pt, ZB, pixB, pxB, pyB);
-            rawB = inB ? load_depth_raw<DEPTH_KIND>(p, f0 + flB, pixB, pxB, pyB) : 0u;
+        // lane l decides for frame fb + l whether ANY point of this warp can be visible in it
+        unsigned todo;
+        {
+            const int fl = fb + lane;
+            bool see = fl < nf && warp_has_points;
+            if (!DEBUG && see) {
+                const double *sp = s_sphere[tid >> 5];
+                see = warp_may_see(s_plane + fl, fc, sp[0], sp[1], sp[2], sp[3], p.z_lo, p.z_hi);
+            }
+            todo = __ballot_sync(0xffffffffu, see);
         }
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            if (half == 1 && !hasB) break;
-            const int fl = half ? flB : flA;
-            const int f = f0 + fl;
-            const int pidx = half ? pixB : pixA;
-            const double Z = half ? ZB : ZA;
-            const float d = depth_value<DEPTH_KIND>(half ? rawB : rawA, p);
+        if (DEBUG && p.dbg_vis != nullptr && lane == 0 && valid) {
+            // frames skipped below still owe their (all-zero) visibility word
+            for (unsigned m = ~todo; m != 0u; m &= m - 1u) {
+                const int fl = fb + __ffs(m) - 1;
+                if (fl < nf) p.dbg_vis[(long long)(f0 + fl) * p.words + word_idx] = 0u;
+            }
+        }
+#if BFF_LIFT_PREFETCH
+        // Software pipeline over the surviving frames: the pixel of frame k+1 is located and its depth gather issued BEFORE
+        // frame k's depth is consumed, so the gather's latency (L2 / DRAM: the depth stack does not fit the L2) overlaps the
+        // compare -> ballot -> mask gather chain of the previous frame instead of stalling the warp.
+        int fl_n = -1, pix_n = 0;
+        double Z_n = 0.0;
+        bool in_n = false;
+        unsigned raw_n = 0u;
+        if (todo != 0u) {
+            fl_n = fb + __ffs(todo) - 1;
+            todo &= todo - 1u;
+            int px, py;
+            in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * 16, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
+            raw_n = in_n ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl_n], pix_n, px, py) : 0u;
+        }
+        while (fl_n >= 0) {
+            const int fl = fl_n, pix = pix_n;
+            const double Z = Z_n;
+            const bool in = in_n;
+            const unsigned raw = raw_n;
+            fl_n = -1;
+            if (todo != 0u) {
+                fl_n = fb + __ffs(todo) - 1;
+                todo &= todo - 1u;
+                int px, py;
+                in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * 16, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
+                raw_n = in_n ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl_n], pix_n, px, py) : 0u;
+            }
+#else
+        while (todo != 0u) {
+            const int fl = fb + __ffs(todo) - 1;
+            todo &= todo - 1u;
+            double Z;
+            int pix, px, py;
+            const bool in = locate_pixel<DEBUG>(p, s_pose + fl * 16, f0 + fl, x, y, z, valid, pt, Z, pix, px, py);
+            const unsigned raw = in ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl], pix, px, py) : 0u;
+#endif
+            const float d = depth_value<DEPTH_KIND>(raw, p);
             // :62-66: in bounds, depth != 0 and |z - depth| < thresh in float64
-            const bool vis = (half ? inB : inA) && (d != 0.0f) && (fabs(Z - (double)d) < p.thresh);
+            const bool vis = in && (d != 0.0f) && (fabs(Z - (double)d) < p.thresh);
             // the warp's visibility word; a warp without any visible point owes this frame nothing more
             const unsigned vw = __ballot_sync(0xffffffffu, vis);
-            if (p.dbg_vis != nullptr && lane == 0 && (pt < p.n_points)) p.dbg_vis[(long long)f * p.words + word_idx] = vw;
+            if (DEBUG && p.dbg_vis != nullptr && lane == 0 && valid) p.dbg_vis[(long long)(f0 + fl) * p.words + word_idx] = vw;
             if (vw == 0u) continue;
-            cnt_view += (vis ? 1 : 0) & s_view[fl];
-            const int m0 = s_moff[fl], m1 = s_moff[fl + 1];
-            if (m0 >= m1) continue;
+            const int4 fr = s_frame[fl];
+            cnt_view += (vis ? 1 : 0) & fr.z;
+            if (fr.x >= fr.y) continue;
             // masks of a frame are consecutive rows of both the packed 2D masks and the packed output rows
-            const uint32_t *mp = p.masks2d + ((long long)m0 * p.mask_words + (pidx >> 5));
-            uint32_t *rp = p.rows != nullptr ? p.rows + ((long long)m0 * p.row_stride + row_base) : nullptr;
-            const int sh = pidx & 31;
-            for (int m = m0; m < m1; ++m) {
-                bool bit = false;
-                if (vis) bit = (__ldg(mp) >> sh) & 1u;
+            const uint32_t *mp = p.masks2d + ((long long)fr.x * p.mask_words + (pix >> 5));
+            long long ro = (long long)fr.x * p.row_stride + row_base;
+            const int sh = pix & 31;
+#pragma unroll 2
+            for (int m = fr.x; m < fr.y; ++m) {
+                const bool bit = vis && ((__ldg(mp) >> sh) & 1u);
                 mp += p.mask_words;
                 const unsigned w = __ballot_sync(0xffffffffu, bit);
-                if (rp != nullptr) {
-                    if (w != 0u && lane == 0) *rp = w;
-                    rp += p.row_stride;
-                }
+                if (has_rows && w != 0u && lane == 0) p.rows[ro] = w;
+                ro += p.row_stride;
                 if (MULTI_Q) {
                     if (bit) s_acc[(p.mask_query ? p.mask_query[m] : 0) * kLiftThreads + tid] += 1;
                 } else {
@@ -490,7 +526,6 @@ lift_kernel(const __grid_constant__ LiftParams p) {
                 }
             }
         }
-      }
     }
 
     // ---- flush votes once per (point, chunk)
@@ -543,6 +578,8 @@ int auto_frames_per_chunk(long long n_points, int n_frames) {
     long long fc = 32;
     while (fc < kMaxFramesPerChunk && tiles * ceil_div64(n_frames, fc) > (1LL << 21)) fc *= 2;
     if (fc > n_frames) fc = n_frames;
+    // the same number of chunks, but of equal length (300 frames: 10 x 30 instead of 9 x 32 + 12; 0.2304 vs 0.2365 ms at c2)
+    if (fc > 0) fc = ceil_div64(n_frames, ceil_div64(n_frames, fc));
     return (int)fc;
 }
 
@@ -662,7 +699,7 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     p.atomic_flush = chunks > 1;
 
     const bool multi_q = d->n_queries > 1;
-    const bool debug = d->debug_pix != nullptr;
+    const bool debug = d->debug_pix != nullptr || d->debug_vis != nullptr;
     LiftKernel k = pick(d->xyz_kind, d->depth_kind, multi_q, debug);
     const size_t smem = (size_t)fc * kFrameSmemBytes + kChunkSmemExtra + (multi_q ? (size_t)d->n_queries * kLiftThreads * 4 : 0);
     BFF_REQUIRE(smem <= 200 * 1024, "bff_lift_scene: %d queries need %zu bytes of shared memory", d->n_queries, smem);

@@ -385,18 +385,29 @@ extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, i
         BFF_LAUNCH_CHECK("bff_mask_iou kernels (few columns)");
         return BFF_OK;
     }
-    if (pop_a) {
-        if (words > 0) row_popcount_kernel<<<n_a, 256, 0, stream>>>(a, words, pop_a);
-        else BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));
-    }
-    if (pop_b) {
-        if (words > 0) row_popcount_kernel<<<n_b, 256, 0, stream>>>(b, words, pop_b);
-        else BFF_CUDA(cudaMemsetAsync(pop_b, 0, (size_t)n_b * 4, stream));
+    const int symmetric = (a == b && n_a == n_b) ? 1 : 0;
+    // the tensor-core kernel counts the rows' bits while it expands them: no separate popcount launches on that path
+    const bool umma = inter && words > 0 && iou_use_umma(n_a, n_b, words);
+    BFF_REQUIRE(symmetric || pop_a == nullptr || pop_a != pop_b, "bff_mask_iou: one popcount buffer for two different operands");
+    int32_t *upa = nullptr, *upb = nullptr;             // what the tensor-core kernel accumulates into
+    if (!umma) {
+        if (pop_a) {
+            if (words > 0) row_popcount_kernel<<<n_a, 256, 0, stream>>>(a, words, pop_a);
+            else BFF_CUDA(cudaMemsetAsync(pop_a, 0, (size_t)n_a * 4, stream));
+        }
+        if (pop_b && pop_b != pop_a) {
+            if (words > 0) row_popcount_kernel<<<n_b, 256, 0, stream>>>(b, words, pop_b);
+            else BFF_CUDA(cudaMemsetAsync(pop_b, 0, (size_t)n_b * 4, stream));
+        }
+    } else {
+        upa = pop_a ? pop_a : (symmetric ? pop_b : nullptr);
+        upb = symmetric ? nullptr : pop_b;
+        if (upa) BFF_CUDA(cudaMemsetAsync(upa, 0, (size_t)n_a * 4, stream));
+        if (upb) BFF_CUDA(cudaMemsetAsync(upb, 0, (size_t)n_b * 4, stream));
     }
     if (inter) {
         BFF_CUDA(cudaMemsetAsync(inter, 0, (size_t)n_a * n_b * 4, stream));
         if (words > 0) {
-            const int symmetric = (a == b && n_a == n_b) ? 1 : 0;
             const int ta = (n_a + kTile - 1) / kTile, tb = (n_b + kTile - 1) / kTile;
             // K-slices: enough CTAs to fill the machine a few times, slices a multiple of kKW words
             long long tiles = (long long)ta * tb;
@@ -408,8 +419,10 @@ extern "C" int bff_mask_iou(const uint32_t *a, int32_t n_a, const uint32_t *b, i
             if (slices > 65535) slices = 65535;
             long long wps = ceil_div64(ceil_div64(words, slices), kKW) * kKW;
             slices = ceil_div64(words, wps);
-            if (iou_use_umma(n_a, n_b, words)) {
-                BFF_CUDA(umma::launch_intersect(a, n_a, b, n_b, words, symmetric, inter, kNumSMs, stream));
+            if (umma) {
+                BFF_CUDA(umma::launch_intersect(a, n_a, b, n_b, words, symmetric, inter, upa, upb, kNumSMs, stream));
+                if (symmetric && pop_a && pop_b && pop_b != pop_a)
+                    BFF_CUDA(cudaMemcpyAsync(pop_b, pop_a, (size_t)n_a * 4, cudaMemcpyDeviceToDevice, stream));
             } else {
                 dim3 grid((unsigned)tb, (unsigned)ta, (unsigned)slices);
                 intersect_kernel<<<grid, 256, 0, stream>>>(a, n_a, b, n_b, words, wps, symmetric, inter);

@@ -14,7 +14,7 @@ int main(int argc, char **argv) {
     cudaMalloc(&da, ha.size() * 4); cudaMalloc(&db, hb.size() * 4); cudaMalloc(&di, (size_t)n * m * 4);
     cudaMemcpy(da, ha.data(), ha.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(db, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(di, 0, (size_t)n * m * 4);
-    cudaError_t e = bff::umma::launch_intersect(da, n, db, m, words, 0, di, 148, 0);
+    cudaError_t e = bff::umma::launch_intersect(da, n, db, m, words, 0, di, nullptr, nullptr, 148, 0);
     printf("launch: %s\n", cudaGetErrorString(e));
     e = cudaDeviceSynchronize();
     printf("sync: %s\n", cudaGetErrorString(e));
@@ -34,7 +34,7 @@ int main(int argc, char **argv) {
     for (int rep = 0; rep < 3; ++rep) {
         cudaMemset(di, 0, (size_t)n * m * 4);
         cudaEventRecord(e0);
-        bff::umma::launch_intersect(da, n, da, n, words, 1, di, 148, 0);
+        bff::umma::launch_intersect(da, n, da, n, words, 1, di, nullptr, nullptr, 148, 0);
         cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         printf("symmetric %dx%d: %.4f ms  %.3e word-ops/s (%s)\n", n, n, ms, (double)n * n * words / (ms * 1e-3), cudaGetErrorString(cudaGetLastError()));
