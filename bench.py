@@ -45,6 +45,10 @@ WORKLOADS = {
     # configs[3]: 2M points, 2000 frames over 8 ranks (250 per rank), 1296x968 masks over 640x480 depth, 500 stage-1 masks
     "c4": dict(n_points=2_000_000, n_frames=250, width=1296, height=968, depth_width=640, depth_height=480,
                n_stage1=500, n_boxes=14, room=(20.0, 15.0, 3.0)),
+    # configs[3] as ONE scene (strong scaling over the GPUs): all 2000 frames
+    "c4s": dict(n_points=2_000_000, n_frames=2000, width=1296, height=968, depth_width=640, depth_height=480,
+                n_stage1=500, n_boxes=14, room=(20.0, 15.0, 3.0)),
+    # configs[2] as ONE scene (20 queries over the c2 scene; = c3, named for symmetry)
     "tiny": dict(n_points=20_000, n_frames=12, width=320, height=240, n_stage1=20, n_boxes=9),
     "tiny3": dict(n_points=20_000, n_frames=12, width=320, height=240, depth_width=160, depth_height=120,
                   n_stage1=20, n_boxes=9, n_queries=3),
@@ -297,14 +301,16 @@ def _step_device(self, d, ev, to_host=True):
     from bff_b200 import devpipe, ops
     inp, cfg = self.inp, self.inp["cfg"]
     ev()
+    # (the stage-1 masks first: they depend on nothing, and the GPU decodes them while the host is still preparing the
+    # lifting launch -- at the start of a step nothing is queued ahead)
+    n1 = len(inp["stage1"]["ins"])
+    s1 = ops.rle_to_bits_dev(d["s1_runs"], n1, self.n)
+    wd = s1.shape[1]
     masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
     ev()
     out = self.lift(d, masks2d, timing=getattr(self, "_timing", False))
     ev()
     ev()                                                         # (no exchange on one GPU)
-    n1 = len(inp["stage1"]["ins"])
-    s1 = ops.rle_to_bits_dev(d["s1_runs"], n1, self.n)
-    wd = s1.shape[1]
     s2s = []
     for qi in self.my_queries:
         rows_q = out.rows if self.row_index_dev is None else ops.rows_gather(out.rows, self.row_index_dev32[qi])
@@ -736,7 +742,7 @@ def run_gpu(args):
                                  "traffic": None, "note": "per-rank launch over this rank's frames"})
         line["frame_sharded"] = fs
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(inp, args.cpu_frames)
+        line["cpu_baseline"] = cpu_baseline(inp, args.cpu_baseline_budget)
     emit(line)
     if ctx:
         ctx.finalize()
@@ -880,24 +886,56 @@ def cpu_step(inp, mask_frames_by_query, view_frames):
     return out
 
 
-def cpu_sample_frames(inp, requested):
-    """Frames in the bounded CPU sample: the reference repeats the whole frame loop per query, so Q queries get 1/Q of them."""
-    return max(4, min(requested // max(len(inp["queries"]), 1), inp["depth"].shape[0]))
+def _set_cpu_threads(k: int):
+    """Threads of torch's intra-op pool and of the BLAS / OpenMP pools numpy and OpenCV use (threadpoolctl)."""
+    torch.set_num_threads(max(1, int(k)))
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=max(1, int(k)))
+    except Exception:
+        pass
 
 
-def cpu_baseline(inp, n_frames):
+def cpu_arm_plan(inp, budget_s: float, runs: int):
+    """How the reference's CPU path is timed on this host within `budget_s` seconds for `runs` passes: a probe over the
+    first frames at 1 thread and at all cores (the path is thread-setting sensitive: numpy's K<=4 dgemms and the dense
+    float32 sgemms pull in opposite directions), the faster setting is kept, and the number of frames per pass follows
+    from the probe's per-frame cost. Returns (threads, n_frames, note)."""
     cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    n_frames = cpu_sample_frames(inp, n_frames)
+    f_all = inp["depth"].shape[0]
+    n_probe = min(f_all, max(6, 24 // max(len(inp["queries"]), 1)))
+    mask_frames, view_frames = cpu_frames_of(inp, n_probe)
+    probe = {}
+    for k in sorted({1, cores}):
+        _set_cpu_threads(k)
+        t0 = time.perf_counter()
+        cpu_step(inp, mask_frames, view_frames)
+        probe[k] = time.perf_counter() - t0
+    threads = min(probe, key=probe.get)
+    per_frame = probe[threads] / n_probe
+    n_frames = int(max(n_probe, min(f_all, (budget_s / max(runs, 1)) / max(per_frame, 1e-6))))
+    note = "thread sweep on the first %d frames: %s; kept %d thread(s)" % (n_probe, ", ".join(f"{k} thr {v:.2f} s" for k, v in probe.items()), threads)
+    return threads, n_frames, note
+
+
+def _lifted_masks_in(inp, n_frames):
+    ids = set(inp["frame_ids"][:n_frames])
+    return [sum(len(r["segmented_frame_masks"]) for r in recs if r["frame_id"][:-4] in ids) for recs in inp["records_by_query"]]
+
+
+def cpu_baseline(inp, budget_s: float = 20.0):
+    threads, n_frames, note = cpu_arm_plan(inp, budget_s, 1)
+    _set_cpu_threads(threads)
     mask_frames, view_frames = cpu_frames_of(inp, n_frames)
     t0 = time.perf_counter()
     cpu_step(inp, mask_frames, view_frames)
     dt = time.perf_counter() - t0
     n = inp["spec"].n_points
-    return {"value": n * n_frames / dt, "unit": "point-views/s", "cores": cores, "kind": "port",
-            "sample": f"first {n_frames} of {inp['depth'].shape[0]} frames of the same scene ({n} points), whole path "
-                      f"(lift + viewed pass + aggregate + filter + refine), {dt:.2f} s, oracle/reference_port.py "
-                      "(numpy/OpenBLAS + torch CPU like the reference)"}
+    f_all = inp["depth"].shape[0]
+    return {"value": n * n_frames / dt, "unit": "point-views/s", "cores": threads, "host_cores": os.cpu_count() or 1, "kind": "port",
+            "frames": n_frames, "frames_full": f_all, "lifted_masks": _lifted_masks_in(inp, n_frames), "same_config": n_frames == f_all,
+            "sample": f"first {n_frames} of {f_all} frames of the same scene ({n} points), whole path (lift + viewed pass + aggregate + "
+                      f"filter + refine), {dt:.2f} s, oracle/reference_port.py (numpy/OpenBLAS + torch CPU like the reference); {note}"}
 
 
 # ----------------------------------------------------------------------------- files -> files (BASELINE configs[0])
@@ -993,33 +1031,42 @@ def run_cli_e2e(args):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port) on the host cores, same metric and config."""
+    """--impl reference: the reference's CPU path on the host cores, same metric and config. The unmodified reference
+    scripts cannot travel to the GPU box (/root/reference exists only in the build container, where
+    oracle/time_reference_cli.py times them: profiles/r02_reference_cli_c1_container.json), so this arm times
+    oracle/reference_port.py -- the same numpy / OpenBLAS / torch-CPU calls in the same order, pinned to the reference's
+    outputs by tests/test_port_e2e.py -- at the faster of {1 thread, all cores}, on as many frames of the scene as fit
+    the time budget (all of them for small K: then `same_config` is true)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
     dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")   # input fabrication only
-    inp = build_inputs(args.workload, 0, 1, dev, max_frames=args.cpu_frames)
-    n_frames = cpu_sample_frames(inp, args.cpu_frames)
+    inp = build_inputs(args.workload, 0, 1, dev)
+    warm = min(args.warmup, 1)
+    threads, n_frames, note = cpu_arm_plan(inp, args.cpu_budget, args.steps + warm)
+    _set_cpu_threads(threads)
     mask_frames, view_frames = cpu_frames_of(inp, n_frames)
-    for _ in range(min(args.warmup, 1)):
+    for _ in range(warm):
         cpu_step(inp, [m[:2] for m in mask_frames], view_frames[:2])
     t0 = time.perf_counter()
     for _ in range(args.steps):
         cpu_step(inp, mask_frames, view_frames)
     dt = (time.perf_counter() - t0) / args.steps
     n = inp["spec"].n_points
+    f_all = inp["depth"].shape[0]
     v = n * n_frames / dt
-    sample = (f"each step = first {n_frames} of {inp['depth'].shape[0]} frames of the scene ({n} points), whole path; "
-              "oracle/reference_port.py (numpy/OpenBLAS + torch CPU)")
+    sample = (f"each step = first {n_frames} of {f_all} frames of the scene ({n} points), whole path; oracle/reference_port.py "
+              f"(numpy/OpenBLAS + torch CPU); {note}")
     emit({
         "impl": "reference", "metric": "point-view projections/sec (whole lifting+aggregation+refinement step)",
         "value": v, "unit": "point-views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": {"workload": f"{args.workload} (bounded sample: {n_frames} frames per step)"},
-        "cpu_baseline": {"value": v, "unit": "point-views/s", "cores": cores, "kind": "port", "sample": sample},
+        "data": "synthetic",
+        "config": {"workload": f"{args.workload}: ScanNet200-shaped scene, {n} points, {f_all} frames, {len(inp['queries'])} quer{'y' if len(inp['queries']) == 1 else 'ies'}",
+                   "frames": n_frames, "frames_full": f_all, "lifted_masks": _lifted_masks_in(inp, n_frames), "same_config": n_frames == f_all,
+                   "n_points": n},
+        "cpu_baseline": {"value": v, "unit": "point-views/s", "cores": threads, "host_cores": os.cpu_count() or 1, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "point-views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
 
@@ -1049,7 +1096,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-frames", type=int, default=40, help="frames in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-budget", type=float, default=150.0, help="--impl reference: seconds of CPU work for all steps together (sizes the frame sample)")
+    ap.add_argument("--cpu-baseline-budget", type=float, default=20.0, help="our arm at N=1: seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-frame-sharded", action="store_true", help="N>1: skip the frame-sharded (strong scaling) measurement")
     ap.add_argument("--sharded-only", action="store_true", help="N>1: only the sharded scene (with its single-GPU cross-check), no replicas")

@@ -76,9 +76,10 @@ __device__ __forceinline__ int uf_find(volatile int *par, int x) {
 }
 
 __global__ void __launch_bounds__(kDecT)
-components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int min_agg, const float *__restrict__ conf, int cap,
-                  int32_t *__restrict__ res, int32_t *__restrict__ scratch) {
+components_kernel(const uint32_t *__restrict__ adj_g, int n, int stride_words, int min_agg, const float *__restrict__ conf, int cap,
+                  int32_t *__restrict__ res, int32_t *__restrict__ scratch, int stage_graph) {
     extern __shared__ int s_lab_raw[];
+    const uint32_t *adj = adj_g;
     volatile int *lab = s_lab_raw;
     __shared__ int s_scan[34];
     const int tid = threadIdx.x;
@@ -91,6 +92,16 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
         lab[i] = i;
         cnt[i] = 0;
         s_conf[i] = __ldg(conf + i);
+    }
+    // small graphs (c2: 525 x 18 words): the adjacency and the member rows live in shared memory too, so that none of the
+    // passes below waits for global memory; large graphs read them from global memory / the scratch block
+    const long long items = (long long)n * stride_words;
+    uint32_t *mem = reinterpret_cast<uint32_t *>(scratch + 2 * (size_t)n);
+    if (stage_graph) {
+        uint32_t *s_adj = reinterpret_cast<uint32_t *>(s_lab_raw + 2 * (size_t)n);
+        for (long long it = tid; it < items; it += kDecT) s_adj[it] = __ldg(adj_g + it);
+        mem = s_adj + items;
+        adj = s_adj;
     }
     __syncthreads();
     // hook(u, v): join the trees of u and v
@@ -122,7 +133,7 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
         const uint32_t *row = adj + (size_t)i * stride_words;
         int best = i;
         for (int w = 0; w <= (i >> 5); ++w) {
-            const uint32_t bits = __ldg(row + w);
+            const uint32_t bits = row[w];
             if (bits) {
                 best = min(i, w * 32 + __ffs(bits) - 1);
                 break;
@@ -133,8 +144,6 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
     __syncthreads();
     flatten();
     // member bit rows of the labels so far: bit i of row lab[i]
-    uint32_t *mem = reinterpret_cast<uint32_t *>(scratch + 2 * (size_t)n);
-    const long long items = (long long)n * stride_words;
     for (long long it = tid; it < items; it += kDecT) mem[it] = 0u;
     __syncthreads();
     for (int i = tid; i < n; i += kDecT) atomicOr(mem + (size_t)lab[i] * stride_words + (i >> 5), 1u << (i & 31));
@@ -145,7 +154,7 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
     // 55k warp instructions, hooking all of them 90 us.
     for (long long it = tid; it < items; it += kDecT) {
         const int i = (int)(it / stride_words), w = (int)(it % stride_words);
-        uint32_t bits = __ldg(adj + it) & ~mem[(size_t)lab[i] * stride_words + w];
+        uint32_t bits = adj[it] & ~mem[(size_t)lab[i] * stride_words + w];
         while (bits) {
             const int j = w * 32 + __ffs(bits) - 1;
             bits &= bits - 1;
@@ -165,7 +174,7 @@ components_kernel(const uint32_t *__restrict__ adj, int n, int stride_words, int
         if (lab[r] == r && cnt[r] >= min_agg) {
             const uint32_t *row = adj + (size_t)r * stride_words;
             uint32_t any = 0;
-            for (int w = 0; w < stride_words; ++w) any |= __ldg(row + w);
+            for (int w = 0; w < stride_words; ++w) any |= row[w];
             keep = any != 0u;
         }
         flag[r] = keep;
@@ -1114,10 +1123,13 @@ extern "C" int bff_stage2_device(bff_ctx *c, const bff_stage2_dev_desc *d, void 
     if ((rc = launch_merge_adjacency(d_inter, d_pop, d->label_id, n, stride_words, d->iou_thres, d_adj, s)) != BFF_OK) return rc;
     // ---- connected components, groups, confidences (:190-274)
     {
-        const size_t smem = (size_t)n * 8;                   // labels + confidences
+        size_t smem = (size_t)n * 8;                         // labels + confidences
         BFF_REQUIRE(smem <= 200 * 1024, "bff_stage2_device: %d rows need %zu bytes of shared memory for the component search", n, smem);
+        const size_t graph_bytes = 2 * (size_t)n * stride_words * 4;      // adjacency + member rows
+        const int stage_graph = smem + graph_bytes <= 160 * 1024;
+        if (stage_graph) smem += graph_bytes;
         if (smem > 48 * 1024) BFF_CUDA(cudaFuncSetAttribute((const void *)components_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        components_kernel<<<1, kDecT, smem, s>>>(d_adj, n, stride_words, d->min_aggregated, d->conf, cap, res, d_scratch);
+        components_kernel<<<1, kDecT, smem, s>>>(d_adj, n, stride_words, d->min_aggregated, d->conf, cap, res, d_scratch, stage_graph);
         BFF_LAUNCH_CHECK("components_kernel");
     }
     // ---- OR-merge the members (:214-223)

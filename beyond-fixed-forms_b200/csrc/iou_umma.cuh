@@ -295,9 +295,21 @@ inline cudaError_t launch_intersect(const uint32_t *a, int n_a, const uint32_t *
                                     int32_t *inter, int32_t *pop_a, int32_t *pop_b, int num_sms, cudaStream_t stream) {
     const int ta = (n_a + kTileM - 1) / kTileM, tb = (n_b + kTileN - 1) / kTileN;
     long long tiles = symmetric ? (long long)ta * (ta + 1) / 2 : (long long)ta * tb;
-    // Two CTAs fit an SM (TMEM columns, shared memory): as many K slices as fill those slots ONCE. Rounding up (20 slices
-    // x 15 tiles = 300 CTAs on 296 slots at c2) left four CTAs for a second wave, i.e. doubled the kernel time.
-    long long slices = ((long long)num_sms * 2) / tiles;
+    // Two CTAs fit an SM (TMEM columns, shared memory), i.e. 2 * num_sms slots per wave. The K slices are chosen so that the
+    // LAST wave is as full as possible: few tiles (c2: 15) -> as many slices as fill the slots once (rounding up instead --
+    // 300 CTAs on 296 slots -- doubled the kernel time); many tiles (c4: 630 on 296 slots = 2.13 waves) -> the slice count
+    // in 1..16 with the best wave efficiency (7 slices: 4410 CTAs = 14.9 waves), as long as a slice keeps >= 256 words.
+    const long long slots = (long long)num_sms * 2;
+    long long slices = slots / tiles;
+    if (slices < 1) {
+        double best = 0.0;
+        slices = 1;
+        for (long long s = 1; s <= 16 && words / s >= 256; ++s) {
+            const long long ctas = tiles * s;
+            const double eff = (double)ctas / (double)(((ctas + slots - 1) / slots) * slots);
+            if (eff > best + 1e-9) { best = eff; slices = s; }
+        }
+    }
     const long long max_slices = (words + 4 * kStageWords - 1) / (4 * kStageWords);
     if (slices > max_slices) slices = max_slices;
     if (slices < 1) slices = 1;

@@ -119,7 +119,7 @@ def test_bench_reference_arm_prints_the_contract_line():
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
-                          "--cpu-frames", "2", "--workload", "tiny"], capture_output=True, text=True, timeout=600, cwd=root)
+                          "--cpu-budget", "5", "--workload", "tiny"], capture_output=True, text=True, timeout=600, cwd=root)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
