@@ -73,11 +73,13 @@ def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, 
     from bff_b200.rle import rle_encode_rows
     w = WORKLOADS[workload]
     f_rank = w["n_frames"]
+    fsel = None
     if strong:
-        # ONE scene of w["n_frames"] frames, rank r takes the contiguous block shard_bounds gives it (strong scaling)
-        from bff_b200.dist import shard_bounds
-        s_lo, s_hi = shard_bounds(w["n_frames"], world, rank)
-        f_rank = s_hi - s_lo
+        # ONE scene of w["n_frames"] frames (strong scaling): rank r takes frames r, r + world, ... -- interleaved, so that
+        # every rank sees the whole trajectory and the ranks' lifting times are equal (contiguous blocks differed by 25 %:
+        # some stretches of the trajectory look at much more of the cloud than others)
+        fsel = list(range(rank, w["n_frames"], world))
+        f_rank = len(fsel)
     nq = w.get("n_queries", 1)
     queries = query_names(nq)
     n_render = f_rank if max_frames is None else min(max_frames, f_rank)   # the CPU arms only need their sample
@@ -86,14 +88,15 @@ def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, 
                            n_boxes=w["n_boxes"], n_stage1=w["n_stage1"], seed=seed, n_queries=nq,
                            room=w.get("room", (6.0, 5.0, 2.8)))
     sc = synth.make_scene(spec)
-    lo, hi = (s_lo, s_hi) if strong else (rank * f_rank, (rank + 1) * f_rank)
+    if fsel is None:
+        fsel = list(range(rank * f_rank, (rank + 1) * f_rank))
     hgt, wid = spec.height, spec.width
     dh, dw = (spec.depth_height or hgt), (spec.depth_width or wid)
     depth = np.zeros((f_rank, dh, dw), np.uint16)
     records = [[] for _ in queries]
-    for f in range(lo, lo + n_render):
+    for k, f in enumerate(fsel[:n_render]):
         mm, obj = synth.render_frame(sc, f, device)
-        depth[f - lo] = mm.cpu().numpy().astype(np.uint16)
+        depth[k] = mm.cpu().numpy().astype(np.uint16)
         rng = np.random.default_rng(spec.seed * 7919 + f)
         obj = obj.cpu()
         for qi, q in enumerate(queries):
@@ -107,10 +110,11 @@ def build_inputs(workload: str, rank: int, world: int, device, max_frames=None, 
     m1, c1, conf1 = synth.stage1_masks(sc, queries, STAGE1_CLASS_NAMES, rng)
     stage1 = {"ins": rle_encode_rows(torch.from_numpy(m1)), "conf": torch.from_numpy(conf1),
               "final_class": torch.from_numpy(c1)}
-    pinv = np.stack([np.linalg.inv(p) for p in sc.poses[lo:hi]])
-    return dict(spec=spec, xyz=sc.xyz, K=sc.K, poses=sc.poses[lo:hi], pinv=pinv, depth=depth, records=records[0],
+    poses = np.stack([sc.poses[f] for f in fsel])
+    pinv = np.stack([np.linalg.inv(p) for p in poses])
+    return dict(spec=spec, xyz=sc.xyz, K=sc.K, poses=poses, pinv=pinv, depth=depth, records=records[0],
                 records_by_query=records, queries=queries,
-                frame_ids=[str(i) for i in sc.frame_ids[lo:hi]], stage1=stage1, cfg=dict(synth.DEFAULT_CFG))
+                frame_ids=[str(sc.frame_ids[f]) for f in fsel], stage1=stage1, cfg=dict(synth.DEFAULT_CFG))
 
 
 def fake_similarity(query: str, label: str) -> float:
@@ -353,14 +357,21 @@ def _step_sharded(self, d, ev, to_host=True):
     masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
     ev()
     votes = torch.empty((self.nq + 1, plan.n_padded), dtype=torch.int32, device=self.dev)
+    peers = getattr(self, "peers", None)
+    if peers is not None:
+        # fused exchange: my receive buffer zeroed, everybody told (one-word all-reduce = barrier on the stream), then the
+        # lifting kernels store their row slices straight into the owners' buffers over NVLink
+        peers.local.zero_()
+        comm.allreduce_(peers.flag)
     out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], self.h, self.w, masks2d=masks2d,
                          mask_offset=d["offsets"] if self.n_masks else None, mask_query=d.get("mask_query") if self.n_masks else None,
                          n_queries=self.nq, frame_viewed=d["viewed"], depth_thresh=0.08, depth_scale=1000.0, depth_range=(0.0, 65.535),
                          native_size=self.native, row_slices=(world, sw), votes=votes,
+                         peer_rows=peers.addrs if peers is not None else None, peer_row0=self.row0,
                          timing_events=self.lift_events if getattr(self, "_timing", False) else None)
     ev()
-    comm.allreduce_(votes)
-    rows = comm.exchange_rows(out.rows, self.rows_per_rank)
+    comm.allreduce_(votes)                           # (with the fused exchange: also the barrier behind the peers' stores)
+    rows = peers.local if peers is not None else comm.exchange_rows(out.rows, self.rows_per_rank)
     ev()
     n1 = len(inp["stage1"]["ins"])
     s1 = ops.rows_slice(ops.rle_to_bits_dev(d["s1_runs"], n1, self.n), plan.rank * sw, sw)
@@ -759,20 +770,36 @@ def frame_sharded_run(args, ctx, dev, flush, barrier, workload=None, steps=None)
     rank, world = ctx.rank, ctx.world_size
     inp = build_inputs(workload, rank, world, dev, strong=True)
     g = GpuScene(inp, dev, ctx)
+    # what every rank has to know about the others' rows (host metadata, once per scene): per query, the confidence, label,
+    # launch position and FRAME of every lifted row. The scene's row order (the reference's file order: frames ascending,
+    # masks in order) is then the stable sort of the rank blocks by frame.
+    frame_of_row = [[int(r["frame_id"][:-4]) for r in recs for _ in r["segmented_frame_masks"]] for recs in inp["records_by_query"]]
     gathered = [None] * world
-    dist.all_gather_object(gathered, (g.n_masks, [[float(c) for c in cq] for cq in g.conf_q], g.labels_q, g.row_index, g.f))
+    dist.all_gather_object(gathered, (g.n_masks, [[float(c) for c in cq] for cq in g.conf_q], g.labels_q, g.row_index, g.f, frame_of_row))
     g.rows_per_rank = [x[0] for x in gathered]
     g.f_total = int(sum(x[4] for x in gathered))
     base = np.concatenate([[0], np.cumsum(g.rows_per_rank)])
-    # per query: confidences, labels and row positions of the whole scene = rank blocks in rank order (file order)
-    g.all_conf_dev = [torch.tensor([c for x in gathered for c in x[1][qi]], dtype=torch.float32).to(dev) for qi in range(g.nq)]
-    g.all_labels = [[l for x in gathered for l in x[2][qi]] for qi in range(g.nq)]
-    g.all_index_dev32 = [torch.tensor([int(base[r]) + i for r, x in enumerate(gathered) for i in x[3][qi]], dtype=torch.int32, device=dev)
-                         for qi in range(g.nq)]
-    if g.nq == 1:
-        g.all_index_dev32 = [None]
+    g.all_conf_dev, g.all_labels, g.all_index_dev32 = [], [], []
+    for qi in range(g.nq):
+        conf = [c for x in gathered for c in x[1][qi]]
+        labels = [l for x in gathered for l in x[2][qi]]
+        pos = [int(base[r]) + i for r, x in enumerate(gathered) for i in x[3][qi]]
+        frame = [f for x in gathered for f in x[5][qi]]
+        order = sorted(range(len(frame)), key=lambda k: frame[k])          # stable: rows of one frame keep their order
+        g.all_conf_dev.append(torch.tensor([conf[k] for k in order], dtype=torch.float32).to(dev))
+        g.all_labels.append([labels[k] for k in order])
+        idx = [pos[k] for k in order]
+        g.all_index_dev32.append(None if idx == list(range(int(base[-1]))) else torch.tensor(idx, dtype=torch.int32, device=dev))
+    g.row0 = int(base[rank])
     torch.cuda.synchronize()
     g.comm = dist_mod.Comm(ctx, dev.index or 0)
+    g.peers = None
+    if os.environ.get("BFF_PEER_ROWS", "1") != "0" and world <= 8:
+        try:
+            g.peers = dist_mod.PeerRows(ctx, int(base[-1]), g.plan.slice_words, dev)
+        except Exception as e:                      # IPC unavailable: the NCCL send/recv exchange stays
+            if rank == 0:
+                print(f"[bench] fused peer exchange unavailable ({e}); using the NCCL row exchange", file=sys.stderr)
     d = g.upload()
     for _ in range(3):
         final = g.step(d)
@@ -832,8 +859,11 @@ def frame_sharded_run(args, ctx, dev, flush, barrier, workload=None, steps=None)
         if not same:
             raise AssertionError("frame-sharded final masks differ from the single-GPU result of the same scene")
     barrier()
+    exchange_kind = "fused: lifting kernel stores row slices into the peers' buffers (CUDA IPC over NVLink)" if g.peers is not None else "grouped NCCL send/recv of row slices"
+    if g.peers is not None:
+        g.peers.close()
     g.comm.close()
-    return {"value": g.n * g.f_total / (ms * 1e-3), "unit": "point-views/s", "ms_per_step": ms, "steps": steps, "scaling": "strong",
+    return {"value": g.n * g.f_total / (ms * 1e-3), "row_exchange": exchange_kind, "unit": "point-views/s", "ms_per_step": ms, "steps": steps, "scaling": "strong",
             "workload": workload, "frames_total": g.f_total, "lifted_masks_total": int(sum(g.rows_per_rank)),
             "stages_ms_rank0": dict(zip(["rle2d_to_bits", "lift_scene", "exchange", "aggregate_filter", "refine"],
                                         (stage / steps).round(4).tolist())),

@@ -35,6 +35,7 @@ class LiftDesc(ctypes.Structure):
         ("src_height", c_int32), ("src_width", c_int32), ("resize_x", c_void_p), ("resize_y", c_void_p),
         ("ev_start", c_void_p), ("ev_stop", c_void_p),
         ("n_row_slices", c_int32), ("reserved2", c_int32), ("row_slice_words", c_int64),
+        ("peer_rows", c_void_p * 8), ("peer_row0", c_int64),
     ]
 
 
@@ -143,6 +144,10 @@ SYMBOLS = {
     "bff_comm_allreduce_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "bff_comm_allgather_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "bff_comm_exchange_rows": (c_int, [c_void_p, c_void_p, c_int32, c_void_p, c_int64, c_void_p, c_void_p]),
+    "bff_ipc_alloc": (c_int, [c_int64, POINTER(c_void_p), c_void_p]),
+    "bff_ipc_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "bff_ipc_close": (c_int, [c_void_p]),
+    "bff_ipc_free": (c_int, [c_void_p]),
     "bff_rows_slice": (c_int, [c_void_p, c_int32, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "bff_rows_unslice": (c_int, [c_void_p, c_int32, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
     "bff_ctx_create": (c_int, [c_int, POINTER(c_void_p)]),

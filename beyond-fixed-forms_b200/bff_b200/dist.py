@@ -224,6 +224,72 @@ class Comm:
             self.handle = None
 
 
+class _RawCuda:
+    """Minimal __cuda_array_interface__ holder: lets torch view device memory this package allocated itself."""
+
+    def __init__(self, addr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(addr), False), "version": 3}
+
+
+class PeerRows:
+    """Receive buffers of the FUSED exchange: every rank owns one (n_total_rows, slice_words) int32 buffer allocated
+    by libbff (cudaMalloc) and mapped into all other ranks with CUDA IPC, so that the lifting kernel of rank r stores
+    slice p of its rows straight into rank p's buffer over NVLink (ops.lift_scene(peer_rows=...)): no separate row
+    exchange, no send buffer. Protocol per scene: the owner zeroes its buffer, the ranks synchronise (a one-word
+    all-reduce on the stream), every rank launches its lifting kernel, and the vote all-reduce that follows is also the
+    barrier after which every rank's stores have landed. Raises BffError when IPC is unavailable (the caller then keeps
+    the NCCL send/recv exchange)."""
+
+    def __init__(self, ctx: DistCtx, n_total_rows: int, slice_words: int, device):
+        import ctypes
+        import torch.distributed as dist
+        from . import _cabi
+        self.ctx, self.shape = ctx, (int(n_total_rows), int(slice_words))
+        nbytes = max(1, self.shape[0] * self.shape[1]) * 4
+        p, h = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+        ok = True
+        try:
+            _cabi.check(_cabi.lib().bff_ipc_alloc(nbytes, ctypes.byref(p), h), "bff_ipc_alloc")
+        except _cabi.BffError:
+            ok = False
+        handles = [None] * ctx.world_size
+        dist.all_gather_object(handles, bytes(h.raw) if ok else None)
+        self.local_ptr = p.value if ok else None
+        self.addrs, self._opened = [], []
+        if ok and all(x is not None for x in handles):
+            for r, hb in enumerate(handles):
+                if r == ctx.rank:
+                    self.addrs.append(p.value)
+                    continue
+                q = ctypes.c_void_p()
+                try:
+                    _cabi.check(_cabi.lib().bff_ipc_open(ctypes.create_string_buffer(hb, 64), ctypes.byref(q)), "bff_ipc_open")
+                except _cabi.BffError:
+                    ok = False
+                    break
+                self._opened.append(q.value)
+                self.addrs.append(q.value)
+        else:
+            ok = False
+        flags = [None] * ctx.world_size
+        dist.all_gather_object(flags, ok)
+        if not all(flags):
+            self.close()
+            raise _cabi.BffError("CUDA IPC is not available between the ranks: falling back to the NCCL row exchange")
+        self.local = torch.as_tensor(_RawCuda(p.value, self.shape, "<i4"), device=device)
+        self.flag = torch.zeros((1,), dtype=torch.int32, device=device)
+
+    def close(self):
+        import ctypes
+        from . import _cabi
+        for a in self._opened:
+            _cabi.lib().bff_ipc_close(ctypes.c_void_p(a))
+        self._opened = []
+        if self.local_ptr:
+            _cabi.lib().bff_ipc_free(ctypes.c_void_p(self.local_ptr))
+            self.local_ptr = None
+
+
 def gather_final(comm: Comm, plan: ShardPlan, rf, to_host: bool = True) -> dict:
     """Final dict of a point-sharded bff_refine_device call: every rank holds its column slice of the saved rows (the
     decisions, hence the counts, are the same everywhere); the slices are all-gathered and re-assembled into (k, N) bool."""

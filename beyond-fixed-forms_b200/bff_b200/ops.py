@@ -48,7 +48,7 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
                want_rows: bool = True, want_counts: bool = True, want_viewed: bool = True,
                debug: bool = False, frames_per_chunk: int = 0, timing_events=None,
                native_size: Optional[Sequence[int]] = None, row_slices: Optional[Sequence[int]] = None,
-               votes: Optional[torch.Tensor] = None) -> LiftOutput:
+               votes: Optional[torch.Tensor] = None, peer_rows: Optional[Sequence[int]] = None, peer_row0: int = 0) -> LiftOutput:
     """One launch over all frames of a scene (bff_lift_scene).
 
     xyz         (N,4) float32 [x,y,z,_] or (N,3) float64, CUDA
@@ -61,6 +61,8 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     row_slices  (G, slice_words): rows come back as (G, sumM, slice_words) -- the words of every row cut into G column
                 slices, slice-major (the send layout of the point-sharded multi-GPU exchange, dist.py)
     votes       optional (Q+1, N) int32 CUDA buffer that receives [masked_counts | viewed_counts] (one all-reduce)
+    peer_rows   with row_slices: G device addresses (ints) of the ranks' receive buffers; slice p of the rows is stored
+                straight into buffer p at row peer_row0 + m (fused exchange over peer memory); no rows tensor is returned
     Returns packed rows (sumM, Wd) int32, masked_counts (Q,N) int32, viewed_counts (N,) int32."""
     dev = xyz.device
     if xyz.dtype == torch.float32:
@@ -116,7 +118,7 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
         g_sl, sw = int(row_slices[0]), int(row_slices[1])
         if g_sl * sw < wd:
             raise ValueError("row slices do not cover the row")
-        rows = torch.empty((g_sl, n_masks, sw), dtype=torch.int32, device=dev) if want_rows else None
+        rows = torch.empty((g_sl, n_masks, sw), dtype=torch.int32, device=dev) if (want_rows and peer_rows is None) else None
     else:
         rows = torch.empty((n_masks, wd), dtype=torch.int32, device=dev) if want_rows else None
     if votes is not None:
@@ -145,6 +147,12 @@ def lift_scene(xyz: torch.Tensor, pose_inv: torch.Tensor, intrinsics, depth: tor
     d.debug_pix, d.debug_vis = ptr(pix), ptr(vis)
     if row_slices is not None:
         d.n_row_slices, d.row_slice_words = g_sl, sw
+        if peer_rows is not None:
+            if len(peer_rows) != g_sl or g_sl > 8:
+                raise ValueError("peer_rows needs one address per slice (at most 8)")
+            for i_p, a_p in enumerate(peer_rows):
+                d.peer_rows[i_p] = int(a_p)
+            d.peer_row0 = int(peer_row0)
     d.frames_per_chunk = int(frames_per_chunk)
     if taps is not None:
         d.src_height, d.src_width, d.resize_x, d.resize_y = hs, ws, ptr(taps[0]), ptr(taps[1])

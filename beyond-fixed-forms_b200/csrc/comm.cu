@@ -178,3 +178,48 @@ extern "C" int bff_comm_exchange_rows(bff_comm *c, const uint32_t *send, int32_t
     BFF_NCCL(g_nccl.GroupEnd());
     return BFF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// CUDA IPC buffers (include/bff.h)
+extern "C" int bff_ipc_alloc(int64_t bytes, void **dev_ptr, void *handle64) {
+    BFF_REQUIRE(bytes > 0 && dev_ptr && handle64, "bff_ipc_alloc: bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    void *p = nullptr;
+    BFF_CUDA(cudaMalloc(&p, (size_t)bytes));
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(p);
+        bff::set_error("bff_ipc_alloc: cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+        return BFF_ECUDA;
+    }
+    memcpy(handle64, &h, 64);
+    *dev_ptr = p;
+    return BFF_OK;
+}
+
+extern "C" int bff_ipc_open(const void *handle64, void **dev_ptr) {
+    BFF_REQUIRE(handle64 && dev_ptr, "bff_ipc_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void *p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        bff::set_error("bff_ipc_open: cudaIpcOpenMemHandle failed: %s", cudaGetErrorString(e));
+        return BFF_ECUDA;
+    }
+    *dev_ptr = p;
+    return BFF_OK;
+}
+
+extern "C" int bff_ipc_close(void *dev_ptr) {
+    if (dev_ptr) BFF_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+    return BFF_OK;
+}
+
+extern "C" int bff_ipc_free(void *dev_ptr) {
+    if (dev_ptr) BFF_CUDA(cudaFree(dev_ptr));
+    return BFF_OK;
+}

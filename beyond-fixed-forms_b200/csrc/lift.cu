@@ -86,6 +86,10 @@ struct LiftParams {
     long long row_stride;
     long long slice_rows;  // rows per slice block (= n_masks)
     int n_slices;
+    // fused exchange: slice p of the rows goes straight into rank p's receive buffer (peer memory), at row peer_row0 + m
+    uint32_t *peer_rows[8];
+    long long peer_row0;
+    int use_peers;
 };
 
 __device__ __forceinline__ long long f64_to_i64_numpy(double v) {
@@ -392,9 +396,15 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     const long long word_idx = pt >> 5;
     // where this warp's word of row 0 lives (a warp = 32 consecutive points = one word, hence one slice)
     long long row_base = word_idx;
+    uint32_t *rows_out = p.rows;
     if (p.n_slices > 1) {
         const long long slice = word_idx / p.row_stride;
-        row_base = slice * p.slice_rows * p.row_stride + (word_idx - slice * p.row_stride);
+        if (p.use_peers) {
+            rows_out = slice < p.n_slices ? p.peer_rows[slice] : nullptr;
+            row_base = p.peer_row0 * p.row_stride + (word_idx - slice * p.row_stride);
+        } else {
+            row_base = slice * p.slice_rows * p.row_stride + (word_idx - slice * p.row_stride);
+        }
     }
     // per-frame records (do not need the poses)
     for (int i = tid; i < nf; i += kLiftThreads) {
@@ -440,7 +450,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
         }
     }
     __syncthreads();
-    const bool has_rows = p.rows != nullptr;
+    const bool has_rows = rows_out != nullptr;
 
     for (int fb = 0; fb < nf; fb += 32) {
         // lane l decides for frame fb + l whether ANY point of this warp can be visible in it
@@ -517,7 +527,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
                 const bool bit = vis && ((__ldg(mp) >> sh) & 1u);
                 mp += p.mask_words;
                 const unsigned w = __ballot_sync(0xffffffffu, bit);
-                if (has_rows && w != 0u && lane == 0) p.rows[ro] = w;
+                if (has_rows && w != 0u && lane == 0) rows_out[ro] = w;
                 ro += p.row_stride;
                 if (MULTI_Q) {
                     if (bit) s_acc[(p.mask_query ? p.mask_query[m] : 0) * kLiftThreads + tid] += 1;
@@ -648,7 +658,13 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     const int n_slices = d->n_row_slices > 1 ? d->n_row_slices : 1;
     const long long row_stride = n_slices > 1 ? d->row_slice_words : words;
     if (n_slices > 1) BFF_REQUIRE(d->row_slice_words > 0 && (long long)n_slices * d->row_slice_words >= words, "bff_lift_scene: %d row slices of %lld words do not cover %lld words", n_slices, (long long)d->row_slice_words, words);
-    if (d->rows && d->n_masks > 0 && words > 0)
+    bool use_peers = n_slices > 1 && d->peer_rows[0] != nullptr;
+    if (use_peers) {
+        BFF_REQUIRE(n_slices <= 8, "bff_lift_scene: at most 8 peers");
+        for (int q = 0; q < n_slices; ++q) BFF_REQUIRE(d->peer_rows[q] != nullptr, "bff_lift_scene: peer_rows[%d] missing", q);
+        BFF_REQUIRE(d->peer_row0 >= 0, "bff_lift_scene: negative peer_row0");
+    }
+    if (!use_peers && d->rows && d->n_masks > 0 && words > 0)
         BFF_CUDA(cudaMemsetAsync(d->rows, 0, (size_t)d->n_masks * (size_t)n_slices * row_stride * 4, stream));
     if (d->masked_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->masked_counts, 0, (size_t)d->n_queries * n * 4, stream));
     if (d->viewed_counts && n > 0) BFF_CUDA(cudaMemsetAsync(d->viewed_counts, 0, (size_t)n * 4, stream));
@@ -684,6 +700,9 @@ extern "C" int bff_lift_scene(const bff_lift_desc *d, void *stream_) {
     }
     p.n_points = n; p.words = words;
     p.row_stride = row_stride; p.slice_rows = d->n_masks; p.n_slices = n_slices;
+    p.use_peers = use_peers ? 1 : 0;
+    p.peer_row0 = d->peer_row0;
+    for (int q = 0; q < 8; ++q) p.peer_rows[q] = use_peers && q < n_slices ? d->peer_rows[q] : nullptr;
     p.mask_words = ceil_div64((long long)d->height * d->width, 32);
     p.n_frames = d->n_frames;
     int fc = d->frames_per_chunk > 0 ? d->frames_per_chunk : auto_frames_per_chunk(n, d->n_frames);

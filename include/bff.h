@@ -120,6 +120,13 @@ typedef struct bff_lift_desc {
     int32_t n_row_slices;
     int32_t reserved2;
     int64_t row_slice_words;
+    /* Fused exchange (n_row_slices = G > 1, optional): peer_rows[p] != NULL for every p < G makes the kernel store slice p
+     * of its rows DIRECTLY into rank p's receive buffer (peer memory over NVLink, opened with bff_ipc_open): row m of this
+     * launch lands at peer_rows[p] + (peer_row0 + m) * row_slice_words. `rows` is then unused (may be NULL), nothing is
+     * zeroed by the call (every owner zeroes its own buffer and the ranks synchronise before the launches), and no
+     * separate row exchange follows. */
+    uint32_t *peer_rows[8];
+    int64_t peer_row0;
 } bff_lift_desc;
 
 BFF_API int bff_version(void);
@@ -345,6 +352,14 @@ BFF_API int bff_comm_allgather_bytes(bff_comm *comm, const void *send, void *rec
  * to this rank's points. rows_per_rank: HOST array (world). One grouped ncclSend/ncclRecv; the own block is a local copy. */
 BFF_API int bff_comm_exchange_rows(bff_comm *comm, const uint32_t *send, int32_t n_local_rows, const int32_t *rows_per_rank,
                                    int64_t slice_words, uint32_t *recv, void *stream);
+/* Device buffers other processes of this node can map (CUDA IPC; the frame-sharded lifting stores row slices straight into
+ * its peers' receive buffers). bff_ipc_alloc: cudaMalloc + the 64-byte handle to hand to the peers; bff_ipc_open: map a
+ * peer's buffer into this process (peer access is enabled on demand); close / free undo them. */
+BFF_API int bff_ipc_alloc(int64_t bytes, void **dev_ptr, void *handle64);
+BFF_API int bff_ipc_open(const void *handle64, void **dev_ptr);
+BFF_API int bff_ipc_close(void *dev_ptr);
+BFF_API int bff_ipc_free(void *dev_ptr);
+
 /* Column slices of packed rows: out (n_rows, slice_words) = words [word0, word0 + slice_words) of rows (n_rows, words),
  * zero beyond `words`; and the inverse for results: in (world, n_rows, slice_words) -> out (n_rows, words). */
 BFF_API int bff_rows_slice(const uint32_t *rows, int32_t n_rows, int64_t words, int64_t word0, int64_t slice_words, uint32_t *out, void *stream);
