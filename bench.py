@@ -185,6 +185,7 @@ class GpuScene:
         from bff_b200 import devpipe
         from bff_b200.refine import STAGE1_CLASS_NAMES
         self.device_decisions = os.environ.get("BFF_DEVICE_DECISIONS", "1") != "0"
+        self.use_graph = os.environ.get("BFF_STEP_GRAPH", "1") != "0"        # replay the step as one CUDA graph
         s1_labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
         for qi, name in enumerate(self.names):
             q_ = name.replace(" ", "_")
@@ -299,50 +300,46 @@ class GpuScene:
 
 
 def _step_device(self, d, ev, to_host=True):
-    """The same step with every decision taken on the device (bff_stage2_device / bff_refine_device): the whole chain
-    lift -> aggregate -> filter -> refine is enqueued without a host round trip; the only synchronisation is the one
-    that brings the final counts back, after the last kernel."""
-    from bff_b200 import devpipe, ops
-    inp, cfg = self.inp, self.inp["cfg"]
-    ev()
-    # (the stage-1 masks first: they depend on nothing, and the GPU decodes them while the host is still preparing the
-    # lifting launch -- at the start of a step nothing is queued ahead)
-    n1 = len(inp["stage1"]["ins"])
-    s1 = ops.rle_to_bits_dev(d["s1_runs"], n1, self.n)
-    wd = s1.shape[1]
-    masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
-    ev()
-    out = self.lift(d, masks2d, timing=getattr(self, "_timing", False))
-    ev()
-    ev()                                                         # (no exchange on one GPU)
-    s2s = []
-    for qi in self.my_queries:
-        rows_q = out.rows if self.row_index_dev is None else ops.rows_gather(out.rows, self.row_index_dev32[qi])
-        if rows_q.shape[0] == 0:                                 # nothing lifted for this query (:465-478): known on the host
-            s2s.append(None)
-            continue
-        s2s.append(devpipe.stage2_device(rows_q, d[f"conf{qi}"], self.labels_q[qi], out.masked_counts[qi], out.viewed_counts, self.n, cfg,
-                                         mc_cap=rows_q.shape[0], vc_cap=self.f))
-    ev()
-    rfs = []
-    for qi, s2 in zip(self.my_queries, s2s):
-        s1_q = s1.clone() if len(self.my_queries) > 1 else s1   # pass 1 ORs matched stage-1 rows in place (refinement.py:248)
-        if s2 is None:
-            rows2, n2, conf2 = torch.zeros((1, wd), dtype=torch.int32, device=self.dev), 0, torch.zeros((1,), dtype=torch.float32, device=self.dev)
-        else:
-            rows2, n2, conf2 = s2.out_rows, s2.n_selected_dev, s2.selected_conf_dev
-        rf = devpipe.refine_device(s1_q, rows2, n2, conf2, d[f"isq{qi}"], d[f"sim{qi}"], self.n, cfg, self.names[qi], select_mode=1)
-        rf.enqueue_unpack()
-        rfs.append(rf)
-    finals = [rf.final(to_host) for rf in rfs]
-    ev()
+    """The same step with every decision taken on the device (bff_b200/scene_step.py: bff_stage2_device /
+    bff_refine_device): the whole chain lift -> aggregate -> filter -> refine is enqueued without a host round trip -- or
+    replayed as ONE CUDA graph when `use_graph` is set (the graph is captured on the first call with a given set of input
+    buffers). The only synchronisation is the one that brings the final counts back, after the last kernel."""
+    from bff_b200.scene_step import SceneStep
+    if getattr(self, "_scene_step", None) is None:
+        self._scene_step = SceneStep(n_points=self.n, height=self.h, width=self.w, intrinsics=self.inp["K"], native_size=self.native,
+                                     names=self.names, labels_q=self.labels_q, cfg=self.inp["cfg"], n_stage1=len(self.inp["stage1"]["ins"]),
+                                     n_masks=self.n_masks, n_frames=self.f,
+                                     row_index=self.row_index_dev32 if self.row_index_dev is not None else None, device=self.dev,
+                                     lanes=int(os.environ.get("BFF_QUERY_LANES", "4")))
+    st = self._scene_step
+    timing = getattr(self, "_timing", False)
+    if st.has_graph(d) and not timing:
+        finals, state = st.run(d, to_host)
+    else:
+        st.timing_events = self.lift_events if timing else None
+        marks = (lambda: ev()) if timing else None
+        finals, state = st.run(d, to_host, marks)
+        st.timing_events = None
+    s2s = [c[0] for c in state["chains"]]
     self.last_stage2_dev = s2s[0] if s2s else None
-    self.last_refine_dev = rfs[0] if rfs else None
+    self.last_refine_dev = state["chains"][0][1] if state["chains"] else None
     self.last_finals = finals
     return finals[0] if finals else None
 
 
 GpuScene.step_device = _step_device
+
+
+def _graph_inputs(self, d):
+    """Record the device-decision step over the buffers of `d` as ONE CUDA graph (later steps on `d` replay it)."""
+    if not (self.use_graph and self.device_decisions and self.inp["cfg"]["min_aggragated_masks"] >= 1) or (self.dist is not None and self.dist.world_size > 1):
+        return False
+    self.step(d, to_host=False)                       # creates the SceneStep, warms workspaces and attributes
+    self._scene_step.capture(d)
+    return True
+
+
+GpuScene.graph_inputs = _graph_inputs
 
 
 def _step_sharded(self, d, ev, to_host=True):
@@ -560,28 +557,45 @@ def run_gpu(args):
         if ctx:
             ctx.finalize()
         return
-    # ---- device-resident timing: K steps, each bracketed by events, L2 flushed in between (untimed)
+    # ---- device-resident timing: K steps, each bracketed by events, L2 flushed in between (untimed). A step replays the
+    # CUDA graph of the whole chain (one launch) and ends with the read-back of the final counts.
+    graphed = g.graph_inputs(d)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     barrier()
     launches0 = _cabi.launch_count
-    tot_ms, lift_ms, iou_ms_acc, stage_acc = 0.0, 0.0, 0.0, np.zeros(5)
+    tot_ms = 0.0
     wall0 = time.time()
     for _ in range(args.steps):
         flush.fill_(1)
         torch.cuda.synchronize()
-        tm = []
-        final = g.step(d, tm, to_host=False)
+        e0 = _event()
+        final = g.step(d, to_host=False)
+        e1 = _event()
         torch.cuda.synchronize()
-        ms = [tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)]
-        stage_acc += np.asarray(ms)
-        tot_ms += tm[0].elapsed_time(tm[-1])
-        lift_ms += g.lift_events[0].elapsed_time(g.lift_events[1])
+        tot_ms += e0.elapsed_time(e1)
     launches = _cabi.launch_count - launches0
     barrier()
     wall_dev = time.time() - wall0
     clocks = sampler.stop() if rank == 0 else None
+    # ---- the same steps kernel by kernel (no graph) with events at the stage boundaries and around the lifting launch:
+    # the break-down and the roofline's launch time (a graph cannot be timed from the inside)
+    lift_ms, stage_acc = 0.0, np.zeros(5)
+    k_break = max(3, min(args.steps, 10))
+    for _ in range(3):                                # the allocator pools of the ungraphed path (per query lane) warm up again
+        g.step(d, [], to_host=False)
+    torch.cuda.synchronize()
+    for _ in range(k_break):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        tm = []
+        g.step(d, tm, to_host=False)
+        torch.cuda.synchronize()
+        stage_acc += np.asarray([tm[i].elapsed_time(tm[i + 1]) for i in range(len(tm) - 1)])
+        lift_ms += g.lift_events[0].elapsed_time(g.lift_events[1])
+    stage_acc *= args.steps / k_break
+    lift_ms *= args.steps / k_break
     # ---- end to end: pinned host buffers -> device -> step -> final masks on the host
     e2e_ms = 0.0
     for _ in range(args.steps):
@@ -597,6 +611,10 @@ def run_gpu(args):
     from bff_b200 import ops
     copy_stream = torch.cuda.Stream(device=dev, priority=-1 if args.upload.endswith('+hi') else 0)
     bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]   # double buffer, no allocation in the loop
+    # (No CUDA graph in this loop. Measured: a graph launch issued while the next scene's 184 MB move on the H2D copy engine
+    # waits for that transfer -- the launch itself ships its command buffers over the same engine -- and the loop went from
+    # 3.5 to 4.1 ms per scene at c2, from 7.9 to 42 ms at c4. Kernel-by-kernel launches do not touch the engine; the loop is
+    # upload-bound either way.)
     done = [None, None]
     # The next scene's buffers move on the H2D copy engine (55 GB/s here, against 46-51 GB/s for an SM copy kernel that
     # shares SMs and the PCIe request queue with the running step). That only works because the running step never
@@ -726,7 +744,7 @@ def run_gpu(args):
                 "numa_bound_cpus_rank0": (len(numa_cpus) if numa_cpus else None),
                 "upload_gbs_probe": {"copy_engine": round(g.host[big].numel() * g.host[big].element_size() / t_ce / 1e6, 1),
                                      "sm_kernel": round(g.host[big].numel() * g.host[big].element_size() / t_sm / 1e6, 1)}},
-        "gpu_launches": int(launches),
+        "gpu_launches": int(launches), "step_as_cuda_graph": bool(graphed),
         "roofline": {"bound": "hbm", "kernel": "bff::lift_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms_lift},
@@ -840,14 +858,16 @@ def frame_sharded_run(args, ctx, dev, flush, barrier, workload=None, steps=None)
         d1 = g1.upload()
         for _ in range(3):
             g1.step(d1)
+        g1.graph_inputs(d1)                           # the 1-GPU step as it is timed at N=1: one CUDA graph
         t1 = 0.0
         for _ in range(steps):
             flush.fill_(1)
             torch.cuda.synchronize()
-            tm = []
-            g1.step(d1, tm, to_host=False)
+            e0 = _event()
+            g1.step(d1, to_host=False)
+            e1 = _event()
             torch.cuda.synchronize()
-            t1 += tm[0].elapsed_time(tm[-1])
+            t1 += e0.elapsed_time(e1)
         single_ms = t1 / steps
 
         def same_final(a, b):

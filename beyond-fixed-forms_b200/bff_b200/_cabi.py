@@ -206,11 +206,12 @@ def current_stream():
 _ctxs = {}
 
 
-def ctx(device_index: int):
-    """One bff_ctx (stream + scratch arenas) per device AND host thread, created on first use: the fused pipelines
-    carve their scratch from the context's arenas, so concurrent callers (bff_b200/pool.py) each need their own."""
+def ctx(device_index: int, lane: int = 0):
+    """One bff_ctx (stream + scratch arenas) per device, host thread AND lane, created on first use: the pipelines carve
+    their scratch from the context's arenas, so chains that run concurrently (queries of one scene on their own streams,
+    scene_step.py) each need their own."""
     import threading
-    key = (int(device_index), threading.get_ident())
+    key = (int(device_index), threading.get_ident(), int(lane))
     if key not in _ctxs:
         h = c_void_p()
         check(lib().bff_ctx_create(int(device_index), ctypes.byref(h)), "bff_ctx_create")

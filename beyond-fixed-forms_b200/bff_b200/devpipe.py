@@ -97,7 +97,7 @@ class Stage2Dev:
 
 def stage2_device(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str], mc: torch.Tensor, vc: Optional[torch.Tensor],
                   n_points: int, cfg, mc_cap: Optional[int] = None, vc_cap: int = 0, label_id: Optional[torch.Tensor] = None,
-                  vote_point0: int = 0, n_vote_points: Optional[int] = None, comm=None) -> Stage2Dev:
+                  vote_point0: int = 0, n_vote_points: Optional[int] = None, comm=None, lane: int = 0) -> Stage2Dev:
     """aggregate + point filter + solve_overlapping + row filter of one query's lifted rows, enqueued without any
     synchronisation. rows (n,Wd) int32 CUDA; conf (n,) float32 CUDA; mc / vc int32 CUDA vote vectors (over ALL points
     when the rows are one rank's point slice: then `vote_point0` is the slice's first point and `n_points` its length);
@@ -128,7 +128,7 @@ def stage2_device(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str],
     d.ratio_is_float, d.ratio_i, d.ratio_f = _scalar_kind(cfg["remove_filtered_masks"])
     d.mc_cap, d.vc_cap = int(n if mc_cap is None else mc_cap), int(vc_cap)
     d.out_rows, d.cap_groups, d.result, d.comm = ptr(out_rows), cap, ptr(result), comm
-    check(lib().bff_stage2_device(_cabi.ctx(dev.index or 0), d, current_stream()), "bff_stage2_device")
+    check(lib().bff_stage2_device(_cabi.ctx(dev.index or 0, lane), d, current_stream()), "bff_stage2_device")
     _cabi.launch_count += 17 if mode != 2 else 13
     return Stage2Dev(n, cap, int(n_points), out_rows, result, labels)
 
@@ -212,7 +212,7 @@ class RefineDev:
 
 
 def refine_device(s1_rows: torch.Tensor, s2_rows: torch.Tensor, n2, s2_conf: torch.Tensor, is_query: torch.Tensor, sim: torch.Tensor,
-                  n_points: int, cfg, query: str, select_mode: int = 1, sim_thres: float = 0.0, comm=None) -> RefineDev:
+                  n_points: int, cfg, query: str, select_mode: int = 1, sim_thres: float = 0.0, comm=None, lane: int = 0) -> RefineDev:
     """Pass 1 (+ pass 2 unless select_mode 0) of tools/refinement.py for one scene, enqueued without synchronisation.
     s1_rows (n1,Wd) int32 CUDA, modified in place (:248); s2_rows (cap2,Wd) of which the first n2 count -- `n2` is an int
     or a 1-element int32 CUDA tensor (Stage2Dev.n_selected_dev); s2_conf (cap2,) float32 CUDA; is_query (n1,) uint8 CUDA:
@@ -237,7 +237,7 @@ def refine_device(s1_rows: torch.Tensor, s2_rows: torch.Tensor, n2, s2_conf: tor
     d.select_mode, d.sim_percentile, d.sim_thres = int(select_mode), float(cfg["refinment_sim_percentile"]), float(sim_thres)
     d.refine_iou_thres = float(np.float32(cfg["refiment_iou_thres"]))
     d.s2_out, d.final_rows, d.result, d.comm = ptr(s2_out), ptr(final_rows), ptr(result), comm
-    check(lib().bff_refine_device(_cabi.ctx(dev.index or 0), d, current_stream()), "bff_refine_device")
+    check(lib().bff_refine_device(_cabi.ctx(dev.index or 0, lane), d, current_stream()), "bff_refine_device")
     _cabi.launch_count += 11 + (2 if select_mode else 0) + (0 if isinstance(n2, torch.Tensor) else 1)
     return RefineDev(d, (s1_rows, s2_rows, n2, s2_conf, is_query, sim), n1, cap2, int(n_points), result, final_rows, s2_out, query)
 

@@ -217,3 +217,60 @@ def test_c4_subset_exact_against_oracle(c4):
     np.testing.assert_array_equal(unpack_rows(part.rows.cpu().numpy(), g.n)[:, sel], rows_o)
     np.testing.assert_array_equal(part.masked_counts.cpu().numpy()[0][sel], mc_o[0])
     np.testing.assert_array_equal(part.viewed_counts.cpu().numpy()[sel], vc_o)
+
+
+def _same_final(a, b, what):
+    assert list(a["final_class"]) == list(b["final_class"]), what
+    if isinstance(a["ins"], list) or isinstance(b["ins"], list):
+        assert isinstance(a["ins"], list) and isinstance(b["ins"], list), what
+        return
+    assert a["ins"].shape == b["ins"].shape, what
+    assert torch.equal(a["ins"].cpu().bool(), b["ins"].cpu().bool()), what
+    np.testing.assert_allclose(torch.as_tensor(a["conf"]).float().numpy(), torch.as_tensor(b["conf"]).float().numpy(), rtol=1e-5, err_msg=what)
+
+
+def test_c2_whole_step_equals_the_cpu_port(c2):
+    """The WHOLE timed step at its real size -- lift -> aggregate (525 lifted masks: the tcgen05 intersections, the 525-node
+    component search) -> point filter -> overlap resolution -> refinement against 200 stage-1 masks -- with the decisions
+    taken on the device (what bench.py times), with the decisions taken on the host, and by the dense CPU port of the
+    reference (oracle/reference_port.py, ~1/2 minute): identical final masks, classes, and confidences within 1e-5."""
+    sys.path.insert(0, ROOT)
+    import bench
+    inp, g, d, _ = c2
+    g.device_decisions = True
+    dev_final = g.step(d)
+    dev_s2 = g.last_stage2_dev.saved_dict()[0]
+    g.device_decisions = False
+    host_final = g.step(d)
+    host_s2 = g.last_stage2
+    g.device_decisions = True
+    assert dev_s2["ins"].shape[0] >= 5 and dev_final["ins"].shape[0] >= 5
+    _same_final(dev_s2, host_s2, "stage 2: device vs host decisions")
+    _same_final(dev_final, host_final, "final: device vs host decisions")
+    torch.set_num_threads(1)                                  # the port's tiny dgemms are fastest single-threaded
+    mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
+    port = bench.cpu_step(inp, mask_frames, view_frames)[0]
+    _same_final(dev_final, port, "final: device decisions vs the CPU port of the reference")
+
+
+def test_c3_subset_whole_step_equals_the_cpu_port(cuda_dev):
+    """Four of c3's twenty concurrent queries over the c2-sized scene (one shared lifting launch, per-query votes and rows):
+    device decisions vs the CPU port, which runs the whole path once per query like one reference process per --cls."""
+    sys.path.insert(0, ROOT)
+    import bench
+    old = dict(bench.WORKLOADS["c3"])
+    bench.WORKLOADS["c3q4"] = dict(old, n_queries=4, n_frames=120)
+    try:
+        inp = bench.build_inputs("c3q4", 0, 1, cuda_dev)
+    finally:
+        del bench.WORKLOADS["c3q4"]
+    g = bench.GpuScene(inp, cuda_dev)
+    d = g.upload()
+    g.step(d)
+    finals = list(g.last_finals)
+    assert len(finals) == 4 and sum(isinstance(f["ins"], torch.Tensor) and f["ins"].shape[0] >= 2 for f in finals) >= 3
+    torch.set_num_threads(1)
+    mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
+    port = bench.cpu_step(inp, mask_frames, view_frames)
+    for qi in range(4):
+        _same_final(finals[qi], port[qi], f"query {qi}")
