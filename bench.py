@@ -131,7 +131,7 @@ class GpuScene:
 
     def __init__(self, inp, device, dist_ctx=None):
         from bff_b200 import lift as lift_mod, scene_io
-        from bff_b200.rle import runs_for_device
+        from bff_b200.rle import pairs_for_device
         self.inp, self.dev, self.dist = inp, device, dist_ctx
         spec = inp["spec"]
         self.n, self.h, self.w = spec.n_points, spec.height, spec.width
@@ -145,8 +145,8 @@ class GpuScene:
         order = {fid: i for i, fid in enumerate(inp["frame_ids"])}
         perm = [order[fid] for fid in self.frame_ids]           # mask frames first, then view-only frames
         rles, mask_query, offsets = lift_mod.mask_layout(self.per_frame, self.queries, 0, len(self.frame_ids))
-        runs, length = runs_for_device(rles)
-        assert length == self.h * self.w
+        counts, pair_off, length = pairs_for_device(rles)
+        assert length == self.h * self.w or not rles
         self.n_masks = len(rles)
         self.row_index = lift_mod.query_row_index(self.per_frame, self.queries)   # per query: its rows in file order
         self.conf_q, self.labels_q = [], []
@@ -156,8 +156,7 @@ class GpuScene:
             self.labels_q.append(l)
         self.conf_list, self.labels = self.conf_q[0], self.labels_q[0]
         self.my_queries = list(range(self.nq))                  # frame-sharded runs split the queries over the ranks
-        self.workers = int(os.environ.get("BFF_QUERY_WORKERS", "1"))   # concurrent per-query chains (bff_b200/pool.py)
-        s1_runs, s1_len = runs_for_device(list(inp["stage1"]["ins"]))
+        s1_counts, s1_off, s1_len = pairs_for_device(list(inp["stage1"]["ins"]))
         assert s1_len == self.n
 
         def pin(a):
@@ -174,8 +173,8 @@ class GpuScene:
             x4 = self.plan.padded_cloud(x4)        # NaN points behind the cloud: every point slice has the same width
         # host side (pinned): exactly what bff's loaders hand to the device
         self.host = dict(xyz=pin(x4), pinv=pin(inp["pinv"][perm]), depth=pin(inp["depth"][perm].view(np.int16)),
-                         runs=pin(runs), offsets=pin(np.asarray(offsets, np.int32)),
-                         viewed=pin(np.asarray(self.viewed, np.uint8)), s1_runs=pin(s1_runs))
+                         counts=pin(counts), pair_off=pin(pair_off), offsets=pin(np.asarray(offsets, np.int32)),
+                         viewed=pin(np.asarray(self.viewed, np.uint8)), s1_counts=pin(s1_counts), s1_pair_off=pin(s1_off))
         if self.nq > 1:
             self.host["mask_query"] = pin(np.asarray(mask_query, np.int32))
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
@@ -203,6 +202,15 @@ class GpuScene:
             # recorded inside bff_lift_scene around its memsets + kernel: the launch itself, without host gaps
             self.lift_events = (_event(), _event())
 
+    def masks2d(self, d):
+        """The 2D masks of all frames as packed bit rows, decoded on the device from the RLE wire format."""
+        from bff_b200 import ops
+        return ops.rle_pairs_to_bits_dev(d["counts"], d["pair_off"], self.h * self.w) if self.n_masks else None
+
+    def stage1_rows(self, d):
+        from bff_b200 import ops
+        return ops.rle_pairs_to_bits_dev(d["s1_counts"], d["s1_pair_off"], self.n)
+
     def upload(self):
         return {k: v.to(self.dev, non_blocking=True) for k, v in self.host.items()}
 
@@ -228,7 +236,7 @@ class GpuScene:
         if self.device_decisions and not (self.dist is not None and self.dist.world_size > 1) and cfg["min_aggragated_masks"] >= 1:
             return self.step_device(d, ev, to_host)
         ev()
-        masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+        masks2d = self.masks2d(d)
         ev()
         out = self.lift(d, masks2d, timing=timers is not None)
         ev()
@@ -238,7 +246,7 @@ class GpuScene:
         if sharded:
             rows, mc, vc = dist_mod.exchange(self.dist, rows, self.rows_per_rank, mc, vc)
         ev()
-        s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), self.n)
+        s1 = self.stage1_rows(d)
 
         def job(qi):
             if sharded:
@@ -266,15 +274,7 @@ class GpuScene:
             thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
             return refine.pass2_scene(p1, name, cfg["refiment_iou_thres"], thr, to_host=to_host)
 
-        if len(self.my_queries) > 1 and self.workers > 1:
-            # the queries' chains are independent: run them on concurrent streams (bff_b200/pool.py); the two stage
-            # timers then cover both stages of all queries together
-            from bff_b200.pool import get_pool
-            both = get_pool(self.dev, self.workers).map(lambda qi: (lambda r2: (r2, refine_query(qi, r2)))(aggregate(qi)), self.my_queries)
-            per_query, finals = [b[0] for b in both], [b[1] for b in both]
-            ev()
-            ev()
-        else:
+        if True:
             if len(self.my_queries) > 1 and os.environ.get("BFF_AGG_BATCH", "1") != "0":
                 # all queries advance phase by phase inside ONE bff_stage2_aggregate_batch call (shared synchronisations)
                 per_query = [r for r, _ in stage2.aggregate_and_filter_batch([job(qi) for qi in self.my_queries], cfg, keep_rows=True,
@@ -351,7 +351,7 @@ def _step_sharded(self, d, ev, to_host=True):
     inp, cfg, plan, comm = self.inp, self.inp["cfg"], self.plan, self.comm
     sw, world = plan.slice_words, plan.world
     ev()
-    masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+    masks2d = self.masks2d(d)
     ev()
     votes = torch.empty((self.nq + 1, plan.n_padded), dtype=torch.int32, device=self.dev)
     peers = getattr(self, "peers", None)
@@ -371,7 +371,7 @@ def _step_sharded(self, d, ev, to_host=True):
     rows = peers.local if peers is not None else comm.exchange_rows(out.rows, self.rows_per_rank)
     ev()
     n1 = len(inp["stage1"]["ins"])
-    s1 = ops.rows_slice(ops.rle_to_bits_dev(d["s1_runs"], n1, self.n), plan.rank * sw, sw)
+    s1 = ops.rows_slice(self.stage1_rows(d), plan.rank * sw, sw)
     s2s = []
     for qi in range(self.nq):
         rows_q = rows if self.all_index_dev32[qi] is None else ops.rows_gather(rows, self.all_index_dev32[qi])
@@ -691,7 +691,7 @@ def run_gpu(args):
     d2h = sum(fn["ins"].numel() * fn["ins"].element_size() for fn in g.last_finals if isinstance(fn["ins"], torch.Tensor))
     # ---- IoU kernel alone (mask-IoU pairs/s of the aggregation-sized square call)
     from bff_b200 import ops
-    rows = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)).rows
+    rows = g.lift(d, g.masks2d(d)).rows
     for _ in range(3):
         ops.mask_iou(rows)
     torch.cuda.synchronize()

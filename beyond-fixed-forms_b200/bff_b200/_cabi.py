@@ -125,6 +125,7 @@ SYMBOLS = {
     "bff_pack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_unpack_bits": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p]),
     "bff_rle_to_bits": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_void_p]),
+    "bff_rle_pairs_to_bits": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_void_p, c_void_p]),
     "bff_stage2_aggregate": (c_int, [c_void_p, POINTER(Stage2Desc), c_void_p]),
     "bff_stage2_aggregate_batch": (c_int, [c_void_p, POINTER(Stage2Desc), c_int32, c_void_p]),
     "bff_refine_match": (c_int, [c_void_p, POINTER(RefineDesc), c_void_p]),

@@ -80,6 +80,8 @@ class Stage2Dev:
         from ._log import log
         h = self.header()
         log("masks_to_be_merged", h["groups"])
+        if h["n_unique"]:
+            log("filter_thres_value", torch.tensor(h["filter_value"]))
         if h["n_groups"] == 0:
             log("No 3d masks detected after aggregation")
             return scene_io.empty_stage2(), False
@@ -184,6 +186,16 @@ class RefineDev:
                 conf_out=get("conf_out", m, np.float32), other=get("other", int(r[_cabi.RFR_N_OTHER])),
                 final_src=get("final_src", k), final_conf=get("final_conf", k, np.float32))
         return self._host
+
+    def set_sims(self, sims: Sequence[float]):
+        """Replace the similarities of the matched pairs (one per remaining stage-2 mask, refinement.py:297-302) before
+        `select`: callers whose similarity function is expensive (CLIP) evaluate it for the MATCHED labels only, like the
+        reference, instead of filling the whole per-mask table up front."""
+        v = np.asarray(list(sims), dtype=np.float64)
+        if v.size:
+            o = self._off()["sims"][0]
+            self.result[o:o + 2 * v.size].copy_(torch.from_numpy(v.view(np.int32)).to(self.result.device))
+        self._host = None
 
     def select(self, sim_thres: float):
         """Pass 2 with the class-global threshold of refinement.py:317-324 (after bff_refine_device in select_mode 0)."""

@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from . import ops, scene_io
-from .rle import runs_for_device
+from .rle import pairs_for_device
 
 
 @dataclasses.dataclass
@@ -118,10 +118,10 @@ def lift_frames(xyz_dev: torch.Tensor, intrinsics: np.ndarray, frames: scene_io.
     hw = height * width
     masks2d = None
     if rles:
-        runs, length = runs_for_device(rles, expect_length=None)
+        counts, pair_off, length = pairs_for_device(rles, expect_length=None)
         if length != hw:
             raise ValueError(f"2D mask length {length} does not match height_2d*width_2d = {hw}")
-        masks2d = ops.rle_to_bits(runs, len(rles), hw, dev)
+        masks2d = ops.rle_pairs_to_bits_dev(torch.from_numpy(counts).to(dev), torch.from_numpy(pair_off).to(dev), hw)
     if frames.depth_is_raw:
         depth_dev = torch.from_numpy(frames.depth.view(np.int16)).to(dev)
     else:

@@ -364,6 +364,20 @@ def rle_to_bits_dev(runs: torch.Tensor, n_rows: int, length: int) -> torch.Tenso
     return out
 
 
+def rle_pairs_to_bits_dev(counts: torch.Tensor, pair_offset: torch.Tensor, length: int) -> torch.Tensor:
+    """RLE wire format -> packed rows on the device (bff_rle_pairs_to_bits): counts int64 CUDA = the masks' (1-based start,
+    length) pairs back to back, pair_offset (R+1,) int64 CUDA. The reference's int32 / slice arithmetic runs in the kernel."""
+    counts = _cuda(counts, torch.int64, "counts").reshape(-1)
+    pair_offset = _cuda(pair_offset, torch.int64, "pair_offset").reshape(-1)
+    n_rows = pair_offset.numel() - 1
+    out = torch.empty((n_rows, words_for(length)), dtype=torch.int32, device=counts.device)
+    check(lib().bff_rle_pairs_to_bits(ptr(counts) if counts.numel() else None, ptr(pair_offset), n_rows, counts.numel() // 2, int(length), ptr(out),
+                                      current_stream()), "bff_rle_pairs_to_bits")
+    if n_rows and length and counts.numel():
+        _count()
+    return out
+
+
 def rle_to_bits(runs: np.ndarray, n_rows: int, length: int, device) -> torch.Tensor:
     """runs (R,3) int32 host [row, lo, hi) -> packed (n_rows, ceil(length/32)) int32 on `device`."""
     runs = np.ascontiguousarray(runs, dtype=np.int32).reshape(-1, 3)

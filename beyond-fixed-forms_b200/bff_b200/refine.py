@@ -11,7 +11,7 @@ import torch
 
 from . import _log, ops, scene_io
 from ._log import log
-from .rle import runs_for_device
+from .rle import pairs_for_device
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 with open(os.path.join(_HERE, "stage1_classes.txt")) as _fh:
@@ -20,6 +20,7 @@ with open(os.path.join(_HERE, "stage1_classes.txt")) as _fh:
 
 
 FUSED = True     # bff_refine_match (C++ decisions next to the launches); False = one Python/torch call per step
+DEVICE = True    # bff_refine_device (every decision a kernel, one synchronisation per scene); takes precedence over FUSED
 
 
 def idx_to_label(idx) -> str:
@@ -38,8 +39,8 @@ def stage1_rows(stage1: dict, device) -> torch.Tensor:
     rles = list(stage1["ins"])
     if not rles:
         return torch.zeros((0, 0), dtype=torch.int32, device=device)
-    runs, length = runs_for_device(rles)
-    return ops.rle_to_bits(runs, len(rles), length, device)
+    counts, pair_off, length = pairs_for_device(rles)
+    return ops.rle_pairs_to_bits_dev(torch.from_numpy(counts).to(device), torch.from_numpy(pair_off).to(device), length)
 
 
 def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
@@ -57,6 +58,8 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
                 "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
     s2 = stage2["rows"] if "rows" in stage2 else ops.pack_bits(stage2["ins"].to(device))
     s2_conf = stage2["conf"]
+    if DEVICE and isinstance(s2_conf, torch.Tensor) and s2_conf.dtype == torch.float32 and s1.shape[0] > 0:
+        return _pass1_device(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device)
     if FUSED and s2_conf.dtype == torch.float32:
         return _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device)
     mm = torch.argmax(iou_between_stages(s1, s2), dim=1)                       # :208-213
@@ -144,6 +147,29 @@ class _RefineJob:
                 "n_points": self.n_points, "other": sel[m:]}
 
 
+def _pass1_device(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:
+    """The matching part of pass 1 (refinement.py:208-312) with every decision on the device: bff_refine_device in
+    select_mode 0, ONE synchronisation (the result block), then the similarity function for the MATCHED labels only, like
+    the reference (:297-302; with CLIP every call is two text encodings). Pass 2 later runs bff_refine_select_device on the
+    state left on the device (`rf`)."""
+    from . import devpipe
+    isq = ops.small_to_device(torch.tensor([l == q_ for l in labels], dtype=torch.uint8), device)
+    sim0 = torch.zeros((len(labels),), dtype=torch.float64, device=device)           # filled in for the matches below
+    cfg = {"stage1_iou_thres": stage1_iou_thres, "refinment_sim_percentile": 0.0, "refiment_iou_thres": 0.0}
+    rf = devpipe.refine_device(s1, s2, int(s2.shape[0]), ops.small_to_device(s2_conf, device), isq, sim0, n_points, cfg, query, select_mode=0)
+    h = rf.header()
+    if _log.VERBOSE:
+        log("DEBUG best_match_after_iou_check", [torch.tensor(int(b)) for b in h["best"]])
+    matched_labels = [labels[int(k)] for k in h["match"]]
+    sims = [float(sim_fn(query, l)) for l in matched_labels]                           # :297-302
+    rf.set_sims(sims)
+    ious = torch.from_numpy(h["match_iou"].copy())
+    log("iou for matched labels", ious)
+    log("Matched labels:", matched_labels)
+    log("Clip similarities:", sims)
+    return {"ious": ious, "sims": sims, "rf": rf, "conf2": torch.from_numpy(h["conf_out"].copy()), "n_points": n_points}
+
+
 def _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device) -> dict:
     """The matching part of pass 1 (refinement.py:208-290) in one call: bff_refine_match."""
     from . import _cabi
@@ -191,6 +217,11 @@ def pass2_scene(p1: dict, query: str, iou_thres: float, sim_thres: float, to_hos
     """Selection (refinement.py:330-426) -> the dict that is saved: the other stage-1 masks of the class first
     (conf 0.5), then per matched pair the stage-1 mask (IoU above the threshold and CLIP-similar enough), nothing
     (IoU above, not similar) or the stage-2 mask (IoU not above); confidences are the stage-2 ones."""
+    if "rf" in p1:                               # state of bff_refine_device: the selection runs on the device too
+        rf = p1["rf"]
+        rf.desc.refine_iou_thres = float(np.float32(iou_thres))
+        rf.select(sim_thres)
+        return rf.final(to_host)
     out = {"ins": [], "conf": [], "final_class": []}
     n_other = p1["other"].shape[0]
     kept, from_s1 = [], []
@@ -282,6 +313,65 @@ def refine_class(cfg, cls: str, device, sim_fn: Callable[[str, str], float]):
         if len(p1["ious"]) != 0 and len(out["final_class"]) != 0:
             ckpt[scene_id] = True                                              # :427-428
             scene_io.write_checkpoint(ckpt_path, ckpt)
+
+
+def refine_classes(cfg, classes: Sequence[str], device, sim_fn: Callable[[str, str], float]):
+    """refine_class for several classes in ONE process (the reference starts one process per class,
+    evaluation/eval/run_evl.py:80, and each reloads CLIP, refinement.py:147): the scenes are walked once, every scene's
+    stage-1 file is read and decoded once and handed to each class as a copy (pass 1 ORs into it, :248), and `sim_fn`
+    (with its cache) is shared. Per class the outputs, the global threshold (:317-324) and the checkpoint file are
+    exactly those of one refine_class call."""
+    g = (lambda k: cfg[k]) if isinstance(cfg, dict) else (lambda k: getattr(cfg, k))
+    stage1_dir, mask_3d_dir = g("stage_1_results_dir"), g("mask_3d_dir")
+    files = {cls: sorted(s for s in os.listdir(os.path.join(mask_3d_dir, cls)) if s.endswith("_00.pth")) for cls in classes}
+    per_scene = {cls: [] for cls in classes}
+    for fn in sorted(set(f for fs in files.values() for f in fs)):
+        scene_id = fn.replace(".pth", "")
+        p1_path = os.path.join(stage1_dir, f"{scene_id}.pth")
+        stage1, master = None, None
+        for cls in classes:
+            if fn not in files[cls]:
+                continue
+            p2_path = os.path.join(mask_3d_dir, cls, fn)
+            if not (os.path.exists(p1_path) and os.path.exists(p2_path)):
+                continue                                                       # :175-178 (B10: misaligns pass 2)
+            if stage1 is None:
+                stage1 = scene_io.torch_load(p1_path)
+                master = stage1_rows(stage1, device)
+            log("Processing class:", cls.replace(" ", "_"), "scene", scene_id)
+            per_scene[cls].append(pass1_scene(stage1, scene_io.torch_load(p2_path), cls, g("stage1_iou_thres"), sim_fn, device,
+                                              s1_rows=master.clone()))
+    for cls in classes:
+        ckpt_path = f"./checkpoints/refinement_checkpoint_{cls}.yaml"
+        ckpt = scene_io.read_checkpoint(ckpt_path)
+        sim_thres = similarity_threshold([p["sims"] for p in per_scene[cls]], g("refinment_sim_percentile"))
+        for s, fn in enumerate(files[cls]):
+            scene_id = fn.replace(".pth", "")
+            p1 = per_scene[cls][s]                                             # positional, like the reference
+            log("DEBUG all ious", p1["ious"])
+            out = pass2_scene(p1, cls, g("refiment_iou_thres"), sim_thres)
+            scene_io.save_result(out, g("final_output_dir"), cls, scene_id)
+            if len(p1["ious"]) != 0 and len(out["final_class"]) != 0:
+                ckpt[scene_id] = True
+                scene_io.write_checkpoint(ckpt_path, ckpt)
+
+
+def main_multi(argv=None):
+    """tools/refinement_multi.py: `--config C --cls q1 q2 ...` -- the outputs and checkpoints of one reference run per
+    class, from one process."""
+    import argparse
+    import yaml
+    parser = argparse.ArgumentParser(description="BeyondFF refinement for several classes at once")
+    parser.add_argument("--config", type=str, required=True)
+    parser.add_argument("--cls", type=str, nargs="+", required=True)
+    args = parser.parse_args(argv)
+    _log.VERBOSE = True
+    cfg = yaml.safe_load(open(args.config, "r").read())
+    if not torch.cuda.is_available():
+        raise RuntimeError("bff_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    device = torch.device("cuda", 0)
+    refine_classes(cfg, args.cls, device, ClipTextSimilarity(device))
+    return 0
 
 
 def main(argv=None):

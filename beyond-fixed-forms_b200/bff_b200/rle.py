@@ -80,3 +80,28 @@ def runs_for_device(rles: Sequence[dict], expect_length: int | None = None):
     if L >= 2 ** 31:
         raise ValueError("mask length must fit int32")
     return np.ascontiguousarray(runs.astype(np.int32)), int(L)
+
+
+def pairs_for_device(rles: Sequence[dict], expect_length: int | None = None):
+    """The wire format as `bff_rle_pairs_to_bits` takes it: (counts int64 (2P,), pair_offset int64 (R+1,), length). Only
+    array concatenation happens here -- the int32 casts and the slice clipping of the reference's decoder run in the
+    kernel -- so the host cost per scene is one np.concatenate instead of one numpy pipeline per mask."""
+    L = expect_length
+    parts, n_pairs = [], np.zeros(len(rles) + 1, np.int64)
+    for r, rle in enumerate(rles):
+        Lr = int(rle["length"])
+        if L is None:
+            L = Lr
+        if Lr != L:
+            raise ValueError(f"RLE row {r} has length {Lr}, expected {L}")
+        c = rle["counts"]
+        c = c.cpu().numpy() if isinstance(c, torch.Tensor) else np.asarray(c)
+        k = c.shape[0] // 2                      # zip() drops an unpaired trailing start
+        parts.append(c[:2 * k])
+        n_pairs[r + 1] = k
+    if L is None:
+        L = 0
+    if L >= 2 ** 31:
+        raise ValueError("mask length must fit int32")
+    counts = np.concatenate(parts).astype(np.int64, copy=False) if parts else np.zeros(0, np.int64)
+    return np.ascontiguousarray(counts), np.cumsum(n_pairs), int(L)

@@ -59,8 +59,8 @@ class SceneStep:
         mark = marks or (lambda: None)
         mark()
         # the stage-1 masks first: they depend on nothing, and the GPU decodes them while the host prepares the lifting launch
-        s1 = ops.rle_to_bits_dev(d["s1_runs"], self.n1, self.n)
-        masks2d = ops.rle_to_bits_dev(d["runs"], self.n_masks, self.h * self.w) if self.n_masks else None
+        s1 = ops.rle_pairs_to_bits_dev(d["s1_counts"], d["s1_pair_off"], self.n)
+        masks2d = ops.rle_pairs_to_bits_dev(d["counts"], d["pair_off"], self.h * self.w) if self.n_masks else None
         mark()
         out = ops.lift_scene(d["xyz"], d["pinv"], self.K, d["depth"], self.h, self.w, masks2d=masks2d,
                              mask_offset=d["offsets"] if self.n_masks else None, mask_query=d.get("mask_query") if self.n_masks else None,

@@ -11,8 +11,8 @@ from . import _log, aggregate, lift as lift_mod, scene_io, schedule
 from ._log import log
 
 
-QUERY_WORKERS = 1     # concurrent per-query aggregation chains of process_scene_queries (1 = sequential loop)
 FUSED = True     # bff_stage2_aggregate (C++ decisions next to the launches); False = one Python/torch call per step
+DEVICE = True    # bff_stage2_device (every decision a kernel, no host round trip inside the call); takes precedence over FUSED
 
 
 def cfg_get(cfg, key):
@@ -42,15 +42,22 @@ def _finish_fused(fused, n_points: int, c, keep_rows: bool, to_host: bool):
 
 
 def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor, vc: Optional[torch.Tensor],
-                         n_points: int, cfg, keep_rows: bool = False, to_host: bool = True, pairs=None):
+                         n_points: int, cfg, keep_rows: bool = False, to_host: bool = True, pairs=None, n_frames: Optional[int] = None):
     """Everything after the frame loop (projection_2d_to_3d.py:463-634) for one query.
     Returns (dict to save, reached_filter) -- the reference only writes its scene checkpoint when
-    the filter stage is reached (:580-581)."""
+    the filter stage is reached (:580-581). `n_frames` (the frames that were lifted: an upper bound of the viewed
+    counts) enables the device-resident path."""
     c = {k: cfg_get(cfg, k) for k in _CFG_KEYS}
     if len(conf_list) == 0:
         log("No 3d masks detected in backprojection!")
         return scene_io.empty_stage2(), False
     conf = conf_list if isinstance(conf_list, torch.Tensor) else torch.tensor(conf_list)    # :484-486
+    if DEVICE and n_frames is not None and pairs is None and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32 \
+            and rows.shape[0] <= 25000:
+        from . import devpipe, ops
+        s2 = devpipe.stage2_device(rows, ops.small_to_device(conf, rows.device), labels, mc, vc, n_points, c,
+                                   mc_cap=rows.shape[0], vc_cap=int(n_frames))
+        return s2.saved_dict(to_host=to_host, keep_rows=keep_rows)
     if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
         fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c, pairs=pairs)
         return _finish_fused(fused, n_points, c, keep_rows, to_host)
@@ -126,7 +133,7 @@ def process_scene(cfg, cls: str, scene_id: str, device, dist_ctx=None, loaded: O
     if sharded and lifted.rows[0].shape[0] >= dist_mod.PAIRS_MIN_ROWS:
         pairs = dist_mod.sharded_pairs(dist_ctx, lifted.rows[0])      # the quadratic IoU step, one row block per rank
     return aggregate_and_filter(lifted.rows[0], conf_list, labels, lifted.masked_counts[0], lifted.viewed_counts,
-                                xyz.shape[0], cfg, pairs=pairs)
+                                xyz.shape[0], cfg, pairs=pairs, n_frames=lifted.n_frames)
 
 
 def scene_loop(cfg, cls: str, scene_ids, device):
@@ -172,12 +179,11 @@ def process_scene_queries(cfg, classes, scene_id: str, device):
     def job(qi):
         conf_list, labels = queries[qi].flat_conf_and_labels()
         return (lifted.rows[qi], conf_list, labels, lifted.masked_counts[qi], lifted.viewed_counts, xyz.shape[0])
-    if QUERY_WORKERS > 1:
-        # the per-query chains are independent: several at once on their own streams (pool.py), same results
-        from .pool import get_pool
-        results = get_pool(device, QUERY_WORKERS).map(lambda qi: aggregate_and_filter(*job(qi), cfg), range(len(queries)))
+    if DEVICE:
+        # every query's chain is enqueue-only (bff_stage2_device); the results are read back once they are all queued
+        results = [aggregate_and_filter(*job(qi), cfg, n_frames=lifted.n_frames) for qi in range(len(queries))]
     else:
-        # default: all queries advance phase by phase inside one call and share its synchronisations
+        # all queries advance phase by phase inside one call and share its synchronisations
         results = aggregate_and_filter_batch([job(qi) for qi in range(len(queries))], cfg)
     for q, r in zip(queries, results):
         out[q.query] = r

@@ -342,9 +342,58 @@ rle_to_bits_kernel(const int32_t *__restrict__ runs, long long n_runs, long long
     }
 }
 
+// RLE -> bits straight from the wire format (rle_encode_decode.py:35-61, refinement.py:26-39): counts holds the masks'
+// (1-based start, run length) int64 pairs back to back, pair_offset[r] .. pair_offset[r + 1] are row r's pairs. One warp
+// per pair: the reference's arithmetic -- both numbers cast to int32, start made 0-based, end = int32(start + length),
+// then Python's slice rule `mask[lo:hi] = 1` (negative bounds count from the end, everything clipped to [0, L]) -- and
+// the touched words are OR-ed in. The row of a pair is found by bisection over pair_offset.
+__global__ void __launch_bounds__(256)
+rle_pairs_to_bits_kernel(const long long *__restrict__ counts, const long long *__restrict__ pair_offset, int n_rows, long long n_pairs,
+                         long long length, long long words, uint32_t *__restrict__ packed) {
+    const long long pair = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (pair >= n_pairs) return;
+    const int lane = threadIdx.x & 31;
+    int lo_r = 0, hi_r = n_rows;                     // largest r with pair_offset[r] <= pair
+    while (hi_r - lo_r > 1) {
+        const int mid = (lo_r + hi_r) >> 1;
+        if (__ldg(pair_offset + mid) <= pair) lo_r = mid; else hi_r = mid;
+    }
+    const long long start = (long long)(int)__ldg(counts + 2 * pair) - 1;
+    const long long num = (long long)(int)__ldg(counts + 2 * pair + 1);
+    const long long end = (long long)(int)(start + num);
+    long long lo = start < 0 ? max(start + length, 0LL) : min(start, length);
+    long long hi = end < 0 ? max(end + length, 0LL) : min(end, length);
+    if (hi <= lo) return;
+    const long long w_first = lo >> 5, w_last = (hi - 1) >> 5;
+    uint32_t *row = packed + (long long)lo_r * words;
+    for (long long w = w_first + lane; w <= w_last; w += 32) {
+        uint32_t m = 0xffffffffu;
+        if (w == w_first) m &= 0xffffffffu << (lo & 31);
+        if (w == w_last) m &= 0xffffffffu >> (31 - ((hi - 1) & 31));
+        atomicOr(row + w, m);
+    }
+}
+
 }  // namespace bff
 
 using namespace bff;
+
+extern "C" int bff_rle_pairs_to_bits(const int64_t *counts, const int64_t *pair_offset, int32_t n_rows, int64_t n_pairs, int64_t length,
+                                     uint32_t *packed, void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(n_rows >= 0 && n_pairs >= 0 && length >= 0, "bff_rle_pairs_to_bits: negative size");
+    const long long words = ceil_div64(length, 32);
+    if (n_rows == 0 || words == 0) return BFF_OK;
+    BFF_REQUIRE(packed, "bff_rle_pairs_to_bits: null output");
+    BFF_CUDA(cudaMemsetAsync(packed, 0, (size_t)n_rows * words * 4, stream));
+    if (n_pairs == 0) return BFF_OK;
+    BFF_REQUIRE(counts && pair_offset, "bff_rle_pairs_to_bits: null input");
+    BFF_REQUIRE(ceil_div64(n_pairs * 32, 256) <= 0x7fffffffLL, "bff_rle_pairs_to_bits: too many runs for one launch");
+    rle_pairs_to_bits_kernel<<<(unsigned)ceil_div64(n_pairs * 32, 256), 256, 0, stream>>>((const long long *)counts, (const long long *)pair_offset,
+                                                                                           n_rows, n_pairs, length, words, packed);
+    BFF_LAUNCH_CHECK("rle_pairs_to_bits_kernel");
+    return BFF_OK;
+}
 
 extern "C" int bff_set_iou_path(int32_t path) {
     BFF_REQUIRE(path >= 0 && path <= 3, "bff_set_iou_path: 0 automatic, 1 few-column, 2 POPC tiles, 3 tcgen05");

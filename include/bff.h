@@ -247,6 +247,13 @@ BFF_API int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n, u
 BFF_API int bff_rle_to_bits(const int32_t *runs, int64_t n_runs, int32_t n_rows, int64_t words,
                     uint32_t *packed, void *stream);
 
+/* The same decode straight from the wire format: `counts` holds the masks' (1-based start, run length) int64 pairs back to
+ * back (an unpaired trailing number of a mask dropped), pair_offset (n_rows + 1) the first pair of every row; both on the
+ * DEVICE. The int32 casts, the int32 end = start + length and Python's slice clipping of the reference's decoder
+ * (rle_encode_decode.py:53-57, refinement.py:33-37) happen in the kernel, so the host only concatenates arrays. */
+BFF_API int bff_rle_pairs_to_bits(const int64_t *counts, const int64_t *pair_offset, int32_t n_rows, int64_t n_pairs, int64_t length,
+                                  uint32_t *packed, void *stream);
+
 /* ---- host-buffer entry points (what a ctypes/numpy binding in the reference would call) ---- */
 typedef struct bff_ctx bff_ctx;
 BFF_API int bff_ctx_create(int device, bff_ctx **out);

@@ -18,7 +18,7 @@ rpr = [x[0] for x in gathered]
 conf = torch.tensor([c for x in gathered for c in x[1]], dtype=torch.float32)
 labels = [l for x in gathered for l in x[2]]
 d = g.upload()
-out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+out = g.lift(d, g.masks2d(d))
 def T(fn, n=3):
     fn(); torch.cuda.synchronize(); dist.barrier(); t0 = time.perf_counter()
     for _ in range(n): r = fn()

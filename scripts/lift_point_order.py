@@ -12,7 +12,7 @@ dev = torch.device("cuda:0")
 inp = bench.build_inputs(sys.argv[1] if len(sys.argv) > 1 else "c2", 0, 1, dev)
 g = bench.GpuScene(inp, dev)
 d = g.upload()
-masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+masks2d = g.masks2d(d)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 xyz = d["xyz"]
 

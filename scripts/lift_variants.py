@@ -26,7 +26,7 @@ def main():
     for lib in libs:
         _cabi._lib = None
         _cabi.LIB_PATH = lib or os.path.join(ROOT, "beyond-fixed-forms_b200", "bff_b200", "libbff.so")
-        masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+        masks2d = g.masks2d(d)
         for fpc in (16, 20, 25, 30, 38, 50):
             ts = []
             for it in range(13):

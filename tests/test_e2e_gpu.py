@@ -103,3 +103,31 @@ def test_two_rank_cli_matches_reference(cuda_dev, tmp_path, mode):
     import yaml
     ck = yaml.safe_load(open(os.path.join(tree, "checkpoints", f"projection_2d_to_3d_checkpoint_{cls}.yaml")))
     assert ck and all(v is True for v in ck.values())
+
+
+@pytest.mark.parametrize("cfg_name,out2,outf", [("config.yaml", "output/mask_3d", "output/final_output"),
+                                                 ("config_occ.yaml", "output_occ/mask_3d", "output_occ/final_output")])
+def test_multi_class_driver_equals_one_reference_run_per_class(cuda_dev, tmp_path, monkeypatch, cfg_name, out2, outf):
+    """tools/run_evl_b200.py (bff_b200/run_classes.py): lifting + refinement for all classes of the tree in one process --
+    shared projection per scene, stage-1 masks decoded once per scene, one similarity cache -- must write the files the
+    unmodified reference wrote with one process per class and stage, and the orchestrator's checkpoint."""
+    import yaml
+    from bff_b200 import run_classes
+    tree = copy_tree(tmp_path)
+    monkeypatch.chdir(tree)
+    _install_fake_clip()
+    expected = load_expected()
+    classes = ["office chair", "table"]
+    ck = run_classes.run(cfg_name, classes, batch=2)
+    assert all(ck[c] == {"projection_2d_to_3d": True, "refinement": True} for c in classes)
+    assert yaml.safe_load(open("process_checkpoint.txt")) == ck
+    for cls in classes:
+        for sid in ("scene0001_00", "scene0002_00", "scene0003_00"):
+            got2 = torch.load(os.path.join(tree, out2, cls, f"{sid}.pth"), weights_only=False)
+            gotf = torch.load(os.path.join(tree, outf, cls, f"{sid}.pth"), weights_only=False)
+            check_against_expected(got2, expected[(cfg_name, cls, "mask_3d", sid)], f"driver stage2 {cls} {sid}")
+            check_against_expected(gotf, expected[(cfg_name, cls, "final", sid)], f"driver final {cls} {sid}")
+    # a second run finds everything done and touches nothing
+    before = {p: os.path.getmtime(p) for p in (os.path.join(tree, outf, classes[0], "scene0001_00.pth"),)}
+    run_classes.run(cfg_name, classes, batch=2)
+    assert all(os.path.getmtime(p) == t for p, t in before.items())

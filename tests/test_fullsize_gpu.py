@@ -23,7 +23,7 @@ def c2(cuda_dev):
     inp = bench.build_inputs("c2", 0, 1, cuda_dev)
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+    masks2d = g.masks2d(d)
     return inp, g, d, masks2d
 
 
@@ -90,7 +90,7 @@ def c3(cuda_dev):
     inp = bench.build_inputs("c3", 0, 1, cuda_dev)
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+    masks2d = g.masks2d(d)
     return inp, g, d, masks2d
 
 
@@ -172,7 +172,7 @@ def c4(cuda_dev):
         bench.WORKLOADS["c4"] = saved
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+    masks2d = g.masks2d(d)
     return inp, g, d, masks2d
 
 

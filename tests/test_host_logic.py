@@ -1,5 +1,6 @@
 """CPU: host-side decision logic of the product (no GPU): component search fast path == general BFS,
 sequential float32 means, label equality, frame planning, RLE run clipping (Python-slice semantics)."""
+import pytest
 import numpy as np
 import torch
 
@@ -129,3 +130,34 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["steps"] == 1 and d["warmup"] == 0 and d["scaling"] == "weak" and d["vs_baseline"] is None
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+
+def test_class_batches_and_orchestrator_checkpoint(tmp_path, monkeypatch):
+    """bff_b200/run_classes.py: classes go through both stages in batches, finished stages (process_checkpoint.txt, the
+    reference orchestrator's file, evaluation/eval/run_evl.py:28-54) are skipped on a re-run."""
+    import yaml
+    from bff_b200 import run_classes
+    monkeypatch.chdir(tmp_path)
+    calls = []
+    s2 = lambda a: calls.append(("lift", a[3:])) or 0
+    rf = lambda a: calls.append(("refine", a[3:])) or 0
+    ck = run_classes.run("c.yaml", ["a", "b", "c"], batch=2, stage2_main=s2, refine_main=rf)
+    assert calls == [("lift", ["a", "b"]), ("refine", ["a", "b"]), ("lift", ["c"]), ("refine", ["c"])]
+    assert yaml.safe_load(open("process_checkpoint.txt")) == ck == {c: {"projection_2d_to_3d": True, "refinement": True} for c in "abc"}
+    calls.clear()
+    ck2 = yaml.safe_load(open("process_checkpoint.txt"))
+    ck2["b"]["refinement"] = False
+    yaml.safe_dump(ck2, open("process_checkpoint.txt", "w"))
+    run_classes.run("c.yaml", ["a", "b", "c", "d"], batch=3, stage2_main=s2, refine_main=rf)
+    assert calls == [("refine", ["b"]), ("lift", ["d"]), ("refine", ["d"])]
+
+
+def test_rle_pairs_for_device_keeps_the_wire_format():
+    from bff_b200 import rle
+    a = {"length": 50, "counts": np.array([3, 4, 10, 2, 7], np.int64)}           # unpaired trailing start
+    b = {"length": 50, "counts": np.zeros(0, np.int64)}
+    c = {"length": 50, "counts": torch.tensor([1, 50])}
+    counts, off, length = rle.pairs_for_device([a, b, c])
+    assert length == 50 and counts.dtype == np.int64 and counts.tolist() == [3, 4, 10, 2, 1, 50] and off.tolist() == [0, 2, 2, 3]
+    with pytest.raises(ValueError):
+        rle.pairs_for_device([a, {"length": 51, "counts": np.zeros(0, np.int64)}])

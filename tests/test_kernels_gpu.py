@@ -164,6 +164,34 @@ def test_pack_unpack_roundtrip_and_rle(cuda_dev):
     np.testing.assert_array_equal(unpack_rows(bits.cpu().numpy(), 100)[0], O.rle_decode(rle).astype(bool))
 
 
+def test_rle_wire_format_decoded_on_the_device(cuda_dev):
+    """bff_rle_pairs_to_bits: the (1-based start, length) int64 pairs go to the device as they are in the files; the int32
+    casts, the int32 end and Python's slice clipping of the reference decoder (rle_encode_decode.py:53-57) run in the
+    kernel. Compared with the C oracle's decoder and with the host-prepared runs on random and hostile encodings."""
+    import oracle as O
+    from bff_b200 import ops
+    from bff_b200.rle import pairs_for_device, rle_encode_rows, runs_for_device
+    rng = np.random.default_rng(12)
+    for n in (1, 33, 1000, 70001):
+        d = rng.random((7, n)) < rng.uniform(0.05, 0.6, (7, 1))
+        d[3] = False
+        rles = rle_encode_rows(torch.from_numpy(d))
+        counts, off, length = pairs_for_device(rles)
+        bits = ops.rle_pairs_to_bits_dev(torch.from_numpy(counts).to(cuda_dev), torch.from_numpy(off).to(cuda_dev), length)
+        np.testing.assert_array_equal(bits.cpu().numpy().view(np.uint32), pack_rows(d))
+    hostile = [{"length": 100, "counts": np.array([5, 10, 8, 30, 95, 50, 0, 3, 60], np.int64)},          # overlaps, past the end, start 0, unpaired tail
+               {"length": 100, "counts": np.array([-20, 5, 2 ** 32 + 7, 4, 50, -3, 99, 2 ** 31], np.int64)},  # negative starts, int32 wrap, negative / huge lengths
+               {"length": 100, "counts": np.zeros(0, np.int64)},
+               {"length": 100, "counts": np.array([1, 100], np.int64)}]
+    counts, off, length = pairs_for_device(hostile)
+    bits = ops.rle_pairs_to_bits_dev(torch.from_numpy(counts).to(cuda_dev), torch.from_numpy(off).to(cuda_dev), length)
+    runs, _ = runs_for_device(hostile)
+    want = ops.rle_to_bits(runs, len(hostile), length, cuda_dev)
+    assert torch.equal(bits, want)
+    for i in (0, 2, 3):
+        np.testing.assert_array_equal(unpack_rows(bits.cpu().numpy(), 100)[i], O.rle_decode(hostile[i]).astype(bool))
+
+
 def test_rows_ops(cuda_dev):
     from bff_b200 import ops
     rng = np.random.default_rng(4)

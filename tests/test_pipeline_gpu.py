@@ -18,12 +18,12 @@ def _run(inp, g, d, fused, cfg):
     import bench
     stage2.FUSED = refine.FUSED = fused
     try:
-        masks2d = ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w)
+        masks2d = g.masks2d(d)
         out = ops.lift_scene(d["xyz"], d["pinv"], inp["K"], d["depth"], g.h, g.w, masks2d=masks2d, mask_offset=d["offsets"],
                              frame_viewed=d["viewed"], depth_range=(0.0, 65.535))
         res2, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, cfg,
                                               keep_rows=fused)
-        s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), g.n)
+        s1 = g.stage1_rows(d)
         p1 = refine.pass1_scene(inp["stage1"], res2, bench.QUERY, cfg["stage1_iou_thres"], bench.fake_similarity, g.dev, s1_rows=s1)
         thr = refine.similarity_threshold([p1["sims"]], cfg["refinment_sim_percentile"]) if len(p1["sims"]) else 0.0
         return res2, p1, refine.pass2_scene(p1, bench.QUERY, cfg["refiment_iou_thres"], thr)
@@ -67,25 +67,30 @@ def test_fused_pipeline_equals_stepwise_and_port(cuda_dev, occurrence, seed):
 
 def test_concurrent_queries_equal_sequential_loop_and_port(cuda_dev, monkeypatch):
     """Three text queries of one scene, depth PNGs at half the mask size (resampled in the lift kernel): the per-query
-    chains run on concurrent streams (bff_b200/pool.py) must give what the sequential loop gives, and both what the
-    dense CPU port of the reference computes with one full run per query (cv2.resize on every frame)."""
+    chains on concurrent stream lanes with the decisions on the device (scene_step.py) must give what the host-decision
+    batch gives, and both what the dense CPU port of the reference computes with one full run per query (cv2.resize on
+    every frame)."""
     sys.path.insert(0, ROOT)
     import bench
     inp = bench.build_inputs("tiny3", 0, 1, cuda_dev)
     g = bench.GpuScene(inp, cuda_dev)
     assert g.nq == 3 and g.native == (120, 160) and (g.h, g.w) == (240, 320)
     d = g.upload()
-    g.workers = 4
+    g.device_decisions = True
     g.step(d)
     pooled = list(g.last_finals)
-    g.workers = 1
+    g.graph_inputs(d)                         # and replayed as one CUDA graph
+    g.step(d)
+    graphed = list(g.last_finals)
+    g.device_decisions = False
     g.step(d)
     serial = list(g.last_finals)
     mask_frames, view_frames = bench.cpu_frames_of(inp, inp["depth"].shape[0])
     port = bench.cpu_step(inp, mask_frames, view_frames)
     assert sum(isinstance(f["ins"], torch.Tensor) and f["ins"].shape[0] >= 2 for f in serial) >= 2
     for qi in range(g.nq):
-        _same(pooled[qi], serial[qi], f"pooled vs serial, query {qi}")
+        _same(pooled[qi], serial[qi], f"lanes vs host batch, query {qi}")
+        _same(graphed[qi], serial[qi], f"CUDA graph vs host batch, query {qi}")
         assert list(serial[qi]["final_class"]) == list(port[qi]["final_class"])
         if isinstance(serial[qi]["ins"], torch.Tensor):
             assert torch.equal(serial[qi]["ins"].cpu(), port[qi]["ins"])
@@ -100,7 +105,7 @@ def test_precomputed_pairs_give_the_same_aggregation(cuda_dev):
     inp = bench.build_inputs("tiny", 0, 1, cuda_dev)
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+    out = g.lift(d, g.masks2d(d))
     a, _ = stage2.aggregate_and_filter(out.rows, g.conf_list, g.labels, out.masked_counts[0], out.viewed_counts, g.n, inp["cfg"])
     top, bottom = out.rows[:11], out.rows[11:]                                # two "rank" blocks of the all-pairs matrix
     i0, p0, _, _ = ops.mask_iou(top, out.rows, want_iou=False)
@@ -120,7 +125,7 @@ def test_batched_aggregation_equals_one_call_per_query(cuda_dev):
     inp = bench.build_inputs("tiny3", 0, 1, cuda_dev)
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
-    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
+    out = g.lift(d, g.masks2d(d))
     cfg = inp["cfg"]
     jobs = []
     for qi in range(g.nq):
@@ -148,8 +153,8 @@ def test_batched_refinement_pass1_equals_one_call_per_query(cuda_dev):
     g = bench.GpuScene(inp, cuda_dev)
     d = g.upload()
     cfg = inp["cfg"]
-    out = g.lift(d, ops.rle_to_bits_dev(d["runs"], g.n_masks, g.h * g.w))
-    s1 = ops.rle_to_bits_dev(d["s1_runs"], len(inp["stage1"]["ins"]), g.n)
+    out = g.lift(d, g.masks2d(d))
+    s1 = g.stage1_rows(d)
     res2 = []
     for qi in range(g.nq):
         idx = g.row_index_dev[qi] if g.row_index_dev is not None else None
