@@ -689,18 +689,41 @@ def run_gpu(args):
                   f"  stages {[round(tm_[j].elapsed_time(tm_[j + 1]), 3) for j in range(len(tm_) - 1)]} lift {g.lift_events[0].elapsed_time(g.lift_events[1]):.3f}",
                   file=sys.stderr)
     d2h = sum(fn["ins"].numel() * fn["ins"].element_size() for fn in g.last_finals if isinstance(fn["ins"], torch.Tensor))
-    # ---- IoU kernel alone (mask-IoU pairs/s of the aggregation-sized square call)
+    # ---- IoU kernels alone: the aggregation-sized square call (tcgen05 int8) and a refinement-shaped call (200 x 27 rows, POPC)
     from bff_b200 import ops
     rows = g.lift(d, g.masks2d(d)).rows
-    for _ in range(3):
-        ops.mask_iou(rows)
-    torch.cuda.synchronize()
-    e0 = _event()
-    for _ in range(10):
-        ops.mask_iou(rows)
-    e1 = _event()
-    torch.cuda.synchronize()
-    iou_ms = e0.elapsed_time(e1) / 10
+
+    def _time_call(fn, reps=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0 = _event()
+        for _ in range(reps):
+            fn()
+        e1 = _event()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    iou_ms = _time_call(lambda: ops.mask_iou(rows, want_iou=False))
+    s1_rows = g.stage1_rows(d)
+    few = rows[:27].contiguous()
+    iou_small_ms = _time_call(lambda: ops.mask_iou(s1_rows, few, want_iou=False))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    int8_peak = 2.0 * float(peaks.get("bf16_tflops", 1672.3))             # TOP/s: int8 runs at twice the measured bf16 rate
+    popc_peak = 148 * 16 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6    # word-ops/s: 16 POPC lanes per SM and clock
+    n_r = rows.shape[0]
+    iou_roofline = {
+        "square": {"call": f"{n_r}x{n_r} rows x {g.n} points (tcgen05 kind::i8, popcounts fused)", "ms": iou_ms, "bound": "tensor",
+                   "achieved": 2.0 * n_r * n_r * g.n / (iou_ms * 1e-3) / 1e12, "peak": int8_peak, "unit": "TOP/s (int8, full square counted)",
+                   "frac": 2.0 * n_r * n_r * g.n / (iou_ms * 1e-3) / 1e12 / int8_peak,
+                   "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (burst)"},
+        "few_columns": {"call": f"{s1_rows.shape[0]}x{few.shape[0]} rows x {g.n} points (POPC, one pass)", "ms": iou_small_ms, "bound": "popc",
+                        "achieved": s1_rows.shape[0] * few.shape[0] * rows.shape[1] / (iou_small_ms * 1e-3) / 1e12, "peak": popc_peak / 1e12,
+                        "unit": "T word-ops/s (AND+POPC)", "frac": s1_rows.shape[0] * few.shape[0] * rows.shape[1] / (iou_small_ms * 1e-3) / popc_peak,
+                        "peak_source": "148 SMs x 16 POPC lanes/clk x sm_max_mhz"}}
     fs = None
     if world > 1 and not args.no_frame_sharded:
         fs = frame_sharded_run(args, ctx, dev, flush, barrier)
@@ -735,6 +758,7 @@ def run_gpu(args):
                               (stage_acc / k).round(4).tolist())),
         "lift_point_views_per_s": pv / (ms_lift * 1e-3),
         "iou_pairs_per_s": (rows.shape[0] ** 2) / (iou_ms * 1e-3), "iou_call": f"{rows.shape[0]}x{rows.shape[0]} rows x {g.n} points, {iou_ms:.4f} ms",
+        "iou_roofline": iou_roofline,
         "e2e": {"value": pv / (ms_e2e_pipe * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": int(g.h2d_bytes),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e_pipe,
                 "how": "K consecutive scenes through the host API: pinned host inputs -> device -> step -> final masks on the "

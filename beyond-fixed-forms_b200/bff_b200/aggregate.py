@@ -87,11 +87,13 @@ def aggregate_rows(rows: torch.Tensor, conf: torch.Tensor, labels: Sequence[str]
     if not used:
         return None, None, [], []
     agg = ops.rows_or_reduce(rows, used)                        # K10
-    # conf = sum(conf_k) / len, the sum taken sequentially in float32 in index order (:220-224)
-    c32 = conf.to(torch.float32).numpy()
-    confs = np.empty(len(used), np.float32)
+    # conf = sum(conf_k) / len, the sum taken sequentially in index order IN THE CONFIDENCES' OWN DTYPE (:220-224: Python's
+    # sum() over 0-d tensors, then torch.tensor(list) keeps the dtype: float64 confidences give float64 means)
+    c = conf.numpy()
+    dt = c.dtype if c.dtype in (np.dtype(np.float32), np.dtype(np.float64)) else np.dtype(np.float32)
+    confs = np.empty(len(used), dt)
     for i, g in enumerate(used):
-        confs[i] = np.cumsum(c32[g], dtype=np.float32)[-1] / np.float32(len(g))
+        confs[i] = np.cumsum(c[g].astype(dt, copy=False), dtype=dt)[-1] / dt.type(len(g))
     return agg, torch.from_numpy(confs), [labels[g[0]] for g in used], groups
 
 

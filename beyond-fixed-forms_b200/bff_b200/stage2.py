@@ -58,7 +58,7 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
         s2 = devpipe.stage2_device(rows, ops.small_to_device(conf, rows.device), labels, mc, vc, n_points, c,
                                    mc_cap=rows.shape[0], vc_cap=int(n_frames))
         return s2.saved_dict(to_host=to_host, keep_rows=keep_rows)
-    if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32:
+    if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32 and rows.shape[0] <= 46340:
         fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c, pairs=pairs)
         return _finish_fused(fused, n_points, c, keep_rows, to_host)
     agg, conf_agg, labels_agg, groups = aggregate.aggregate_rows(rows, conf, labels, c["iou_thres"], c["min_aggragated_masks"])

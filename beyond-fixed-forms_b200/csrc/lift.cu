@@ -754,13 +754,18 @@ visibility_kernel(const long long *__restrict__ pix, const double *__restrict__ 
 
 __global__ void __launch_bounds__(256)
 mask_gather_kernel(const long long *__restrict__ pix, const uint32_t *__restrict__ vis, long long n, const uint32_t *__restrict__ masks2d,
-                   long long mask_words, int width, long long words, uint32_t *__restrict__ rows) {
+                   long long mask_words, int height, int width, long long words, uint32_t *__restrict__ rows) {
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
     const int m = blockIdx.y;
     bool bit = false;
     if (i < n && ((vis[i >> 5] >> (i & 31)) & 1u)) {
-        const long long p = pix[2 * i + 1] * width + pix[2 * i];
-        bit = (__ldg(masks2d + (long long)m * mask_words + (p >> 5)) >> (p & 31)) & 1u;
+        // the caller's visibility flags are trusted for WHICH points to sample, not for the pixel being inside the image:
+        // a flagged point with an out-of-range pixel reads nothing (the reference would raise or wrap there)
+        const long long px = pix[2 * i], py = pix[2 * i + 1];
+        if (px >= 0 && px < width && py >= 0 && py < height) {
+            const long long p = py * width + px;
+            bit = (__ldg(masks2d + (long long)m * mask_words + (p >> 5)) >> (p & 31)) & 1u;
+        }
     }
     const unsigned w = __ballot_sync(0xffffffffu, bit);
     if ((threadIdx.x & 31) == 0 && i < n) rows[(long long)m * words + (i >> 5)] = w;
@@ -785,7 +790,7 @@ extern "C" int bff_mask_gather(const int64_t *pix, const uint32_t *vis, int64_t 
     BFF_REQUIRE(n_masks <= 65535, "bff_mask_gather: too many masks");
     dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_masks);
     mask_gather_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>((const long long *)pix, vis, n, masks2d,
-                                                                ceil_div64((long long)height * width, 32), width, ceil_div64(n, 32), rows);
+                                                                ceil_div64((long long)height * width, 32), height, width, ceil_div64(n, 32), rows);
     BFF_LAUNCH_CHECK("mask_gather_kernel");
     return BFF_OK;
 }

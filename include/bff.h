@@ -19,6 +19,16 @@
  *    point row has Wd = ceil(N/32) words, a packed H x W image mask has ceil(H*W/32) words
  *    with element index y*W + x (the reference's flattening, rle_encode_decode.py:63-99);
  *  - bits beyond N in the last word of a row are always written as 0 and must be 0 on input.
+ *
+ * Size limits (checked, BFF_EINVAL beyond them; the host package routes larger jobs to its step-by-step path):
+ *  - row counts that become a grid dimension are limited to 65 535: n_groups of bff_rows_or_reduce, n_rows of
+ *    bff_rows_and_popcount / bff_pack_bits / bff_unpack_bits / bff_rows_slice / bff_rows_unslice, n_idx of
+ *    bff_rows_gather (bff_rows_gather_dev has no limit), n_masks of bff_mask_gather, 16 x 65 535 rows in bff_rows_permute;
+ *  - bff_stage2_aggregate: n_rows <= 46 340 (n_rows^2 int32 intersections); bff_refine_match: n2 <= 65 535;
+ *  - bff_stage2_device: n_rows <= 25 000 (8 bytes of shared memory per row in the component search);
+ *    bff_refine_device: cap2 <= 40 960;
+ *  - point counts < 2^31 x 32, image sizes H x W < 2^31, counts (votes, intersections) < 2^31; IoUs are exact while
+ *    counts stay below 2^24 (float32), as in the reference.
  */
 #ifndef BFF_H_
 #define BFF_H_

@@ -248,3 +248,26 @@ def test_unpack_dc_guard_bands(cuda_dev):
         assert (got[:guard] == 0xAB).all() and (got[guard + cap * n:] == 0xAB).all()
         assert np.array_equal(got[guard:guard + k * n].reshape(k, n).astype(bool), rows[:k])
         assert (got[guard + k * n:guard + cap * n] == 0xAB).all()
+
+
+def test_workspace_arenas_survive_growing_jobs(cuda_dev):
+    """A sweep of scenes with growing mask counts (the n^2 intersection scratch grows with every new record size) through
+    both pipelines: the arenas merge their blocks between calls instead of running into their block limit."""
+    from bff_b200 import devpipe, stage2
+    rng = np.random.default_rng(5)
+    n = 4099
+    for k, n_rows in enumerate([5, 40, 90, 150, 260, 410, 640, 900, 1300, 1700] * 4):
+        rows = _object_rows(rng, n_rows, n, 12, empty=1, dup=1)
+        labels = ["chair"] * n_rows
+        conf = torch.from_numpy(rng.uniform(0.2, 0.45, n_rows).astype(np.float32))
+        mc = torch.from_numpy(rows.sum(0).astype(np.int32)).to(cuda_dev)
+        vc = (mc + 3).contiguous()
+        d_rows = torch.from_numpy(pack_rows(rows).view(np.int32)).to(cuda_dev)
+        stage2.DEVICE = False
+        try:
+            want, _ = stage2.aggregate_and_filter(d_rows, conf, labels, mc, vc, n, CFG)
+        finally:
+            stage2.DEVICE = True
+        if k % 7 == 0:
+            got, _ = devpipe.stage2_device(d_rows, conf.to(cuda_dev), labels, mc, vc, n, CFG, mc_cap=n_rows, vc_cap=n_rows + 3).saved_dict()
+            _same(got, want, f"{n_rows} rows")

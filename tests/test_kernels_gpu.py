@@ -613,3 +613,48 @@ def test_small_to_device_ring_wraps_without_losing_data(cuda_dev):
     torch.cuda.synchronize()
     for o, w in zip(outs, wants):
         assert o.device.type == "cuda" and torch.equal(o.cpu(), w)
+
+
+def test_outputs_stay_inside_their_buffers(cuda_dev):
+    """Guard bands (compute-sanitizer is not available on this pool): poisoned bytes before and after the outputs of the
+    kernels with ragged tails -- bff_unpack_bits (16-byte stores over the flattened matrix), bff_upload (tail bytes),
+    bff_rows_permute, bff_rows_slice / bff_rows_unslice -- must survive, for sizes around every alignment boundary."""
+    from bff_b200 import _cabi, ops
+    rng = np.random.default_rng(77)
+    G = 128
+
+    def guarded(nbytes, dtype):
+        buf = torch.full((G + nbytes + G,), 0xCD, dtype=torch.uint8, device=cuda_dev)
+        return buf, buf[G:G + nbytes].view(dtype)
+
+    def intact(buf, nbytes):
+        b = buf.cpu().numpy()
+        return bool((b[:G] == 0xCD).all() and (b[G + nbytes:] == 0xCD).all())
+    for r, n in [(1, 1), (3, 15), (2, 16), (5, 17), (4, 31), (3, 33), (7, 250007 % 997 + 16), (2, 4099)]:
+        dense = rng.random((r, n)) < 0.5
+        packed = torch.from_numpy(pack_rows(dense).view(np.int32)).to(cuda_dev)
+        buf, out = guarded(r * n, torch.uint8)
+        _cabi.check(_cabi.lib().bff_unpack_bits(_cabi.ptr(packed), r, n, _cabi.ptr(out), _cabi.current_stream()), "bff_unpack_bits")
+        assert intact(buf, r * n) and np.array_equal(out.cpu().numpy().reshape(r, n).astype(bool), dense), (r, n)
+        # permute back and forth
+        perm = torch.from_numpy(rng.permutation(n).astype(np.int32)).to(cuda_dev)
+        wd = (n + 31) // 32
+        buf, outp = guarded(r * wd * 4, torch.int32)
+        _cabi.check(_cabi.lib().bff_rows_permute(_cabi.ptr(packed), r, n, _cabi.ptr(perm), _cabi.ptr(outp), _cabi.current_stream()), "bff_rows_permute")
+        assert intact(buf, r * wd * 4)
+        np.testing.assert_array_equal(unpack_rows(outp.cpu().numpy().reshape(r, wd), n), dense[:, perm.cpu().numpy()])
+        # column slices and back
+        world = 3
+        sw = max(1, -(-wd // world))
+        buf, outs = guarded(world * r * sw * 4, torch.int32)
+        sl = outs.view(world, r, sw)
+        for p_ in range(world):
+            _cabi.check(_cabi.lib().bff_rows_slice(_cabi.ptr(packed), r, wd, p_ * sw, sw, _cabi.ptr(sl[p_]), _cabi.current_stream()), "bff_rows_slice")
+        assert intact(buf, world * r * sw * 4)
+        assert torch.equal(ops.rows_unslice(sl.contiguous(), wd), packed)
+    for nbytes in (1, 15, 16, 17, 31, 4096, 4097, 65551):
+        src = torch.from_numpy(rng.integers(0, 256, nbytes + 16, dtype=np.uint8)).pin_memory()
+        buf, out = guarded(nbytes, torch.uint8)
+        _cabi.check(_cabi.lib().bff_upload(_cabi.ptr(out), _cabi.ptr(src), nbytes, _cabi.current_stream()), "bff_upload")
+        torch.cuda.synchronize()
+        assert intact(buf, nbytes) and torch.equal(out.cpu(), src[:nbytes]), nbytes

@@ -163,8 +163,20 @@ def test_batched_refinement_pass1_equals_one_call_per_query(cuda_dev):
         res2.append(r)
     res2.append(scene_io.empty_stage2())
     names = list(g.names) + [g.names[0]]
-    single = [refine.pass1_scene(inp["stage1"], r, nm, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev, s1_rows=s1.clone())
-              for r, nm in zip(res2, names)]
+    # the device-decision pass 1 (what pass1_scene takes by default) ...
+    on_device = [refine.pass1_scene(inp["stage1"], r, nm, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev, s1_rows=s1.clone())
+                 for r, nm in zip(res2, names)]
+    # ... and the host-decision one, single and batched
+    refine.DEVICE = False
+    try:
+        single = [refine.pass1_scene(inp["stage1"], r, nm, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev, s1_rows=s1.clone())
+                  for r, nm in zip(res2, names)]
+    finally:
+        refine.DEVICE = True
+    for k, (a, b) in enumerate(zip(on_device, single)):
+        assert a["sims"] == b["sims"] and torch.equal(torch.as_tensor(a["ious"]), torch.as_tensor(b["ious"])), k
+        _same(refine.pass2_scene(a, names[k], cfg["refiment_iou_thres"], 0.0), refine.pass2_scene(b, names[k], cfg["refiment_iou_thres"], 0.0),
+              f"device pass 1 + 2 vs host pass 1 + 2, query {k}")
     batch = refine.pass1_scene_batch(inp["stage1"], res2, names, cfg["stage1_iou_thres"], bench.fake_similarity, cuda_dev,
                                      [s1.clone() for _ in names])
     assert sum(len(p["sims"]) > 0 for p in single) >= 2
