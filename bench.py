@@ -611,10 +611,11 @@ def run_gpu(args):
     from bff_b200 import ops
     copy_stream = torch.cuda.Stream(device=dev, priority=-1 if args.upload.endswith('+hi') else 0)
     bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]   # double buffer, no allocation in the loop
-    # (No CUDA graph in this loop. Measured: a graph launch issued while the next scene's 184 MB move on the H2D copy engine
-    # waits for that transfer -- the launch itself ships its command buffers over the same engine -- and the loop went from
-    # 3.5 to 4.1 ms per scene at c2, from 7.9 to 42 ms at c4. Kernel-by-kernel launches do not touch the engine; the loop is
-    # upload-bound either way.)
+    # CUDA graphs and the copy engine do not mix here. Measured: a graph launch issued while the next scene's 184 MB move on
+    # the H2D copy engine waits for that transfer -- the launch itself ships its command buffers over the same engine -- and
+    # the loop went from 3.5 to 4.1 ms per scene at c2, from 7.9 to 42 ms at c4. So: with uploads on the copy engine (the
+    # default for one query, where the loop is upload-bound anyway) the step is launched kernel by kernel; with uploads by
+    # the SM copy kernel (--upload sm) the step replays its graph -- which measured slower still (c3: 13.9 vs 8.65 ms).
     done = [None, None]
     # The next scene's buffers move on the H2D copy engine (55 GB/s here, against 46-51 GB/s for an SM copy kernel that
     # shares SMs and the PCIe request queue with the running step). That only works because the running step never
@@ -630,8 +631,18 @@ def run_gpu(args):
         return a.elapsed_time(b) / 2
     t_ce = _time_copy(lambda: bufs[0][big].copy_(g.host[big], non_blocking=True))
     t_sm = _time_copy(lambda: ops.upload(bufs[0][big], g.host[big])) if g.host[big].numel() * g.host[big].element_size() >= 16 else float("inf")
-    mode = args.upload.replace("+hi", "")   # "sm" | "ce" | "ce:<MiB>" (copy engine in chunks, so that other streams' small copies interleave)
+    mode = args.upload.replace("+hi", "")   # "auto" | "sm" | "ce" | "ce:<MiB>" (copy engine in chunks, so that other streams' small copies interleave)
+    if mode == "auto":
+        # measured at c3 (20 queries): SM-kernel uploads + graph replay 13.9 ms per scene, copy-engine uploads + kernel-by-kernel
+        # launches 8.65 ms -- the copy kernel shares SMs and the PCIe request queue with the step (r01 finding), so: the engine
+        mode = "ce"
     use_sm_copy = mode == "sm"
+    if use_sm_copy:
+        for b_ in bufs:                               # one CUDA graph per buffer set (contents change, addresses do not)
+            for k_, v_ in g.host.items():
+                b_[k_].copy_(v_, non_blocking=True)
+            g.graph_inputs(b_)
+        torch.cuda.synchronize()
     chunk = int(float(mode.split(":")[1]) * (1 << 20)) if mode.startswith("ce:") else 0
 
     def upload_async(slot):
@@ -1177,7 +1188,7 @@ def main():
     ap.add_argument("--sharded-only", action="store_true", help="N>1: only the sharded scene (with its single-GPU cross-check), no replicas")
     ap.add_argument("--pyprofile", action="store_true", help="cProfile K steps of the host path (stderr) and exit")
     ap.add_argument("--cli-e2e", action="store_true", help="files-to-files run of both drop-in CLIs on an on-disk tree (configs[0]) and exit")
-    ap.add_argument("--upload", default="ce", help="pipelined e2e: how scene i+1's buffers move while scene i runs: ce (copy engine) | sm (bff_upload kernel) | ce:<MiB>")
+    ap.add_argument("--upload", default="auto", help="pipelined e2e: how scene i+1's buffers move while scene i runs: ce (copy engine) | sm (bff_upload kernel) | ce:<MiB>")
     ap.add_argument("--profile", action="store_true", help="run K steps between cudaProfilerStart/Stop and exit (for ncu)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -45,7 +45,12 @@ constexpr int kMaxFramesPerChunk = 256;   // <= kLiftThreads: one thread prepare
 //   0..5   camera-z as a function of the world point: n(3), d, |n|(1+eps), eps|d|
 //   6..25  four image-border planes (left, right, top, bottom), each n(3), d(+slack), |n|(1+eps)
 constexpr int kPlaneDoubles = 26;
-constexpr int kFrameSmemBytes = 128 + kPlaneDoubles * 8 + 8 + 16;   // + depth offset (int64) + frame record (int4)
+// A frame's inverse pose occupies kPoseStride doubles in shared memory, not 16: with 128-byte rows the lanes that build
+// the culling tables (lane = frame) all hit the same banks (ncu r02: 8.4 M of the kernel's 25.5 M shared-memory wavefronts
+// were conflict replays of those loads); 144-byte rows spread 32 consecutive frames over 8 bank groups and keep the rows
+// 16-byte aligned for the main loop's LDS.128.
+constexpr int kPoseStride = 18;
+constexpr int kFrameSmemBytes = kPoseStride * 8 + kPlaneDoubles * 8 + 8 + 16;   // + depth offset (int64) + frame record (int4)
 constexpr int kChunkSmemExtra = 16;                                  // alignment of the records
 
 struct LiftParams {
@@ -348,8 +353,8 @@ __global__ void __launch_bounds__(kLiftThreads, BFF_LIFT_MIN_BLOCKS)
 lift_kernel(const __grid_constant__ LiftParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int fc = p.frames_per_chunk;
-    double *s_pose = reinterpret_cast<double *>(smem_raw);                       // fc x 16 doubles
-    double *s_plane = s_pose + (size_t)fc * 16;                                   // kPlaneDoubles x fc (SoA)
+    double *s_pose = reinterpret_cast<double *>(smem_raw);                       // fc x kPoseStride doubles (16 used)
+    double *s_plane = s_pose + (size_t)fc * kPoseStride;                          // kPlaneDoubles x fc (SoA)
     long long *s_doff = reinterpret_cast<long long *>(s_plane + (size_t)fc * kPlaneDoubles);   // fc
     int4 *s_frame = reinterpret_cast<int4 *>(s_doff + fc + (fc & 1));             // fc (16-byte aligned)
     int32_t *s_acc = reinterpret_cast<int32_t *>(s_frame + fc);                   // Q x blockDim (MULTI_Q)
@@ -361,7 +366,8 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     const int f0 = blockIdx.y * fc;
     const int nf = min(fc, p.n_frames - f0);
 
-    // ---- stage the chunk's inverse poses in shared memory: one bulk async copy (TMA)
+    // ---- stage the chunk's inverse poses in shared memory: bulk async copies (TMA), one 128-byte row per frame into its
+    // padded slot, all completing on one mbarrier
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -370,10 +376,11 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     if (tid == 0) {
         const uint32_t bytes = (uint32_t)nf * 128u;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar)), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(s_pose)),
-            "l"(p.pose_inv + (size_t)f0 * 16), "r"(bytes), "r"(smem_u32(&s_bar))
-            : "memory");
+        for (int i = 0; i < nf; ++i)
+            asm volatile(
+                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(s_pose + i * kPoseStride)),
+                "l"(p.pose_inv + (size_t)(f0 + i) * 16), "r"(128u), "r"(smem_u32(&s_bar))
+                : "memory");
     }
 
     // ---- this thread's point (overlaps the pose copy)
@@ -435,7 +442,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     if (!DEBUG) {
         for (int item = tid; item < nf * 5; item += kLiftThreads) {
             const int fr = item % nf;
-            build_frame_plane(s_pose + fr * 16, p, s_plane + fr, fc, item / nf);
+            build_frame_plane(s_pose + fr * kPoseStride, p, s_plane + fr, fc, item / nf);
         }
     }
     // ---- bounding sphere of the warp's 32 points (fp64, NaN coordinates ignored: such points are never visible);
@@ -483,7 +490,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             fl_n = fb + __ffs(todo) - 1;
             todo &= todo - 1u;
             int px, py;
-            in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * 16, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
+            in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * kPoseStride, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
             raw_n = in_n ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl_n], pix_n, px, py) : 0u;
         }
         while (fl_n >= 0) {
@@ -496,7 +503,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
                 fl_n = fb + __ffs(todo) - 1;
                 todo &= todo - 1u;
                 int px, py;
-                in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * 16, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
+                in_n = locate_pixel<DEBUG>(p, s_pose + fl_n * kPoseStride, f0 + fl_n, x, y, z, valid, pt, Z_n, pix_n, px, py);
                 raw_n = in_n ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl_n], pix_n, px, py) : 0u;
             }
 #else
@@ -505,7 +512,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             todo &= todo - 1u;
             double Z;
             int pix, px, py;
-            const bool in = locate_pixel<DEBUG>(p, s_pose + fl * 16, f0 + fl, x, y, z, valid, pt, Z, pix, px, py);
+            const bool in = locate_pixel<DEBUG>(p, s_pose + fl * kPoseStride, f0 + fl, x, y, z, valid, pt, Z, pix, px, py);
             const unsigned raw = in ? load_depth_raw<DEPTH_KIND>(p, s_doff[fl], pix, px, py) : 0u;
 #endif
             const float d = depth_value<DEPTH_KIND>(raw, p);
