@@ -350,14 +350,30 @@ rle_to_bits_kernel(const int32_t *__restrict__ runs, long long n_runs, long long
 __global__ void __launch_bounds__(256)
 rle_pairs_to_bits_kernel(const long long *__restrict__ counts, const long long *__restrict__ pair_offset, int n_rows, long long n_pairs,
                          long long length, long long words, uint32_t *__restrict__ packed) {
-    const long long pair = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
-    if (pair >= n_pairs) return;
+    __shared__ int s_row0;
+    const long long pair0 = ((long long)blockIdx.x * 256) >> 5;          // first pair of this CTA (8 consecutive pairs, one per warp)
+    if (pair0 >= n_pairs) return;
     const int lane = threadIdx.x & 31;
-    int lo_r = 0, hi_r = n_rows;                     // largest r with pair_offset[r] <= pair
-    while (hi_r - lo_r > 1) {
-        const int mid = (lo_r + hi_r) >> 1;
-        if (__ldg(pair_offset + mid) <= pair) lo_r = mid; else hi_r = mid;
+    if (threadIdx.x < 32) {
+        // row of the CTA's first pair = largest r with pair_offset[r] <= pair0, by a 32-ary search (two rounds up to 1024
+        // rows): the lanes probe evenly spaced offsets at once instead of ten dependent loads of a bisection per warp
+        int lo_r = 0, hi_r = n_rows;
+        while (hi_r - lo_r > 1) {
+            const int step = (hi_r - lo_r + 31) / 32;
+            const int idx = lo_r + (lane + 1) * step;
+            const bool le = idx < hi_r && __ldg(pair_offset + idx) <= pair0;
+            const int cnt = __popc(__ballot_sync(0xffffffffu, le));         // monotone: the probes <= pair0 are a prefix of the lanes
+            const int new_lo = lo_r + cnt * step;
+            hi_r = min(hi_r, new_lo + step);
+            lo_r = new_lo;
+        }
+        if (lane == 0) s_row0 = lo_r;
     }
+    __syncthreads();
+    const long long pair = pair0 + (threadIdx.x >> 5);
+    if (pair >= n_pairs) return;
+    int lo_r = s_row0;
+    while (lo_r + 1 < n_rows && __ldg(pair_offset + lo_r + 1) <= pair) ++lo_r;   // the CTA's pairs span a row or two
     const long long start = (long long)(int)__ldg(counts + 2 * pair) - 1;
     const long long num = (long long)(int)__ldg(counts + 2 * pair + 1);
     const long long end = (long long)(int)(start + num);
