@@ -11,9 +11,13 @@ RLE 2D masks -> packed bits, projection + visibility + mask gather + votes for e
 stage-1/stage-2 refinement of that scene. `value` = point-view projections (N x F, each
 (frame, point) counted once) per second of the WHOLE step with inputs resident in HBM; `e2e`
 is the same through the host API with pinned host buffers in and the final masks out.
-With N > 1 every rank processes its OWN scene of that shape (scenes are the path's independent units:
-weak scaling, no data-path collective); the frame-sharded variant of one (300 x N)-frame scene with its
-NCCL exchange (allreduce of votes + allgather of rows) is measured in the same run as `frame_sharded`.
+The whole step is device-resident (no host round trip between the stages) and `value` replays it as ONE CUDA graph.
+With N > 1 the headline line is ONE scene (BASELINE.json configs[3] at 1000 frames, "c4s") strong-scaled over the N GPUs:
+frames interleaved over the ranks, the lift kernel stores each peer's point slice of the rows straight into that peer's
+buffer (CUDA IPC over NVLink), votes are all-reduced, aggregation / filter / refinement run point-sharded with int32
+all-reduces inside, and the final rows are all-gathered; rank 0 re-runs the same scene on one GPU in the same run and
+asserts bit-identical final masks (`single_gpu_ms`). `replicas` (one c2 scene per GPU, no collective) and
+`frame_sharded_c2` are secondaries of the same line.
 
 Only the cpu_baseline / --impl reference legs touch oracle/ (the reference's numpy path
 restated, oracle/reference_port.py); the GPU arm raises if libbff.so is missing.
@@ -947,6 +951,138 @@ def frame_sharded_run(args, ctx, dev, flush, barrier, workload=None, steps=None)
 
 
 # ----------------------------------------------------------------------------- CPU baseline (oracle port)
+# ----------------------------------------------------------------------------- config 5: the 312-scene sweep
+SWEEP_SCENES, SWEEP_POOL = 312, 5
+
+
+def sweep_plan(world: int, n_scenes: int = SWEEP_SCENES, n_pool: int = SWEEP_POOL, seed: int = 5):
+    """BASELINE.json configs[4]: a val-set sweep of `n_scenes` ScanNet200-val-shaped scenes, scene-parallel over the ranks.
+    Scene shapes are seeded draws over the ranges SURVEY F8 gives for the val set (40k-420k points, 58-543 frames, log-
+    uniform). Fabricating 312 distinct scenes would take longer than the whole bench, so the shapes are bucketed by cost
+    (points x frames) into `n_pool` quantile classes and every scene is served by its class's fabricated scene (the class's
+    mean shape); each of the 312 passes still uploads all of its inputs from the host and brings its masks back.
+    Returns (pool shapes [(points, frames)], class of every scene, per-rank scene lists by schedule.lpt_assign)."""
+    from bff_b200 import schedule
+    rng = np.random.default_rng(seed)
+    pts = np.exp(rng.uniform(np.log(40_000), np.log(420_000), n_scenes))
+    frs = np.exp(rng.uniform(np.log(58), np.log(543), n_scenes))
+    cost = pts * frs
+    order = np.argsort(cost, kind="stable")
+    cls = np.empty(n_scenes, np.int64)
+    pool = []
+    for k, idx in enumerate(np.array_split(order, n_pool)):
+        cls[idx] = k
+        pool.append((int(round(pts[idx].mean() / 1000.0)) * 1000, int(round(frs[idx].mean()))))
+    costs = [float(pool[c][0] * pool[c][1]) for c in cls]
+    return pool, cls.tolist(), schedule.lpt_assign(costs, world)
+
+
+def run_sweep(args):
+    """`--workload c5`: every rank serves its LPT share of the 312 scenes end to end (pinned host buffers -> device ->
+    whole step -> final masks on the host), scene i+1's upload overlapping scene i's step. No data-path collective: scenes
+    are the reference's outermost loop (projection_2d_to_3d.py:365). value = point-views of ALL scenes / max-over-ranks time."""
+    from bff_b200 import _cabi, dist as dist_mod
+    _cabi.lib()
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (GPU arm) needs a CUDA device; there is no CPU fallback")
+    ctx = dist_mod.init_from_env("nccl")
+    rank, world = (ctx.rank, ctx.world_size) if ctx else (0, 1)
+    local = ctx.local_rank if ctx else 0
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    import torch.distributed as dist
+    numa_cpus = dist_mod.bind_to_gpu_numa(local) if world > 1 else None
+    pool, cls, shares = sweep_plan(world)
+    mine = shares[rank]
+    scenes = {}
+    for c in sorted({cls[i] for i in mine}):
+        n_pts, n_fr = pool[c]
+        WORKLOADS[f"c5p{c}"] = dict(n_points=n_pts, n_frames=n_fr, width=640, height=480, n_stage1=max(20, min(200, n_pts // 1250)), n_boxes=14)
+        inp = build_inputs(f"c5p{c}", 0, 1, dev, seed=5000 + c)
+        g = GpuScene(inp, dev, None)
+        bufs = [{k: torch.empty_like(v, device=dev) for k, v in g.host.items()} for _ in range(2)]
+        scenes[c] = dict(g=g, bufs=bufs, done=[None, None], turn=0)
+    copy_stream = torch.cuda.Stream(device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def upload_async(c):
+        sc = scenes[c]
+        slot = sc["turn"]
+        sc["turn"] ^= 1
+        with torch.cuda.stream(copy_stream):
+            if sc["done"][slot] is not None:
+                copy_stream.wait_event(sc["done"][slot])
+            for k_, v_ in sc["g"].host.items():
+                sc["bufs"][slot][k_].copy_(v_, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return slot, ev
+
+    def serve(order):
+        n_masks_out, d2h = 0, 0
+        nxt = upload_async(cls[order[0]]) if order else None
+        for j, i in enumerate(order):
+            c = cls[i]
+            slot, ev = nxt
+            if j + 1 < len(order):
+                nxt = upload_async(cls[order[j + 1]])
+            torch.cuda.current_stream().wait_event(ev)
+            sc = scenes[c]
+            final = sc["g"].step(sc["bufs"][slot])
+            sc["done"][slot] = torch.cuda.Event()
+            sc["done"][slot].record()
+            if isinstance(final["ins"], torch.Tensor):
+                n_masks_out += final["ins"].shape[0]
+                d2h += final["ins"].numel() * final["ins"].element_size()
+        torch.cuda.synchronize()
+        return n_masks_out, d2h
+
+    for c in scenes:                                   # warm-up: every class of scene W times (workspaces, allocator pools)
+        serve([next(i for i in mine if cls[i] == c)] * max(3, args.warmup))
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _cabi.launch_count
+    barrier()
+    t0 = time.perf_counter()
+    n_out, d2h = serve(mine)
+    ms = (time.perf_counter() - t0) * 1e3
+    launches = _cabi.launch_count - launches0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    pv_mine = float(sum(pool[cls[i]][0] * pool[cls[i]][1] for i in mine))
+    h2d_mine = float(sum(scenes[cls[i]]["g"].h2d_bytes for i in mine))
+    t = torch.tensor([ms, -ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([pv_mine, h2d_mine, float(d2h), float(n_out), float(launches), float(len(mine))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_max, ms_min = float(t[0]), -float(t[1])
+    pv, h2d, d2h_all, n_out_all, launches_all, n_served = (float(x) for x in tot.cpu())
+    if rank == 0:
+        assert int(n_served) == SWEEP_SCENES
+        emit({"metric": "point-view projections/sec (whole lifting+aggregation+refinement step)", "value": pv / (ms_max * 1e-3),
+              "unit": "point-views/s", "n_gpus": world, "steps": SWEEP_SCENES, "warmup": max(3, args.warmup), "ms_per_step": ms_max / SWEEP_SCENES * world,
+              "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+              "config": {"workload": f"c5: sweep of {SWEEP_SCENES} ScanNet200-val-shaped scenes (40k-420k points, 58-543 frames 640x480, 1 query), "
+                                     f"{SWEEP_POOL} distinct fabricated scenes serve the {SWEEP_SCENES} passes by size class: "
+                                     + ", ".join(f"{p_}x{f_}" for p_, f_ in pool),
+                         "parallelism": f"scene-parallel: longest-processing-time-first over {world} GPU(s) (bff_b200/schedule.py), no data-path collective",
+                         "scenes_per_rank": [len(s_) for s_ in shares], "l2": "every pass re-uploads its scene (36-390 MB > L2 for all but the smallest class)"},
+              "sweep_ms": ms_max, "sweep_ms_fastest_rank": ms_min, "scenes_per_s": SWEEP_SCENES / (ms_max * 1e-3), "final_masks": int(n_out_all),
+              "e2e": {"value": pv / (ms_max * 1e-3), "unit": "point-views/s", "h2d_bytes_per_step": int(h2d / SWEEP_SCENES), "d2h_bytes_per_step": int(d2h_all / SWEEP_SCENES),
+                      "how": "the sweep IS end to end: every pass copies its inputs from pinned host memory and its final masks back; wall clock, max over ranks",
+                      "h2d_gbs_per_gpu": h2d / world / (ms_max * 1e-3) / 1e9, "numa_bound_cpus_rank0": (len(numa_cpus) if numa_cpus else None)},
+              "gpu_launches": int(launches_all), "clocks": clocks})
+    if ctx:
+        ctx.finalize()
+
+
 def cpu_frames_of(inp, n_frames):
     """First n_frames of the rank's block as the reference's per-frame inputs (dense float32 masks / depth at mask
     resolution, cv2.resize like :436 when the depth PNGs are smaller). Returns (per-query mask frames, view frames)."""
@@ -1196,7 +1332,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + ["c5"])
     ap.add_argument("--cpu-budget", type=float, default=150.0, help="--impl reference: seconds of CPU work for all steps together (sizes the frame sample)")
     ap.add_argument("--cpu-baseline-budget", type=float, default=20.0, help="our arm at N=1: seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -1214,6 +1350,8 @@ def main():
         run_cli_e2e(args)
     elif args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_sweep(args)
     else:
         run_gpu(args)
 

@@ -40,6 +40,10 @@ constexpr int kLiftThreads = BFF_LIFT_THREADS;
 #define BFF_LIFT_PREFETCH 0        // software pipeline over the surviving frames (next frame's depth gather in flight): measured
                                    // 0.239 ms against 0.226 ms without at c2 -- the extra live registers cost more than the gather latency
 #endif
+#ifndef BFF_LIFT_AABB
+#define BFF_LIFT_AABB 1            // cull with the warp's axis-aligned box (half extents against |n|) instead of its bounding sphere:
+                                   // a census at c2 passes 30.2 % of the (warp, frame) pairs instead of 34.1 % (22.4 % hold a point in the frustum)
+#endif
 constexpr int kMaxFramesPerChunk = 256;   // <= kLiftThreads: one thread prepares one frame's culling planes
 // Per-frame culling data in shared memory (structure of arrays, index [k * fc + frame]):
 //   0..5   camera-z as a function of the world point: n(3), d, |n|(1+eps), eps|d|
@@ -131,7 +135,9 @@ __device__ __forceinline__ void store_plane(double *dst, int fc, int k, double a
     dst[(k + 1) * fc] = n1;
     dst[(k + 2) * fc] = n2;
     dst[(k + 3) * fc] = d + kCullEps * fabs(d);
+#if !BFF_LIFT_AABB
     dst[(k + 4) * fc] = norm_upper(n0, n1, n2);
+#endif
 }
 
 // One of the five culling functionals of a frame (which = 0: camera z, 1..4: the image-border planes); the chunk's
@@ -144,7 +150,9 @@ __device__ __forceinline__ void build_frame_plane(const double *P, const LiftPar
         dst[1 * fc] = P[9];
         dst[2 * fc] = P[10];
         dst[3 * fc] = P[11];
+#if !BFF_LIFT_AABB
         dst[4 * fc] = norm_upper(P[8], P[9], P[10]);
+#endif
         dst[5 * fc] = kCullEps * fabs(P[11]);
         break;
     case 1: store_plane(dst, fc, 6, p.k[0], p.k[1], p.k[2] + 1.0, P); break;          // q0 + z >= 0      (u >= -1)
@@ -166,7 +174,13 @@ __device__ __forceinline__ double warp_max(double v) {
 // Sphere (centre of the bounding box, radius to the farthest point) of the valid lanes' points.
 // The radius is inflated so that n.c evaluated in floating point stays an upper bound (|n.c| error
 // <= eps |n| (|cx|+|cy|+|cz|)). Returns false when the warp holds no point at all.
-__device__ __forceinline__ bool warp_sphere(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr) {
+// Half extents of the box around the same centre, inflated like the radius (the box test adds |n_i| h_i instead of |n| r).
+__device__ __forceinline__ double half_extent(double lo, double hi, double c) {
+    return (0.5 * hi - 0.5 * lo) * (1.0 + kCullEps) + kCullEps * fabs(c);
+}
+
+__device__ __forceinline__ bool warp_sphere(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr,
+                                            double &ex, double &ey, double &ez) {
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     const double lx = warp_min(valid ? x : inf), hx = warp_max(valid ? x : -inf);
     const double ly = warp_min(valid ? y : inf), hy = warp_max(valid ? y : -inf);
@@ -174,9 +188,16 @@ __device__ __forceinline__ bool warp_sphere(bool valid, double x, double y, doub
     cx = 0.5 * lx + 0.5 * hx;
     cy = 0.5 * ly + 0.5 * hy;
     cz = 0.5 * lz + 0.5 * hz;
+    ex = half_extent(lx, hx, cx);
+    ey = half_extent(ly, hy, cy);
+    ez = half_extent(lz, hz, cz);
+#if BFF_LIFT_AABB
+    cr = 0.0;
+#else
     const double dx = x - cx, dy = y - cy, dz = z - cz;
     const double d2 = warp_max(valid ? (dx * dx + dy * dy + dz * dz) : 0.0);
     cr = sqrt(d2) * (1.0 + kCullEps) + kCullEps * (fabs(cx) + fabs(cy) + fabs(cz));
+#endif
     return __any_sync(0xffffffffu, valid);
 }
 
@@ -190,7 +211,8 @@ __device__ __forceinline__ unsigned f32_ordered(float v) {
 __device__ __forceinline__ double f32_unordered(unsigned u) {
     return (double)__uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
-__device__ __forceinline__ bool warp_sphere_f32(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr) {
+__device__ __forceinline__ bool warp_sphere_f32(bool valid, double x, double y, double z, double &cx, double &cy, double &cz, double &cr,
+                                                double &ex, double &ey, double &ez) {
     const float fx = (float)x, fy = (float)y, fz = (float)z;      // exact: the cloud is float32
     const bool use = valid && fx == fx && fy == fy && fz == fz;
     const unsigned lo = 0xff800000u /* ordered(+inf) */, hi = 0x007fffffu /* ordered(-inf) */;
@@ -203,23 +225,43 @@ __device__ __forceinline__ bool warp_sphere_f32(bool valid, double x, double y, 
     cx = 0.5 * lx + 0.5 * hx;
     cy = 0.5 * ly + 0.5 * hy;
     cz = 0.5 * lz + 0.5 * hz;
+    ex = half_extent(lx, hx, cx);
+    ey = half_extent(ly, hy, cy);
+    ez = half_extent(lz, hz, cz);
+#if BFF_LIFT_AABB
+    cr = 0.0;
+#else
     const double dx = x - cx, dy = y - cy, dz = z - cz;
     const float d2 = use ? __double2float_ru(dx * dx + dy * dy + dz * dz) : 0.0f;   // >= 0: bit pattern order == value order
     const double r2 = (double)__uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(d2)));
     cr = sqrt(r2) * (1.0 + kCullEps) + kCullEps * (fabs(cx) + fabs(cy) + fabs(cz));
+#endif
     return __any_sync(0xffffffffu, valid);
 }
 
-__device__ __forceinline__ bool warp_may_see(const double *pl, int fc, double cx, double cy, double cz, double cr,
-                                             double z_lo, double z_hi) {
+__device__ __forceinline__ bool warp_may_see(const double *pl, int fc, const double *sp, double z_lo, double z_hi) {
+    // sp: centre (0..2), sphere radius (3), box half extents (4..6) of the warp's points
+    const double cx = sp[0], cy = sp[1], cz = sp[2];
     const double zc = pl[0 * fc] * cx + pl[1 * fc] * cy + pl[2 * fc] * cz + pl[3 * fc];
+#if BFF_LIFT_AABB
+    // support of the box along n: sum |n_i| h_i  (<= |n| r, the sphere's); the 1e-9 factor covers the rounding of the sum itself
+    const double ex = sp[4], ey = sp[5], ez = sp[6];
+    const double zr = (fabs(pl[0 * fc]) * ex + fabs(pl[1 * fc]) * ey + fabs(pl[2 * fc]) * ez) * (1.0 + kCullEps) + pl[5 * fc];
+#else
+    const double cr = sp[3];
     const double zr = pl[4 * fc] * cr + pl[5 * fc];
-    if (zc + zr < z_lo || zc - zr > z_hi) return false;      // no depth value can match anywhere in the sphere
-    if (zc - zr > 0.0) {                                      // whole sphere in front of the camera: border planes apply
+#endif
+    if (zc + zr < z_lo || zc - zr > z_hi) return false;      // no depth value can match anywhere in the box / sphere
+    if (zc - zr > 0.0) {                                      // all of it in front of the camera: border planes apply
 #pragma unroll
         for (int k = 6; k < kPlaneDoubles; k += 5) {
-            const double v = pl[k * fc] * cx + pl[(k + 1) * fc] * cy + pl[(k + 2) * fc] * cz + pl[(k + 3) * fc];
+            const double n0 = pl[k * fc], n1 = pl[(k + 1) * fc], n2 = pl[(k + 2) * fc];
+            const double v = n0 * cx + n1 * cy + n2 * cz + pl[(k + 3) * fc];
+#if BFF_LIFT_AABB
+            if (v + (fabs(n0) * ex + fabs(n1) * ey + fabs(n2) * ez) * (1.0 + kCullEps) < 0.0) return false;
+#else
             if (v + pl[(k + 4) * fc] * cr < 0.0) return false;
+#endif
         }
     }
     return true;
@@ -359,7 +401,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     int4 *s_frame = reinterpret_cast<int4 *>(s_doff + fc + (fc & 1));             // fc (16-byte aligned)
     int32_t *s_acc = reinterpret_cast<int32_t *>(s_frame + fc);                   // Q x blockDim (MULTI_Q)
     __shared__ __align__(8) unsigned long long s_bar;
-    __shared__ double s_sphere[kLiftThreads / 32][4];
+    __shared__ double s_sphere[kLiftThreads / 32][8];
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -449,12 +491,15 @@ lift_kernel(const __grid_constant__ LiftParams p) {
     // parked in shared memory: it is read once per 32-frame batch and would otherwise hold 8 registers for the whole loop
     bool warp_has_points;
     {
-        double cx, cy, cz, cr;
-        warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr) : warp_sphere(valid, x, y, z, cx, cy, cz, cr);
-        if (lane == 0) {
-            double *sp = s_sphere[tid >> 5];
-            sp[0] = cx; sp[1] = cy; sp[2] = cz; sp[3] = cr;
-        }
+        double cx, cy, cz, cr, ex, ey, ez;
+        warp_has_points = XYZ_KIND == BFF_XYZ_F32X4 ? warp_sphere_f32(valid, x, y, z, cx, cy, cz, cr, ex, ey, ez)
+                                                    : warp_sphere(valid, x, y, z, cx, cy, cz, cr, ex, ey, ez);
+        // every lane stores (the values are warp-uniform). Not `if (lane == 0)`: with 64-byte rows nvcc 12.9 folds the row
+        // address under that condition to s_sphere + 2 * tid and re-uses the folded form for the loads below, where the
+        // lane bits are NOT zero -> misaligned LDS.64 (seen in the PTX; the 32-byte rows of the sphere-only table hid it)
+        double *sp = s_sphere[tid >> 5];
+        sp[0] = cx; sp[1] = cy; sp[2] = cz; sp[3] = cr;
+        sp[4] = ex; sp[5] = ey; sp[6] = ez;
     }
     __syncthreads();
     const bool has_rows = rows_out != nullptr;
@@ -466,8 +511,7 @@ lift_kernel(const __grid_constant__ LiftParams p) {
             const int fl = fb + lane;
             bool see = fl < nf && warp_has_points;
             if (!DEBUG && see) {
-                const double *sp = s_sphere[tid >> 5];
-                see = warp_may_see(s_plane + fl, fc, sp[0], sp[1], sp[2], sp[3], p.z_lo, p.z_hi);
+                see = warp_may_see(s_plane + fl, fc, s_sphere[tid >> 5], p.z_lo, p.z_hi);
             }
             todo = __ballot_sync(0xffffffffu, see);
         }

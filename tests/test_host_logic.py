@@ -161,3 +161,21 @@ def test_rle_pairs_for_device_keeps_the_wire_format():
     assert length == 50 and counts.dtype == np.int64 and counts.tolist() == [3, 4, 10, 2, 1, 50] and off.tolist() == [0, 2, 2, 3]
     with pytest.raises(ValueError):
         rle.pairs_for_device([a, {"length": 51, "counts": np.zeros(0, np.int64)}])
+
+
+def test_sweep_plan_covers_every_scene_once_and_balances_the_ranks():
+    """bench.py --workload c5 (BASELINE configs[4]): 312 scene shapes in the val set's ranges, bucketed into size classes,
+    spread over the ranks by schedule.lpt_assign -- every scene served exactly once, loads within 1 %."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    for world in (1, 2, 8):
+        pool, cls, shares = bench.sweep_plan(world)
+        assert len(pool) == bench.SWEEP_POOL and len(cls) == bench.SWEEP_SCENES and len(shares) == world
+        assert sorted(i for s in shares for i in s) == list(range(bench.SWEEP_SCENES))
+        assert all(40_000 <= p <= 420_000 and 58 <= f <= 543 for p, f in pool)
+        assert [p * f for p, f in pool] == sorted(p * f for p, f in pool)
+        load = [sum(pool[cls[i]][0] * pool[cls[i]][1] for i in s) for s in shares]
+        assert max(load) <= 1.01 * min(load)
+        assert (pool, cls, shares) == bench.sweep_plan(world)          # every rank computes the same plan
