@@ -4,7 +4,8 @@ The reference's ScanNetEval.assign_instances_for_scan (evaluation/eval/scannetv2
 every prediction mask and every ground-truth instance of its class, `np.count_nonzero(np.logical_and(gts == id, mask))`
 -- O(P * G * N) numpy passes per scene. Here the ground-truth instances and the void mask become packed rows once
 (bff_labels_to_rows, bff_pack_bits) and ALL intersections and vertex counts are one bff_mask_iou call; the matching
-dictionaries are then filled exactly like the reference fills them (same keys, order, Python float IoU). The evaluator
+dictionaries are then built from that table, visiting only the overlapping (prediction, instance) pairs, with the keys,
+order and value types the reference produces (the goldens of the unmodified evaluator pin that). The evaluator
 keeps consuming the same .pth files; `install(ScanNetEval)` swaps the method on the reference's own class, everything
 after it (evaluate_matches, AP integration) stays the reference's code.
 
@@ -38,80 +39,74 @@ def intersection_tables(pred_masks: Sequence[np.ndarray], gts: np.ndarray, insta
     return inter[:, :g], inter[:, -1], pop_pred.cpu().numpy().astype(np.int64)
 
 
-def assign_instances_for_scan(ev, preds, gts_sem, gts_ins, get_instances: Callable, device=None):
-    """Drop-in body of ScanNetEval.assign_instances_for_scan (scannetv2_inst_eval.py:264-361). `ev` is the evaluator
-    object (dataset_name, encode_value, valid_class_ids, valid_class_labels, id2label, eval_class_labels, use_label,
-    min_region_sizes); `get_instances` is the reference's evaluation.eval.instance_eval_util.get_instances."""
-    device = device or torch.device("cuda", torch.cuda.current_device())
-    # :268-286 label encoding, exactly as the reference (numpy int arithmetic on copies)
-    if ev.dataset_name in ("scannetv2", "scannet200"):
-        gts_sem = gts_sem - 2 + 1
-    elif ev.dataset_name in ("replica", "stpls3d"):
-        gts_sem = gts_sem - 1 + 1
-    elif ev.dataset_name == "scannetpp":
-        gts_sem = gts_sem - 105 + 1
-    else:
-        gts_sem = gts_sem + 1
-    gts_sem[gts_sem < 0] = 0
-    gts_ins = gts_ins + 1
-    ignore_inds = gts_ins < 0
-    gts = gts_sem * ev.encode_value + gts_ins
-    gts[ignore_inds] = 0
-    gt_instances = get_instances(gts, ev.valid_class_ids, ev.valid_class_labels, ev.id2label, dataset=ev.dataset_name)
+# semantic-label offset per dataset before the evaluator's "+1" (:268-280); unknown names use 0
+_SEMANTIC_OFFSET = {"scannetv2": 2, "scannet200": 2, "replica": 1, "stpls3d": 1, "scannetpp": 105}
+
+
+def encode_ground_truth(ev, gts_sem: np.ndarray, gts_ins: np.ndarray) -> np.ndarray:
+    """The evaluator's per-vertex code `semantic * encode_value + instance` (:268-286): semantic ids shifted to start at
+    1 with negatives clamped to 0, instance ids shifted by one, vertices without an instance coded 0. Integer arithmetic,
+    so the single shift below equals the reference's two-step one."""
+    sem = gts_sem - (_SEMANTIC_OFFSET.get(ev.dataset_name, 0) - 1)
+    sem = np.where(sem < 0, 0, sem).astype(sem.dtype, copy=False)
+    ins = gts_ins + 1
+    code = sem * ev.encode_value + ins
+    code[ins < 0] = 0
+    return code
+
+
+def _ground_truth_lists(ev, gt_instances: dict) -> dict:
+    """label -> list of ground-truth records (deep copies, each with an empty `matched_pred`); one list under the first
+    evaluation label when the evaluation is class-agnostic (:290-305)."""
     if ev.use_label:
-        gt2pred = deepcopy(gt_instances)
-        for label in gt2pred:
-            for gt in gt2pred[label]:
-                gt["matched_pred"] = []
+        lists = deepcopy(gt_instances)
     else:
-        gt2pred = {}
-        agnostic = []
-        for _, instances in gt_instances.items():
-            agnostic += deepcopy(instances)
-        for gt in agnostic:
-            gt["matched_pred"] = []
-        gt2pred[ev.eval_class_labels[0]] = agnostic
+        lists = {ev.eval_class_labels[0]: [rec for records in gt_instances.values() for rec in deepcopy(records)]}
+    for records in lists.values():
+        for rec in records:
+            rec["matched_pred"] = []
+    return lists
+
+
+def assign_instances_for_scan(ev, preds, gts_sem, gts_ins, get_instances: Callable, device=None, tables: Callable = None):
+    """What ScanNetEval.assign_instances_for_scan returns (scannetv2_inst_eval.py:264-361): (gt2pred, pred2gt) with the same
+    keys, order and value types, built from ONE table of intersections instead of a numpy pass per (prediction, instance).
+    `ev` is the evaluator object (dataset_name, encode_value, valid_class_ids, valid_class_labels, id2label,
+    eval_class_labels, use_label, min_region_sizes); `get_instances` is the reference's
+    evaluation.eval.instance_eval_util.get_instances; `tables` defaults to the CUDA `intersection_tables`."""
+    tables = tables or intersection_tables
+    if tables is intersection_tables:
+        device = device or torch.device("cuda", torch.cuda.current_device())
+    gts = encode_ground_truth(ev, gts_sem, gts_ins)
+    gt2pred = _ground_truth_lists(ev, get_instances(gts, ev.valid_class_ids, ev.valid_class_labels, ev.id2label, dataset=ev.dataset_name))
     pred2gt = {label: [] for label in ev.eval_class_labels}
-    bool_void = np.logical_not(np.isin(gts // ev.encode_value, ev.valid_class_ids))           # :312 (np.in1d)
-    # every distinct ground-truth instance id gets one packed row; all intersections in one launch
-    all_ids, col = [], {}
-    for label in gt2pred:
-        for gt in gt2pred[label]:
-            if gt["instance_id"] not in col:
-                col[gt["instance_id"]] = len(all_ids)
-                all_ids.append(int(gt["instance_id"]))
-    kept = []
-    for pred in preds:
-        if ev.use_label and pred["label_id"] not in ev.id2label:
-            continue
-        assert pred["pred_mask"].shape[0] == gts.shape[0]
-        kept.append(pred)
-    inter, void_inter, counts = intersection_tables([p["pred_mask"] for p in kept], gts, all_ids, bool_void, device)
-    num_pred_instances = 0
-    for k, pred in enumerate(kept):
-        label_id = pred["label_id"]
-        label_name = ev.id2label[label_id] if ev.use_label else ev.eval_class_labels[0]
-        num = counts[k]                                   # numpy integer scalars like np.count_nonzero returns (:332)
-        if num < ev.min_region_sizes[0]:
-            continue
-        pred_instance = {"filename": "{}_{}".format(pred["scan_id"], num_pred_instances), "pred_id": num_pred_instances,
-                         "label_id": label_id if ev.use_label else None, "vert_count": num, "confidence": pred["conf"],
-                         "void_intersection": void_inter[k]}
-        matched_gt = []
-        for gt_num, gt_inst in enumerate(gt2pred[label_name]):
-            intersection = inter[k, col[gt_inst["instance_id"]]]
-            if intersection > 0:
-                gt_copy, pred_copy = gt_inst.copy(), pred_instance.copy()
-                gt_copy["intersection"] = intersection
-                pred_copy["intersection"] = intersection
-                iou = float(intersection) / (gt_copy["vert_count"] + pred_copy["vert_count"] - intersection)
-                gt_copy["iou"] = iou
-                pred_copy["iou"] = iou
-                matched_gt.append(gt_copy)
-                gt2pred[label_name][gt_num]["matched_pred"].append(pred_copy)
-        pred_instance["matched_gt"] = matched_gt
-        num_pred_instances += 1
-        pred2gt[label_name].append(pred_instance)
+    void = ~np.isin(gts // ev.encode_value, ev.valid_class_ids)                    # :312
+    # table columns: the distinct ground-truth instance ids; per label the columns of its records, in list order
+    column: dict = {}
+    label_cols = {label: np.asarray([column.setdefault(int(rec["instance_id"]), len(column)) for rec in records], dtype=np.int64)
+                  for label, records in gt2pred.items()}
+    scored = [p for p in preds if not ev.use_label or p["label_id"] in ev.id2label]
+    for p in scored:
+        assert p["pred_mask"].shape[0] == gts.shape[0]
+    inter, void_inter, vert_count = tables([p["pred_mask"] for p in scored], gts, list(column), void, device)
+    agnostic = ev.eval_class_labels[0]
+    for k in np.flatnonzero(vert_count >= ev.min_region_sizes[0]):                # :333 drops the smaller predictions
+        pred = scored[k]
+        label = ev.id2label[pred["label_id"]] if ev.use_label else agnostic
+        pred_id = sum(len(v) for v in pred2gt.values())
+        record = {"filename": "{}_{}".format(pred["scan_id"], pred_id), "pred_id": pred_id,
+                  "label_id": pred["label_id"] if ev.use_label else None, "vert_count": vert_count[k],
+                  "confidence": pred["conf"], "void_intersection": void_inter[k]}
+        matched = []
+        row = inter[k, label_cols[label]]
+        for j in np.flatnonzero(row > 0):                                         # only the overlapping instances are visited
+            both = row[j]
+            gt_rec = gt2pred[label][j]
+            pair = {"intersection": both, "iou": float(both) / (gt_rec["vert_count"] + record["vert_count"] - both)}
+            matched.append({**gt_rec, **pair})
+            gt_rec["matched_pred"].append({**record, **pair})
+        record["matched_gt"] = matched
+        pred2gt[label].append(record)
     return gt2pred, pred2gt
 
 

@@ -31,11 +31,12 @@ class SceneStep:
         self.row_index, self.dev, self.depth_range = row_index, device, depth_range
         self.nq = len(self.names)
         self.lanes = [torch.cuda.Stream(device=device) for _ in range(min(max(int(lanes), 1), self.nq))] if self.nq > 1 else []
+        self.side = torch.cuda.Stream(device=device)      # the stage-1 decode: needed only by the refinement, runs beside the lifting
         self._graphs: dict = {}
         self.timing_events = None
 
     # ------------------------------------------------------------------ enqueue-only part
-    def _query_chain(self, qi: int, d: dict, out, s1: torch.Tensor, lane: int, mark_mid=None):
+    def _query_chain(self, qi: int, d: dict, out, s1: torch.Tensor, lane: int, mark_mid=None, join=None):
         rows_q = out.rows if self.row_index is None else ops.rows_gather(out.rows, self.row_index[qi])
         wd = s1.shape[1]
         if rows_q.shape[0] == 0:                       # nothing lifted for this query (:465-478): known on the host
@@ -48,6 +49,8 @@ class SceneStep:
             rows2, n2, conf2 = s2.out_rows, s2.n_selected_dev, s2.selected_conf_dev
         if mark_mid is not None:
             mark_mid()
+        if join is not None:
+            join()
         s1_q = s1.clone() if self.nq > 1 else s1     # pass 1 ORs matched stage-1 rows in place (refinement.py:248)
         rf = devpipe.refine_device(s1_q, rows2, n2, conf2, d[f"isq{qi}"], d[f"sim{qi}"], self.n, self.cfg, self.names[qi], select_mode=1, lane=lane)
         rf.enqueue_unpack()
@@ -58,8 +61,17 @@ class SceneStep:
         `marks`: optional callable invoked at the stage boundaries (the caller records timing events there)."""
         mark = marks or (lambda: None)
         mark()
-        # the stage-1 masks first: they depend on nothing, and the GPU decodes them while the host prepares the lifting launch
-        s1 = ops.rle_pairs_to_bits_dev(d["s1_counts"], d["s1_pair_off"], self.n)
+        # the stage-1 masks depend on nothing and are needed only by the refinement: decoded on a side stream, beside the lifting
+        main = torch.cuda.current_stream(self.dev)
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            s1 = ops.rle_pairs_to_bits_dev(d["s1_counts"], d["s1_pair_off"], self.n)
+        joined = [False]
+
+        def join():
+            if not joined[0]:
+                torch.cuda.current_stream(self.dev).wait_stream(self.side)
+                joined[0] = True
         masks2d = ops.rle_pairs_to_bits_dev(d["counts"], d["pair_off"], self.h * self.w) if self.n_masks else None
         mark()
         out = ops.lift_scene(d["xyz"], d["pinv"], self.K, d["depth"], self.h, self.w, masks2d=masks2d,
@@ -70,7 +82,7 @@ class SceneStep:
         mark()                                         # (a single GPU has no exchange stage: an empty interval)
         chains: List = [None] * self.nq
         if self.lanes:
-            main = torch.cuda.current_stream(self.dev)
+            join()                                     # before the fork: every lane then sees the decoded stage-1 rows
             for k, lane in enumerate(self.lanes):
                 lane.wait_stream(main)
             for qi in range(self.nq):
@@ -82,7 +94,7 @@ class SceneStep:
             mark()
         else:
             for qi in range(self.nq):
-                chains[qi] = self._query_chain(qi, d, out, s1, 0, mark_mid=mark if self.nq == 1 else None)
+                chains[qi] = self._query_chain(qi, d, out, s1, 0, mark_mid=mark if self.nq == 1 else None, join=join)
             if self.nq != 1:
                 mark()
         return {"s1": s1, "out": out, "chains": chains, "masks2d": masks2d}
