@@ -19,6 +19,8 @@ with open(os.path.join(_HERE, "stage1_classes.txt")) as _fh:
     STAGE1_CLASS_NAMES: List[str] = [l.strip() for l in _fh if l.strip()]
 
 
+MAX_DEVICE_ROWS, MAX_FUSED_ROWS = 40960, 65535   # stage-2 mask counts bff_refine_device / bff_refine_match accept (include/bff.h);
+                                                 # larger jobs take the next path down, the step-by-step one has no limit
 FUSED = True     # bff_refine_match (C++ decisions next to the launches); False = one Python/torch call per step
 DEVICE = True    # bff_refine_device (every decision a kernel, one synchronisation per scene); takes precedence over FUSED
 
@@ -58,9 +60,9 @@ def pass1_scene(stage1: dict, stage2: dict, query: str, stage1_iou_thres: float,
                 "other": s1[ops.small_to_device(torch.tensor(other, dtype=torch.long), device)] if other else s1[:0]}
     s2 = stage2["rows"] if "rows" in stage2 else ops.pack_bits(stage2["ins"].to(device))
     s2_conf = stage2["conf"]
-    if DEVICE and isinstance(s2_conf, torch.Tensor) and s2_conf.dtype == torch.float32 and s1.shape[0] > 0:
+    if DEVICE and isinstance(s2_conf, torch.Tensor) and s2_conf.dtype == torch.float32 and s1.shape[0] > 0 and s2.shape[0] <= MAX_DEVICE_ROWS:
         return _pass1_device(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device)
-    if FUSED and s2_conf.dtype == torch.float32:
+    if FUSED and s2_conf.dtype == torch.float32 and s2.shape[0] <= MAX_FUSED_ROWS:
         return _pass1_fused(s1, s2, s2_conf, labels, query, q_, stage1_iou_thres, sim_fn, n_points, device)
     mm = torch.argmax(iou_between_stages(s1, s2), dim=1)                       # :208-213
     sel = s1[mm.to(device)]
@@ -189,7 +191,8 @@ def pass1_scene_batch(stage1: dict, stage2_list: Sequence[dict], queries: Sequen
     out = [None] * len(queries)
     at, jobs = [], []
     for k, (stage2, query) in enumerate(zip(stage2_list, queries)):
-        fused = FUSED and len(stage2["conf"]) and isinstance(stage2["conf"], torch.Tensor) and stage2["conf"].dtype == torch.float32
+        fused = (FUSED and len(stage2["conf"]) and isinstance(stage2["conf"], torch.Tensor) and stage2["conf"].dtype == torch.float32
+                 and len(stage2["conf"]) <= MAX_FUSED_ROWS)
         if not fused:
             out[k] = pass1_scene(stage1, stage2, query, stage1_iou_thres, sim_fn, device, s1_rows=s1_rows_list[k])
             continue

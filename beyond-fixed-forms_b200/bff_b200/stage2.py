@@ -12,6 +12,7 @@ from ._log import log
 
 
 FUSED = True     # bff_stage2_aggregate (C++ decisions next to the launches); False = one Python/torch call per step
+MAX_DEVICE_ROWS, MAX_FUSED_ROWS = 25000, 46340   # lifted-mask counts bff_stage2_device / bff_stage2_aggregate accept (include/bff.h); beyond: next path down
 DEVICE = True    # bff_stage2_device (every decision a kernel, no host round trip inside the call); takes precedence over FUSED
 
 
@@ -53,12 +54,12 @@ def aggregate_and_filter(rows: torch.Tensor, conf_list, labels, mc: torch.Tensor
         return scene_io.empty_stage2(), False
     conf = conf_list if isinstance(conf_list, torch.Tensor) else torch.tensor(conf_list)    # :484-486
     if DEVICE and n_frames is not None and pairs is None and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32 \
-            and rows.shape[0] <= 25000:
+            and rows.shape[0] <= MAX_DEVICE_ROWS:
         from . import devpipe, ops
         s2 = devpipe.stage2_device(rows, ops.small_to_device(conf, rows.device), labels, mc, vc, n_points, c,
                                    mc_cap=rows.shape[0], vc_cap=int(n_frames))
         return s2.saved_dict(to_host=to_host, keep_rows=keep_rows)
-    if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32 and rows.shape[0] <= 46340:
+    if FUSED and c["min_aggragated_masks"] >= 1 and conf.dtype == torch.float32 and rows.shape[0] <= MAX_FUSED_ROWS:
         fused = aggregate.aggregate_filter_fused(rows, conf, labels, mc, vc, n_points, c, pairs=pairs)
         return _finish_fused(fused, n_points, c, keep_rows, to_host)
     agg, conf_agg, labels_agg, groups = aggregate.aggregate_rows(rows, conf, labels, c["iou_thres"], c["min_aggragated_masks"])

@@ -37,6 +37,7 @@ void set_error(const char *fmt, ...);
     } while (0)
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+constexpr int32_t kMaxGridY = 65535;       // rows per launch of the kernels that index rows by blockIdx.y: the entry points loop over row blocks
 
 constexpr int kNumSMs = 148;  // B200
 

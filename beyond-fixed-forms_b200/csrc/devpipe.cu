@@ -1186,7 +1186,7 @@ int refine_check(const bff_refine_dev_desc *d, const char *who) {
 int refine_select(const bff_refine_dev_desc *d, int mode, double thres, cudaStream_t s) {
     const RefineLayout L{d->n1, d->cap2};
     const long long words = ceil_div64(d->n_points, 32);
-    BFF_REQUIRE(d->cap2 <= 40 * 1024, "bff_refine_device: cap2 too large");
+    BFF_REQUIRE(d->cap2 <= 40960, "bff_refine_device: cap2 too large");
     refine_select_kernel<<<1, kDecT, (size_t)d->cap2, s>>>(L, mode, d->sim_percentile, thres, d->refine_iou_thres, d->result);
     BFF_LAUNCH_CHECK("refine_select_kernel");
     dim3 grid((unsigned)ceil_div64(words, 256), loop_rows(d->n1 + d->cap2));
@@ -1310,10 +1310,11 @@ extern "C" int bff_rows_slice(const uint32_t *rows, int32_t n_rows, int64_t word
     BFF_REQUIRE(n_rows >= 0 && words >= 0 && word0 >= 0 && slice_words >= 0, "bff_rows_slice: negative size");
     if (n_rows == 0 || slice_words == 0) return BFF_OK;
     BFF_REQUIRE(rows && out, "bff_rows_slice: null pointer");
-    BFF_REQUIRE(n_rows <= 65535, "bff_rows_slice: too many rows");
-    dim3 grid((unsigned)ceil_div64(slice_words, 256), (unsigned)n_rows);
-    rows_slice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows, words, word0, slice_words, out);
-    BFF_LAUNCH_CHECK("rows_slice_kernel");
+    for (int32_t r0 = 0; r0 < n_rows; r0 += kMaxGridY) {
+        dim3 grid((unsigned)ceil_div64(slice_words, 256), (unsigned)std::min(n_rows - r0, kMaxGridY));
+        rows_slice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows + (size_t)r0 * words, words, word0, slice_words, out + (size_t)r0 * slice_words);
+        BFF_LAUNCH_CHECK("rows_slice_kernel");
+    }
     return BFF_OK;
 }
 
@@ -1321,9 +1322,10 @@ extern "C" int bff_rows_unslice(const uint32_t *slices, int32_t world, int32_t n
     BFF_REQUIRE(world >= 1 && n_rows >= 0 && slice_words > 0 && words >= 0 && (int64_t)world * slice_words >= words, "bff_rows_unslice: bad sizes");
     if (n_rows == 0 || words == 0) return BFF_OK;
     BFF_REQUIRE(slices && out, "bff_rows_unslice: null pointer");
-    BFF_REQUIRE(n_rows <= 65535, "bff_rows_unslice: too many rows");
-    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_rows);
-    rows_unslice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(slices, n_rows, slice_words, words, out);
-    BFF_LAUNCH_CHECK("rows_unslice_kernel");
+    for (int32_t r0 = 0; r0 < n_rows; r0 += kMaxGridY) {       // n_rows stays the rank stride of `slices`; only the first row moves
+        dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)std::min(n_rows - r0, kMaxGridY));
+        rows_unslice_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(slices + (size_t)r0 * slice_words, n_rows, slice_words, words, out + (size_t)r0 * words);
+        BFF_LAUNCH_CHECK("rows_unslice_kernel");
+    }
     return BFF_OK;
 }

@@ -4,6 +4,7 @@
 // A packed row is Wd = ceil(N/32) uint32 words; every kernel here is integer work on those
 // words (AND / OR / POPC), bit-exact by construction. Reference lines replaced are cited at
 // each entry point and in include/bff.h.
+#include <algorithm>
 #include <stdlib.h>
 
 #include <atomic>
@@ -508,10 +509,11 @@ extern "C" int bff_rows_or_reduce(const uint32_t *rows, int64_t words, const int
     BFF_REQUIRE(n_groups >= 0 && words >= 0, "bff_rows_or_reduce: negative size");
     if (n_groups == 0 || words == 0) return BFF_OK;
     BFF_REQUIRE(rows && idx && seg && out, "bff_rows_or_reduce: null pointer");
-    BFF_REQUIRE(n_groups <= 65535, "bff_rows_or_reduce: too many groups");
-    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_groups);
-    rows_or_reduce_kernel<<<grid, 256, 0, stream>>>(rows, words, idx, seg, out);
-    BFF_LAUNCH_CHECK("rows_or_reduce_kernel");
+    for (int32_t g0 = 0; g0 < n_groups; g0 += kMaxGridY) {      // blockIdx.y = group: at most 65535 per launch
+        dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)std::min(n_groups - g0, kMaxGridY));
+        rows_or_reduce_kernel<<<grid, 256, 0, stream>>>(rows, words, idx, seg + g0, out + (size_t)g0 * words);
+        BFF_LAUNCH_CHECK("rows_or_reduce_kernel");
+    }
     return BFF_OK;
 }
 
@@ -551,11 +553,12 @@ extern "C" int bff_rows_and_popcount(uint32_t *rows, int32_t n_rows, int64_t wor
         return BFF_OK;
     }
     BFF_REQUIRE(rows, "bff_rows_and_popcount: null rows");
-    BFF_REQUIRE(n_rows <= 65535, "bff_rows_and_popcount: too many rows");
     if (pop) BFF_CUDA(cudaMemsetAsync(pop, 0, (size_t)n_rows * 4, stream));
-    dim3 grid((unsigned)ceil_div64(words, kAndPopWordsPerBlock), (unsigned)n_rows);
-    rows_and_popcount_kernel<<<grid, 256, 0, stream>>>(rows, words, keep, pop);
-    BFF_LAUNCH_CHECK("rows_and_popcount_kernel");
+    for (int32_t r0 = 0; r0 < n_rows; r0 += kMaxGridY) {
+        dim3 grid((unsigned)ceil_div64(words, kAndPopWordsPerBlock), (unsigned)std::min(n_rows - r0, kMaxGridY));
+        rows_and_popcount_kernel<<<grid, 256, 0, stream>>>(rows + (size_t)r0 * words, words, keep, pop ? pop + r0 : nullptr);
+        BFF_LAUNCH_CHECK("rows_and_popcount_kernel");
+    }
     return BFF_OK;
 }
 
@@ -564,11 +567,12 @@ extern "C" int bff_pack_bits(const uint8_t *dense, int32_t n_rows, int64_t n, ui
     BFF_REQUIRE(n_rows >= 0 && n >= 0, "bff_pack_bits: negative size");
     if (n_rows == 0 || n == 0) return BFF_OK;
     BFF_REQUIRE(dense && packed, "bff_pack_bits: null pointer");
-    BFF_REQUIRE(n_rows <= 65535, "bff_pack_bits: too many rows");
     const long long words = ceil_div64(n, 32);
-    dim3 grid((unsigned)ceil_div64(words * 32, 256), (unsigned)n_rows);
-    pack_bits_kernel<<<grid, 256, 0, stream>>>(dense, n, words, packed);
-    BFF_LAUNCH_CHECK("pack_bits_kernel");
+    for (int32_t r0 = 0; r0 < n_rows; r0 += kMaxGridY) {
+        dim3 grid((unsigned)ceil_div64(words * 32, 256), (unsigned)std::min(n_rows - r0, kMaxGridY));
+        pack_bits_kernel<<<grid, 256, 0, stream>>>(dense + (size_t)r0 * n, n, words, packed + (size_t)r0 * words);
+        BFF_LAUNCH_CHECK("pack_bits_kernel");
+    }
     return BFF_OK;
 }
 
@@ -577,14 +581,15 @@ extern "C" int bff_unpack_bits(const uint32_t *packed, int32_t n_rows, int64_t n
     BFF_REQUIRE(n_rows >= 0 && n >= 0, "bff_unpack_bits: negative size");
     if (n_rows == 0 || n == 0) return BFF_OK;
     BFF_REQUIRE(dense && packed, "bff_unpack_bits: null pointer");
-    BFF_REQUIRE(n_rows <= 65535, "bff_unpack_bits: too many rows");
     const long long words = ceil_div64(n, 32);
     const long long total = (long long)n_rows * n;
     if ((reinterpret_cast<uintptr_t>(dense) & 15) == 0 && n >= 16 && ceil_div64(total, 16 * 256) <= 0x7fffffffLL) {
         unpack_bits_wide_kernel<<<(unsigned)ceil_div64(total, 16 * 256), 256, 0, stream>>>(packed, n, words, total, reinterpret_cast<uint4 *>(dense));
     } else {
-        dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)n_rows);
-        unpack_bits_kernel<<<grid, 256, 0, stream>>>(packed, n, words, dense);
+        for (int32_t r0 = 0; r0 < n_rows; r0 += kMaxGridY) {
+            dim3 grid((unsigned)ceil_div64(n, 256), (unsigned)std::min(n_rows - r0, kMaxGridY));
+            unpack_bits_kernel<<<grid, 256, 0, stream>>>(packed + (size_t)r0 * words, n, words, dense + (size_t)r0 * n);
+        }
     }
     BFF_LAUNCH_CHECK("unpack_bits_kernel");
     return BFF_OK;
@@ -634,9 +639,14 @@ extern "C" int bff_rows_permute(const uint32_t *rows_in, int32_t n_rows, int64_t
     if (n_rows == 0 || n_points == 0) return BFF_OK;
     BFF_REQUIRE(rows_in && src_index && rows_out && rows_in != rows_out, "bff_rows_permute: null or aliased pointer");
     BFF_REQUIRE(n_points < (1LL << 31), "bff_rows_permute: too many points for int32 indices");
-    dim3 grid((unsigned)ceil_div64(n_points, 256), (unsigned)ceil_div64(n_rows, bff::kPermuteRowsPerBlock));
-    BFF_REQUIRE(grid.y <= 65535, "bff_rows_permute: too many rows");
-    bff::rows_permute_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows_in, n_rows, n_points, ceil_div64(n_points, 32), src_index, rows_out);
-    BFF_LAUNCH_CHECK("rows_permute_kernel");
+    const long long words = ceil_div64(n_points, 32);
+    const int32_t rows_per_launch = kMaxGridY * bff::kPermuteRowsPerBlock;
+    for (int32_t r0 = 0; r0 < n_rows; r0 += rows_per_launch) {
+        const int32_t nr = std::min(n_rows - r0, rows_per_launch);
+        dim3 grid((unsigned)ceil_div64(n_points, 256), (unsigned)ceil_div64(nr, bff::kPermuteRowsPerBlock));
+        bff::rows_permute_kernel<<<grid, 256, 0, (cudaStream_t)stream_>>>(rows_in + (size_t)r0 * words, nr, n_points, words, src_index,
+                                                                         rows_out + (size_t)r0 * words);
+        BFF_LAUNCH_CHECK("rows_permute_kernel");
+    }
     return BFF_OK;
 }

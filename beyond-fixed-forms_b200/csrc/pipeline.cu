@@ -106,15 +106,16 @@ extern "C" int bff_rows_gather(bff_ctx *c, const uint32_t *rows, int64_t words, 
     BFF_REQUIRE(c && n_idx >= 0 && words >= 0, "bff_rows_gather: bad arguments");
     if (n_idx == 0 || words == 0) return BFF_OK;
     BFF_REQUIRE(rows && idx_host && out, "bff_rows_gather: null pointer");
-    BFF_REQUIRE(n_idx <= 65535, "bff_rows_gather: too many rows");
     c->dev.reset();
     c->pin.reset();
     int32_t *d_idx = nullptr;
     int rc = upload_i32(c, std::vector<int32_t>(idx_host, idx_host + n_idx), &d_idx, s);
     if (rc != BFF_OK) return rc;
-    dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)n_idx);
-    rows_gather_kernel<<<grid, 256, 0, s>>>(rows, words, d_idx, out);
-    BFF_LAUNCH_CHECK("rows_gather_kernel");
+    for (int32_t r0 = 0; r0 < n_idx; r0 += kMaxGridY) {
+        dim3 grid((unsigned)ceil_div64(words, 256), (unsigned)std::min(n_idx - r0, kMaxGridY));
+        rows_gather_kernel<<<grid, 256, 0, s>>>(rows, words, d_idx + r0, out + (size_t)r0 * words);
+        BFF_LAUNCH_CHECK("rows_gather_kernel");
+    }
     // the pinned staging buffer is reused by the next call: make sure the copy has been consumed
     BFF_CUDA(cudaStreamSynchronize(s));
     return BFF_OK;

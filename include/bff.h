@@ -21,9 +21,10 @@
  *  - bits beyond N in the last word of a row are always written as 0 and must be 0 on input.
  *
  * Size limits (checked, BFF_EINVAL beyond them; the host package routes larger jobs to its step-by-step path):
- *  - row counts that become a grid dimension are limited to 65 535: n_groups of bff_rows_or_reduce, n_rows of
- *    bff_rows_and_popcount / bff_pack_bits / bff_unpack_bits / bff_rows_slice / bff_rows_unslice, n_idx of
- *    bff_rows_gather (bff_rows_gather_dev has no limit), n_masks of bff_mask_gather, 16 x 65 535 rows in bff_rows_permute;
+ *  - the row-indexed kernels address rows by blockIdx.y; their entry points loop over blocks of 65 535 rows, so
+ *    bff_rows_or_reduce / bff_rows_and_popcount / bff_pack_bits / bff_unpack_bits / bff_rows_slice / bff_rows_unslice /
+ *    bff_rows_gather / bff_rows_permute take any int32 row count. Still limited to 65 535: n_masks of bff_mask_gather,
+ *    n_frames and the output height of bff_depth_resize;
  *  - bff_stage2_aggregate: n_rows <= 46 340 (n_rows^2 int32 intersections); bff_refine_match: n2 <= 65 535;
  *  - bff_stage2_device: n_rows <= 25 000 (8 bytes of shared memory per row in the component search);
  *    bff_refine_device: cap2 <= 40 960;

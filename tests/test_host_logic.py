@@ -179,3 +179,21 @@ def test_sweep_plan_covers_every_scene_once_and_balances_the_ranks():
         load = [sum(pool[cls[i]][0] * pool[cls[i]][1] for i in s) for s in shares]
         assert max(load) <= 1.01 * min(load)
         assert (pool, cls, shares) == bench.sweep_plan(world)          # every rank computes the same plan
+
+
+def test_pipeline_row_limits_match_the_header():
+    """stage2.py / refine.py route jobs beyond the fused entry points' row limits to the next path down; the numbers they
+    compare with are the ones include/bff.h documents and the library enforces."""
+    import os
+    import re
+    from bff_b200 import refine, stage2
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "include", "bff.h")).read().replace(" ", " ")
+    num = lambda pat: int(re.search(pat, text).group(1).replace(" ", ""))
+    assert stage2.MAX_FUSED_ROWS == num(r"bff_stage2_aggregate: n_rows <= ([\d ]+\d)")
+    assert stage2.MAX_DEVICE_ROWS == num(r"bff_stage2_device: n_rows <= ([\d ]+\d)")
+    assert refine.MAX_FUSED_ROWS == num(r"bff_refine_match: n2 <= ([\d ]+\d)")
+    assert refine.MAX_DEVICE_ROWS == num(r"bff_refine_device: cap2 <= ([\d ]+\d)")
+    src = "".join(open(os.path.join(root, "beyond-fixed-forms_b200", "csrc", f)).read() for f in ("devpipe.cu", "pipeline.cu"))
+    for limit in (stage2.MAX_FUSED_ROWS, stage2.MAX_DEVICE_ROWS, refine.MAX_FUSED_ROWS, refine.MAX_DEVICE_ROWS):
+        assert f"<= {limit}" in src

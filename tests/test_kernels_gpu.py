@@ -658,3 +658,36 @@ def test_outputs_stay_inside_their_buffers(cuda_dev):
         _cabi.check(_cabi.lib().bff_upload(_cabi.ptr(out), _cabi.ptr(src), nbytes, _cabi.current_stream()), "bff_upload")
         torch.cuda.synchronize()
         assert intact(buf, nbytes) and torch.equal(out.cpu(), src[:nbytes]), nbytes
+
+
+def test_row_kernels_accept_more_rows_than_one_grid_dimension(cuda_dev):
+    """The row-indexed kernels address rows by blockIdx.y (<= 65535 per launch); their entry points loop over row blocks, so
+    70 000 short rows go through pack / unpack / AND+popcount / segmented OR / slice / unslice / permute like any other input."""
+    from bff_b200 import ops
+    rng = np.random.default_rng(77)
+    r, n = 70_000, 45                                      # 2 words per row, ragged tail
+    dense = rng.random((r, n)) < 0.3
+    d_dense = torch.from_numpy(dense).to(cuda_dev)
+    packed = ops.pack_bits(d_dense)
+    assert torch.equal(packed.cpu(), torch.from_numpy(pack_rows(dense).view(np.int32)))
+    n_narrow = 13                                          # < 16: the byte-wise unpack kernel (blockIdx.y = row)
+    assert torch.equal(ops.unpack_bits(ops.pack_bits(d_dense[:, :n_narrow].contiguous()), n_narrow).cpu(), torch.from_numpy(dense[:, :n_narrow]))
+    assert torch.equal(ops.unpack_bits(packed, n).cpu(), torch.from_numpy(dense))
+    keep = rng.random(n) < 0.5
+    d_keep = torch.from_numpy(pack_rows(keep[None]).view(np.int32)).to(cuda_dev).reshape(-1)
+    kept = packed.clone()
+    pop = ops.rows_and_popcount(kept, d_keep)
+    np.testing.assert_array_equal(pop.cpu().numpy(), (dense & keep).sum(1))
+    assert torch.equal(ops.unpack_bits(kept, n).cpu(), torch.from_numpy(dense & keep))
+    groups = [[i, (i * 7 + 3) % r] for i in range(r)]      # 70 000 groups of two rows
+    ored = ops.rows_or_reduce(packed, groups)
+    want = dense | dense[[(i * 7 + 3) % r for i in range(r)]]
+    assert torch.equal(ops.unpack_bits(ored, n).cpu(), torch.from_numpy(want))
+    sl = torch.stack([ops.rows_slice(packed, 0, 1), ops.rows_slice(packed, 1, 1)])
+    assert torch.equal(sl[0, :, 0], packed[:, 0]) and torch.equal(sl[1, :, 0], packed[:, 1])
+    assert torch.equal(ops.rows_unslice(sl.contiguous(), 2), packed)
+    perm = rng.permutation(n).astype(np.int32)
+    out = ops.rows_permute(packed, torch.from_numpy(perm).to(cuda_dev), n)
+    assert torch.equal(ops.unpack_bits(out, n).cpu(), torch.from_numpy(dense[:, perm]))
+    idx = torch.from_numpy(rng.integers(0, r, r).astype(np.int32)).to(cuda_dev)
+    assert torch.equal(ops.rows_gather(packed, idx), packed[idx.long()])
