@@ -99,6 +99,8 @@ def refine_dev_result_words(n1: int, cap2: int) -> int:
 
 
 # name -> (restype, argtypes); every symbol include/bff.h declares
+VOTE_UNIQUE_STATIC_MAX_BINS = 131072       # include/bff.h BFF_VOTE_UNIQUE_STATIC_MAX_BINS
+
 SYMBOLS = {
     "bff_version": (c_int, []),
     "bff_last_error": (c_char_p, []),
@@ -116,6 +118,7 @@ SYMBOLS = {
     "bff_vote_hist": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
     "bff_vote_unique_table_size": (c_int64, [c_int32, c_int32]),
     "bff_vote_unique": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "bff_vote_unique_static": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
     "bff_point_keep": (c_int, [c_void_p, c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
     "bff_labels_to_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int32, c_void_p, c_void_p]),
     "bff_rows_permute": (c_int, [c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_void_p]),

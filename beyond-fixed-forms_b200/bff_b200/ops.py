@@ -275,6 +275,21 @@ def vote_unique(hist: torch.Tensor, mode: int) -> torch.Tensor:
     return torch.sort(vals[: int(cnt.item())]).values
 
 
+def vote_unique_static(hist: torch.Tensor, mode: int, values: torch.Tensor, count: torch.Tensor) -> None:
+    """bff_vote_unique_static: vote_unique with the scratch table inside the library and no allocation anywhere -- the
+    caller brings `values` (float32, >= hist.numel()) and `count` (int32, 1) and reads them itself (nothing is allocated,
+    copied or synchronised here). At most _cabi.VOTE_UNIQUE_STATIC_MAX_BINS histogram bins; calls must not overlap on the GPU."""
+    if not (hist.is_cuda and hist.dtype == torch.int32 and hist.is_contiguous() and hist.dim() == 2):
+        raise TypeError("hist must be a contiguous 2-D int32 CUDA tensor")
+    if not (values.is_cuda and values.dtype == torch.float32 and values.is_contiguous() and values.numel() >= hist.numel()):
+        raise TypeError("values must be a contiguous float32 CUDA tensor with one slot per histogram bin")
+    if not (count.is_cuda and count.dtype == torch.int32 and count.numel() >= 1):
+        raise TypeError("count must be an int32 CUDA tensor")
+    check(lib().bff_vote_unique_static(ptr(hist), hist.shape[0], hist.shape[1], int(mode), ptr(values), ptr(count), current_stream()),
+          "bff_vote_unique_static")
+    _count(2)
+
+
 def point_keep(mc: torch.Tensor, vc: Optional[torch.Tensor], mode: int, thr: float) -> torch.Tensor:
     mc = _cuda(mc, torch.int32, "mc").reshape(-1)
     if vc is not None:

@@ -1,6 +1,8 @@
 // Vote statistics for the point filter of tools/projection_2d_to_3d.py:512-583:
 // max of the count vectors, the 2-D (masked_count, viewed_count) histogram from which the host
 // derives detected_ratio.unique() / masked_counts.unique(), and the per-point keep predicate.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace bff {
@@ -190,6 +192,64 @@ extern "C" int bff_vote_unique(const uint32_t *hist, int32_t mc_bins, int32_t vc
                                                                                      32 - (int)(63 - __builtin_clzll((unsigned long long)table_size)));
     vote_unique_compact_kernel<<<(unsigned)ceil_div64(table_size, 256), 256, 0, stream>>>(table, (uint32_t)table_size, values, count);
     BFF_LAUNCH_CHECK("vote_unique kernels");
+    return BFF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// bff_vote_unique_static: bff_vote_unique for callers that cannot allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc). No counterpart in the reference. The hash-set
+// table -- the scratch the caller of bff_vote_unique has to provide -- lives in a file-scope device array of
+// BFF_VOTE_UNIQUE_STATIC_TABLE_WORDS words (1 MiB per GPU that loads the library, held until exit). In host code the
+// array's NAME is only a host-side stand-in; its device address is resolved once per device, with that device current,
+// by cudaGetSymbolAddress and handed to the same two kernels bff_vote_unique launches. Nothing here calls cudaMalloc,
+// cudaFree or an allocating library routine. All calls on a device share the one table (it keeps the previous call's
+// contents, so each call re-initialises the part it uses on its stream): calls that overlap on the GPU race.
+namespace bff {
+constexpr long long kStaticTableWords = BFF_VOTE_UNIQUE_STATIC_TABLE_WORDS;
+static_assert((kStaticTableWords & (kStaticTableWords - 1)) == 0 && kStaticTableWords == 2LL * BFF_VOTE_UNIQUE_STATIC_MAX_BINS,
+              "the static table is a power of two, twice the largest accepted bin count");
+static __device__ __align__(256) uint32_t g_unique_table_static[kStaticTableWords];
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static uint32_t *g_static_table_addr[kStaticMaxDevices] = {};
+
+// device address of g_unique_table_static on the CURRENT device (resolved on that device's first call, then cached)
+static int static_table_address(uint32_t **out) {
+    int dev = -1;
+    BFF_CUDA(cudaGetDevice(&dev));
+    BFF_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "bff_vote_unique_static: device index %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (g_static_table_addr[dev] == nullptr) {
+        void *addr = nullptr;
+        BFF_CUDA(cudaGetSymbolAddress(&addr, g_unique_table_static));
+        BFF_REQUIRE(addr != nullptr, "bff_vote_unique_static: cudaGetSymbolAddress returned a null address");
+        g_static_table_addr[dev] = static_cast<uint32_t *>(addr);
+    }
+    *out = g_static_table_addr[dev];
+    return BFF_OK;
+}
+}  // namespace bff
+
+extern "C" int bff_vote_unique_static(const uint32_t *hist, int32_t mc_bins, int32_t vc_bins, int32_t mode, float *values, int32_t *count,
+                                      void *stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    BFF_REQUIRE(hist && values && count && mc_bins >= 1 && vc_bins >= 1 && (mode == 0 || mode == 1), "bff_vote_unique_static: bad arguments");
+    const long long bins = (long long)mc_bins * vc_bins;
+    BFF_REQUIRE(bins <= BFF_VOTE_UNIQUE_STATIC_MAX_BINS,
+                "bff_vote_unique_static: %d x %d = %lld histogram bins exceed the static scratch table's limit of %d bins "
+                "(use bff_vote_unique with a caller-provided table)", mc_bins, vc_bins, bins, BFF_VOTE_UNIQUE_STATIC_MAX_BINS);
+    const int64_t table_size = bff_vote_unique_table_size(mc_bins, vc_bins);       // power of two >= 2 * bins, <= the static table
+    BFF_REQUIRE(table_size <= bff::kStaticTableWords, "bff_vote_unique_static: table size %lld beyond the static table", (long long)table_size);
+    uint32_t *table = nullptr;
+    const int rc = bff::static_table_address(&table);
+    if (rc != BFF_OK) return rc;
+    // the table keeps the last call's contents: the slots this call probes start empty (0xffffffff), the count at zero
+    BFF_CUDA(cudaMemsetAsync(table, 0xff, (size_t)table_size * 4, stream));
+    BFF_CUDA(cudaMemsetAsync(count, 0, 4, stream));
+    bff::vote_unique_insert_kernel<<<(unsigned)ceil_div64(bins, 256), 256, 0, stream>>>(hist, mc_bins, vc_bins, mode, table, (uint32_t)(table_size - 1),
+                                                                                          32 - (int)(63 - __builtin_clzll((unsigned long long)table_size)));
+    bff::vote_unique_compact_kernel<<<(unsigned)ceil_div64(table_size, 256), 256, 0, stream>>>(table, (uint32_t)table_size, values, count);
+    BFF_LAUNCH_CHECK("vote_unique kernels (static table)");
     return BFF_OK;
 }
 

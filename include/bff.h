@@ -213,6 +213,20 @@ BFF_API int64_t bff_vote_unique_table_size(int32_t mc_bins, int32_t vc_bins);
 BFF_API int bff_vote_unique(const uint32_t *hist, int32_t mc_bins, int32_t vc_bins, int32_t mode, uint32_t *table, int64_t table_size,
                             float *values, int32_t *count, void *stream);
 
+/* bff_vote_unique without caller-provided scratch and without ANY allocation -- for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). No counterpart in the reference.
+ * Same inputs, outputs and kernels as bff_vote_unique; the hash-set table is a
+ * file-scope device array inside the library: BFF_VOTE_UNIQUE_STATIC_TABLE_WORDS uint32 = 1 MiB on every GPU that loads
+ * the library, held until the process exits. Limit: mc_bins * vc_bins <= BFF_VOTE_UNIQUE_STATIC_MAX_BINS, beyond it the call
+ * returns BFF_EINVAL (bff_last_error names the limit). The call uses the CURRENT device; the first call per device
+ * resolves the array's device address (cudaGetSymbolAddress) -- make that call outside a capture. Every call on a device
+ * shares the one table, which keeps the previous call's contents: each call re-initialises the slots it uses on its own
+ * stream, and two calls that overlap on the GPU (different streams, no dependency) RACE -- serialise them. */
+#define BFF_VOTE_UNIQUE_STATIC_MAX_BINS 131072
+#define BFF_VOTE_UNIQUE_STATIC_TABLE_WORDS 262144
+BFF_API int bff_vote_unique_static(const uint32_t *hist, int32_t mc_bins, int32_t vc_bins, int32_t mode, float *values, int32_t *count,
+                                   void *stream);
+
 /* Per-point keep predicate -> packed bits keep (Wd):
  *  mode 0 (detected ratio, :571-583): keep = mc > 0 && !(f32(mc) / (f32(vc) + 1) < thr)
  *  mode 1 (occurrence, :512-522,583):  keep = mc > 0 && !(f32(mc) < thr)
