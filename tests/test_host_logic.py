@@ -197,3 +197,58 @@ def test_pipeline_row_limits_match_the_header():
     src = "".join(open(os.path.join(root, "beyond-fixed-forms_b200", "csrc", f)).read() for f in ("devpipe.cu", "pipeline.cu"))
     for limit in (stage2.MAX_FUSED_ROWS, stage2.MAX_DEVICE_ROWS, refine.MAX_FUSED_ROWS, refine.MAX_DEVICE_ROWS):
         assert f"<= {limit}" in src
+
+
+def test_fast_pose_reader_returns_np_loadtxt_bits(tmp_path):
+    """scene_io.read_matrix4 == np.loadtxt on pose files: the golden tree's, random matrices written like ScanNet writes
+    them (%.18e and short decimals), invalid poses (-inf), nan, and layouts that must fall back to np.loadtxt."""
+    import glob
+    import os
+    import warnings
+    from bff_b200 import scene_io
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    files = sorted(glob.glob(os.path.join(root, "tests", "golden", "tree", "data", "Scannet200", "Scannet200_2D", "*", "pose", "*.txt")))
+    assert len(files) >= 10
+    rng = np.random.default_rng(3)
+    for k in range(40):
+        m = rng.normal(size=(4, 4)) * float(rng.choice([1e-6, 1.0, 1e5]))
+        path = tmp_path / f"m{k}.txt"
+        np.savetxt(path, m, fmt=["%.18e", "%.6f", "%r", "%.3g"][k % 4] if k % 4 != 2 else "%.17g")
+        files.append(str(path))
+    hostile = {"inf.txt": "-inf -inf -inf -inf\n" * 4, "nan.txt": "nan 1 2 3\n0 1 0 0\n0 0 1 0\n0 0 0 1\n",
+               "crlf.txt": "1 0 0 0.5\r\n0 1 0 0\r\n0 0 1 0\r\n0 0 0 1\r\n", "blank.txt": "\n1 0 0 0\n\n0 1 0 0\n0 0 1 0\n0 0 0 1\n\n",
+               "comment.txt": "# pose\n1 0 0 0\n0 1 0 0\n0 0 1 0\n0 0 0 1\n", "one_line.txt": "1 0 0 0 0 1 0 0 0 0 1 0 0 0 0 1\n",
+               "three.txt": "1 0 0\n0 1 0\n0 0 1\n"}
+    for name, text in hostile.items():
+        (tmp_path / name).write_text(text)
+        files.append(str(tmp_path / name))
+    for f in files:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            want = np.loadtxt(f)
+            got = scene_io.read_matrix4(f)
+        assert got.shape == want.shape and got.dtype == want.dtype, f
+        assert np.array_equal(got.view(np.int64), want.view(np.int64)), f
+
+
+@pytest.mark.parametrize("threads", [1, 8])
+def test_load_frames_equals_the_reference_calls_per_frame(monkeypatch, threads):
+    """scene_io.load_frames (thread pool for the PNGs, poses parsed beside it) hands over exactly what the reference computes
+    per frame: np.linalg.inv(np.loadtxt(pose)) (:422-425) and cv2.imread(depth, -1) (:431)."""
+    import glob
+    import os
+    import cv2
+    from bff_b200 import scene_io
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    d2 = os.path.join(root, "tests", "golden", "tree", "data", "Scannet200", "Scannet200_2D")
+    scene = sorted(os.listdir(d2))[0]
+    ids = sorted((os.path.basename(f)[:-4] for f in glob.glob(os.path.join(d2, scene, "pose", "*.txt"))), key=int)
+    assert len(ids) >= 5
+    first = cv2.imread(os.path.join(d2, scene, "depth", f"{ids[0]}.png"), cv2.IMREAD_UNCHANGED)
+    monkeypatch.setattr(scene_io, "INGEST_THREADS", threads)
+    fs = scene_io.load_frames(d2, scene, ids, [True] * len(ids), first.shape[1], first.shape[0])
+    assert fs.pose_inv.shape == (len(ids), 4, 4) and fs.depth.shape == (len(ids),) + first.shape and fs.depth.dtype == np.uint16
+    for i, fid in enumerate(ids):
+        want = np.linalg.inv(np.loadtxt(os.path.join(d2, scene, "pose", f"{fid}.txt")))
+        assert np.array_equal(fs.pose_inv[i].view(np.int64), want.view(np.int64))
+        assert np.array_equal(fs.depth[i], cv2.imread(os.path.join(d2, scene, "depth", f"{fid}.png"), cv2.IMREAD_UNCHANGED))
