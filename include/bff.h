@@ -102,7 +102,9 @@ typedef struct bff_lift_desc {
     double depth_min, depth_max;
     /* 2D masks: :395-421, packed bits, all frames concatenated in frame order */
     const uint32_t *masks2d;    /* (n_masks, ceil(H*W/32)) */
-    const int32_t *mask_offset; /* (n_frames + 1) exclusive prefix of masks per frame; NULL = no masks */
+    const int32_t *mask_offset; /* (n_frames + 1) exclusive prefix of masks per frame; NULL = no masks. A DEVICE array, so its
+                                 * contents are the caller's contract and are not checked: non-decreasing, mask_offset[0] = 0,
+                                 * mask_offset[n_frames] = n_masks (bff_b200/lift.py:mask_layout builds it from the files) */
     const int32_t *mask_query;  /* (n_masks) query id in [0, n_queries); NULL = all 0 */
     int32_t n_masks;            /* sum of M_f */
     int32_t n_queries;          /* Q >= 1 */
