@@ -2,8 +2,9 @@
 the kernels -- frames interleaved over the ranks and lifted over ALL points of the NaN-padded cloud (dist.ShardPlan),
 row slices handed to the owners of the points, votes all-reduced, then aggregation / point filter / overlap resolution /
 row filter on every rank's POINT SLICE with only the additive integers (intersections, popcounts) all-reduced and every
-decision taken redundantly. The final masks, re-assembled from the ranks' column slices, must equal the single-process
-result of the port on the same scene. (The CUDA form of the same algorithm is checked on hardware by
+decision taken redundantly; then both refinement passes on the same slices (the port's own code with its IoU function fed
+by all-reduced integers). The saved stage-2 masks and the final masks, re-assembled from the ranks' column slices, must
+equal the single-process results of the port on the same scene. (The CUDA form of the same algorithm is checked on hardware by
 tests/test_sharded_gpu.py; this test pins the host-side arithmetic -- padding, slice bounds, frame interleave, scene row
 order -- and the claim that point-sharding changes no decision.)"""
 import os
@@ -118,22 +119,61 @@ def _sharded_stage2(rank, world, occurrence):
     return agg[sel], conf_a[sel], [l for l, s in zip(labels_a, sel.tolist()) if s], plan, dict(n_rows=len(labels), n_groups=len(groups))
 
 
+def _sharded_refine(inp, cfg, plan, s2_local):
+    """Both refinement passes on this rank's point slice: the port's own code, with the one function that needs ALL
+    points -- the IoU between two mask sets -- fed by all-reduced intersections and popcounts."""
+    import bench
+    import reference_port as RP
+    from bff_b200.refine import STAGE1_CLASS_NAMES
+    p0, p1 = plan.point0, plan.point0 + plan.slice_points
+    s1 = np.zeros((len(inp["stage1"]["ins"]), plan.n_padded), np.uint8)
+    s1[:, :plan.n_points] = np.stack([RP.rle_to_mask(r) for r in inp["stage1"]["ins"]])
+    s1 = torch.from_numpy(np.ascontiguousarray(s1[:, p0:p1]))
+    labels = [STAGE1_CLASS_NAMES[int(i)] for i in inp["stage1"]["final_class"]]
+
+    def iou_all_points(m1, m2):
+        a, b = m1.float(), m2.float()
+        inter = _allreduce(a @ b.T).float()
+        sa, sb = _allreduce(a.sum(dim=-1, keepdim=True)).float(), _allreduce(b.sum(dim=-1, keepdim=True)).float()
+        return (inter / (sa + sb.T - inter)).T
+
+    whole, RP.iou_between = RP.iou_between, iou_all_points
+    try:
+        query = inp["queries"][0]
+        pass1 = RP.refine_pass1(s1, labels, s2_local, query, cfg["stage1_iou_thres"], bench.fake_similarity)
+        thr = RP.sim_threshold([pass1["sims"]], cfg["refinment_sim_percentile"]) if len(pass1["sims"]) else 0.0
+        return RP.refine_pass2(pass1, query, cfg["refiment_iou_thres"], thr)
+    finally:
+        RP.iou_between = whole
+
+
+def _gather_columns(local, plan):
+    import torch.distributed as dist
+    box = [None] * plan.world
+    dist.all_gather_object(box, None if local is None else np.asarray(local))
+    return None if local is None else torch.from_numpy(np.concatenate(box, axis=1)[:, :plan.n_points])
+
+
 def _worker(rank, world, port, out_dir, occurrence):
     _paths()
     import torch.distributed as dist
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     ins, conf, classes, plan, info = _sharded_stage2(rank, world, occurrence)
-    box = [None] * world
-    dist.all_gather_object(box, None if ins is None else ins.numpy())
+    full = _gather_columns(None if ins is None else ins.numpy(), plan)
+    final = None
+    if ins is not None:
+        inp, cfg, *_ = _scene(occurrence)
+        out = _sharded_refine(inp, cfg, plan, {"ins": ins, "conf": conf, "final_class": classes})
+        final = {"ins": _gather_columns(out["ins"].numpy(), plan) if len(out["ins"]) else [], "conf": out["conf"], "final_class": out["final_class"]}
     if rank == 0:
-        full = None if ins is None else torch.from_numpy(np.concatenate(box, axis=1)[:, :plan.n_points])
-        torch.save({"ins": full, "conf": conf, "final_class": classes, "info": info}, os.path.join(out_dir, "sharded.pth"))
+        torch.save({"ins": full, "conf": conf, "final_class": classes, "info": info, "final": final}, os.path.join(out_dir, "sharded.pth"))
     dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("world,occurrence", [(2, False), (3, False), (2, True)])
-def test_point_sharded_stage2_equals_single_process(tmp_path, world, occurrence):
+def test_point_sharded_stage2_and_refinement_equal_single_process(tmp_path, world, occurrence):
     _paths()
+    import bench
     import reference_port as RP
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), occurrence), nprocs=world, join=True)
     got = torch.load(os.path.join(str(tmp_path), "sharded.pth"), weights_only=False)
@@ -144,6 +184,13 @@ def test_point_sharded_stage2_equals_single_process(tmp_path, world, occurrence)
     assert got["final_class"] == want["final_class"]
     assert torch.equal(got["ins"], want["ins"])
     assert torch.equal(got["conf"], want["conf"])
+    # ... and after both refinement passes (stage-1 matching, merges, similarity threshold, selection)
+    inp["cfg"] = cfg
+    want_final = bench.cpu_step(inp, [mask_frames], view_frames)[0]
+    final = got["final"]
+    assert len(want_final["final_class"]) >= 1 and final["final_class"] == want_final["final_class"]
+    assert torch.equal(final["ins"], want_final["ins"])
+    assert torch.equal(torch.as_tensor(final["conf"]), torch.as_tensor(want_final["conf"]))
 
 
 def test_shard_plan_slices_tile_the_padded_cloud():
